@@ -1,0 +1,136 @@
+/*
+ * tmdiff_b200 -- C ABI of the B200-native TMDiff sampling hot path.
+ *
+ * The reference (codgodtao/TMDiff) is pure Python/PyTorch and has no FFI of its own; the
+ * entry points below are what a binding for its sampling path would bind.  Each one names
+ * the reference interface it replaces (paths relative to the reference repository).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types.
+ *   - every function returns 0 on success, non-zero on failure; tmd_last_error() returns a
+ *     message for the last failure on the calling thread.
+ *   - "dev" pointers are CUDA device pointers owned by the caller; "host" pointers are
+ *     ordinary host memory.  Image tensors use the reference's layout: contiguous fp32
+ *     [B, bands, H, W] (PAN: [B, 1, H, W]).
+ *   - all device work is enqueued on the cudaStream_t passed as `stream` (a void* here so
+ *     the header has no CUDA dependency); no call synchronises the host unless stated.
+ *   - a handle is bound to the CUDA device current at tmd_create and is not thread-safe.
+ */
+#ifndef TMDIFF_B200_H
+#define TMDIFF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tmd_engine* tmd_handle;
+
+enum { TMD_F32 = 0, TMD_BF16 = 1 };                       /* arithmetic mode of the conv path   */
+enum { TMD_QB = 0, TMD_WV3 = 1, TMD_GF2 = 2, TMD_WV2 = 3, TMD_WV4 = 4, TMD_NUM_SENSORS = 5 };
+
+/* WavBEST(channels, embed_dim, inter_dim) -- GeneralModel/Hyper_unet_general.py:523-564 */
+typedef struct {
+    int32_t channels[4];   /* e.g. {32,64,128,256} (config/general_finetune.json:63-66)        */
+    int32_t embed_dim;     /* 128                                                              */
+    int32_t inter_dim;     /* 32 (sinusoidal time-embedding width)                             */
+    int32_t max_batch;     /* workspace is sized for this many patches per call                */
+    int32_t max_bands;     /* 4 (QB/GF2) or 8 (WV3)                                            */
+    int32_t height, width; /* patch size, multiples of 8 (three Haar levels)                   */
+    int32_t dtype;         /* TMD_F32: fp32 SIMT convs (parity mode); TMD_BF16: tcgen05 convs  */
+} tmd_config;
+
+/* One network evaluation of the sampler = DPM_Solver.model_fn(x, t) for model_type "x_start",
+ * algorithm "dpmsolver++", dynamic thresholding (core/dpm_solver_pytorch.py:296-306, 430-465).
+ * The scalars are the fp32 values the reference computes on the host side of each call. */
+typedef struct {
+    int32_t src;           /* slot holding x                                                   */
+    int32_t dst;           /* slot receiving the thresholded x0 prediction                     */
+    float   t_input;       /* (t - 1/N)*1000                            (:291-292)             */
+    float   alpha_t;       /* marginal_alpha(t)                          (:304)                */
+    float   sigma_t;       /* marginal_std(t)                                                  */
+} tmd_eval;
+
+/* dst = (c1*x - c2*m) [+ c3*(m1 - m)] -- the dpmsolver++ update family
+ * (core/dpm_solver_pytorch.py:589-592, :648-658, :744-760), evaluated in that order in fp32. */
+typedef struct {
+    int32_t dst, x, m, m1; /* slots; m1 < 0 => no third term                                   */
+    float   c1, c2, c3;
+} tmd_update;
+
+typedef struct {
+    int32_t kind;          /* 0 = eval, 1 = update                                             */
+    tmd_eval   eval;
+    tmd_update update;
+} tmd_step;
+
+enum { TMD_NUM_SLOTS = 8 };  /* slot 0 holds x_T on entry; the result is read from `result_slot` */
+
+typedef struct {
+    const tmd_step* steps; /* host array                                                       */
+    int32_t n_steps;
+    int32_t result_slot;
+    float   q_weight;      /* torch.quantile(|x0|, 0.995): rank = q*(n-1); q_lo = floor(rank), */
+    int32_t q_lo;          /*   q_weight = rank - q_lo (fp32, as ATen computes them)  (:436)   */
+    float   max_val;       /* thresholding_max_val (1.0)                              (:437)   */
+} tmd_plan;
+
+const char* tmd_last_error(void);
+int tmd_version(void);
+
+/* networks.define_General -> WavBEST(...)                       GeneralModel/networks.py:80-85 */
+int tmd_create(const tmd_config* cfg, tmd_handle* out);
+int tmd_destroy(tmd_handle h);
+
+/* nn.Module.load_state_dict for denoise_fn.*  (GeneralModel/model.py:122-134).  `key` is the
+ * reference state-dict name (e.g. "down1.conv20.conv21.weight"); data is host fp32, contiguous,
+ * in the reference shape.  Unknown keys are an error; call tmd_finalize_weights afterwards. */
+int tmd_load_weight(tmd_handle h, const char* key, const float* host, const int64_t* shape, int32_t ndim);
+/* 16 (= inter_dim/2) sinusoid frequencies of gamma_embedding (Hyper_unet_general.py:89-92), host fp32 */
+int tmd_set_time_frequencies(tmd_handle h, const float* host, int32_t n);
+/* WavBEST.{qb,wv3,gf2,wv2,wv4}_embeding: cached pooled CLIP vector [768], host fp32 (:566-598) */
+int tmd_set_text_embedding(tmd_handle h, int32_t sensor, const float* host768);
+/* repack + upload; synchronises the device */
+int tmd_finalize_weights(tmd_handle h);
+
+/* The step-invariant half of WavBEST.forward (condition branch conv1/down{1,2,3}_1, :611-618, and
+ * the convH_0 high-frequency convs of the up path, :381): run once per batch of patches.
+ * pan [B,1,H,W], ms [B,bands,H,W] device fp32; sensor_ids host int32[B] (all patches share `bands`). */
+int tmd_precompute_condition(tmd_handle h, const float* pan_dev, const float* ms_dev, const int32_t* sensor_ids,
+                             int32_t B, int32_t bands, int32_t H, int32_t W, void* stream);
+
+/* WavBEST.forward(x_t, t_input, PAN, MS, prompt) (:600-636) for the batch bound by the last
+ * tmd_precompute_condition.  x_t/out device fp32 [B,bands,H,W]; t_input device fp32[B]
+ * (the reference passes a device tensor, core/dpm_solver_pytorch.py:299; no host sync here). */
+int tmd_denoise(tmd_handle h, const float* x_t_dev, const float* t_input_dev, float* out_dev, void* stream);
+
+/* DPM_Solver.sample(x_T, ...) (core/dpm_solver_pytorch.py:1081-1289) as a straight-line program of
+ * evaluations and updates prepared by the host (tmdiff_b200/dpm_solver.py).  x_T / out: device fp32
+ * [B,bands,H,W].  trace_dev (optional, may be NULL): receives the raw network output of every
+ * evaluation, [n_eval, B, bands, H, W]. */
+int tmd_sample(tmd_handle h, const float* x_T_dev, const tmd_plan* plan, float* out_dev, float* trace_dev,
+               void* stream);
+
+/* ---- stand-alone operators (parity tests, per-operator sweep) -------------------------------- */
+/* DWT_2D("haar").forward (DWT_IDWT/DWT_IDWT_layer.py:321-334): x [B,C,H,W] -> 4 x [B,C,H/2,W/2].
+ * lh/hl/hh may be NULL (LL-only variant). */
+int tmd_dwt2d(const float* x, float* ll, float* lh, float* hl, float* hh, int64_t BC, int32_t H, int32_t W, void* stream);
+/* IDWT_2D("haar").forward (:409-430): 4 x [B,C,h,w] -> [B,C,2h,2w] */
+int tmd_idwt2d(const float* ll, const float* lh, const float* hl, const float* hh, float* out, int64_t BC,
+               int32_t h, int32_t w, void* stream);
+/* modulated_conv3d(x, w, s, padding=k/2) (Hyper_unet_general.py:51-77) with optional bias:
+ * x [B,Ci,N,H,W], w [Co,Ci,k,k,k] (k = 1 or 3), s [B,Ci] or NULL, bias [Co] or NULL -> y [B,Co,N,H,W];
+ * all device fp32 in the reference (channels-first) layout.  dtype selects the SIMT-fp32 or tcgen05-bf16 kernel. */
+int tmd_conv3d_mod(const float* x, const float* w, const float* s, const float* bias, float* y, int32_t B, int32_t Ci,
+                   int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t dtype, void* stream);
+/* DPM_Solver.dynamic_thresholding_fn (core/dpm_solver_pytorch.py:430-439) in place on x0 [B, n] */
+int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream);
+
+/* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
+int64_t tmd_launch_count(tmd_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMDIFF_B200_H */

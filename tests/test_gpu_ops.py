@@ -1,0 +1,120 @@
+"""CUDA operators (through the C ABI) against the oracle and the reference's golden vectors."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import dpm_ref, wavbest_ref
+from util import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(lib_built):
+    from tmdiff_b200 import ops
+    return ops
+
+
+def test_haar_golden(golden, ops):
+    x = torch.from_numpy(golden["haar_x"]).cuda()
+    got = ops.DWT_2D("haar")(x)
+    for g, key in zip(got, ("haar_LL", "haar_LH", "haar_HL", "haar_HH")):
+        assert torch.allclose(g.cpu(), torch.from_numpy(golden[key]), atol=1e-6), key
+    rec = ops.IDWT_2D("haar")(*got)
+    assert torch.allclose(rec.cpu(), torch.from_numpy(golden["haar_rec"]), atol=1e-6)
+    assert torch.equal(ops.DWT_2D("haar")(x, ll_only=True), got[0])
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 2, 2), (3, 3, 24, 24), (2, 5, 6, 10), (1, 2048, 16, 16), (64, 512, 64, 64), (0, 4, 8, 8)])
+def test_haar_shapes_and_round_trip(ops, shape):
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(shape, generator=g).cuda()
+    bands = ops.DWT_2D("haar")(x)
+    if x.numel():
+        want = wavbest_ref.dwt2d_closed(x[:2].cpu())
+        for b, w in zip(bands, want):
+            assert torch.allclose(b[:2].cpu(), w, atol=1e-6)
+    rec = ops.IDWT_2D("haar")(*bands)
+    assert rec.shape == x.shape
+    assert torch.allclose(rec, x, atol=1e-6)          # the reference's own round-trip check (DWT_IDWT_layer.py:650-667)
+    # linearity / energy preservation of the orthonormal transform at full size
+    if x.numel():
+        e_in = float((x.double() ** 2).sum())
+        e_out = sum(float((b.double() ** 2).sum()) for b in bands)
+        assert abs(e_in - e_out) <= 1e-5 * e_in
+
+
+def test_haar_rejects_odd_and_non_4d(ops):
+    with pytest.raises(RuntimeError):
+        ops.DWT_2D("haar")(torch.zeros(1, 1, 5, 8).cuda())
+    with pytest.raises(AssertionError):
+        ops.DWT_2D("haar")(torch.zeros(1, 8, 8).cuda())
+    with pytest.raises(ValueError):
+        ops.DWT_2D("db2")
+
+
+CONV_CASES = [
+    # B, Ci, Co, N, H, W, k
+    (2, 32, 32, 4, 16, 16, 3),
+    (1, 32, 64, 8, 16, 16, 3),
+    (2, 64, 64, 4, 8, 8, 3),
+    (1, 128, 256, 4, 8, 8, 3),
+    (1, 768, 128, 4, 8, 8, 3),
+    (2, 96, 32, 4, 16, 16, 1),
+    (1, 256, 256, 8, 8, 8, 1),
+    (1, 8, 16, 3, 4, 4, 3),
+    (1, 16, 8, 1, 8, 8, 3),
+    (3, 32, 32, 5, 24, 40, 3),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+@pytest.mark.parametrize("dtype,tol", [("fp32", 5e-6), ("bf16", 1e-2)]  # fp32: summation-order noise over K <= 27*768 terms)
+def test_modulated_conv3d(ops, case, dtype, tol):
+    B, Ci, Co, N, H, W, k = case
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(B, Ci, N, H, W, generator=g)
+    w = torch.randn(Co, Ci, k, k, k, generator=g) / (Ci * k ** 3) ** 0.5
+    s = torch.randn(B, Ci, 1, 1, generator=g)
+    bias = torch.randn(Co, generator=g)
+    want = wavbest_ref.modulated_conv3d(x, w, s, k // 2, faithful=True)             # the reference formulation
+    got = ops.modulated_conv3d(x.cuda(), w.cuda(), s.cuda(), padding=k // 2, dtype=dtype)
+    assert rel_l2(got, want) < tol
+    want_b = F.conv3d(x, w, bias, padding=k // 2)
+    got_b = ops.modulated_conv3d(x.cuda(), w.cuda(), None, padding=k // 2, bias=bias.cuda(), dtype=dtype)
+    assert rel_l2(got_b, want_b) < tol
+
+
+def test_modulated_conv3d_linearity_full_size(ops):
+    """Size-independent property at a BASELINE-sized layer (B=16 of 64x64 4-band, 64->64): conv(a*x+y) = a*conv(x)+conv(y)."""
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(16, 64, 4, 64, 64, generator=g).cuda()
+    y = torch.randn(16, 64, 4, 64, 64, generator=g).cuda()
+    w = (torch.randn(64, 64, 3, 3, 3, generator=g) / 41.6).cuda()
+    f = lambda t: ops.modulated_conv3d(t, w, None, padding=1, dtype="fp32")
+    assert rel_l2(f(0.5 * x + y), 0.5 * f(x) + f(y)) < 1e-5
+
+
+@pytest.mark.parametrize("scale", [0.3, 1.0, 3.0, 50.0])
+@pytest.mark.parametrize("n", [4 * 32 * 32, 4 * 64 * 64, 8 * 64 * 64, 1000])
+def test_dynamic_threshold(ops, scale, n):
+    g = torch.Generator().manual_seed(int(scale * 10) + n)
+    x = torch.randn(3, n, generator=g) * scale
+    x[1] *= 0.01                       # a sample whose quantile stays below max_val
+    want = dpm_ref.dynamic_threshold(x)
+    got = ops.dynamic_thresholding(x.cuda())
+    assert torch.allclose(got.cpu(), want, rtol=0, atol=1e-6), float((got.cpu() - want).abs().max())
+    assert rel_l2(got, want) < 1e-6
+
+
+def test_dynamic_threshold_boundary_counts(ops):
+    """Exactly need_hi-1, need_hi, need_lo values above 1: exercises the three selection branches."""
+    n = 4096
+    lo, w = ops.quantile_position(n, 0.995)
+    for k in (n - lo - 2, n - lo - 1, n - lo, n - lo + 5, n):
+        x = torch.linspace(0.01, 0.99, n).repeat(2, 1)
+        x[:, :k] = torch.linspace(1.5, 4.0, k)
+        x[1] = -x[1]
+        want = dpm_ref.dynamic_threshold(x)
+        got = ops.dynamic_thresholding(x.cuda()).cpu()
+        assert torch.allclose(got, want, rtol=0, atol=1e-6), k

@@ -1,0 +1,879 @@
+// Engine behind the C ABI (include/tmdiff_b200.h): weights, workspace, the WavBEST data-flow as
+// a list of fused kernel launches, the step-invariant condition cache and the sampler loop.
+//
+// Data-flow restated from GeneralModel/Hyper_unet_general.py:600-636 (WavBEST.forward) and the
+// block bodies :158-273, :334-414; see DESIGN.md for the fusion map.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/tmdiff_b200.h"
+#include "kernels.h"
+
+using namespace tmd;
+
+static thread_local char g_err[1024] = "";
+static int fail(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+#define CK(expr)                                                                                     \
+    do {                                                                                             \
+        cudaError_t _e = (expr);                                                                     \
+        if (_e != cudaSuccess) return fail("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+    } while (0)
+
+namespace {
+
+struct View {  // channel slice of a channels-last activation tensor
+    void* p = nullptr;
+    int C = 0, ld = 0;
+};
+struct ActSpec {
+    View dst;
+    const float* tb = nullptr;
+    const float* sc = nullptr;
+};
+struct OutSpec {
+    View raw;
+    ActSpec act[2];
+};
+struct ConvW {
+    float* w_f32 = nullptr;
+    __nv_bfloat16* w_bf16 = nullptr;
+    float* bias = nullptr;
+    int Co = 0, Ci = 0, taps = 0;
+};
+struct HostTensor {
+    std::vector<float> data;
+    std::vector<int64_t> shape;
+};
+
+using Launch = std::function<cudaError_t(cudaStream_t)>;
+
+}  // namespace
+
+struct tmd_engine {
+    tmd_config cfg{};
+    int dtype = 0;
+    size_t esize = 4;
+    int device = 0;
+    std::map<std::string, HostTensor> host;
+    std::map<std::string, std::vector<int64_t>> inv_shapes;
+    std::map<std::string, ConvW> convs;
+    std::map<std::string, int> time_off, text_off;
+    int time_rows = 0, text_rows = 0;
+    bool finalized = false, text_dirty = true;
+    std::vector<void*> allocs;
+
+    // conditioning
+    float *d_freqs = nullptr, *d_e_w1 = nullptr, *d_e_b1 = nullptr, *d_e_w2 = nullptr, *d_e_b2 = nullptr;
+    float *d_p_w[3] = {}, *d_p_b[3] = {};
+    float *d_Wt = nullptr, *d_bt = nullptr, *d_Ws = nullptr, *d_bs = nullptr;
+    float *d_text = nullptr, *d_p_tmp0 = nullptr, *d_p_tmp1 = nullptr, *d_prompt = nullptr, *d_sc_sensor = nullptr;
+    float *d_tb = nullptr, *d_sc = nullptr, *d_tin = nullptr, *d_embed = nullptr;
+    int* d_sensor = nullptr;
+    float *d_stem_w[2] = {}, *d_stem_b[2] = {}, *d_proj_w = nullptr;
+    bool have_text[TMD_NUM_SENSORS] = {};
+    std::vector<float> freqs_host;
+
+    // bound geometry + launch lists
+    int B = 0, N = 0, H = 0, W = 0;
+    char* arena = nullptr;
+    size_t arena_size = 0, arena_used = 0;
+    std::map<std::string, void*> bufs;
+    std::vector<Launch> pre_ops, step_ops;
+    std::vector<UmmaPlan*> plans;
+    const float* cur_x = nullptr;
+    const float* cur_pan = nullptr;
+    const float* cur_ms = nullptr;
+    float* cur_out = nullptr;
+    const float* cur_t_dev = nullptr;
+    float cur_t_scalar = 0.f;
+    float* slots[TMD_NUM_SLOTS] = {};
+    float* d_out = nullptr;
+    int64_t launches = 0;
+
+    template <typename T> int dmalloc(T** p, size_t n) {
+        CK(cudaMalloc((void**)p, n * sizeof(T)));
+        allocs.push_back(*p);
+        return 0;
+    }
+    template <typename T> int upload(T** p, const std::vector<T>& v) {
+        if (dmalloc(p, v.size())) return 1;
+        CK(cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return 0;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// parameter inventory (mirrors the module constructors; names are the reference state-dict keys)
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct Inventory {
+    std::vector<std::pair<std::string, std::vector<int64_t>>> items;
+    void conv(const std::string& n, int co, int ci, int k) {
+        items.push_back({n + ".weight", {co, ci, k, k, k}});
+        items.push_back({n + ".bias", {co}});
+    }
+    void lin(const std::string& n, int co, int ci) {
+        items.push_back({n + ".weight", {co, ci}});
+        items.push_back({n + ".bias", {co}});
+    }
+    void resblock(const std::string& p, int ci, int co, int E) {  // ResBlockModulateBEST :220-235
+        conv(p + ".conv20", co, ci, 3);
+        conv(p + ".conv21", co, co, 3);
+        lin(p + ".dense1.dense", ci, E);
+        lin(p + ".dense2.dense", co, E);
+        if (ci != co) conv(p + ".res_conv", co, ci, 1);
+    }
+    void wavelet(const std::string& p, int c, int E, int hi) {  // WaveletUPorDown :334-367
+        conv(p + ".Conv_0", c, c, 3);
+        lin(p + ".Dense_0", c, E);
+        conv(p + ".Conv_1", c, c, 3);
+        conv(p + ".Conv_2", c, c, 1);
+        if (hi > 0) {
+            items.push_back({p + ".convH_0.0.weight", {3 * c, hi, 3, 3, 3}});
+            items.push_back({p + ".convH_0.0.bias", {3 * c}});
+        }
+        lin(p + ".dense1.dense", c, E);
+        lin(p + ".dense2.dense", c, E);
+    }
+};
+
+Inventory build_inventory(const tmd_config& cfg) {
+    const int* c = cfg.channels;
+    const int E = cfg.embed_dim;
+    Inventory I;
+    I.lin("embed.0", E, cfg.inter_dim);
+    I.lin("embed.2", E, E);
+    I.lin("embed2.0", 4 * E, 768);
+    I.lin("embed2.2", 4 * E, 4 * E);
+    I.lin("embed2.4", E, 4 * E);
+    for (const char* s : {"conv1", "conv2"}) {
+        I.conv(std::string(s) + ".conv20", c[0], 1, 1);
+        I.conv(std::string(s) + ".conv21", c[0], c[0], 3);
+        I.lin(std::string(s) + ".dense2.dense", c[0], E);
+    }
+    const char* downs[6] = {"down1", "down2", "down3", "down1_1", "down2_1", "down3_1"};
+    for (int i = 0; i < 6; ++i) {
+        const int l = i % 3;
+        I.resblock(std::string(downs[i]) + ".conv20", c[l], c[l + 1], E);
+        I.wavelet(std::string(downs[i]) + ".down", c[l + 1], E, 0);
+    }
+    I.resblock("middle1", c[3], c[3], E);
+    const char* ups[3] = {"up1", "up2", "up3"};
+    for (int i = 0; i < 3; ++i) {
+        const int ci = c[3 - i], co = c[2 - i];
+        I.wavelet(std::string(ups[i]) + ".up1", co, E, ci);
+        I.resblock(std::string(ups[i]) + ".conv20", 3 * ci, co, E);
+    }
+    for (int i = 0; i < 4; ++i) I.resblock("final.conv2" + std::to_string(i), i == 0 ? 3 * c[0] : c[0], c[0], E);
+    I.conv("final.conv24", 1, c[0], 1);
+    I.lin("final.dense2.dense", c[0], E);
+    return I;
+}
+
+bool ends_with(const std::string& s, const std::string& suf) {
+    return s.size() >= suf.size() && s.compare(s.size() - suf.size(), suf.size(), suf) == 0;
+}
+bool contains(const std::string& s, const std::string& sub) { return s.find(sub) != std::string::npos; }
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI: lifecycle + weights
+// ---------------------------------------------------------------------------------------------
+extern "C" const char* tmd_last_error(void) { return g_err; }
+extern "C" int tmd_version(void) { return 1; }
+
+extern "C" int tmd_create(const tmd_config* cfg, tmd_handle* out) {
+    if (!cfg || !out) return fail("tmd_create: null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail("tmd_create: no CUDA device (this library has no CPU path)");
+    if (cfg->height % 8 || cfg->width % 8 || cfg->height <= 0 || cfg->width <= 0)
+        return fail("tmd_create: H and W must be positive multiples of 8 (three Haar levels), got %dx%d", cfg->height, cfg->width);
+    for (int i = 0; i < 4; ++i)
+        if (cfg->channels[i] <= 0 || cfg->channels[i] % 8) return fail("tmd_create: channels[%d]=%d must be a positive multiple of 8", i, cfg->channels[i]);
+    if (cfg->dtype != TMD_F32 && cfg->dtype != TMD_BF16) return fail("tmd_create: dtype must be TMD_F32 or TMD_BF16");
+    if (cfg->max_batch <= 0 || cfg->max_bands <= 0) return fail("tmd_create: max_batch and max_bands must be positive");
+    if (cfg->embed_dim % 32 || cfg->inter_dim % 2) return fail("tmd_create: embed_dim must be a multiple of 32 and inter_dim even");
+    auto* e = new tmd_engine();
+    e->cfg = *cfg;
+    e->dtype = cfg->dtype;
+    e->esize = cfg->dtype == TMD_F32 ? 4 : 2;
+    cudaGetDevice(&e->device);
+    *out = e;
+    return 0;
+}
+
+extern "C" int tmd_destroy(tmd_handle h) {
+    if (!h) return 0;
+    for (auto* p : h->plans) conv_umma_plan_destroy(p);
+    for (void* p : h->allocs) cudaFree(p);
+    if (h->arena) cudaFree(h->arena);
+    delete h;
+    return 0;
+}
+
+extern "C" int tmd_load_weight(tmd_handle h, const char* key, const float* host, const int64_t* shape, int32_t ndim) {
+    if (!h || !key || !host || !shape) return fail("tmd_load_weight: null argument");
+    auto& inv = h->inv_shapes;
+    if (inv.empty())
+        for (auto& it : build_inventory(h->cfg).items) inv[it.first] = it.second;
+    auto it = inv.find(key);
+    if (it == inv.end()) return fail("tmd_load_weight: unexpected key '%s'", key);
+    std::vector<int64_t> shp(shape, shape + ndim);
+    if (shp != it->second) return fail("tmd_load_weight: shape mismatch for '%s'", key);
+    size_t n = 1;
+    for (auto d : shp) n *= (size_t)d;
+    HostTensor t;
+    t.data.assign(host, host + n);
+    t.shape = shp;
+    h->host[key] = std::move(t);
+    h->finalized = false;
+    return 0;
+}
+
+extern "C" int tmd_set_time_frequencies(tmd_handle h, const float* host, int32_t n) {
+    if (!h || !host) return fail("tmd_set_time_frequencies: null argument");
+    if (n != h->cfg.inter_dim / 2) return fail("tmd_set_time_frequencies: expected %d frequencies", h->cfg.inter_dim / 2);
+    h->freqs_host.assign(host, host + n);
+    h->finalized = false;
+    return 0;
+}
+
+static int pack_conv(tmd_engine* e, const std::string& name, const float* w, const float* bias, int Co, int Ci, int k, float bias_scale) {
+    const int taps = k * k * k;
+    ConvW cw;
+    cw.Co = Co; cw.Ci = Ci; cw.taps = taps;
+    std::vector<float> pf((size_t)taps * Ci * Co);
+    std::vector<__nv_bfloat16> pb((size_t)taps * Ci * Co);
+    for (int co = 0; co < Co; ++co)
+        for (int ci = 0; ci < Ci; ++ci)
+            for (int t = 0; t < taps; ++t) {
+                const float v = w[((size_t)co * Ci + ci) * taps + t];  // [Co][Ci][kd][kh][kw], t = (kd*k+kh)*k+kw
+                pf[((size_t)t * Ci + ci) * Co + co] = v;
+                pb[(size_t)co * taps * Ci + (size_t)t * Ci + ci] = __float2bfloat16(v);
+            }
+    if (e->upload(&cw.w_f32, pf)) return 1;
+    if (e->upload(&cw.w_bf16, pb)) return 1;
+    if (bias) {
+        std::vector<float> b(bias, bias + Co);
+        for (auto& v : b) v *= bias_scale;
+        if (e->upload(&cw.bias, b)) return 1;
+    }
+    e->convs[name] = cw;
+    return 0;
+}
+
+extern "C" int tmd_finalize_weights(tmd_handle h) {
+    if (!h) return fail("tmd_finalize_weights: null handle");
+    auto inv = build_inventory(h->cfg);
+    for (auto& it : inv.items)
+        if (!h->host.count(it.first)) return fail("tmd_finalize_weights: missing weight '%s'", it.first.c_str());
+    if (h->freqs_host.empty()) return fail("tmd_finalize_weights: tmd_set_time_frequencies was not called");
+    CK(cudaSetDevice(h->device));
+    const int E = h->cfg.embed_dim;
+    auto H = [&](const std::string& k) -> const std::vector<float>& { return h->host[k].data; };
+
+    // ---- convolutions ----
+    h->convs.clear();
+    for (auto& it : inv.items) {
+        const std::string& key = it.first;
+        if (!ends_with(key, ".weight") || it.second.size() != 5) continue;
+        const std::string name = key.substr(0, key.size() - 7);
+        const int Co = (int)it.second[0], Ci = (int)it.second[1], k = (int)it.second[2];
+        const float* w = H(key).data();
+        const float* b = H(name + ".bias").data();
+        // modulated convs never use their bias (callers pass bias=None, :171, :247, :271, :404)
+        const bool modulated = ends_with(name, ".conv21") || ends_with(name, ".Conv_1") || name == "final.conv24";
+        if (contains(name, ".convH_0.0")) {
+            // groups=3 (:359-361): three independent convs; skipH = convH(cat/2)*2 == W*S + 2b (:381)
+            const int co = Co / 3;
+            for (int g = 0; g < 3; ++g)
+                if (pack_conv(h, name + "#" + std::to_string(g), w + (size_t)g * co * Ci * 27, b + g * co, co, Ci, k, 2.0f)) return 1;
+        } else if (Ci == 1 && k == 1) {
+            const int s = name.rfind("conv1", 0) == 0 ? 0 : 1;   // stems conv1.conv20 / conv2.conv20
+            std::vector<float> wv(w, w + Co), bv(b, b + Co);
+            if (h->upload(&h->d_stem_w[s], wv) || h->upload(&h->d_stem_b[s], bv)) return 1;
+        } else if (Co == 1 && k == 1) {
+            std::vector<float> wv(w, w + Ci);
+            if (h->upload(&h->d_proj_w, wv)) return 1;
+        } else {
+            if (pack_conv(h, name, w, modulated ? nullptr : b, Co, Ci, k, 1.0f)) return 1;
+        }
+    }
+
+    // ---- conditioning tables ----
+    h->time_off.clear(); h->text_off.clear();
+    std::vector<float> Wt, bt, Ws, bs;
+    auto append = [&](std::vector<float>& Wm, std::vector<float>& bm, std::map<std::string, int>& off, const std::string& mod,
+                      const std::string& key) {
+        const auto& w = H(key + ".weight");
+        const auto& b = H(key + ".bias");
+        off[mod] = (int)bm.size();
+        Wm.insert(Wm.end(), w.begin(), w.end());
+        bm.insert(bm.end(), b.begin(), b.end());
+    };
+    for (auto& it : inv.items) {
+        const std::string& key = it.first;
+        if (!ends_with(key, ".weight") || it.second.size() != 2) continue;
+        const std::string name = key.substr(0, key.size() - 7);
+        if (name.rfind("embed", 0) == 0) continue;
+        const bool cond_branch = contains(name, "_1.");   // flag=True blocks never read their time Dense (:238-241, :400-401)
+        const bool wavelet = contains(name, ".down.") || contains(name, ".up1.");
+        if (ends_with(name, ".Dense_0")) {
+            if (!cond_branch) append(Wt, bt, h->time_off, name, name);
+        } else if (ends_with(name, ".dense1.dense")) {
+            const std::string mod = name.substr(0, name.size() - 6);
+            if (wavelet) append(Ws, bs, h->text_off, mod, name);             // s = dense1(zemb) (:404)
+            else if (!cond_branch) append(Wt, bt, h->time_off, mod, name);   // h = x + dense1(embed) (:239)
+        } else if (ends_with(name, ".dense2.dense")) {
+            const std::string mod = name.substr(0, name.size() - 6);
+            if (!wavelet) append(Ws, bs, h->text_off, mod, name);            // s = dense2(prompt) (:171, :247, :271); wavelet dense2 is unused
+        }
+    }
+    h->time_rows = (int)bt.size();
+    h->text_rows = (int)bs.size();
+    if (h->upload(&h->d_Wt, Wt) || h->upload(&h->d_bt, bt) || h->upload(&h->d_Ws, Ws) || h->upload(&h->d_bs, bs)) return 1;
+    if (h->upload(&h->d_freqs, h->freqs_host)) return 1;
+    if (h->upload(&h->d_e_w1, H("embed.0.weight")) || h->upload(&h->d_e_b1, H("embed.0.bias")) ||
+        h->upload(&h->d_e_w2, H("embed.2.weight")) || h->upload(&h->d_e_b2, H("embed.2.bias")))
+        return 1;
+    const char* pk[3] = {"embed2.0", "embed2.2", "embed2.4"};
+    for (int i = 0; i < 3; ++i)
+        if (h->upload(&h->d_p_w[i], H(std::string(pk[i]) + ".weight")) || h->upload(&h->d_p_b[i], H(std::string(pk[i]) + ".bias"))) return 1;
+    const int MB = h->cfg.max_batch;
+    if (!h->d_text) {
+        if (h->dmalloc(&h->d_text, (size_t)TMD_NUM_SENSORS * 768) || h->dmalloc(&h->d_p_tmp0, (size_t)TMD_NUM_SENSORS * 4 * E) ||
+            h->dmalloc(&h->d_p_tmp1, (size_t)TMD_NUM_SENSORS * 4 * E) || h->dmalloc(&h->d_prompt, (size_t)TMD_NUM_SENSORS * E) ||
+            h->dmalloc(&h->d_tin, (size_t)MB) || h->dmalloc(&h->d_embed, (size_t)MB * E) || h->dmalloc(&h->d_sensor, (size_t)MB))
+            return 1;
+        CK(cudaMemset(h->d_text, 0, (size_t)TMD_NUM_SENSORS * 768 * sizeof(float)));
+    }
+    if (h->dmalloc(&h->d_sc_sensor, (size_t)TMD_NUM_SENSORS * h->text_rows) || h->dmalloc(&h->d_tb, (size_t)MB * h->time_rows) ||
+        h->dmalloc(&h->d_sc, (size_t)MB * h->text_rows))
+        return 1;
+    h->text_dirty = true;
+    h->finalized = true;
+    h->B = 0;  // force a re-plan
+    CK(cudaDeviceSynchronize());
+    return 0;
+}
+
+extern "C" int tmd_set_text_embedding(tmd_handle h, int32_t sensor, const float* host768) {
+    if (!h || !host768) return fail("tmd_set_text_embedding: null argument");
+    if (sensor < 0 || sensor >= TMD_NUM_SENSORS) return fail("tmd_set_text_embedding: sensor id %d out of range", sensor);
+    if (!h->finalized) return fail("tmd_set_text_embedding: call tmd_finalize_weights first");
+    CK(cudaMemcpy(h->d_text + (size_t)sensor * 768, host768, 768 * sizeof(float), cudaMemcpyHostToDevice));
+    h->have_text[sensor] = true;
+    h->text_dirty = true;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// plan: bind a geometry, carve the workspace, build the launch lists
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct Planner {
+    tmd_engine* e;
+    std::vector<Launch>* ops;
+    int B, N, H, W;
+    const char* err = nullptr;
+
+    size_t vox(int lvl) const { return (size_t)B * N * (H >> lvl) * (W >> lvl); }
+
+    View buf(const std::string& name, int lvl, int C) {
+        auto it = e->bufs.find(name);
+        if (it == e->bufs.end()) {
+            const size_t bytes = (vox(lvl) * C * e->esize + 255) & ~(size_t)255;
+            if (e->arena_used + bytes > e->arena_size) { err = "workspace arena exhausted"; return View{}; }
+            void* p = e->arena + e->arena_used;
+            e->arena_used += bytes;
+            it = e->bufs.emplace(name, p).first;
+        }
+        return View{it->second, C, C};
+    }
+    View slice(View v, int c0, int C) const { return View{(char*)v.p + (size_t)c0 * e->esize, C, v.ld}; }
+    const float* tb(const std::string& mod, int c0 = 0) {
+        auto it = e->time_off.find(mod);
+        if (it == e->time_off.end()) { err = "missing time table entry"; return nullptr; }
+        return e->d_tb + it->second + c0;
+    }
+    const float* sc(const std::string& mod) {
+        auto it = e->text_off.find(mod);
+        if (it == e->text_off.end()) { err = "missing text table entry"; return nullptr; }
+        return e->d_sc + it->second;
+    }
+
+    void conv(const std::string& wname, View src, int lvl, int mode, const OutSpec& out, View add0 = View{}, View add1 = View{},
+              View* hf = nullptr) {
+        auto it = e->convs.find(wname);
+        if (it == e->convs.end()) { err = "missing conv weights"; return; }
+        const ConvW& cw = it->second;
+        if (cw.Ci != src.C) { err = "conv input channel mismatch"; return; }
+        ConvOp op{};
+        op.B = B; op.N = N; op.H = H >> lvl; op.W = W >> lvl;
+        op.Ci = cw.Ci; op.ld_in = src.ld; op.src = src.p;
+        op.Co = cw.Co; op.taps = cw.taps;
+        op.w_f32 = cw.w_f32; op.w_bf16 = cw.w_bf16;
+        ConvEpilogue& ep = op.epi;
+        ep.mode = mode;
+        ep.bias = cw.bias;
+        ep.add0 = add0.p; ep.ld_add0 = add0.ld;
+        ep.add1 = add1.p; ep.ld_add1 = add1.ld;
+        ep.raw_out = out.raw.p; ep.ld_raw = out.raw.ld;
+        for (int i = 0; i < 2; ++i) {
+            ep.act_out[i] = out.act[i].dst.p; ep.ld_act[i] = out.act[i].dst.ld;
+            ep.tb[i] = out.act[i].tb; ep.sc[i] = out.act[i].sc;
+        }
+        ep.ld_tb = e->time_rows; ep.ld_sc = e->text_rows;
+        if (hf) { for (int i = 0; i < 3; ++i) ep.hf_out[i] = hf[i].p; ep.ld_hf = hf[0].ld; }
+        if (e->dtype == TMD_F32) {
+            ops->push_back([op](cudaStream_t s) { return conv_simt_f32(op, s); });
+        } else if (conv_umma_supported(op)) {
+            UmmaPlan* plan = conv_umma_plan_create(op);
+            if (!plan) { err = "tensor map creation failed"; return; }
+            e->plans.push_back(plan);
+            ops->push_back([op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); });
+        } else {
+            ops->push_back([op](cudaStream_t s) { return conv_simt_bf16(op, s); });
+        }
+    }
+
+    // ResBlockModulateBEST.forward (:237-249).  in_act = swish(x [+ dense1(embed)]) prepared by the producer.
+    void resblock(const std::string& p, View in_act, View in_raw, int Co, int lvl, const OutSpec& out) {
+        View a2 = buf("a2@" + std::to_string(lvl), lvl, cmax(lvl));
+        a2.C = Co;
+        OutSpec o1;
+        o1.act[0] = ActSpec{a2, nullptr, sc(p + ".dense2")};
+        conv(p + ".conv20", in_act, lvl, CONV_NORMAL, o1);
+        View res = in_raw;
+        if (e->convs.count(p + ".res_conv")) {
+            View r = buf("r@" + std::to_string(lvl), lvl, cmax(lvl));
+            r.C = Co;
+            OutSpec o2;
+            o2.raw = r;
+            conv(p + ".res_conv", in_raw, lvl, CONV_NORMAL, o2);
+            res = r;
+        }
+        conv(p + ".conv21", a2, lvl, CONV_NORMAL, out, res);
+    }
+
+    // WaveletUPorDown.forward, down=True (:369-414); lvl = input level, outputs at lvl+1
+    void wavelet_down(const std::string& p, View in_act, View in_raw, int C, int lvl, bool flag, View* hf, const OutSpec& out) {
+        View xp = buf("xp@" + std::to_string(lvl + 1), lvl + 1, cmax(lvl + 1));
+        xp.C = C;
+        OutSpec o1;
+        o1.raw = xp;
+        conv(p + ".Conv_2", in_raw, lvl, CONV_POOL, o1);
+        View ac1 = buf("ac1@" + std::to_string(lvl + 1), lvl + 1, cmax(lvl + 1));
+        ac1.C = C;
+        OutSpec o2;
+        o2.act[0] = ActSpec{ac1, flag ? nullptr : tb(p + ".Dense_0"), sc(p + ".dense1")};
+        conv(p + ".Conv_0", in_act, lvl, CONV_POOL, o2, View{}, View{}, hf);
+        conv(p + ".Conv_1", ac1, lvl + 1, CONV_NORMAL, out, xp);
+    }
+
+    // WaveletUPorDown.forward, up=True; lvl = input (low) level, outputs at lvl-1.  T = IDWT(0, skipH').
+    void wavelet_up(const std::string& p, View in_act, View in_raw, int C, int lvl, View T, const OutSpec& out) {
+        View xl = buf("xl@" + std::to_string(lvl), lvl, cmax(lvl));
+        xl.C = C;
+        OutSpec o1;
+        o1.raw = xl;
+        conv(p + ".Conv_2", in_raw, lvl, CONV_NORMAL, o1);
+        View ac1 = buf("ac1u@" + std::to_string(lvl - 1), lvl - 1, cmax(lvl - 1));
+        ac1.C = C;
+        OutSpec o2;
+        o2.act[0] = ActSpec{ac1, tb(p + ".Dense_0"), sc(p + ".dense1")};
+        conv(p + ".Conv_0", in_act, lvl, CONV_UPSAMPLE, o2, T);
+        conv(p + ".Conv_1", ac1, lvl - 1, CONV_NORMAL, out, T, xl);
+    }
+
+    int cmax(int lvl) const { return e->cfg.channels[lvl < 3 ? lvl + 1 : 3]; }
+};
+
+int build_plan(tmd_engine* e, int B, int N, int H, int W) {
+    const int* c = e->cfg.channels;
+    for (auto* p : e->plans) conv_umma_plan_destroy(p);
+    e->plans.clear();
+    e->pre_ops.clear();
+    e->step_ops.clear();
+    e->bufs.clear();
+    e->arena_used = 0;
+    if (!e->arena) {
+        // worst-case footprint at (max_batch, max_bands, H, W): sum over levels of channel-widths of all named buffers
+        const size_t v0 = (size_t)e->cfg.max_batch * e->cfg.max_bands * e->cfg.height * e->cfg.width;
+        size_t elems = 0;
+        const int cm[4] = {c[1], c[2], c[3], c[3]};
+        for (int l = 0; l < 4; ++l) {
+            const size_t v = v0 >> (2 * l);
+            elems += v * (size_t)(2 * 3 * c[l] + 8 * cm[l] + 8 * c[l]);
+        }
+        e->arena_size = elems * e->esize + ((size_t)64 << 20);
+        CK(cudaMalloc((void**)&e->arena, e->arena_size));
+        for (int i = 0; i < TMD_NUM_SLOTS; ++i)
+            if (e->dmalloc(&e->slots[i], v0)) return 1;
+        if (e->dmalloc(&e->d_out, v0)) return 1;
+    }
+    Planner P{e, &e->pre_ops, B, N, H, W};
+    const int dt = e->dtype;
+    const int tr = e->time_rows, sr = e->text_rows;
+    const int HW = H * W;
+    auto L = [](int l) { return std::to_string(l); };
+
+    // concat buffers: [h | cond skip | main skip] per level (:631-634), raw and activated forms
+    View cat_raw[4], cat_act[4];
+    for (int l = 0; l < 4; ++l) {
+        cat_raw[l] = P.buf("cat_raw@" + L(l), l, 3 * c[l]);
+        cat_act[l] = P.buf("cat_act@" + L(l), l, 3 * c[l]);
+    }
+    View Tup[3];  // IDWT(0, skipH') for up1 (level 2), up2 (level 1), up3 (level 0)
+    for (int l = 0; l < 3; ++l) Tup[l] = P.buf("T@" + L(l), l, c[l]);
+
+    // ======================= step-invariant condition branch (:611-618) =======================
+    {
+        View a_stem = P.buf("a_stem", 0, c[0]);
+        const float* scs = P.sc("conv1.dense2");
+        P.ops->push_back([=](cudaStream_t s) {
+            return stem_expand(dt, e->cur_ms, e->cur_pan, e->d_stem_w[0], e->d_stem_b[0], scs, sr, a_stem.p, c[0], B, N, HW, s);
+        });
+        View in_act = P.buf("in_act@0", 0, c[0]);
+        OutSpec o;
+        o.raw = P.slice(cat_raw[0], c[0], c[0]);
+        o.act[0] = ActSpec{in_act, nullptr, nullptr};
+        P.conv("conv1.conv21", a_stem, 0, CONV_NORMAL, o);
+        View in_raw = o.raw;
+        const char* names[3] = {"down1_1", "down2_1", "down3_1"};
+        for (int l = 0; l < 3; ++l) {
+            const std::string nm = names[l];
+            View y = P.buf("y@" + L(l), l, c[l + 1]);
+            View ay = P.buf("ay@" + L(l), l, c[l + 1]);
+            OutSpec ro;
+            ro.raw = y;
+            ro.act[0] = ActSpec{ay, nullptr, nullptr};
+            P.resblock(nm + ".conv20", in_act, in_raw, c[l + 1], l, ro);
+            View hf[3];
+            for (int g = 0; g < 3; ++g) hf[g] = P.buf("S" + L(g) + "@" + L(l + 1), l + 1, c[l + 1]);
+            View nxt = P.buf("in_act@" + L(l + 1), l + 1, c[l + 1]);
+            OutSpec wo;
+            wo.raw = P.slice(cat_raw[l + 1], c[l + 1], c[l + 1]);
+            if (l < 2) wo.act[0] = ActSpec{nxt, nullptr, nullptr};
+            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, true, hf, wo);
+            in_act = nxt;
+            in_raw = wo.raw;
+            // convH_0 of the matching up block consumes only these skips (:381): hoist it here
+            const std::string up = std::string("up") + L(3 - l) + ".up1.convH_0.0#";
+            View hq[3];
+            for (int g = 0; g < 3; ++g) {
+                hq[g] = P.buf("HQ" + L(g) + "@" + L(l + 1), l + 1, c[l]);
+                OutSpec ho;
+                ho.raw = hq[g];
+                P.conv(up + L(g), hf[g], l + 1, CONV_NORMAL, ho);
+            }
+            View T = Tup[l];
+            const size_t planes = (size_t)B * N;
+            const int hh = H >> (l + 1), ww = W >> (l + 1), C = c[l];
+            P.ops->push_back([=](cudaStream_t s) { return idwt_highbands(dt, hq[0].p, hq[1].p, hq[2].p, T.p, C, planes, hh, ww, s); });
+        }
+    }
+
+    // ================================ per-step main branch ===================================
+    P.ops = &e->step_ops;
+    {
+        const int E = e->cfg.embed_dim;
+        P.ops->push_back([=](cudaStream_t s) {
+            return time_table(e->cur_t_dev, e->cur_t_scalar, e->d_freqs, e->cfg.inter_dim, e->d_e_w1, e->d_e_b1, e->d_e_w2, e->d_e_b2,
+                              e->d_Wt, e->d_bt, e->d_embed, e->d_tb, B, E, tr, s);
+        });
+        // activations of the cached condition slices for this step's time embedding
+        const char* consumer[4] = {"final.conv20", "up3.conv20", "up2.conv20", "up1.conv20"};
+        for (int l = 0; l < 4; ++l) {
+            View src = P.slice(cat_raw[l], c[l], c[l]), dst = P.slice(cat_act[l], c[l], c[l]);
+            const float* t = P.tb(std::string(consumer[l]) + ".dense1", c[l]);
+            const int C = c[l];
+            const size_t vps = (size_t)N * (H >> l) * (W >> l);
+            P.ops->push_back([=](cudaStream_t s) { return slice_activate(dt, src.p, src.ld, dst.p, dst.ld, t, tr, C, B, vps, s); });
+        }
+        View a_stem = P.buf("a_stem", 0, c[0]);
+        const float* scs = P.sc("conv2.dense2");
+        P.ops->push_back([=](cudaStream_t s) {
+            return stem_expand(dt, e->cur_x, nullptr, e->d_stem_w[1], e->d_stem_b[1], scs, sr, a_stem.p, c[0], B, N, HW, s);
+        });
+        View in_act = P.buf("in_act@0", 0, c[0]);
+        OutSpec o;
+        o.raw = P.slice(cat_raw[0], 2 * c[0], c[0]);
+        o.act[0] = ActSpec{in_act, P.tb("down1.conv20.dense1"), nullptr};
+        o.act[1] = ActSpec{P.slice(cat_act[0], 2 * c[0], c[0]), P.tb("final.conv20.dense1", 2 * c[0]), nullptr};
+        P.conv("conv2.conv21", a_stem, 0, CONV_NORMAL, o);
+        View in_raw = o.raw;
+        const char* names[3] = {"down1", "down2", "down3"};
+        const char* next_res[3] = {"down2.conv20", "down3.conv20", "middle1"};
+        for (int l = 0; l < 3; ++l) {
+            const std::string nm = names[l];
+            View y = P.buf("y@" + L(l), l, c[l + 1]);
+            View ay = P.buf("ay@" + L(l), l, c[l + 1]);
+            OutSpec ro;
+            ro.raw = y;
+            ro.act[0] = ActSpec{ay, nullptr, nullptr};
+            P.resblock(nm + ".conv20", in_act, in_raw, c[l + 1], l, ro);
+            View nxt = P.buf("in_act@" + L(l + 1), l + 1, c[l + 1]);
+            OutSpec wo;
+            wo.raw = P.slice(cat_raw[l + 1], 2 * c[l + 1], c[l + 1]);
+            wo.act[0] = ActSpec{nxt, P.tb(std::string(next_res[l]) + ".dense1"), nullptr};
+            wo.act[1] = ActSpec{P.slice(cat_act[l + 1], 2 * c[l + 1], c[l + 1]),
+                                P.tb(std::string(consumer[l + 1]) + ".dense1", 2 * c[l + 1]), nullptr};
+            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, false, nullptr, wo);  // high bands of the main branch are never read (:620-627)
+            in_act = nxt;
+            in_raw = wo.raw;
+        }
+        {   // middle1 (:629)
+            OutSpec mo;
+            mo.raw = P.slice(cat_raw[3], 0, c[3]);
+            mo.act[0] = ActSpec{P.slice(cat_act[3], 0, c[3]), P.tb("up1.conv20.dense1", 0), nullptr};
+            P.resblock("middle1", in_act, in_raw, c[3], 3, mo);
+        }
+        for (int i = 0; i < 3; ++i) {  // up1..up3 (:631-633): level 3-i -> 2-i
+            const int l = 3 - i;
+            const std::string nm = std::string("up") + L(i + 1);
+            View y = P.buf("y@" + L(l), l, P.cmax(l));
+            y.C = c[l - 1];
+            View ay = P.buf("ay@" + L(l), l, P.cmax(l));
+            ay.C = c[l - 1];
+            OutSpec ro;
+            ro.raw = y;
+            ro.act[0] = ActSpec{ay, nullptr, nullptr};
+            P.resblock(nm + ".conv20", cat_act[l], cat_raw[l], c[l - 1], l, ro);
+            OutSpec wo;
+            wo.raw = P.slice(cat_raw[l - 1], 0, c[l - 1]);
+            wo.act[0] = ActSpec{P.slice(cat_act[l - 1], 0, c[l - 1]), P.tb(std::string(consumer[l - 1]) + ".dense1", 0), nullptr};
+            P.wavelet_up(nm + ".up1", ay, y, c[l - 1], l, Tup[l - 1], wo);
+        }
+        {   // final (:265-273)
+            View f[2] = {P.buf("f0", 0, c[0]), P.buf("f1", 0, c[0])};
+            View af[2] = {P.buf("af0", 0, c[0]), P.buf("af1", 0, c[0])};
+            View ia = cat_act[0], ir = cat_raw[0];
+            for (int i = 0; i < 4; ++i) {
+                OutSpec fo;
+                if (i < 3) {
+                    fo.raw = f[i & 1];
+                    fo.act[0] = ActSpec{af[i & 1], P.tb("final.conv2" + L(i + 1) + ".dense1"), nullptr};
+                } else {
+                    fo.act[0] = ActSpec{af[i & 1], nullptr, P.sc("final.dense2")};  // act(h) then conv24's modulation
+                }
+                P.resblock("final.conv2" + L(i), ia, ir, c[0], 0, fo);
+                ia = af[i & 1];
+                ir = f[i & 1];
+            }
+            const size_t nvox = P.vox(0);
+            const int C = c[0];
+            View last = af[1];
+            P.ops->push_back([=](cudaStream_t s) { return project_to_band(dt, last.p, last.ld, e->d_proj_w, e->cur_out, C, nvox, s); });
+        }
+    }
+    if (P.err) return fail("plan: %s", P.err);
+    e->B = B; e->N = N; e->H = H; e->W = W;
+    return 0;
+}
+
+int run_ops(tmd_engine* e, std::vector<Launch>& ops, cudaStream_t s) {
+    for (auto& op : ops) {
+        cudaError_t err = op(s);
+        if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
+        ++e->launches;
+    }
+    return 0;
+}
+
+int refresh_text(tmd_engine* e, cudaStream_t s) {
+    const int E = e->cfg.embed_dim;
+    // prompt = act(embed2(clip_emb)) (:602-603), then every text Dense
+    CK(dense_rows(e->d_text, e->d_p_w[0], e->d_p_b[0], e->d_p_tmp0, TMD_NUM_SENSORS, 768, 4 * E, 1, s));
+    CK(dense_rows(e->d_p_tmp0, e->d_p_w[1], e->d_p_b[1], e->d_p_tmp1, TMD_NUM_SENSORS, 4 * E, 4 * E, 1, s));
+    CK(dense_rows(e->d_p_tmp1, e->d_p_w[2], e->d_p_b[2], e->d_prompt, TMD_NUM_SENSORS, 4 * E, E, 1, s));
+    CK(dense_rows(e->d_prompt, e->d_Ws, e->d_bs, e->d_sc_sensor, TMD_NUM_SENSORS, E, e->text_rows, 0, s));
+    e->launches += 4;
+    e->text_dirty = false;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int tmd_precompute_condition(tmd_handle h, const float* pan, const float* ms, const int32_t* sensor_ids, int32_t B,
+                                        int32_t bands, int32_t H, int32_t W, void* stream) {
+    if (!h || !pan || !ms || !sensor_ids) return fail("tmd_precompute_condition: null argument");
+    if (!h->finalized) return fail("tmd_precompute_condition: weights not finalized");
+    if (B <= 0 || B > h->cfg.max_batch) return fail("tmd_precompute_condition: batch %d outside [1, %d]", B, h->cfg.max_batch);
+    if (bands <= 0 || bands > h->cfg.max_bands) return fail("tmd_precompute_condition: bands %d outside [1, %d]", bands, h->cfg.max_bands);
+    if (H % 8 || W % 8 || H <= 0 || W <= 0 || (size_t)H * W > (size_t)h->cfg.height * h->cfg.width)
+        return fail("tmd_precompute_condition: patch %dx%d must be a multiple of 8 and fit the configured %dx%d", H, W, h->cfg.height, h->cfg.width);
+    for (int i = 0; i < B; ++i) {
+        if (sensor_ids[i] < 0 || sensor_ids[i] >= TMD_NUM_SENSORS) return fail("tmd_precompute_condition: sensor id %d out of range", sensor_ids[i]);
+        if (!h->have_text[sensor_ids[i]]) return fail("tmd_precompute_condition: no text embedding set for sensor %d", sensor_ids[i]);
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(h->device));
+    if (B != h->B || bands != h->N || H != h->H || W != h->W)
+        if (build_plan(h, B, bands, H, W)) return 1;
+    if (h->text_dirty && refresh_text(h, s)) return 1;
+    CK(cudaMemcpyAsync(h->d_sensor, sensor_ids, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, s));
+    CK(gather_rows(h->d_sc_sensor, h->d_sensor, h->d_sc, B, h->text_rows, s));
+    ++h->launches;
+    h->cur_pan = pan;
+    h->cur_ms = ms;
+    return run_ops(h, h->pre_ops, s);
+}
+
+static int denoise_impl(tmd_handle h, const float* x, const float* t_dev, float t_scalar, float* out, cudaStream_t s) {
+    h->cur_x = x;
+    h->cur_out = out;
+    h->cur_t_dev = t_dev;
+    h->cur_t_scalar = t_scalar;
+    return run_ops(h, h->step_ops, s);
+}
+
+extern "C" int tmd_denoise(tmd_handle h, const float* x_t, const float* t_input_dev, float* out, void* stream) {
+    if (!h || !x_t || !t_input_dev || !out) return fail("tmd_denoise: null argument");
+    if (h->B == 0 || h->step_ops.empty()) return fail("tmd_denoise: call tmd_precompute_condition first");
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(h->device));
+    return denoise_impl(h, x_t, t_input_dev, 0.f, out, s);
+}
+
+extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, float* out, float* trace, void* stream) {
+    if (!h || !x_T || !plan || !out || !plan->steps) return fail("tmd_sample: null argument");
+    if (h->B == 0 || h->step_ops.empty()) return fail("tmd_sample: call tmd_precompute_condition first");
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(h->device));
+    const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * h->B;
+    if (n_per > 51200) return fail("tmd_sample: %zu values per patch exceeds the in-shared-memory quantile select (51200)", n_per);
+    auto slot_ok = [](int i) { return i >= 0 && i < TMD_NUM_SLOTS; };
+    if (!slot_ok(plan->result_slot)) return fail("tmd_sample: bad result slot");
+    CK(cudaMemcpyAsync(h->slots[0], x_T, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    int n_eval = 0;
+    for (int i = 0; i < plan->n_steps; ++i) {
+        const tmd_step& st = plan->steps[i];
+        if (st.kind == 0) {
+            const tmd_eval& ev = st.eval;
+            if (!slot_ok(ev.src) || !slot_ok(ev.dst)) return fail("tmd_sample: bad slot in step %d", i);
+            float* net_out = trace ? trace + (size_t)n_eval * n : h->d_out;
+            if (denoise_impl(h, h->slots[ev.src], nullptr, ev.t_input, net_out, s)) return 1;
+            CK(x0_threshold(h->slots[ev.src], net_out, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, h->B, (int)n_per, plan->q_lo,
+                            plan->q_weight, plan->max_val, s));
+            ++h->launches;
+            ++n_eval;
+        } else {
+            const tmd_update& u = st.update;
+            if (!slot_ok(u.dst) || !slot_ok(u.x) || !slot_ok(u.m) || u.m1 >= TMD_NUM_SLOTS) return fail("tmd_sample: bad slot in step %d", i);
+            CK(solver_update(h->slots[u.dst], h->slots[u.x], h->slots[u.m], u.m1 >= 0 ? h->slots[u.m1] : nullptr, u.c1, u.c2, u.c3, n, s));
+            ++h->launches;
+        }
+    }
+    CK(cudaMemcpyAsync(out, h->slots[plan->result_slot], n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
+extern "C" int64_t tmd_launch_count(tmd_handle h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// stand-alone operators
+// ---------------------------------------------------------------------------------------------
+extern "C" int tmd_dwt2d(const float* x, float* ll, float* lh, float* hl, float* hh, int64_t BC, int32_t H, int32_t W, void* stream) {
+    if (BC == 0) return 0;
+    if (!x || !ll) return fail("tmd_dwt2d: null argument");
+    if ((lh || hl || hh) && !(lh && hl && hh)) return fail("tmd_dwt2d: give all three high bands or none");
+    if (H % 2 || W % 2 || H <= 0 || W <= 0) return fail("tmd_dwt2d: H and W must be even (the reference mishandles odd sizes, DWT_IDWT_layer.py:1-4)");
+    if (BC == 0) return 0;
+    CK(dwt2d_nchw(x, ll, lh, hl, hh, BC, H, W, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int tmd_idwt2d(const float* ll, const float* lh, const float* hl, const float* hh, float* out, int64_t BC, int32_t h, int32_t w,
+                          void* stream) {
+    if (BC == 0) return 0;
+    if (!ll || !lh || !hl || !hh || !out) return fail("tmd_idwt2d: null argument");
+    if (h <= 0 || w <= 0) return fail("tmd_idwt2d: bad size");
+    if (BC == 0) return 0;
+    CK(idwt2d_nchw(ll, lh, hl, hh, out, BC, h, w, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream) {
+    if (!x0) return fail("tmd_dynamic_threshold: null argument");
+    if (B <= 0 || n <= 0 || q_lo < 0 || q_lo >= n) return fail("tmd_dynamic_threshold: bad sizes");
+    if (n > 51200) return fail("tmd_dynamic_threshold: n=%d exceeds the in-shared-memory select limit (51200)", n);
+    CK(dynamic_threshold_inplace(x0, B, n, q_lo, q_weight, max_val, (cudaStream_t)stream));
+    return 0;
+}
+
+namespace {
+__global__ void pack_weights_kernel(const float* __restrict__ w, float* __restrict__ pf, __nv_bfloat16* __restrict__ pb, int Co, int Ci,
+                                    int taps) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t total = (size_t)Co * Ci * taps;
+    if (i >= total) return;
+    const int t = (int)(i % taps);
+    const int ci = (int)((i / taps) % Ci);
+    const int co = (int)(i / ((size_t)taps * Ci));
+    const float v = w[i];
+    pf[((size_t)t * Ci + ci) * Co + co] = v;
+    pb[(size_t)co * taps * Ci + (size_t)t * Ci + ci] = __float2bfloat16(v);
+}
+}  // namespace
+
+extern "C" int tmd_conv3d_mod(const float* x, const float* w, const float* sc, const float* bias, float* y, int32_t B, int32_t Ci,
+                              int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t dtype, void* stream) {
+    if (!x || !w || !y) return fail("tmd_conv3d_mod: null argument");
+    if (k != 1 && k != 3) return fail("tmd_conv3d_mod: kernel size must be 1 or 3");
+    if (Ci % 4 || Co % 4) return fail("tmd_conv3d_mod: Ci and Co must be multiples of 4");
+    if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_conv3d_mod: bad dtype");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
+    const int taps = k * k * k;
+    void *xin = nullptr, *yout = nullptr;
+    float* pf = nullptr;
+    __nv_bfloat16* pb = nullptr;
+    CK(cudaMallocAsync(&xin, (size_t)B * nhw * Ci * es, s));
+    CK(cudaMallocAsync(&yout, (size_t)B * nhw * Co * es, s));
+    CK(cudaMallocAsync((void**)&pf, (size_t)taps * Ci * Co * 4, s));
+    CK(cudaMallocAsync((void**)&pb, (size_t)taps * Ci * Co * 2, s));
+    const size_t total = (size_t)Co * Ci * taps;
+    pack_weights_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(w, pf, pb, Co, Ci, taps);
+    CK(cudaGetLastError());
+    CK(ncdhw_to_cl(dtype, x, sc, xin, B, Ci, nhw, s));   // x * s == modulating the weights (no demodulation, :68-76)
+    ConvOp op{};
+    op.B = B; op.N = N; op.H = H; op.W = W; op.Ci = Ci; op.ld_in = Ci; op.src = xin; op.Co = Co; op.taps = taps;
+    op.w_f32 = pf; op.w_bf16 = pb;
+    op.epi.mode = CONV_NORMAL; op.epi.bias = bias; op.epi.raw_out = yout; op.epi.ld_raw = Co;
+    int rc = 0;
+    if (dtype == TMD_F32) {
+        CK(conv_simt_f32(op, s));
+    } else if (conv_umma_supported(op)) {
+        UmmaPlan* plan = conv_umma_plan_create(op);
+        if (!plan) rc = fail("tmd_conv3d_mod: tensor map creation failed");
+        else {
+            cudaError_t err = conv_umma_bf16(op, plan, s);
+            conv_umma_plan_destroy(plan);
+            if (err != cudaSuccess) rc = fail("tmd_conv3d_mod: %s", cudaGetErrorString(err));
+        }
+    } else {
+        CK(conv_simt_bf16(op, s));
+    }
+    if (!rc) CK(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s));
+    cudaFreeAsync(xin, s); cudaFreeAsync(yout, s); cudaFreeAsync(pf, s); cudaFreeAsync(pb, s);
+    return rc;
+}

@@ -1,0 +1,62 @@
+// Launchers of the hand-written kernels (all sm_100a).  Every launcher only enqueues on `stream`.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "conv_op.h"
+
+namespace tmd {
+
+// ---- convolution back ends (conv_simt.cu, conv_umma.cu) ----
+cudaError_t conv_simt_f32(const ConvOp& op, cudaStream_t stream);
+cudaError_t conv_simt_bf16(const ConvOp& op, cudaStream_t stream);
+// tcgen05/TMA implicit GEMM; returns cudaErrorNotSupported when the shape is outside its envelope
+bool conv_umma_supported(const ConvOp& op);
+struct UmmaPlan;  // per-op TMA descriptors + launch geometry, built once
+UmmaPlan* conv_umma_plan_create(const ConvOp& op);
+void conv_umma_plan_destroy(UmmaPlan*);
+cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t stream);
+
+// ---- element-wise / glue (elementwise.cu) ----
+// stem: a[vox][c] = swish(w[c]*v + bias[c]) * sc[b][c], v = x[vox] or pan[b,y,x]-ms[vox]
+// (AdaptionModulateBEST.conv20 + Swish + modulation of conv21; cond = PAN.repeat - MS, :605-609)
+cudaError_t stem_expand(int dtype, const float* x, const float* pan, const float* w, const float* bias, const float* sc,
+                        int ld_sc, void* out, int C, int B, int N, int HW, cudaStream_t s);
+// dst[vox][c] = swish(src[vox][c] + tb[b][c])  for a channel slice (per-step activation of cached tensors)
+cudaError_t slice_activate(int dtype, const void* src, int ld_src, void* dst, int ld_dst, const float* tb, int ld_tb, int C,
+                           int B, size_t vox_per_sample, cudaStream_t s);
+// out[vox] = sum_c w[c]*a[vox][c]   (final.conv24: 1x1x1, Co = 1, no bias)
+cudaError_t project_to_band(int dtype, const void* a, int ld, const float* w, float* out, int C, size_t nvox, cudaStream_t s);
+// T[hi vox][c] = IDWT(0, LH, HL, HH)  channels-last (WaveletUPorDown up branch, :383-386)
+cudaError_t idwt_highbands(int dtype, const void* lh, const void* hl, const void* hh, void* out, int C, size_t planes, int h, int w,
+                           cudaStream_t s);
+// reference-layout Haar transforms [BC][H][W] fp32
+cudaError_t dwt2d_nchw(const float* x, float* ll, float* lh, float* hl, float* hh, int64_t BC, int H, int W, cudaStream_t s);
+cudaError_t idwt2d_nchw(const float* ll, const float* lh, const float* hl, const float* hh, float* out, int64_t BC, int h, int w,
+                        cudaStream_t s);
+// layout converters for the stand-alone conv operator: [B,C,N,H,W] fp32 <-> [B,N,H,W,C] T (optionally x *= s[b][c])
+cudaError_t ncdhw_to_cl(int dtype, const float* x, const float* s, void* out, int B, int C, size_t nhw, cudaStream_t st);
+cudaError_t cl_to_ncdhw(int dtype, const void* x, float* out, int B, int C, size_t nhw, cudaStream_t st);
+
+// ---- conditioning (elementwise.cu) ----
+// t_b = t_input[b] (device) or t_scalar when t_input is null.
+// embed[b] = swish(L2(swish(L1(gamma(t_b)))))  then  table[b][j] = W[j].embed[b] + bias[j]
+// (gamma_embedding :80-97, WavBEST.embed :529, every time-Dense :105/:346)
+cudaError_t time_table(const float* t_input, float t_scalar, const float* freqs, int inter_dim, const float* w1, const float* b1, const float* w2,
+                       const float* b2, const float* Wt, const float* bt, float* embed_out, float* table, int B, int E, int rows,
+                       cudaStream_t s);
+// y[r][j] = act(W[j].x[r] + b[j])  small dense layer (rows r), act: 0 none, 1 swish
+cudaError_t dense_rows(const float* x, const float* W, const float* b, float* y, int rows, int in_dim, int out_dim, int act,
+                       cudaStream_t s);
+cudaError_t gather_rows(const float* table, const int* ids, float* out, int B, int width, cudaStream_t s);
+
+// ---- solver (solver.cu) ----
+// eps = (x - a*out)/s ; x0 = (x - s*eps)/a ; dynamic threshold (quantile 0.995, max 1) -> dst
+cudaError_t x0_threshold(const float* x, const float* out, float* dst, float alpha, float sigma, int B, int n, int q_lo,
+                         float q_w, float max_val, cudaStream_t s);
+cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s);
+cudaError_t solver_update(float* dst, const float* x, const float* m, const float* m1, float c1, float c2, float c3, size_t n,
+                          cudaStream_t s);
+
+}  // namespace tmd

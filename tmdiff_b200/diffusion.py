@@ -1,0 +1,118 @@
+"""`GeneralDiffusion` sampling surface (GeneralModel/diffusion_general.py:66-339) over the CUDA path.
+
+Sampling methods only; the training loss (`p_losses_dynamic`, :349-370) needs a backward pass and
+is out of scope for this hot path.
+"""
+import math
+
+import numpy as np
+import torch
+from torch import nn
+
+from .dpm_solver import DPM_Solver, NoiseScheduleVP, model_wrapper
+
+
+def make_beta_schedule(schedule, n_timestep):
+    """:29-63 (float64 numpy, clipped at 0.999 for the cosine schedule)."""
+    if schedule == "linear":
+        scale = 1000 / n_timestep
+        return np.linspace(scale * 1e-6, scale * 1e-2, n_timestep, dtype=np.float64)
+    if schedule == "cosine":
+        bar = lambda t: math.cos((t + 0.008) / 1.008 * math.pi / 2) ** 2
+        return np.array([min(1 - bar((i + 1) / n_timestep) / bar(i / n_timestep), 0.999) for i in range(n_timestep)])
+    raise NotImplementedError(schedule)
+
+
+def res2img(img_, img_lr_up):
+    """utils/util.py:135-137"""
+    return img_ + img_lr_up
+
+
+class GeneralDiffusion(nn.Module):
+    def __init__(self, denoise_fn, loss_type="l1"):
+        super().__init__()
+        self.denoise_fn = denoise_fn
+        self.loss_type = loss_type
+
+    def set_loss(self, device):
+        pass  # training only
+
+    def set_new_noise_schedule(self, schedule_opt, device):
+        """:86-132 -- only the buffers the sampling methods read."""
+        betas = make_beta_schedule(schedule_opt["schedule"], schedule_opt["n_timestep"])
+        to_torch = lambda a: torch.tensor(a, dtype=torch.float32, device=device)
+        alphas = 1.0 - betas
+        ac = np.cumprod(alphas, axis=0)
+        ac_prev = np.append(1.0, ac[:-1])
+        self.sqrt_alphas_cumprod_prev = np.sqrt(np.append(1.0, ac))
+        self.num_timesteps = int(betas.shape[0])
+        self.register_buffer("betas", to_torch(betas))
+        self.register_buffer("alphas_cumprod", to_torch(ac))
+        self.register_buffer("sqrt_recip_alphas_cumprod_1", to_torch(np.sqrt(1.0 / ac)))
+        self.register_buffer("sqrt_recipm1_alphas_cumprod_1", to_torch(np.sqrt(1.0 / ac - 1)))
+        pv = betas * (1.0 - ac_prev) / (1.0 - ac)
+        self.register_buffer("posterior_variance", to_torch(pv))
+        self.register_buffer("posterior_log_variance_clipped", to_torch(np.log(np.maximum(pv, 1e-20))))
+        self.register_buffer("posterior_mean_coef1", to_torch(betas * np.sqrt(ac_prev) / (1.0 - ac)))
+        self.register_buffer("posterior_mean_coef2", to_torch((1.0 - ac_prev) * np.sqrt(alphas) / (1.0 - ac)))
+
+    # ---- ancestral DDPM step (:155-225): one denoiser call + element-wise torch ops -------------
+    def predict_start_from_noise(self, x_t, t, noise):                     # :376-378
+        return self.sqrt_recip_alphas_cumprod_1[t] * x_t - self.sqrt_recipm1_alphas_cumprod_1[t] * noise
+
+    def q_posterior(self, x_start, x_t, t):                                # :134-138
+        mean = self.posterior_mean_coef1[t] * x_start + self.posterior_mean_coef2[t] * x_t
+        return mean, self.posterior_log_variance_clipped[t]
+
+    @torch.no_grad()
+    def p_mean_variance(self, x, t, clip_denoised=True, x_in=None, prompt="QB", guidance=1.0):
+        B = x.shape[0]
+        time_in = torch.full((B, 1), t + 1, device=x.device)
+        # the reference treats the network output as eps here (:163-164)
+        x_recon = self.predict_start_from_noise(x, t=t, noise=self.denoise_fn(x, time_in, x_in["PAN"], x_in["MS"], prompt))
+        if clip_denoised:
+            x_recon = x_recon.clamp(-1.0, 1.0)
+        return self.q_posterior(x_start=x_recon, x_t=x, t=t)
+
+    @torch.no_grad()
+    def p_sample(self, x, t, clip_denoised=True, condition_x=None, prompt="QB", guidance=1.0):
+        mean, log_var = self.p_mean_variance(x=x, t=t, clip_denoised=clip_denoised, x_in=condition_x, prompt=prompt,
+                                             guidance=guidance)
+        noise = torch.randn_like(x) if t > 0 else torch.zeros_like(x)
+        return mean + noise * (0.5 * log_var).exp()
+
+    @torch.no_grad()
+    def p_sample_loop(self, x_in, continous=False, prompt="QB", guidance=1.0):
+        device = self.betas.device
+        sample_inter = 1 | (self.num_timesteps // 10)
+        img = torch.randn(x_in["Res"].shape, device=device)
+        ret = res2img(img, x_in["MS"])
+        for i in reversed(range(self.num_timesteps)):
+            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, guidance=guidance)
+            if i % sample_inter == 0:
+                ret = torch.cat([ret, res2img(img, x_in["MS"])], dim=0)
+        return ret if continous else ret[-1]
+
+    @torch.no_grad()
+    def super_resolution(self, x_in, continous, prompt, guidance):
+        return self.p_sample_loop(x_in, prompt)    # sic: the reference passes prompt into `continous` (:338-339)
+
+    # ---- DPM-Solver++ (:227-255), the hot path --------------------------------------------------
+    @torch.no_grad()
+    def sample_by_dpmsolver(self, x_in, prompt, steps=30, x_T=None, return_trace=False):
+        """steps defaults to the reference's hard-coded 30; BASELINE configs use 10 / 20."""
+        device = self.betas.device
+        if x_T is None:
+            x_T = torch.randn(x_in["Res"].shape, device=device)
+        ns = NoiseScheduleVP(schedule="discrete", betas=self.betas)
+        fn = model_wrapper(self.denoise_fn, ns, model_type="x_start",
+                           model_kwargs={"PAN": x_in["PAN"], "MS": x_in["MS"], "prompt": prompt})
+        solver = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+        res = solver.sample(x_T, steps=steps, order=3, skip_type="logSNR", method="singlestep", denoise_to_zero=True,
+                            return_trace=return_trace)
+        if return_trace:
+            return res2img(res[0], x_in["MS"]), res[1]
+        return res2img(res, x_in["MS"])
+
+    def forward(self, x, *args, **kwargs):
+        raise NotImplementedError("training loss (p_losses_dynamic) is outside the sampling hot path")

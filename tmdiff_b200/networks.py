@@ -1,0 +1,264 @@
+"""Drop-in `WavBEST` denoiser module backed by the CUDA library.
+
+Mirrors GeneralModel/Hyper_unet_general.py:523-636 (constructor, `forward(x_t, t_input, PAN, MS,
+prompt)`, `get_embeding`, the five `*_embeding` attributes) and the 272-tensor state-dict layout,
+so `GeneralDiffusion(denoise_fn=WavBEST(...))`, `model_wrapper(model, ...)` and
+`load_state_dict(torch.load("I*_gen.pth"), strict=False)` work as with the reference module
+(GeneralModel/networks.py:80-92, GeneralModel/model.py:122-134).  Forward only (sampling path).
+"""
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+SENSORS = ("QB", "WV3", "GF2", "WV2", "WV4")
+
+
+# ----------------------------------------------------------------------------------------------
+# parameter inventory, in the reference's naming (Hyper_unet_general.py:158-273, :334-367, :523-556)
+# ----------------------------------------------------------------------------------------------
+def _inventory(channels, E, inter_dim):
+    c = list(channels)
+    out = []
+
+    def conv(n, co, ci, k):
+        out.append((n + ".weight", (co, ci, k, k, k)))
+        out.append((n + ".bias", (co,)))
+
+    def lin(n, co, ci):
+        out.append((n + ".weight", (co, ci)))
+        out.append((n + ".bias", (co,)))
+
+    def resblock(p, ci, co):
+        conv(p + ".conv20", co, ci, 3)
+        conv(p + ".conv21", co, co, 3)
+        lin(p + ".dense1.dense", ci, E)
+        lin(p + ".dense2.dense", co, E)
+        if ci != co:
+            conv(p + ".res_conv", co, ci, 1)
+
+    def wavelet(p, ch, hi=None):
+        conv(p + ".Conv_0", ch, ch, 3)
+        lin(p + ".Dense_0", ch, E)
+        conv(p + ".Conv_1", ch, ch, 3)
+        conv(p + ".Conv_2", ch, ch, 1)
+        if hi is not None:
+            out.append((p + ".convH_0.0.weight", (3 * ch, hi, 3, 3, 3)))
+            out.append((p + ".convH_0.0.bias", (3 * ch,)))
+        lin(p + ".dense1.dense", ch, E)
+        lin(p + ".dense2.dense", ch, E)
+
+    lin("embed.0", E, inter_dim)
+    lin("embed.2", E, E)
+    lin("embed2.0", 4 * E, 768)
+    lin("embed2.2", 4 * E, 4 * E)
+    lin("embed2.4", E, 4 * E)
+    for s in ("conv1", "conv2"):
+        conv(s + ".conv20", c[0], 1, 1)
+        conv(s + ".conv21", c[0], c[0], 3)
+        lin(s + ".dense2.dense", c[0], E)
+    for i, n in enumerate(("down1", "down2", "down3", "down1_1", "down2_1", "down3_1")):
+        lvl = i % 3
+        resblock(n + ".conv20", c[lvl], c[lvl + 1])
+        wavelet(n + ".down", c[lvl + 1])
+    resblock("middle1", c[3], c[3])
+    for i, n in enumerate(("up1", "up2", "up3")):
+        ci, co = c[3 - i], c[2 - i]
+        wavelet(n + ".up1", co, hi=ci)
+        resblock(n + ".conv20", 3 * ci, co)
+    for i in range(4):
+        resblock("final.conv2%d" % i, 3 * c[0] if i == 0 else c[0], c[0])
+    conv("final.conv24", 1, c[0], 1)
+    lin("final.dense2.dense", c[0], E)
+    return out
+
+
+class _Node(nn.Module):
+    """Structure-only container: gives parameters their dotted reference names."""
+
+
+def _register(root, dotted, param):
+    *path, leaf = dotted.split(".")
+    m = root
+    for p in path:
+        if not hasattr(m, p):
+            m.add_module(p, _Node())
+        m = getattr(m, p)
+    m.register_parameter(leaf, param)
+
+
+class WavBEST(nn.Module):
+    """`WavBEST(channels=None, embed_dim=128, inter_dim=32)` -- same positional signature as the
+    reference.  Extra keyword-only arguments select the arithmetic mode and supply the cached CLIP
+    text embeddings (the reference builds them with a FrozenCLIPEmbedder at construction,
+    :561-572; here they are inputs: `text_embeddings={"QB": [1,768] tensor, ...}` or
+    `set_text_embedding`)."""
+
+    def __init__(self, channels=None, embed_dim=128, inter_dim=32, *, dtype="fp32", text_embeddings=None,
+                 max_batch=None):
+        super().__init__()
+        if channels is None:
+            channels = [16, 32, 64, 128]                      # :526-527
+        if dtype not in ("fp32", "bf16"):
+            raise ValueError("dtype must be 'fp32' or 'bf16'")
+        self.channels = [int(v) for v in channels]
+        self.embed_dim, self.inter_dim = int(embed_dim), int(inter_dim)
+        self.compute_dtype = dtype
+        self.max_batch = max_batch
+        self._names = []
+        for name, shape in _inventory(self.channels, self.embed_dim, self.inter_dim):
+            p = nn.Parameter(torch.empty(shape), requires_grad=False)
+            if len(shape) >= 2:   # nn.Conv3d / nn.Linear default init family (kaiming_uniform, a=sqrt(5))
+                fan_in = int(torch.tensor(shape[1:]).prod())
+                bound = 1.0 / math.sqrt(fan_in)
+                nn.init.uniform_(p, -bound, bound)
+            else:
+                nn.init.zeros_(p)
+            _register(self, name, p)
+            self._names.append(name)
+        for s in SENSORS:
+            setattr(self, s.lower() + "_embeding", None)
+        if text_embeddings:
+            for k, v in text_embeddings.items():
+                self.set_text_embedding(k, v)
+        self._handle = None
+        self._handle_key = None
+        self._weights_key = None
+        self._text_key = None
+        self._cond_key = None
+        self._cond_keepalive = None
+
+    # ---- reference surface ---------------------------------------------------------------
+    def get_embeding(self, prompt):                            # :587-598
+        return getattr(self, prompt.lower() + "_embeding", None) if prompt in SENSORS else None
+
+    def set_text_embedding(self, prompt, emb):
+        if prompt not in SENSORS:
+            raise ValueError("unknown sensor prompt %r (expected one of %s)" % (prompt, SENSORS))
+        emb = torch.as_tensor(emb, dtype=torch.float32).reshape(1, 768).detach().cpu().clone()
+        setattr(self, prompt.lower() + "_embeding", emb)
+        self._text_key = None
+
+    def encode_prompt(self, clip_text_model, get_prompt):      # :566-572
+        """Fill the five cached embeddings from a reference `FrozenCLIPEmbedder` and its prompt texts."""
+        for s in SENSORS:
+            self.set_text_embedding(s, clip_text_model.encode(get_prompt(s)))
+
+    # ---- engine management ---------------------------------------------------------------
+    def _lib(self):
+        return _lib.load()
+
+    def _ensure_engine(self, B, N, H, W, device):
+        if not torch.cuda.is_available():
+            raise RuntimeError("tmdiff_b200.WavBEST needs a CUDA device; there is no CPU or PyTorch fallback")
+        lib = self._lib()
+        key = self._handle_key
+        need = (key is None or key[0] < B or key[1] < N or key[2] * key[3] < H * W or key[4] != self.compute_dtype
+                or key[5] != device.index)
+        if need:
+            self.release()
+            mb = max(B, self.max_batch or 0)
+            cfg = _lib.Config((C.c_int32 * 4)(*self.channels), self.embed_dim, self.inter_dim, mb, N, H, W,
+                              _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16)
+            h = C.c_void_p()
+            with torch.cuda.device(device):
+                _lib.check(lib.tmd_create(C.byref(cfg), C.byref(h)))
+            self._handle = h
+            self._handle_key = (mb, N, H, W, self.compute_dtype, device.index)
+            self._weights_key = self._text_key = self._cond_key = None
+        wkey = tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if wkey != self._weights_key:
+            for name in self._names:
+                t = self.get_parameter(name).detach().float().cpu().contiguous()
+                shp = (C.c_int64 * t.dim())(*t.shape)
+                _lib.check(lib.tmd_load_weight(self._handle, name.encode(), _lib.ptr(t), shp, t.dim()))
+            half = self.inter_dim // 2
+            # exactly the reference's expression so the fp32 frequencies are bit-identical (:90-92)
+            freqs = torch.exp(-math.log(10000) * torch.arange(start=0, end=half, dtype=torch.float32) / half).contiguous()
+            _lib.check(lib.tmd_set_time_frequencies(self._handle, _lib.ptr(freqs), half))
+            with torch.cuda.device(device):
+                _lib.check(lib.tmd_finalize_weights(self._handle))
+            self._weights_key = wkey
+            self._text_key = self._cond_key = None
+        tkey = tuple(id(getattr(self, s.lower() + "_embeding")) for s in SENSORS)
+        if tkey != self._text_key:
+            for s in SENSORS:
+                e = getattr(self, s.lower() + "_embeding")
+                if e is not None:
+                    e = e.detach().float().cpu().contiguous()
+                    _lib.check(lib.tmd_set_text_embedding(self._handle, _lib.SENSOR_IDS[s], _lib.ptr(e)))
+            self._text_key = tkey
+            self._cond_key = None
+        return self._handle
+
+    def release(self):
+        if getattr(self, "_handle", None) is not None:
+            self._lib().tmd_destroy(self._handle)
+            self._handle = None
+            self._handle_key = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+    def bind_condition(self, PAN, MS, prompt):
+        """Run the step-invariant half of the network (condition branch + high-frequency convs) for
+        this (PAN, MS, prompt) unless it is already cached.  `prompt` is one sensor name (reference
+        semantics) or a sequence of B names (mixed-sensor batch with equal band counts)."""
+        if not (PAN.is_cuda and MS.is_cuda):
+            raise RuntimeError("PAN/MS must be CUDA tensors (no CPU path)")
+        B, N, H, W = MS.shape
+        if PAN.shape != (B, 1, H, W):
+            raise ValueError("PAN must be [B,1,H,W] matching MS [B,N,H,W]")
+        prompts = [prompt] * B if isinstance(prompt, str) else list(prompt)
+        if len(prompts) != B:
+            raise ValueError("need one prompt or one per patch")
+        for p in set(prompts):
+            if self.get_embeding(p) is None:
+                raise ValueError("no text embedding for prompt %r" % (p,))   # reference: .repeat on None raises
+        h = self._ensure_engine(B, N, H, W, MS.device)
+        key = (PAN.data_ptr(), PAN._version, MS.data_ptr(), MS._version, tuple(prompts), B, N, H, W)
+        if key != self._cond_key:
+            pan, ms = PAN.contiguous().float(), MS.contiguous().float()
+            ids = (C.c_int32 * B)(*[_lib.SENSOR_IDS[p] for p in prompts])
+            with torch.cuda.device(MS.device):
+                _lib.check(self._lib().tmd_precompute_condition(h, _lib.ptr(pan), _lib.ptr(ms), ids, B, N, H, W,
+                                                                _lib.stream_ptr()))
+            self._cond_key = key
+            self._cond_keepalive = (pan, ms)
+        return h
+
+    @torch.no_grad()
+    def forward(self, x_t, t_input, PAN=None, MS=None, prompt=None):
+        """:600-636.  x_t [B,N,H,W]; t_input [B] or [B,1] (float from DPM-Solver, int from p_sample)."""
+        if PAN is None or MS is None or prompt is None:
+            raise ValueError("PAN, MS and prompt are required")      # the reference dereferences all three
+        h = self.bind_condition(PAN, MS, prompt)
+        x = x_t.contiguous().float()
+        B = x.shape[0]
+        if x.shape != MS.shape:
+            raise ValueError("x_t must have the shape of MS")
+        t = t_input.reshape(-1).to(device=x.device, dtype=torch.float32).contiguous()
+        if t.numel() != B:
+            raise ValueError("t_input must have one entry per patch")
+        out = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(self._lib().tmd_denoise(h, _lib.ptr(x), _lib.ptr(t), _lib.ptr(out), _lib.stream_ptr()))
+        return out.to(x_t.dtype)
+
+    def launch_count(self):
+        return int(self._lib().tmd_launch_count(self._handle)) if self._handle is not None else 0
+
+
+def define_General(opt, text_embeddings=None, dtype="fp32"):
+    """networks.define_General (GeneralModel/networks.py:80-92): WavBEST + GeneralDiffusion from the
+    reference's option dict.  DataParallel is not used: multi-GPU runs one process per GPU."""
+    from .diffusion import GeneralDiffusion
+    model_opt = opt["model"]
+    model = WavBEST(channels=model_opt["unet"]["channel_multiplier"], dtype=dtype, text_embeddings=text_embeddings)
+    return GeneralDiffusion(model, loss_type=model_opt.get("loss_type", "l1") if hasattr(model_opt, "get") else "l1")
