@@ -1,0 +1,319 @@
+#!/usr/bin/env python
+"""Headline benchmark of the TMDiff sampling hot path on B200 (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one pass of the hot path over one batch of synthetic patches: the step-invariant
+condition branch once, then the whole DPM-Solver++ trajectory (20 solver steps = 21 network
+evaluations, order 3, logSNR spacing, dynamic thresholding, denoise_to_zero), then res2img.
+The workload at every N is BASELINE config 2 per GPU: 64 four-band 64x64 patches, bf16
+(weak scaling; N=8 is config 3's 512 patches).  N>1 is launched by torchrun, one rank per GPU;
+patches are independent, so the only collective is the final all-gather of output tiles.
+
+One JSON line on stdout (rank 0):
+  value      patches/s with PAN/MS/x_T already resident in HBM
+  e2e        the same through GeneralDiffusion.sample_by_dpmsolver with HOST (pinned) buffers:
+             H2D of PAN/MS/x_T and D2H of the fused image inside the timed region
+  roofline   the dominant kernel family (3x3x3 implicit-GEMM conv): algorithmic FLOPs of the
+             launches / their summed CUDA-event time, against the measured bf16 peak
+  cpu_baseline  the oracle's faithful restatement of the reference (torch fp32 on the host
+             cores) timed on one patch of the same workload
+`--impl reference` times that CPU path alone (rank 0 only), one patch per step.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CHANNELS = (32, 64, 128, 256)          # config/general_finetune.json:63-66
+METRIC = "patches/s (64x64 PAN patches through the full DPM-Solver++ trajectory)"
+# conv FLOPs per 4-band 64x64 denoiser evaluation (2*MACs), split into the part
+# that depends on (x_t, t) and the step-invariant part (condition branch + convH_0)
+GFLOP_VARIANT_PER_BAND = 50.71 / 4
+GFLOP_INVARIANT_PER_BAND = 35.49 / 4
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="patches per GPU per step")
+    ap.add_argument("--bands", type=int, default=4)
+    ap.add_argument("--patch", type=int, default=64)
+    ap.add_argument("--solver-steps", type=int, default=20)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--sensor", default="QB")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0)
+    return ap.parse_args()
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region
+# ------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every 100 ms through NVML (the same
+    counters as the profiling recipe's nvidia-smi line)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self._stop_evt, self.max_mhz = index, [], set(), threading.Event(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                 "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.1)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(2.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's faithful restatement of the reference, on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_sample_seconds(bands, patch, solver_steps, sensor, threads):
+    """Seconds for ONE patch through the reference algorithm on the CPU (B=1, as the reference's
+    loaders run it, data/__init__.py:18-19)."""
+    import torch
+    from oracle import dpm_ref, wavbest_ref
+    from oracle.inputs import make_inputs
+    torch.set_num_threads(threads)
+    sd, emb = wavbest_ref.seeded_weights(CHANNELS), wavbest_ref.seeded_text_embeddings()
+    pan, ms, x_T = make_inputs(1, bands, patch, patch)
+    ns = dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000))
+    net = lambda x, t: wavbest_ref.wavbest_forward(sd, x, t, pan, ms, emb[sensor], faithful=True)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        out = dpm_ref.Sampler(net, ns).sample(x_T, steps=solver_steps, order=3) + ms
+    dt = time.perf_counter() - t0
+    assert bool(torch.isfinite(out).all())
+    return dt
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU implementation of the path (the oracle port -- the
+    reference is Python and /root/reference does not exist on the GPU box), all host threads,
+    one patch of the workload per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    threads = args.cpu_threads or os.cpu_count()
+    for _ in range(args.warmup):
+        cpu_sample_seconds(args.bands, args.patch, max(1, args.solver_steps // 10), args.sensor, threads)  # short warm-up passes
+    times = [cpu_sample_seconds(args.bands, args.patch, args.solver_steps, args.sensor, threads) for _ in range(args.steps)]
+    total = sum(times)
+    v = args.steps / total
+    sample = "1 patch (%d-band %dx%d, %d solver steps = %d NFE) per step, B=1 as the reference runs it" % (
+        args.bands, args.patch, args.patch, args.solver_steps, args.solver_steps + 1)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "patches/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "fp32", "data": "synthetic (seeded PAN/MS/x_T, seeded weights and text embeddings)",
+        "config": workload_config(args, per_step_patches=1),
+        "cpu_baseline": {"value": v, "unit": "patches/s", "cores": threads, "kind": "port", "sample": sample,
+                         "torch_threads": torch.get_num_threads()},
+        "e2e": {"value": v, "unit": "patches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(args, per_step_patches):
+    return {"workload": "BASELINE config 2: %d-band %dx%d patches, batch %d per GPU, %d DPM-Solver++ steps (%d NFE), %s"
+                        % (args.bands, args.patch, args.patch, args.batch, args.solver_steps, args.solver_steps + 1, args.dtype),
+            "patches_per_step_per_gpu": per_step_patches, "bands": args.bands, "patch": args.patch,
+            "solver": "dpmsolver++ singlestep order 3, logSNR, dynamic thresholding 0.995, denoise_to_zero",
+            "solver_steps": args.solver_steps, "channels": list(CHANNELS), "sensor_prompt": args.sensor,
+            "l2": "no flush: each step streams >2 GB of activations per GPU (L2 is 126 MB) and every step re-reads its inputs from HBM",
+            "parallelism": "patches sharded across GPUs, one all-gather of output tiles per step"}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from oracle import wavbest_ref                       # seeded weights/embeddings only (inputs, not compute)
+    from oracle.inputs import make_inputs
+    from tmdiff_b200 import GeneralDiffusion, WavBEST
+    from tmdiff_b200.parallel import gather_tiles
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; tmdiff_b200 has no CPU path (use --impl reference for the CPU arm)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    B, N, P = args.batch, args.bands, args.patch
+    model = WavBEST(channels=list(CHANNELS), dtype=args.dtype, text_embeddings=wavbest_ref.seeded_text_embeddings(),
+                    max_batch=B)
+    model.load_state_dict(wavbest_ref.seeded_weights(CHANNELS), strict=True)
+    model = model.to(dev)
+    G = GeneralDiffusion(model)
+    G.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 1000}, dev)
+
+    pan_h, ms_h, xT_h = [t.pin_memory() for t in make_inputs(B, N, P, P, seed=3407 + rank)]
+    out_h = torch.empty_like(ms_h).pin_memory()
+    pan_d, ms_d, xT_d = pan_h.to(dev), ms_h.to(dev), xT_h.to(dev)
+    total = world * B
+
+    def step_resident():
+        model.reset_condition_cache()                    # a new batch of patches every step: nothing carried over
+        img = G.sample_by_dpmsolver({"PAN": pan_d, "MS": ms_d, "Res": xT_d}, args.sensor, steps=args.solver_steps, x_T=xT_d)
+        return gather_tiles(img, total) if world > 1 else img
+
+    def step_e2e():
+        pan, ms, xT = pan_h.to(dev, non_blocking=True), ms_h.to(dev, non_blocking=True), xT_h.to(dev, non_blocking=True)
+        model.reset_condition_cache()
+        img = G.sample_by_dpmsolver({"PAN": pan, "MS": ms, "Res": xT}, args.sensor, steps=args.solver_steps, x_T=xT)
+        out_h.copy_(img, non_blocking=True)              # this rank's fused tiles back to the host
+        if world > 1:
+            gather_tiles(img, total)
+        torch.cuda.current_stream().synchronize()        # the caller holds the host result before the next batch
+
+    def timed(fn, k):
+        """k steps bracketed by barrier + synchronize; device time from CUDA events, max over ranks."""
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = model.launch_count()
+    t_ms = timed(step_resident, args.steps)
+    launches = model.launch_count() - l0
+    clocks = sampler.finish()
+
+    step_e2e()
+    e2e_ms = timed(step_e2e, args.steps)
+
+    # per-kernel-kind device time: the same step again with every launch bracketed by CUDA events on
+    # the launching stream (kept out of the timed regions above so the event records cost them nothing)
+    prof = None
+    if rank == 0:
+        model.profile_begin()
+        step_resident()
+        prof = model.profile_end()
+    if world > 1:
+        dist.barrier()
+
+    if rank == 0:
+        peaks = measured_peaks()
+        value = total * args.steps / (t_ms * 1e-3)
+        e2e = total * args.steps / (e2e_ms * 1e-3)
+        c3 = prof["conv3x3x3"]
+        ach = c3["flops"] / (c3["ms"] * 1e-3) / 1e12 if c3["ms"] > 0 else 0.0
+        prof_total = sum(k["ms"] for k in prof.values())
+        peak = peaks["bf16_tflops_sustained"]
+        gflop_patch = N * (GFLOP_INVARIANT_PER_BAND + (args.solver_steps + 1) * GFLOP_VARIANT_PER_BAND)
+        line = {
+            "metric": METRIC, "value": value, "unit": "patches/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic (seeded PAN/MS/x_T, seeded weights and text embeddings)",
+            "config": workload_config(args, B),
+            "e2e": {"value": e2e, "unit": "patches/s", "h2d_bytes_per_step": int(world * (pan_h.numel() + ms_h.numel() + xT_h.numel()) * 4),
+                    "d2h_bytes_per_step": int(world * out_h.numel() * 4), "ms_per_step": e2e_ms / args.steps,
+                    "api": "tmdiff_b200.GeneralDiffusion.sample_by_dpmsolver on pinned host tensors"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"kernel": "conv3d 3x3x3 implicit GEMM (all %d launches of one step)" % c3["launches"],
+                         "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                         "traffic": None, "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peaks["source"],
+                         "share_of_step": c3["ms"] / prof_total if prof_total else None,
+                         "how": "CUDA events around every launch on the launching stream, one extra step after the timed region"},
+            "end_to_end_tensor_frac": value / world * gflop_patch * 1e9 / (peak * 1e12),
+            "kernel_kinds": {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
+                                 "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 2) if v["ms"] > 0 else 0.0,
+                                 "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1) if v["ms"] > 0 else 0.0}
+                             for k, v in prof.items()},
+        }
+        if not args.no_cpu_baseline:
+            threads = args.cpu_threads or os.cpu_count()
+            sec = cpu_sample_seconds(N, P, args.solver_steps, args.sensor, threads)
+            line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "patches/s", "cores": threads, "kind": "port",
+                                    "sample": "1 patch of the workload (%d-band %dx%d, %d NFE), B=1, oracle faithful=True, %.1f s"
+                                              % (N, P, P, args.solver_steps + 1, sec)}
+        print(json.dumps(line))
+        sys.stdout.flush()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -130,6 +130,23 @@ int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);
 
+/* ---- measurement (no reference counterpart: the reference only prints time.time() deltas,
+ * general_sharpening_joint_random_batch_finetune.py:131,146-147) -------------------------------
+ * Between tmd_profile_begin and tmd_profile_end every kernel this handle launches is bracketed by
+ * a CUDA event pair on the launching stream.  tmd_profile_end synchronises the device and returns,
+ * per kernel kind, the summed device time and the ALGORITHMIC flops / bytes of those launches
+ * (2*MACs; each operand and result tensor counted once) -- the numerator of bench.py's roofline. */
+enum { TMD_K_CONV3 = 0,        /* 3x3x3 implicit-GEMM convolutions (tensor-bound)                 */
+       TMD_K_CONV1 = 1,        /* 1x1x1 convolutions (HBM-bound)                                  */
+       TMD_K_ELEMENTWISE = 2,  /* stems, Haar synthesis of cached bands, slice activations, 32->1 */
+       TMD_K_SOLVER = 3,       /* x0 conversion + dynamic threshold, dpmsolver++ updates          */
+       TMD_K_COND = 4,         /* time-embedding MLP + per-layer bias table                       */
+       TMD_NUM_KINDS = 5 };
+typedef struct { double ms, flops, bytes; int64_t launches; } tmd_profile_kind;
+typedef struct { tmd_profile_kind kind[TMD_NUM_KINDS]; } tmd_profile;
+int tmd_profile_begin(tmd_handle h);
+int tmd_profile_end(tmd_handle h, tmd_profile* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,7 +69,7 @@ CONV_CASES = [
 
 
 @pytest.mark.parametrize("case", CONV_CASES)
-@pytest.mark.parametrize("dtype,tol", [("fp32", 5e-6), ("bf16", 1e-2)]  # fp32: summation-order noise over K <= 27*768 terms)
+@pytest.mark.parametrize("dtype,tol", [("fp32", 5e-6), ("bf16", 1e-2)])  # fp32: summation-order noise over K <= 27*768 terms
 def test_modulated_conv3d(ops, case, dtype, tol):
     B, Ci, Co, N, H, W, k = case
     g = torch.Generator().manual_seed(11)

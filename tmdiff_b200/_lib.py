@@ -36,6 +36,17 @@ class Plan(C.Structure):
                 ("q_weight", C.c_float), ("q_lo", C.c_int32), ("max_val", C.c_float)]
 
 
+KIND_NAMES = ("conv3x3x3", "conv1x1x1", "elementwise", "solver", "conditioning")
+
+
+class ProfileKind(C.Structure):
+    _fields_ = [("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double), ("launches", C.c_int64)]
+
+
+class Profile(C.Structure):
+    _fields_ = [("kind", ProfileKind * len(KIND_NAMES))]
+
+
 # name -> (restype, argtypes); every symbol declared in include/tmdiff_b200.h
 _P = C.c_void_p
 SIGNATURES = {
@@ -56,6 +67,8 @@ SIGNATURES = {
     "tmd_conv3d_mod": (C.c_int, [_P, _P, _P, _P, _P] + [C.c_int32] * 8 + [_P]),
     "tmd_dynamic_threshold": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, _P]),
     "tmd_launch_count": (C.c_int64, [_P]),
+    "tmd_profile_begin": (C.c_int, [_P]),
+    "tmd_profile_end": (C.c_int, [_P, C.POINTER(Profile)]),
 }
 
 _lib = None

@@ -59,7 +59,18 @@ struct HostTensor {
     std::vector<int64_t> shape;
 };
 
-using Launch = std::function<cudaError_t(cudaStream_t)>;
+struct ProfSpan {
+    cudaEvent_t a, b;
+    int kind;
+    double flops, bytes;
+};
+using LaunchFn = std::function<cudaError_t(cudaStream_t)>;
+struct Launch {       // one kernel launch of the plan + what it costs algorithmically (bench.py's roofline)
+    LaunchFn fn;
+    int kind = TMD_K_ELEMENTWISE;
+    double flops = 0.0, bytes = 0.0;
+    cudaError_t operator()(cudaStream_t s) const { return fn(s); }
+};
 
 }  // namespace
 
@@ -103,6 +114,9 @@ struct tmd_engine {
     float* slots[TMD_NUM_SLOTS] = {};
     float* d_out = nullptr;
     int64_t launches = 0;
+    bool profiling = false;
+    std::vector<ProfSpan> prof_events;
+    size_t prof_used = 0;
 
     template <typename T> int dmalloc(T** p, size_t n) {
         CK(cudaMalloc((void**)p, n * sizeof(T)));
@@ -223,6 +237,7 @@ extern "C" int tmd_destroy(tmd_handle h) {
     if (!h) return 0;
     for (auto* p : h->plans) conv_umma_plan_destroy(p);
     for (void* p : h->allocs) cudaFree(p);
+    for (auto& sp : h->prof_events) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     if (h->arena) cudaFree(h->arena);
     delete h;
     return 0;
@@ -396,6 +411,11 @@ struct Planner {
     const char* err = nullptr;
 
     size_t vox(int lvl) const { return (size_t)B * N * (H >> lvl) * (W >> lvl); }
+    void push(int kind, double flops, double bytes, LaunchFn fn) {
+        Launch l;
+        l.fn = std::move(fn); l.kind = kind; l.flops = flops; l.bytes = bytes;
+        ops->push_back(std::move(l));
+    }
 
     View buf(const std::string& name, int lvl, int C) {
         auto it = e->bufs.find(name);
@@ -443,15 +463,25 @@ struct Planner {
         }
         ep.ld_tb = e->time_rows; ep.ld_sc = e->text_rows;
         if (hf) { for (int i = 0; i < 3; ++i) ep.hf_out[i] = hf[i].p; ep.ld_hf = hf[0].ld; }
+        // algorithmic cost of this launch: 2*MACs; every operand/result tensor touched once
+        const double nv = (double)vox(lvl);
+        const double flops = 2.0 * nv * cw.Ci * cw.taps * cw.Co;
+        const double ovox = mode == CONV_POOL ? nv / 4 : (mode == CONV_UPSAMPLE ? nv * 4 : nv);
+        int n_out = (out.raw.p ? 1 : 0) + (out.act[0].dst.p ? 1 : 0) + (out.act[1].dst.p ? 1 : 0);
+        double bytes = nv * cw.Ci * e->esize + ovox * cw.Co * e->esize * n_out + (double)cw.Ci * cw.taps * cw.Co * e->esize;
+        if (add0.p) bytes += ovox * cw.Co * e->esize;
+        if (add1.p) bytes += ovox / 4 * cw.Co * e->esize;
+        if (hf) bytes += 3 * ovox * cw.Co * e->esize;
+        const int kind = cw.taps == 27 ? TMD_K_CONV3 : TMD_K_CONV1;
         if (e->dtype == TMD_F32) {
-            ops->push_back([op](cudaStream_t s) { return conv_simt_f32(op, s); });
+            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); });
         } else if (conv_umma_supported(op)) {
             UmmaPlan* plan = conv_umma_plan_create(op);
             if (!plan) { err = "tensor map creation failed"; return; }
             e->plans.push_back(plan);
-            ops->push_back([op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); });
+            push(kind, flops, bytes, [op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); });
         } else {
-            ops->push_back([op](cudaStream_t s) { return conv_simt_bf16(op, s); });
+            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_bf16(op, s); });
         }
     }
 
@@ -549,7 +579,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     {
         View a_stem = P.buf("a_stem", 0, c[0]);
         const float* scs = P.sc("conv1.dense2");
-        P.ops->push_back([=](cudaStream_t s) {
+        P.push(TMD_K_ELEMENTWISE, 0, (double)P.vox(0) * (4 + c[0] * e->esize), [=](cudaStream_t s) {
             return stem_expand(dt, e->cur_ms, e->cur_pan, e->d_stem_w[0], e->d_stem_b[0], scs, sr, a_stem.p, c[0], B, N, HW, s);
         });
         View in_act = P.buf("in_act@0", 0, c[0]);
@@ -588,7 +618,9 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             View T = Tup[l];
             const size_t planes = (size_t)B * N;
             const int hh = H >> (l + 1), ww = W >> (l + 1), C = c[l];
-            P.ops->push_back([=](cudaStream_t s) { return idwt_highbands(dt, hq[0].p, hq[1].p, hq[2].p, T.p, C, planes, hh, ww, s); });
+            // IDWT: 3 coefficient planes in, one double-resolution tensor out
+            P.push(TMD_K_ELEMENTWISE, 0, (double)planes * hh * ww * C * e->esize * 7.0,
+                   [=](cudaStream_t s) { return idwt_highbands(dt, hq[0].p, hq[1].p, hq[2].p, T.p, C, planes, hh, ww, s); });
         }
     }
 
@@ -596,7 +628,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     P.ops = &e->step_ops;
     {
         const int E = e->cfg.embed_dim;
-        P.ops->push_back([=](cudaStream_t s) {
+        P.push(TMD_K_COND, 0, ((double)tr * E + (double)B * tr) * 4, [=](cudaStream_t s) {
             return time_table(e->cur_t_dev, e->cur_t_scalar, e->d_freqs, e->cfg.inter_dim, e->d_e_w1, e->d_e_b1, e->d_e_w2, e->d_e_b2,
                               e->d_Wt, e->d_bt, e->d_embed, e->d_tb, B, E, tr, s);
         });
@@ -607,11 +639,12 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const float* t = P.tb(std::string(consumer[l]) + ".dense1", c[l]);
             const int C = c[l];
             const size_t vps = (size_t)N * (H >> l) * (W >> l);
-            P.ops->push_back([=](cudaStream_t s) { return slice_activate(dt, src.p, src.ld, dst.p, dst.ld, t, tr, C, B, vps, s); });
+            P.push(TMD_K_ELEMENTWISE, 0, 2.0 * B * vps * C * e->esize,
+                   [=](cudaStream_t s) { return slice_activate(dt, src.p, src.ld, dst.p, dst.ld, t, tr, C, B, vps, s); });
         }
         View a_stem = P.buf("a_stem", 0, c[0]);
         const float* scs = P.sc("conv2.dense2");
-        P.ops->push_back([=](cudaStream_t s) {
+        P.push(TMD_K_ELEMENTWISE, 0, (double)P.vox(0) * (4 + c[0] * e->esize), [=](cudaStream_t s) {
             return stem_expand(dt, e->cur_x, nullptr, e->d_stem_w[1], e->d_stem_b[1], scs, sr, a_stem.p, c[0], B, N, HW, s);
         });
         View in_act = P.buf("in_act@0", 0, c[0]);
@@ -682,7 +715,8 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const size_t nvox = P.vox(0);
             const int C = c[0];
             View last = af[1];
-            P.ops->push_back([=](cudaStream_t s) { return project_to_band(dt, last.p, last.ld, e->d_proj_w, e->cur_out, C, nvox, s); });
+            P.push(TMD_K_ELEMENTWISE, 2.0 * nvox * C, (double)nvox * (C * e->esize + 4),
+                   [=](cudaStream_t s) { return project_to_band(dt, last.p, last.ld, e->d_proj_w, e->cur_out, C, nvox, s); });
         }
     }
     if (P.err) return fail("plan: %s", P.err);
@@ -690,10 +724,33 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     return 0;
 }
 
+// Profiling (tmd_profile_begin/end): every launch is bracketed by a CUDA event pair on the launching
+// stream; the pairs are resolved into per-kind totals at tmd_profile_end.
+int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t s, bool begin) {
+    if (!e->profiling) return 0;
+    if (begin) {
+        if (e->prof_used == e->prof_events.size()) {
+            ProfSpan sp{};
+            CK(cudaEventCreate(&sp.a));
+            CK(cudaEventCreate(&sp.b));
+            e->prof_events.push_back(sp);
+        }
+        ProfSpan& sp = e->prof_events[e->prof_used];
+        sp.kind = kind; sp.flops = flops; sp.bytes = bytes;
+        CK(cudaEventRecord(sp.a, s));
+    } else {
+        CK(cudaEventRecord(e->prof_events[e->prof_used].b, s));
+        ++e->prof_used;
+    }
+    return 0;
+}
+
 int run_ops(tmd_engine* e, std::vector<Launch>& ops, cudaStream_t s) {
     for (auto& op : ops) {
+        if (prof_mark(e, op.kind, op.flops, op.bytes, s, true)) return 1;
         cudaError_t err = op(s);
         if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
+        if (prof_mark(e, op.kind, op.flops, op.bytes, s, false)) return 1;
         ++e->launches;
     }
     return 0;
@@ -772,14 +829,18 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
             if (!slot_ok(ev.src) || !slot_ok(ev.dst)) return fail("tmd_sample: bad slot in step %d", i);
             float* net_out = trace ? trace + (size_t)n_eval * n : h->d_out;
             if (denoise_impl(h, h->slots[ev.src], nullptr, ev.t_input, net_out, s)) return 1;
+            if (prof_mark(h, TMD_K_SOLVER, 0, 5.0 * n * 4, s, true)) return 1;   // x, out in; x0 written, re-read, re-written
             CK(x0_threshold(h->slots[ev.src], net_out, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, h->B, (int)n_per, plan->q_lo,
                             plan->q_weight, plan->max_val, s));
+            if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             ++h->launches;
             ++n_eval;
         } else {
             const tmd_update& u = st.update;
             if (!slot_ok(u.dst) || !slot_ok(u.x) || !slot_ok(u.m) || u.m1 >= TMD_NUM_SLOTS) return fail("tmd_sample: bad slot in step %d", i);
+            if (prof_mark(h, TMD_K_SOLVER, 0, (u.m1 >= 0 ? 4.0 : 3.0) * n * 4, s, true)) return 1;
             CK(solver_update(h->slots[u.dst], h->slots[u.x], h->slots[u.m], u.m1 >= 0 ? h->slots[u.m1] : nullptr, u.c1, u.c2, u.c3, n, s));
+            if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             ++h->launches;
         }
     }
@@ -788,6 +849,31 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
 }
 
 extern "C" int64_t tmd_launch_count(tmd_handle h) { return h ? h->launches : 0; }
+
+extern "C" int tmd_profile_begin(tmd_handle h) {
+    if (!h) return fail("tmd_profile_begin: null handle");
+    h->profiling = true;
+    h->prof_used = 0;
+    return 0;
+}
+
+extern "C" int tmd_profile_end(tmd_handle h, tmd_profile* out) {
+    if (!h || !out) return fail("tmd_profile_end: null argument");
+    if (!h->profiling) return fail("tmd_profile_end: tmd_profile_begin was not called");
+    h->profiling = false;
+    memset(out, 0, sizeof(*out));
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    for (size_t i = 0; i < h->prof_used; ++i) {
+        const ProfSpan& sp = h->prof_events[i];
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        tmd_profile_kind& k = out->kind[sp.kind];
+        k.ms += ms; k.flops += sp.flops; k.bytes += sp.bytes; k.launches += 1;
+    }
+    h->prof_used = 0;
+    return 0;
+}
 
 // ---------------------------------------------------------------------------------------------
 // stand-alone operators

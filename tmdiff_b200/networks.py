@@ -254,6 +254,24 @@ class WavBEST(nn.Module):
     def launch_count(self):
         return int(self._lib().tmd_launch_count(self._handle)) if self._handle is not None else 0
 
+    def reset_condition_cache(self):
+        """Forget the bound (PAN, MS, prompt): the next call re-runs the step-invariant half."""
+        self._cond_key = None
+
+    # ---- measurement -----------------------------------------------------------------------
+    def profile_begin(self):
+        if self._handle is None:
+            raise RuntimeError("no engine yet: run the model once first")
+        _lib.check(self._lib().tmd_profile_begin(self._handle))
+
+    def profile_end(self):
+        """{kind: {"ms", "flops", "bytes", "launches"}} summed over the launches since profile_begin
+        (device time from CUDA events on the launching stream; algorithmic flops / bytes)."""
+        prof = _lib.Profile()
+        _lib.check(self._lib().tmd_profile_end(self._handle, C.byref(prof)))
+        return {name: {"ms": k.ms, "flops": k.flops, "bytes": k.bytes, "launches": int(k.launches)}
+                for name, k in zip(_lib.KIND_NAMES, prof.kind)}
+
 
 def define_General(opt, text_embeddings=None, dtype="fp32"):
     """networks.define_General (GeneralModel/networks.py:80-92): WavBEST + GeneralDiffusion from the
