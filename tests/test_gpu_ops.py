@@ -65,6 +65,11 @@ CONV_CASES = [
     (1, 8, 16, 3, 4, 4, 3),
     (1, 16, 8, 1, 8, 8, 3),
     (3, 32, 32, 5, 24, 40, 3),
+    (2, 64, 128, 8, 16, 16, 3),      # tcgen05 reuse schedule, 2 accumulators, two n-tiles
+    (1, 128, 256, 4, 16, 24, 3),     # one accumulator per tile
+    (2, 96, 32, 4, 32, 32, 3),       # 3 K-chunks, 4 accumulators
+    (5, 64, 64, 4, 4, 4, 3),         # batch folded into the 128-row tile
+    (3, 192, 48, 2, 8, 16, 1),
 ]
 
 

@@ -1,9 +1,603 @@
-// placeholder until the tcgen05 kernel lands
+// tcgen05 / TMA implicit-GEMM 3-D convolution for sm_100a (bf16 operands, fp32 accumulation in TMEM).
+//
+// Replaces the nn.Conv3d / F.conv3d(groups=B) call sites of the reference denoiser
+// (GeneralModel/Hyper_unet_general.py:74, :161-164, :224-231, :344-361) in bf16 mode.
+//
+// GEMM view:  M = output voxels (128 per accumulator), N = Co (one MMA covers all output
+// channels), K = taps x Ci.  Activations are channels-last bf16 [B][N][H][W][C], so the A operand
+// of one tap is a 5-D TMA box of the input shifted by that tap, with the zero padding supplied by
+// TMA's out-of-bounds fill.  Weights are [Co][taps*Ci] (K-major) and arrive as 2-D TMA tiles.
+//
+// Two schedules share the kernel:
+//   * REUSE (3x3x3, H >= 16, W >= 8): the CTA owns an output tile of NACC band-planes x 16 x 8
+//     voxels (NACC accumulators of M=128).  Per (dx, 32-channel chunk) ONE haloed box
+//     [NACC+2][18][8] voxels is loaded; the 9 (dz,dy) taps x NACC planes are then UMMA descriptor
+//     offsets into that box (8 voxels = one swizzle atom, so every offset is atom-aligned).  This
+//     cuts L2->smem activation traffic ~5x against loading each tap separately, which is what
+//     bounds a 3x3x3 conv with 32..128 output channels (L2 feeds ~42 B/cycle/SM).
+//   * SIMPLE (1x1x1, small planes): one box of 128 voxels [TB][TN][TH][TW] per (tap, chunk).
+//
+// Warp roles (256 threads, persistent CTAs, one per SM):
+//   warp 0  lane 0: TMA producer for activation boxes     (ring of SA stages)
+//   warp 1  lane 0: TMA producer for weight tiles         (ring of SB tiles)
+//   warp 2  lane 0: tcgen05.mma issuer; accumulators double-buffered in TMEM
+//   warp 3        : TMEM allocation / release
+//   warps 4-7     : epilogue: tcgen05.ld -> bias / residual adds / Haar pooling or 2x upsampling /
+//                   time-bias + Swish + text-scale views -> bf16 stores (conv_op.h)
+#include <cuda.h>
+
+#include <cstdlib>
+#include <cstring>
+
+#include "conv_op.h"
 #include "kernels.h"
+
 namespace tmd {
-struct UmmaPlan { int dummy; };
-bool conv_umma_supported(const ConvOp&) { return false; }
-UmmaPlan* conv_umma_plan_create(const ConvOp&) { return nullptr; }
-void conv_umma_plan_destroy(UmmaPlan* p) { delete p; }
-cudaError_t conv_umma_bf16(const ConvOp&, const UmmaPlan*, cudaStream_t) { return cudaErrorNotSupported; }
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxSA = 4, kMaxSB = 16;
+
+struct UmmaParams {
+    CUtensorMap tmA, tmB;
+    ConvEpilogue epi;
+    int B, N, H, W, Ci, Co, taps;
+    int mode;                   // 0 = SIMPLE, 1 = REUSE
+    int KC, nkc;                // channels per chunk, chunks per tap
+    int TW, TH, TN, TB;         // output tile (voxels per accumulator = 128)
+    int NACC;                   // accumulators (band planes) per tile
+    int tiles_x, tiles_y, tiles_n, tiles_b, num_tiles;
+    int SA, SB;
+    uint32_t a_stage_bytes, a_stage_stride, b_tile_bytes, b_tile_stride;
+    uint32_t row_bytes, layout_type, sbo16;
+    uint32_t tmem_cols, idesc;
+};
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Spin on the phase parity; a wait that lasts ~4 s means a broken pipeline: trap instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t spins = 0;; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if ((spins & 0xfff) == 0xfff) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 8000000000LL) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3, int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major shared-memory matrix descriptor (tcgen05 "smem descriptor"): 8-row swizzle atoms of
+// `row_bytes` per row, atoms `sbo` bytes apart.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo16, uint32_t layout_type) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)sbo16 << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)layout_type << 61);
+}
+
+// ------------------------------------------------------------------------------------------
+// epilogue helpers (8 consecutive output channels = one 16-byte bf16 vector)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load8_bf16(const __nv_bfloat16* p, float v[8]) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+__device__ __forceinline__ void store8_bf16(__nv_bfloat16* p, const float v[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ void load8_f32(const float* p, float v[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+// v = accumulator + bias for channels [co, co+8) of one output voxel: residual adds, raw view and
+// the activated views (same contract as epilogue_store4 in conv_op.h).
+__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8]) {
+    typedef __nv_bfloat16 T;
+    if (e.add0) {
+        float a[8];
+        load8_bf16(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, a);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] += a[i];
+    }
+    if (e.add1) {
+        float a[8];
+        load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] += a[i];
+    }
+    if (e.raw_out) store8_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (!e.act_out[k]) continue;
+        float u[8], t[8], s[8];
+        if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co, t);
+        if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co, s);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float x = v[i];
+            if (e.tb[k]) x += t[i];
+            x = swish<true>(x);
+            if (e.sc[k]) x *= s[i];
+            u[i] = x;
+        }
+        store8_bf16(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, u);
+    }
+}
+
+// One 16-channel slab of one accumulator row.  All 32 lanes of the warp call this together (the
+// POOL mode exchanges rows through shuffles); `valid` guards the stores only.
+__device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int n, int y, int x, bool valid) {
+    const ConvEpilogue& e = P.epi;
+    float bias[16];
+    if (e.bias) {
+        load8_f32(e.bias + co, bias);
+        load8_f32(e.bias + co + 8, bias + 8);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) bias[i] = 0.f;
+    }
+    const size_t bn = (size_t)b * P.N + n;
+    if (e.mode == CONV_NORMAL) {
+        if (!valid) return;
+        const size_t ovox = (bn * P.H + y) * P.W + x;
+        const size_t hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
+            store_views8(e, b, ovox, hvox, co + 8 * h, v);
+        }
+    } else if (e.mode == CONV_POOL) {
+        // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
+        float ll[16], lh[16], hl[16], hh[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float t = __shfl_xor_sync(0xffffffffu, acc[i], 1);
+            const float L = acc[i] + t, D = acc[i] - t;                 // a+b, a-b   (on the even-x lane)
+            const float u = __shfl_xor_sync(0xffffffffu, L, P.TW), w = __shfl_xor_sync(0xffffffffu, D, P.TW);
+            ll[i] = (L + u) * 0.25f + bias[i];                           // LL/2 == 2x2 average (:396)
+            hl[i] = (L - u) * 0.5f;                                      // (a+b)-(c+d)
+            lh[i] = (D + w) * 0.5f;                                      // (a-b)+(c-d)
+            hh[i] = (D - w) * 0.5f;                                      // (a-b)-(c-d)
+        }
+        if (!valid || (x & 1) || (y & 1)) return;
+        const size_t ovox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (e.hf_out[0]) {
+                typedef __nv_bfloat16 T;
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co + 8 * h, lh + 8 * h);
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co + 8 * h, hl + 8 * h);
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co + 8 * h, hh + 8 * h);
+            }
+            store_views8(e, b, ovox, 0, co + 8 * h, ll + 8 * h);
+        }
+    } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
+        if (!valid) return;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const size_t ovox = (bn * (2 * P.H) + 2 * y + (r >> 1)) * (2 * P.W) + 2 * x + (r & 1);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
+                store_views8(e, b, ovox, 0, co + 8 * h, v);
+            }
+        }
+    }
+}
+
+struct TileCoord { int b0, n0, y0, x0; };
+__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int t) {
+    TileCoord c;
+    c.x0 = (t % P.tiles_x) * P.TW; t /= P.tiles_x;
+    c.y0 = (t % P.tiles_y) * P.TH; t /= P.tiles_y;
+    c.n0 = (t % P.tiles_n) * (P.mode ? P.NACC : P.TN); t /= P.tiles_n;
+    c.b0 = t * P.TB;
+    return c;
+}
+
+// ------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_constant__ UmmaParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 4];
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
+    const uint32_t a_base = smem_base;
+    const uint32_t b_base = a_base + P.SA * P.a_stage_stride;
+    const uint32_t bar0 = smem_u32(bars);
+    auto a_full = [&](int s) { return bar0 + 8u * s; };
+    auto a_empty = [&](int s) { return bar0 + 8u * (kMaxSA + s); };
+    auto b_full = [&](int s) { return bar0 + 8u * (2 * kMaxSA + s); };
+    auto b_empty = [&](int s) { return bar0 + 8u * (2 * kMaxSA + kMaxSB + s); };
+    auto acc_full = [&](int s) { return bar0 + 8u * (2 * kMaxSA + 2 * kMaxSB + s); };
+    auto acc_empty = [&](int s) { return bar0 + 8u * (2 * kMaxSA + 2 * kMaxSB + 2 + s); };
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < P.SA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
+        for (int s = 0; s < P.SB; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 3) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(P.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    const int ngroups = P.mode ? 3 : P.taps;           // tap groups that need their own activation box
+    const int taps_per_stage = P.mode ? 9 : 1;
+
+    if (warp == 0 && lane == 0) {
+        // ================= activation boxes =================
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
+            const TileCoord tc = decode_tile(P, tile);
+            for (int g = 0; g < ngroups; ++g) {
+                int cx = tc.x0, cy = tc.y0, cn = tc.n0;
+                if (P.mode) { cx += g - 1; cy -= 1; cn -= 1; }
+                else if (P.taps == 27) { cx += g % 3 - 1; cy += (g / 3) % 3 - 1; cn += g / 9 - 1; }
+                for (int kc = 0; kc < P.nkc; ++kc, ++it) {
+                    const int s = it % P.SA;
+                    mbar_wait(a_empty(s), ((it / P.SA) & 1) ^ 1);
+                    mbar_expect_tx(a_full(s), P.a_stage_bytes);
+                    tma_load_5d(a_base + s * P.a_stage_stride, &P.tmA, a_full(s), kc * P.KC, cx, cy, cn, tc.b0);
+                }
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ================= weight tiles =================
+        uint32_t it = 0;
+        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
+            for (int g = 0; g < ngroups; ++g)
+                for (int kc = 0; kc < P.nkc; ++kc)
+                    for (int t = 0; t < taps_per_stage; ++t, ++it) {
+                        const int tap = P.mode ? t * 3 + g : g;          // (dz*3+dy)*3+dx
+                        const int s = it % P.SB;
+                        mbar_wait(b_empty(s), ((it / P.SB) & 1) ^ 1);
+                        mbar_expect_tx(b_full(s), P.b_tile_bytes);
+                        tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB, b_full(s), tap * P.Ci + kc * P.KC, 0);
+                    }
+        }
+    } else if (warp == 2 && lane == 0) {
+        // ================= MMA issue =================
+        uint32_t ia = 0, ib = 0, lt = 0;
+        const int kmma = P.KC / 16;
+        const uint32_t plane_rows = (uint32_t)(P.TH + 2) * P.TW;
+        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
+            const TileCoord tc = decode_tile(P, tile);
+            const int ab = lt & 1;
+            mbar_wait(acc_empty(ab), ((lt >> 1) & 1) ^ 1);
+            tc_fence_after();
+            int nacc = P.NACC;
+            if (P.mode && tc.n0 + nacc > P.N) nacc = P.N - tc.n0;       // planes past the last band are skipped
+            for (int g = 0; g < ngroups; ++g)
+                for (int kc = 0; kc < P.nkc; ++kc, ++ia) {
+                    const int sa = ia % P.SA;
+                    mbar_wait(a_full(sa), (ia / P.SA) & 1);
+                    tc_fence_after();
+                    const uint32_t a_stage = a_base + sa * P.a_stage_stride;
+                    for (int t = 0; t < taps_per_stage; ++t, ++ib) {
+                        const int sb = ib % P.SB;
+                        mbar_wait(b_full(sb), (ib / P.SB) & 1);
+                        tc_fence_after();
+                        const uint32_t b_tile = b_base + sb * P.b_tile_stride;
+                        const bool first = (g == 0 && kc == 0 && t == 0);
+                        const int dz = t / 3, dy = t % 3;
+                        for (int p = 0; p < nacc; ++p) {
+                            const uint32_t a_off = P.mode ? ((uint32_t)(p + dz) * plane_rows + (uint32_t)dy * P.TW) * P.row_bytes : 0u;
+                            const uint32_t d_tmem = tmem_base + (uint32_t)(ab * P.NACC + p) * P.Co;
+                            for (int k = 0; k < kmma; ++k) {
+                                const uint64_t ad = make_desc(a_stage + a_off + k * 32, P.sbo16, P.layout_type);
+                                const uint64_t bd = make_desc(b_tile + k * 32, P.sbo16, P.layout_type);
+                                tc_mma_bf16(d_tmem, ad, bd, P.idesc, (first && k == 0) ? 0u : 1u);
+                            }
+                        }
+                        tc_commit(b_empty(sb));          // weight tile free once these MMAs retire
+                    }
+                    tc_commit(a_empty(sa));
+                }
+            tc_commit(acc_full(ab));
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue =================
+        const int q = warp & 3;                           // TMEM lane quarter this warp may read
+        const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
+        uint32_t lt = 0;
+        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
+            const TileCoord tc = decode_tile(P, tile);
+            const int ab = lt & 1;
+            mbar_wait(acc_full(ab), (lt >> 1) & 1);
+            tc_fence_after();
+            int b, n_off, y, x;
+            if (P.mode) { x = r % P.TW; y = r / P.TW; n_off = 0; b = tc.b0; }
+            else {
+                int t = r;
+                x = t % P.TW; t /= P.TW;
+                y = t % P.TH; t /= P.TH;
+                n_off = t % P.TN; t /= P.TN;
+                b = tc.b0 + t;
+            }
+            x += tc.x0; y += tc.y0;
+            int nacc = P.NACC;
+            if (P.mode && tc.n0 + nacc > P.N) nacc = P.N - tc.n0;
+            for (int p = 0; p < nacc; ++p) {
+                const int n = tc.n0 + n_off + p;
+                const bool valid = b < P.B && n < P.N && y < P.H && x < P.W;
+                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * P.NACC + p) * P.Co;
+                for (int c0 = 0; c0 < P.Co; c0 += 16) {
+                    float acc[16];
+                    tc_ld16(t_row + c0, acc);
+                    epilogue16(P, acc, c0, b, n, y, x, valid);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty(ab));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 3) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(P.tmem_cols) : "memory");
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// host side: geometry, tensor maps, launch
+// ------------------------------------------------------------------------------------------
+struct UmmaPlan {
+    UmmaParams p;
+    int grid;
+    size_t smem;
+};
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+int floor_pow2(int v) {
+    int p = 1;
+    while (p * 2 <= v) p *= 2;
+    return p;
+}
+
+bool umma_disabled() {
+    static const bool off = []() {
+        const char* e = getenv("TMD_DISABLE_UMMA");
+        return e && e[0] == '1';
+    }();
+    return off;
+}
+
+int sm_count() {
+    static const int n = []() {
+        int dev = 0, v = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        return v;
+    }();
+    return n;
+}
+
+}  // namespace
+
+bool conv_umma_supported(const ConvOp& op) {
+    if (umma_disabled()) return false;
+    if (op.taps != 27 && op.taps != 1) return false;
+    if (op.Ci % 32 || op.Co % 16 || op.Co < 16 || op.Co > 256) return false;
+    if (op.ld_in % 8 || (reinterpret_cast<uintptr_t>(op.src) & 15)) return false;
+    const ConvEpilogue& e = op.epi;
+    // 16-byte vector accesses in the epilogue
+    if ((e.raw_out && e.ld_raw % 8) || (e.add0 && e.ld_add0 % 8) || (e.add1 && e.ld_add1 % 8) || (e.hf_out[0] && e.ld_hf % 8)) return false;
+    for (int k = 0; k < 2; ++k)
+        if (e.act_out[k] && e.ld_act[k] % 8) return false;
+    if ((e.tb[0] || e.tb[1]) && e.ld_tb % 4) return false;
+    if ((e.sc[0] || e.sc[1]) && e.ld_sc % 4) return false;
+    const void* ptrs[] = {e.bias, e.add0, e.add1, e.raw_out, e.act_out[0], e.act_out[1], e.tb[0], e.tb[1], e.sc[0], e.sc[1],
+                          e.hf_out[0], e.hf_out[1], e.hf_out[2], op.w_bf16};
+    for (const void* q : ptrs)
+        if (reinterpret_cast<uintptr_t>(q) & 15) return false;
+    if (e.mode == CONV_POOL && (op.H % 2 || op.W % 2)) return false;
+    if (op.W < 2 || op.H < 2) return false;
+    return true;
+}
+
+UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) return nullptr;
+    auto* plan = new UmmaPlan();
+    UmmaParams& P = plan->p;
+    memset(&P, 0, sizeof(P));
+    P.epi = op.epi;
+    P.B = op.B; P.N = op.N; P.H = op.H; P.W = op.W; P.Ci = op.Ci; P.Co = op.Co; P.taps = op.taps;
+    P.mode = (op.taps == 27 && op.H >= 16 && op.W >= 8) ? 1 : 0;
+    cuuint32_t boxA[5];
+    if (P.mode) {
+        P.KC = 32;
+        P.TW = 8; P.TH = 16; P.TN = 1; P.TB = 1;
+        P.NACC = 256 / op.Co;                       // two accumulator sets must fit 512 TMEM columns
+        if (P.NACC > 4) P.NACC = 4;
+        if (P.NACC > op.N) P.NACC = op.N;
+        if (P.NACC < 1) P.NACC = 1;
+        boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH + 2; boxA[3] = P.NACC + 2; boxA[4] = 1;
+        P.tiles_n = (op.N + P.NACC - 1) / P.NACC;
+    } else {
+        P.KC = (op.Ci % 64 == 0) ? 64 : 32;
+        P.TW = floor_pow2(op.W < 16 ? op.W : 16);
+        P.TH = floor_pow2(op.H < 128 / P.TW ? op.H : 128 / P.TW);
+        P.TN = floor_pow2(op.N < 128 / (P.TW * P.TH) ? op.N : 128 / (P.TW * P.TH));
+        P.TB = 128 / (P.TW * P.TH * P.TN);
+        P.NACC = 1;
+        boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH; boxA[3] = P.TN; boxA[4] = P.TB;
+        P.tiles_n = (op.N + P.TN - 1) / P.TN;
+    }
+    P.nkc = op.Ci / P.KC;
+    P.tiles_x = (op.W + P.TW - 1) / P.TW;
+    P.tiles_y = (op.H + P.TH - 1) / P.TH;
+    P.tiles_b = (op.B + P.TB - 1) / P.TB;
+    P.num_tiles = P.tiles_x * P.tiles_y * P.tiles_n * P.tiles_b;
+    P.row_bytes = P.KC * 2;
+    P.layout_type = P.KC == 64 ? 2u : 4u;           // SWIZZLE_128B : SWIZZLE_64B
+    P.sbo16 = (8 * P.row_bytes) >> 4;               // 8-row swizzle atoms are contiguous
+    P.a_stage_bytes = boxA[1] * boxA[2] * boxA[3] * boxA[4] * P.row_bytes;
+    P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
+    P.b_tile_bytes = op.Co * P.row_bytes;
+    P.b_tile_stride = (P.b_tile_bytes + 1023u) & ~1023u;
+    int cols = 2 * P.NACC * op.Co;
+    P.tmem_cols = 32;
+    while ((int)P.tmem_cols < cols) P.tmem_cols *= 2;
+    // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
+    P.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(op.Co >> 3) << 17) | ((128u >> 4) << 24);
+
+    // ring depths from the shared-memory budget
+    const size_t budget = 220 * 1024;
+    P.SA = P.mode ? 2 : 4;
+    if ((size_t)P.SA * P.a_stage_stride > budget * 3 / 4) P.SA = 1;
+    size_t left = budget - (size_t)P.SA * P.a_stage_stride;
+    P.SB = (int)(left / P.b_tile_stride);
+    const int want_sb = P.mode ? 12 : P.SA;
+    if (P.SB > want_sb) P.SB = want_sb;
+    if (P.SB > kMaxSB) P.SB = kMaxSB;
+    if (P.SB < 2 || P.SA < 1) { delete plan; return nullptr; }
+    plan->smem = (size_t)P.SA * P.a_stage_stride + (size_t)P.SB * P.b_tile_stride + 1024;
+
+    const CUtensorMapSwizzle sw = P.KC == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    {   // activations [B][N][H][W][ld] bf16, channels innermost
+        cuuint64_t dims[5] = {(cuuint64_t)op.Ci, (cuuint64_t)op.W, (cuuint64_t)op.H, (cuuint64_t)op.N, (cuuint64_t)op.B};
+        const cuuint64_t e = 2ull * op.ld_in;
+        cuuint64_t strides[4] = {e, e * op.W, e * op.W * op.H, e * op.W * op.H * op.N};
+        cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+        if (enc(&P.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(op.src), dims, strides, boxA, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+            delete plan;
+            return nullptr;
+        }
+    }
+    {   // weights [Co][taps*Ci] bf16
+        cuuint64_t dims[2] = {(cuuint64_t)op.taps * op.Ci, (cuuint64_t)op.Co};
+        cuuint64_t strides[1] = {2ull * op.taps * op.Ci};
+        cuuint32_t box[2] = {(cuuint32_t)P.KC, (cuuint32_t)op.Co};
+        cuuint32_t estr[2] = {1, 1};
+        if (enc(&P.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(op.w_bf16), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+            delete plan;
+            return nullptr;
+        }
+    }
+    plan->grid = P.num_tiles < sm_count() ? P.num_tiles : sm_count();
+    return plan;
+}
+
+void conv_umma_plan_destroy(UmmaPlan* p) { delete p; }
+
+cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t stream) {
+    (void)op;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    conv_umma_kernel<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
+    return cudaGetLastError();
+}
+
+}  // namespace tmd
