@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--sensor", default="QB")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
+    ap.add_argument("--launch-csv", default=None, help="write the per-launch CUDA-event times of the profiled step here")
     return ap.parse_args()
 
 
@@ -260,7 +261,7 @@ def run_ours(args):
     if rank == 0:
         model.profile_begin()
         step_resident()
-        prof = model.profile_end()
+        prof = model.profile_end(args.launch_csv)
     if world > 1:
         dist.barrier()
 

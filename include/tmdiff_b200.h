@@ -145,7 +145,8 @@ enum { TMD_K_CONV3 = 0,        /* 3x3x3 implicit-GEMM convolutions (tensor-bound
 typedef struct { double ms, flops, bytes; int64_t launches; } tmd_profile_kind;
 typedef struct { tmd_profile_kind kind[TMD_NUM_KINDS]; } tmd_profile;
 int tmd_profile_begin(tmd_handle h);
-int tmd_profile_end(tmd_handle h, tmd_profile* out);
+/* csv_path (optional, may be NULL): also write one line per launch (label, ms, flops, bytes) */
+int tmd_profile_end(tmd_handle h, tmd_profile* out, const char* csv_path);
 
 #ifdef __cplusplus
 }

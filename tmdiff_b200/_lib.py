@@ -68,7 +68,7 @@ SIGNATURES = {
     "tmd_dynamic_threshold": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, _P]),
     "tmd_launch_count": (C.c_int64, [_P]),
     "tmd_profile_begin": (C.c_int, [_P]),
-    "tmd_profile_end": (C.c_int, [_P, C.POINTER(Profile)]),
+    "tmd_profile_end": (C.c_int, [_P, C.POINTER(Profile), C.c_char_p]),
 }
 
 _lib = None

@@ -26,6 +26,7 @@
 //                   time-bias + Swish + text-scale views -> bf16 stores (conv_op.h)
 #include <cuda.h>
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -52,6 +53,10 @@ struct UmmaParams {
     uint32_t a_stage_bytes, a_stage_stride, b_tile_bytes, b_tile_stride;
     uint32_t row_bytes, layout_type, sbo16;
     uint32_t tmem_cols, idesc;
+    int a_planes, a_ysplit;     // REUSE: the haloed box is fetched as a_planes x a_ysplit TMA instructions (more requests in flight)
+    uint32_t a_piece_bytes;
+    long long* trace;           // diagnostics (TMD_UMMA_TRACE=1): per-role cycle counters of CTA 0
+    int dbg;                    // diagnostics (TMD_UMMA_DEBUG): 1 no MMA, 2 no activation loads, 4 no weight loads, 8 no epilogue stores
 };
 
 // ------------------------------------------------------------------------------------------
@@ -272,12 +277,26 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int t) {
 // ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
+// Warp-uniform control flow throughout: every lane of a role's warp runs the loops and one elected
+// lane issues the TMA / tcgen05 instructions, so their operands stay in uniform registers (a
+// divergent `lane == 0` branch makes ptxas wrap every UTCHMMA in an election loop).
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(pred));
+    return pred;
+}
+
+template <int MODE, int NACC, int KMMA>
 __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_constant__ UmmaParams P) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 4];
     __shared__ uint32_t tmem_base_slot;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
     const uint32_t a_base = smem_base;
     const uint32_t b_base = a_base + P.SA * P.a_stage_stride;
@@ -305,92 +324,146 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
 
-    const int ngroups = P.mode ? 3 : P.taps;           // tap groups that need their own activation box
-    const int taps_per_stage = P.mode ? 9 : 1;
+    constexpr int KC = KMMA * 16;
+    const int ngroups = MODE ? 3 : P.taps;              // tap groups that need their own activation box
+    constexpr int taps_per_stage = MODE ? 9 : 1;
+    const int nkc = P.nkc;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
         // ================= activation boxes =================
-        uint32_t it = 0;
+        uint32_t s = 0, ph = 1;                            // ring slot, parity of its "empty" phase
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
             const TileCoord tc = decode_tile(P, tile);
             for (int g = 0; g < ngroups; ++g) {
                 int cx = tc.x0, cy = tc.y0, cn = tc.n0;
-                if (P.mode) { cx += g - 1; cy -= 1; cn -= 1; }
+                if (MODE) { cx += g - 1; cy -= 1; cn -= 1; }
                 else if (P.taps == 27) { cx += g % 3 - 1; cy += (g / 3) % 3 - 1; cn += g / 9 - 1; }
-                for (int kc = 0; kc < P.nkc; ++kc, ++it) {
-                    const int s = it % P.SA;
-                    mbar_wait(a_empty(s), ((it / P.SA) & 1) ^ 1);
-                    mbar_expect_tx(a_full(s), P.a_stage_bytes);
-                    tma_load_5d(a_base + s * P.a_stage_stride, &P.tmA, a_full(s), kc * P.KC, cx, cy, cn, tc.b0);
+                for (int kc = 0; kc < nkc; ++kc) {
+                    mbar_wait(a_empty(s), ph);
+                    if (elect_one()) {
+                        if (P.dbg & 2) mbar_arrive(a_full(s));
+                        else {
+                            mbar_expect_tx(a_full(s), P.a_stage_bytes);
+                            uint32_t dst = a_base + s * P.a_stage_stride;
+                            if (MODE) {
+#pragma unroll
+                                for (int pl = 0; pl < NACC + 2; ++pl, dst += P.a_piece_bytes)
+                                    tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn + pl, tc.b0);
+                            } else {
+                                tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn, tc.b0);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (++s == (uint32_t)P.SA) { s = 0; ph ^= 1; }
                 }
             }
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
         // ================= weight tiles =================
-        uint32_t it = 0;
+        uint32_t s = 0, ph = 1;
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
             for (int g = 0; g < ngroups; ++g)
-                for (int kc = 0; kc < P.nkc; ++kc)
-                    for (int t = 0; t < taps_per_stage; ++t, ++it) {
-                        const int tap = P.mode ? t * 3 + g : g;          // (dz*3+dy)*3+dx
-                        const int s = it % P.SB;
-                        mbar_wait(b_empty(s), ((it / P.SB) & 1) ^ 1);
-                        mbar_expect_tx(b_full(s), P.b_tile_bytes);
-                        tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB, b_full(s), tap * P.Ci + kc * P.KC, 0);
-                    }
-        }
-    } else if (warp == 2 && lane == 0) {
-        // ================= MMA issue =================
-        uint32_t ia = 0, ib = 0, lt = 0;
-        const int kmma = P.KC / 16;
-        const uint32_t plane_rows = (uint32_t)(P.TH + 2) * P.TW;
-        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
-            const TileCoord tc = decode_tile(P, tile);
-            const int ab = lt & 1;
-            mbar_wait(acc_empty(ab), ((lt >> 1) & 1) ^ 1);
-            tc_fence_after();
-            int nacc = P.NACC;
-            if (P.mode && tc.n0 + nacc > P.N) nacc = P.N - tc.n0;       // planes past the last band are skipped
-            for (int g = 0; g < ngroups; ++g)
-                for (int kc = 0; kc < P.nkc; ++kc, ++ia) {
-                    const int sa = ia % P.SA;
-                    mbar_wait(a_full(sa), (ia / P.SA) & 1);
-                    tc_fence_after();
-                    const uint32_t a_stage = a_base + sa * P.a_stage_stride;
-                    for (int t = 0; t < taps_per_stage; ++t, ++ib) {
-                        const int sb = ib % P.SB;
-                        mbar_wait(b_full(sb), (ib / P.SB) & 1);
-                        tc_fence_after();
-                        const uint32_t b_tile = b_base + sb * P.b_tile_stride;
-                        const bool first = (g == 0 && kc == 0 && t == 0);
-                        const int dz = t / 3, dy = t % 3;
-                        for (int p = 0; p < nacc; ++p) {
-                            const uint32_t a_off = P.mode ? ((uint32_t)(p + dz) * plane_rows + (uint32_t)dy * P.TW) * P.row_bytes : 0u;
-                            const uint32_t d_tmem = tmem_base + (uint32_t)(ab * P.NACC + p) * P.Co;
-                            for (int k = 0; k < kmma; ++k) {
-                                const uint64_t ad = make_desc(a_stage + a_off + k * 32, P.sbo16, P.layout_type);
-                                const uint64_t bd = make_desc(b_tile + k * 32, P.sbo16, P.layout_type);
-                                tc_mma_bf16(d_tmem, ad, bd, P.idesc, (first && k == 0) ? 0u : 1u);
+                for (int kc = 0; kc < nkc; ++kc)
+#pragma unroll 1
+                    for (int t = 0; t < taps_per_stage; ++t) {
+                        const int tap = MODE ? t * 3 + g : g;          // (dz*3+dy)*3+dx
+                        mbar_wait(b_empty(s), ph);
+                        if (elect_one()) {
+                            if (P.dbg & 4) mbar_arrive(b_full(s));
+                            else {
+                                mbar_expect_tx(b_full(s), P.b_tile_bytes);
+                                tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB, b_full(s), tap * P.Ci + kc * KC, 0);
                             }
                         }
-                        tc_commit(b_empty(sb));          // weight tile free once these MMAs retire
+                        __syncwarp();
+                        if (++s == (uint32_t)P.SB) { s = 0; ph ^= 1; }
                     }
-                    tc_commit(a_empty(sa));
+        }
+    } else if (warp == 2) {
+        // ================= MMA issue =================
+        // Descriptors differ only in their 14-bit start-address field, so the loops below just add
+        // 16-byte-unit offsets to the low word.
+        const uint32_t desc_hi = P.sbo16 | (1u << 14) | (P.layout_type << 29);
+        const uint32_t a_lo0 = ((a_base & 0x3FFFFu) >> 4) | (1u << 16);
+        const uint32_t b_lo0 = ((b_base & 0x3FFFFu) >> 4) | (1u << 16);
+        const uint32_t a_stride16 = P.a_stage_stride >> 4, b_stride16 = P.b_tile_stride >> 4;
+        const uint32_t plane16 = ((uint32_t)(P.TH + 2) * P.TW * P.row_bytes) >> 4;   // one haloed band plane
+        const uint32_t line16 = ((uint32_t)P.TW * P.row_bytes) >> 4;                  // one line of 8 voxels = one swizzle atom
+        const uint32_t idesc = P.idesc;
+        const uint32_t Co = P.Co;
+        const bool do_mma = !(P.dbg & 1);
+        uint32_t sa = 0, pha = 0, sb = 0, phb = 0, lt = 0;
+        long long tw_acc = 0, tw_a = 0, tw_b = 0, t_issue = 0, t_all0 = clock64(), tq = 0;
+        const bool tr = P.trace && blockIdx.x == 0;
+        for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
+            const uint32_t ab = lt & 1;
+            if (tr) tq = clock64();
+            mbar_wait(acc_empty(ab), ((lt >> 1) & 1) ^ 1);
+            if (tr) tw_acc += clock64() - tq;
+            tc_fence_after();
+            const uint32_t d0 = tmem_base + ab * NACC * Co;
+            uint32_t fresh = 0;                                   // 0 for the first MMA into each accumulator of this tile
+            for (int g = 0; g < ngroups; ++g)
+                for (int kc = 0; kc < nkc; ++kc) {
+                    if (tr) tq = clock64();
+                    mbar_wait(a_full(sa), pha);
+                    if (tr) tw_a += clock64() - tq;
+                    tc_fence_after();
+                    const uint32_t a_lo = a_lo0 + sa * a_stride16;
+#pragma unroll 1
+                    for (int t = 0; t < taps_per_stage; ++t) {
+                        if (tr) tq = clock64();
+                        mbar_wait(b_full(sb), phb);
+                        if (tr) { tw_b += clock64() - tq; tq = clock64(); }
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint32_t b_lo = b_lo0 + sb * b_stride16;
+                            const uint32_t a_tap = MODE ? a_lo + (uint32_t)(t / 3) * plane16 + (uint32_t)(t % 3) * line16 : a_lo;
+                            if (do_mma) {
+#pragma unroll
+                                for (int p = 0; p < NACC; ++p)
+#pragma unroll
+                                    for (int k = 0; k < KMMA; ++k) {
+                                        const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_tap + p * plane16 + k * 2);
+                                        const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + k * 2);
+                                        tc_mma_bf16(d0 + p * Co, ad, bd, idesc, k == 0 ? fresh : 1u);
+                                    }
+                            }
+                            tc_commit(b_empty(sb));              // weight tile free once these MMAs retire
+                        }
+                        __syncwarp();
+                        fresh = 1;
+                        if (++sb == (uint32_t)P.SB) { sb = 0; phb ^= 1; }
+                        if (tr) t_issue += clock64() - tq;
+                    }
+                    if (elect_one()) tc_commit(a_empty(sa));
+                    __syncwarp();
+                    if (++sa == (uint32_t)P.SA) { sa = 0; pha ^= 1; }
                 }
-            tc_commit(acc_full(ab));
+            if (elect_one()) tc_commit(acc_full(ab));
+            __syncwarp();
+        }
+        if (tr && lane == 0) {
+            P.trace[0] = clock64() - t_all0; P.trace[1] = tw_acc; P.trace[2] = tw_a; P.trace[3] = tw_b; P.trace[4] = t_issue;
+            P.trace[6] = lt;
         }
     } else if (warp >= 4) {
         // ================= epilogue =================
         const int q = warp & 3;                           // TMEM lane quarter this warp may read
         const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
         uint32_t lt = 0;
+        long long tw_full = 0, t_all0 = clock64(), tq = 0;
+        const bool tr = P.trace && blockIdx.x == 0 && threadIdx.x == 128;
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
             const TileCoord tc = decode_tile(P, tile);
             const int ab = lt & 1;
+            if (tr) tq = clock64();
             mbar_wait(acc_full(ab), (lt >> 1) & 1);
+            if (tr) tw_full += clock64() - tq;
             tc_fence_after();
             int b, n_off, y, x;
-            if (P.mode) { x = r % P.TW; y = r / P.TW; n_off = 0; b = tc.b0; }
+            if (MODE) { x = r % P.TW; y = r / P.TW; n_off = 0; b = tc.b0; }
             else {
                 int t = r;
                 x = t % P.TW; t /= P.TW;
@@ -399,12 +472,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 b = tc.b0 + t;
             }
             x += tc.x0; y += tc.y0;
-            int nacc = P.NACC;
-            if (P.mode && tc.n0 + nacc > P.N) nacc = P.N - tc.n0;
-            for (int p = 0; p < nacc; ++p) {
+            for (int p = 0; p < NACC; ++p) {
                 const int n = tc.n0 + n_off + p;
-                const bool valid = b < P.B && n < P.N && y < P.H && x < P.W;
-                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * P.NACC + p) * P.Co;
+                const bool valid = b < P.B && n < P.N && y < P.H && x < P.W && !(P.dbg & 8);
+                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + p) * P.Co;
                 for (int c0 = 0; c0 < P.Co; c0 += 16) {
                     float acc[16];
                     tc_ld16(t_row + c0, acc);
@@ -415,6 +486,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty(ab));
         }
+        if (tr) { P.trace[8] = clock64() - t_all0; P.trace[9] = tw_full; }
     }
 
     tc_fence_before();
@@ -457,6 +529,11 @@ int floor_pow2(int v) {
     int p = 1;
     while (p * 2 <= v) p *= 2;
     return p;
+}
+
+int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e && *e ? atoi(e) : dflt;
 }
 
 bool umma_disabled() {
@@ -513,11 +590,16 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     if (P.mode) {
         P.KC = 32;
         P.TW = 8; P.TH = 16; P.TN = 1; P.TB = 1;
-        P.NACC = 256 / op.Co;                       // two accumulator sets must fit 512 TMEM columns
-        if (P.NACC > 4) P.NACC = 4;
-        if (P.NACC > op.N) P.NACC = op.N;
-        if (P.NACC < 1) P.NACC = 1;
-        boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH + 2; boxA[3] = P.NACC + 2; boxA[4] = 1;
+        // accumulators per tile: two sets must fit the 512 TMEM columns, the haloed box must leave room for
+        // two stages in shared memory, and NACC divides the band count (no plane is computed for nothing)
+        int cap = 256 / op.Co;
+        if (cap > 4) cap = 4;
+        P.NACC = 1;
+        for (int c = 2; c <= cap; c *= 2)
+            if (op.N % c == 0) P.NACC = c;
+        P.a_planes = P.NACC + 2;
+        P.a_ysplit = 1;
+        boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH + 2; boxA[3] = 1; boxA[4] = 1;   // one TMA instruction per haloed plane
         P.tiles_n = (op.N + P.NACC - 1) / P.NACC;
     } else {
         P.KC = (op.Ci % 64 == 0) ? 64 : 32;
@@ -537,7 +619,9 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.row_bytes = P.KC * 2;
     P.layout_type = P.KC == 64 ? 2u : 4u;           // SWIZZLE_128B : SWIZZLE_64B
     P.sbo16 = (8 * P.row_bytes) >> 4;               // 8-row swizzle atoms are contiguous
-    P.a_stage_bytes = boxA[1] * boxA[2] * boxA[3] * boxA[4] * P.row_bytes;
+    P.a_piece_bytes = boxA[1] * boxA[2] * boxA[3] * boxA[4] * P.row_bytes;
+    P.a_stage_bytes = P.mode ? P.a_piece_bytes * P.a_planes * P.a_ysplit : P.a_piece_bytes;
+    P.dbg = env_int("TMD_UMMA_DEBUG", 0);
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
     P.b_tile_bytes = op.Co * P.row_bytes;
     P.b_tile_stride = (P.b_tile_bytes + 1023u) & ~1023u;
@@ -588,15 +672,48 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
 
 void conv_umma_plan_destroy(UmmaPlan* p) { delete p; }
 
+namespace {
+typedef void (*KernelFn)(const UmmaParams);
+KernelFn pick_kernel(const UmmaParams& p) {
+    if (p.mode) {
+        if (p.NACC == 4) return conv_umma_kernel<1, 4, 2>;
+        if (p.NACC == 2) return conv_umma_kernel<1, 2, 2>;
+        return conv_umma_kernel<1, 1, 2>;
+    }
+    return p.KC == 64 ? conv_umma_kernel<0, 1, 4> : conv_umma_kernel<0, 1, 2>;
+}
+}  // namespace
+
 cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t stream) {
     (void)op;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-        if (e != cudaSuccess) return e;
+        KernelFn all[5] = {conv_umma_kernel<1, 4, 2>, conv_umma_kernel<1, 2, 2>, conv_umma_kernel<1, 1, 2>, conv_umma_kernel<0, 1, 4>,
+                           conv_umma_kernel<0, 1, 2>};
+        for (KernelFn f : all) {
+            cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+            if (e != cudaSuccess) return e;
+        }
         attr_set = true;
     }
-    conv_umma_kernel<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
+    KernelFn kern = pick_kernel(plan->p);
+    if (env_int("TMD_UMMA_TRACE", 0)) {
+        UmmaParams p = plan->p;
+        cudaMalloc((void**)&p.trace, 16 * sizeof(long long));
+        cudaMemset(p.trace, 0, 16 * sizeof(long long));
+        kern<<<plan->grid, kThreads, plan->smem, stream>>>(p);
+        cudaDeviceSynchronize();
+        long long t[16];
+        cudaMemcpy(t, p.trace, sizeof(t), cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        const long long mmas = t[6] * (p.mode ? 27 : p.taps) * p.nkc * p.NACC * (p.KC / 16);
+        fprintf(stderr, "[umma trace] Ci=%d Co=%d %dx%dx%d mode=%d NACC=%d tiles=%d grid=%d | mma warp: total %lld cyc, wait acc %lld, wait A %lld, "
+                "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld\n",
+                p.Ci, p.Co, p.N, p.H, p.W, p.mode, p.NACC, p.num_tiles, plan->grid, t[0], t[1], t[2], t[3], t[4],
+                mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9]);
+        return cudaGetLastError();
+    }
+    kern<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
     return cudaGetLastError();
 }
 

@@ -63,12 +63,14 @@ struct ProfSpan {
     cudaEvent_t a, b;
     int kind;
     double flops, bytes;
+    const char* label;
 };
 using LaunchFn = std::function<cudaError_t(cudaStream_t)>;
 struct Launch {       // one kernel launch of the plan + what it costs algorithmically (bench.py's roofline)
     LaunchFn fn;
     int kind = TMD_K_ELEMENTWISE;
     double flops = 0.0, bytes = 0.0;
+    std::string label;
     cudaError_t operator()(cudaStream_t s) const { return fn(s); }
 };
 
@@ -411,9 +413,9 @@ struct Planner {
     const char* err = nullptr;
 
     size_t vox(int lvl) const { return (size_t)B * N * (H >> lvl) * (W >> lvl); }
-    void push(int kind, double flops, double bytes, LaunchFn fn) {
+    void push(int kind, double flops, double bytes, LaunchFn fn, const std::string& label = "") {
         Launch l;
-        l.fn = std::move(fn); l.kind = kind; l.flops = flops; l.bytes = bytes;
+        l.fn = std::move(fn); l.kind = kind; l.flops = flops; l.bytes = bytes; l.label = label;
         ops->push_back(std::move(l));
     }
 
@@ -473,15 +475,19 @@ struct Planner {
         if (add1.p) bytes += ovox / 4 * cw.Co * e->esize;
         if (hf) bytes += 3 * ovox * cw.Co * e->esize;
         const int kind = cw.taps == 27 ? TMD_K_CONV3 : TMD_K_CONV1;
+        char lb[160];
+        snprintf(lb, sizeof(lb), "%s Ci=%d Co=%d L%d %s", wname.c_str(), cw.Ci, cw.Co, lvl,
+                 mode == CONV_POOL ? "pool" : (mode == CONV_UPSAMPLE ? "up" : "same"));
+        const std::string label(lb);
         if (e->dtype == TMD_F32) {
-            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); });
+            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); }, label);
         } else if (conv_umma_supported(op)) {
             UmmaPlan* plan = conv_umma_plan_create(op);
             if (!plan) { err = "tensor map creation failed"; return; }
             e->plans.push_back(plan);
-            push(kind, flops, bytes, [op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); });
+            push(kind, flops, bytes, [op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); }, label + " umma");
         } else {
-            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_bf16(op, s); });
+            push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_bf16(op, s); }, label + " simt");
         }
     }
 
@@ -726,7 +732,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
 
 // Profiling (tmd_profile_begin/end): every launch is bracketed by a CUDA event pair on the launching
 // stream; the pairs are resolved into per-kind totals at tmd_profile_end.
-int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t s, bool begin) {
+int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t s, bool begin, const char* label = "") {
     if (!e->profiling) return 0;
     if (begin) {
         if (e->prof_used == e->prof_events.size()) {
@@ -736,7 +742,7 @@ int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t 
             e->prof_events.push_back(sp);
         }
         ProfSpan& sp = e->prof_events[e->prof_used];
-        sp.kind = kind; sp.flops = flops; sp.bytes = bytes;
+        sp.kind = kind; sp.flops = flops; sp.bytes = bytes; sp.label = label;
         CK(cudaEventRecord(sp.a, s));
     } else {
         CK(cudaEventRecord(e->prof_events[e->prof_used].b, s));
@@ -747,7 +753,7 @@ int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t 
 
 int run_ops(tmd_engine* e, std::vector<Launch>& ops, cudaStream_t s) {
     for (auto& op : ops) {
-        if (prof_mark(e, op.kind, op.flops, op.bytes, s, true)) return 1;
+        if (prof_mark(e, op.kind, op.flops, op.bytes, s, true, op.label.c_str())) return 1;
         cudaError_t err = op(s);
         if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
         if (prof_mark(e, op.kind, op.flops, op.bytes, s, false)) return 1;
@@ -857,20 +863,24 @@ extern "C" int tmd_profile_begin(tmd_handle h) {
     return 0;
 }
 
-extern "C" int tmd_profile_end(tmd_handle h, tmd_profile* out) {
+extern "C" int tmd_profile_end(tmd_handle h, tmd_profile* out, const char* csv_path) {
     if (!h || !out) return fail("tmd_profile_end: null argument");
     if (!h->profiling) return fail("tmd_profile_end: tmd_profile_begin was not called");
     h->profiling = false;
     memset(out, 0, sizeof(*out));
     CK(cudaSetDevice(h->device));
     CK(cudaDeviceSynchronize());
+    FILE* csv = csv_path ? fopen(csv_path, "w") : nullptr;
+    if (csv) fprintf(csv, "index,kind,label,ms,flops,bytes\n");
     for (size_t i = 0; i < h->prof_used; ++i) {
         const ProfSpan& sp = h->prof_events[i];
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        if (csv) fprintf(csv, "%zu,%d,%s,%.6f,%.0f,%.0f\n", i, sp.kind, sp.label ? sp.label : "", ms, sp.flops, sp.bytes);
         tmd_profile_kind& k = out->kind[sp.kind];
         k.ms += ms; k.flops += sp.flops; k.bytes += sp.bytes; k.launches += 1;
     }
+    if (csv) fclose(csv);
     h->prof_used = 0;
     return 0;
 }

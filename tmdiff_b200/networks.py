@@ -264,11 +264,11 @@ class WavBEST(nn.Module):
             raise RuntimeError("no engine yet: run the model once first")
         _lib.check(self._lib().tmd_profile_begin(self._handle))
 
-    def profile_end(self):
+    def profile_end(self, csv_path=None):
         """{kind: {"ms", "flops", "bytes", "launches"}} summed over the launches since profile_begin
         (device time from CUDA events on the launching stream; algorithmic flops / bytes)."""
         prof = _lib.Profile()
-        _lib.check(self._lib().tmd_profile_end(self._handle, C.byref(prof)))
+        _lib.check(self._lib().tmd_profile_end(self._handle, C.byref(prof), csv_path.encode() if csv_path else None))
         return {name: {"ms": k.ms, "flops": k.flops, "bytes": k.bytes, "launches": int(k.launches)}
                 for name, k in zip(_lib.KIND_NAMES, prof.kind)}
 
