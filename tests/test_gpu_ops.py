@@ -70,6 +70,9 @@ CONV_CASES = [
     (2, 96, 32, 4, 32, 32, 3),       # 3 K-chunks, 4 accumulators
     (5, 64, 64, 4, 4, 4, 3),         # batch folded into the 128-row tile
     (3, 192, 48, 2, 8, 16, 1),
+    (1, 32, 32, 8, 16, 24, 3),       # 8 accumulators per tile, merged-dz MMAs (N = 96)
+    (2, 64, 48, 2, 32, 16, 3),       # 2 accumulators, merged (N = 144)
+    (1, 32, 16, 6, 16, 8, 3),        # band count 6 -> 2 accumulators, three n-tiles
 ]
 
 

@@ -130,12 +130,9 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// K-major shared-memory matrix descriptor (tcgen05 "smem descriptor"): 8-row swizzle atoms of
-// `row_bytes` per row, atoms `sbo` bytes apart.
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo16, uint32_t layout_type) {
-    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)sbo16 << 32) | ((uint64_t)1 << 46) |
-           ((uint64_t)layout_type << 61);
-}
+// K-major shared-memory matrix descriptors (tcgen05 "smem descriptor") are assembled in the MMA loop:
+// start address >> 4 in bits [0,14), LBO = 1 at [16,30), SBO (8-row swizzle atom pitch) >> 4 at [32,46),
+// version 1 at [46,48), swizzle mode at [61,64).
 
 // ------------------------------------------------------------------------------------------
 // epilogue helpers (8 consecutive output channels = one 16-byte bf16 vector)
@@ -280,6 +277,16 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int t) {
 // Warp-uniform control flow throughout: every lane of a role's warp runs the loops and one elected
 // lane issues the TMA / tcgen05 instructions, so their operands stay in uniform registers (a
 // divergent `lane == 0` branch makes ptxas wrap every UTCHMMA in an election loop).
+// Issue order of the input planes q = -1..NACC of a haloed box for the merged-dz MMAs, and how many
+// leading entries of that order overwrite (their column spans tile the NACC accumulators exactly).
+template <int NACC> __device__ __forceinline__ constexpr int merge_order(int i) {
+    if (NACC == 4) { constexpr int o[6] = {1, 4, -1, 0, 2, 3}; return o[i]; }      // q=1 -> planes 2,1,0 ; q=4 -> plane 3
+    if (NACC == 2) { constexpr int o[4] = {0, -1, 1, 2}; return o[i]; }            // q=0 -> planes 1,0
+    if (NACC == 8) { constexpr int o[10] = {1, 4, 7, -1, 0, 2, 3, 5, 6, 8}; return o[i]; }   // 2,1,0 ; 5,4,3 ; 7,6 (q=7: dz 1,2)
+    return i - 1;                                                                  // NACC == 1: q=-1 -> plane 0
+}
+template <int NACC> __device__ __forceinline__ constexpr int merge_fresh() { return NACC == 4 ? 2 : (NACC == 8 ? 3 : 1); }
+
 __device__ __forceinline__ uint32_t elect_one() {
     uint32_t pred;
     asm volatile(
@@ -290,7 +297,7 @@ __device__ __forceinline__ uint32_t elect_one() {
     return pred;
 }
 
-template <int MODE, int NACC, int KMMA>
+template <int MODE, int NACC, int KMMA, bool MERGE>
 __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_constant__ UmmaParams P) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 4];
@@ -326,7 +333,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 
     constexpr int KC = KMMA * 16;
     const int ngroups = MODE ? 3 : P.taps;              // tap groups that need their own activation box
-    constexpr int taps_per_stage = MODE ? 9 : 1;
+    constexpr int b_stages_per_a = MODE ? 3 : 1;        // weight stages consumed per activation stage
     const int nkc = P.nkc;
 
     if (warp == 0) {
@@ -366,14 +373,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             for (int g = 0; g < ngroups; ++g)
                 for (int kc = 0; kc < nkc; ++kc)
 #pragma unroll 1
-                    for (int t = 0; t < taps_per_stage; ++t) {
-                        const int tap = MODE ? t * 3 + g : g;          // (dz*3+dy)*3+dx
+                    for (int t = 0; t < b_stages_per_a; ++t) {           // REUSE: t = dy
                         mbar_wait(b_empty(s), ph);
                         if (elect_one()) {
                             if (P.dbg & 4) mbar_arrive(b_full(s));
                             else {
-                                mbar_expect_tx(b_full(s), P.b_tile_bytes);
-                                tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB, b_full(s), tap * P.Ci + kc * KC, 0);
+                                const uint32_t dst = b_base + s * P.b_tile_stride;
+                                if (MODE) {
+                                    mbar_expect_tx(b_full(s), 3 * P.b_tile_bytes);
+#pragma unroll
+                                    for (int dz = 0; dz < 3; ++dz)       // tap = (dz*3+dy)*3+dx; rows [dz*Co, (dz+1)*Co) of the stage
+                                        tma_load_2d(dst + dz * P.b_tile_bytes, &P.tmB, b_full(s), ((dz * 3 + t) * 3 + g) * P.Ci + kc * KC, 0);
+                                } else {
+                                    mbar_expect_tx(b_full(s), P.b_tile_bytes);
+                                    tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, 0);
+                                }
                             }
                         }
                         __syncwarp();
@@ -391,7 +405,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const uint32_t plane16 = ((uint32_t)(P.TH + 2) * P.TW * P.row_bytes) >> 4;   // one haloed band plane
         const uint32_t line16 = ((uint32_t)P.TW * P.row_bytes) >> 4;                  // one line of 8 voxels = one swizzle atom
         const uint32_t idesc = P.idesc;
+        const uint32_t idesc_base = P.idesc & ~(0x3Fu << 17);
         const uint32_t Co = P.Co;
+        const uint32_t co16 = (Co * P.row_bytes) >> 4;                                 // one tap's weight rows
         const bool do_mma = !(P.dbg & 1);
         uint32_t sa = 0, pha = 0, sb = 0, phb = 0, lt = 0;
         long long tw_acc = 0, tw_a = 0, tw_b = 0, t_issue = 0, t_all0 = clock64(), tq = 0;
@@ -412,25 +428,57 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     tc_fence_after();
                     const uint32_t a_lo = a_lo0 + sa * a_stride16;
 #pragma unroll 1
-                    for (int t = 0; t < taps_per_stage; ++t) {
+                    for (int t = 0; t < b_stages_per_a; ++t) {           // REUSE: t = dy
                         if (tr) tq = clock64();
                         mbar_wait(b_full(sb), phb);
                         if (tr) { tw_b += clock64() - tq; tq = clock64(); }
                         tc_fence_after();
                         if (elect_one()) {
                             const uint32_t b_lo = b_lo0 + sb * b_stride16;
-                            const uint32_t a_tap = MODE ? a_lo + (uint32_t)(t / 3) * plane16 + (uint32_t)(t % 3) * line16 : a_lo;
                             if (do_mma) {
+                                if (!MODE) {
 #pragma unroll
-                                for (int p = 0; p < NACC; ++p)
+                                    for (int k = 0; k < KMMA; ++k)
+                                        tc_mma_bf16(d0, ((uint64_t)desc_hi << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
+                                                    k == 0 ? fresh : 1u);
+                                } else if (MERGE) {
+                                    // One MMA per input plane q (box plane q+1) and K=16 slice: its A view feeds the output planes
+                                    // q+1, q, q-1 through the taps dz = 0, 1, 2, whose weights are consecutive row blocks of the
+                                    // stage and whose accumulators are consecutive TMEM column blocks (planes in decreasing order).
+                                    // Order: first the MMAs whose column spans tile the accumulators (they overwrite at the
+                                    // start of a tile), then the rest.
 #pragma unroll
-                                    for (int k = 0; k < KMMA; ++k) {
-                                        const uint64_t ad = ((uint64_t)desc_hi << 32) | (a_tap + p * plane16 + k * 2);
-                                        const uint64_t bd = ((uint64_t)desc_hi << 32) | (b_lo + k * 2);
-                                        tc_mma_bf16(d0 + p * Co, ad, bd, idesc, k == 0 ? fresh : 1u);
+                                    for (int i = 0; i < NACC + 2; ++i) {
+                                        const int q = merge_order<NACC>(i);                  // -1 .. NACC
+                                        const int dz_lo = q + 1 > NACC - 1 ? q + 1 - (NACC - 1) : 0;   // p = q+1-dz <= NACC-1
+                                        const int dz_hi = q + 1 < 2 ? q + 1 : 2;                         // p >= 0
+                                        const int nblk = dz_hi - dz_lo + 1;
+                                        const int p_top = q + 1 - dz_lo;
+                                        const uint32_t id = idesc_base | ((uint32_t)((nblk * Co) >> 3) << 17);
+                                        const uint32_t a_view = a_lo + (uint32_t)(q + 1) * plane16 + (uint32_t)t * line16;
+                                        const uint32_t b_view = b_lo + (uint32_t)dz_lo * co16;
+                                        const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
+#pragma unroll
+                                        for (int k = 0; k < KMMA; ++k)
+                                            tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id,
+                                                        (k == 0 && i < merge_fresh<NACC>()) ? fresh : 1u);
                                     }
+                                } else {
+#pragma unroll
+                                    for (int dz = 0; dz < 3; ++dz)
+#pragma unroll
+                                        for (int pp = 0; pp < NACC; ++pp) {
+                                            const uint32_t a_view = a_lo + (uint32_t)(pp + dz) * plane16 + (uint32_t)t * line16;
+                                            const uint32_t b_view = b_lo + (uint32_t)dz * co16;
+                                            const uint32_t d = d0 + (uint32_t)(NACC - 1 - pp) * Co;
+#pragma unroll
+                                            for (int k = 0; k < KMMA; ++k)
+                                                tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
+                                                            (k == 0 && dz == 0) ? fresh : 1u);
+                                        }
+                                }
                             }
-                            tc_commit(b_empty(sb));              // weight tile free once these MMAs retire
+                            tc_commit(b_empty(sb));              // weight stage free once these MMAs retire
                         }
                         __syncwarp();
                         fresh = 1;
@@ -475,7 +523,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             for (int p = 0; p < NACC; ++p) {
                 const int n = tc.n0 + n_off + p;
                 const bool valid = b < P.B && n < P.N && y < P.H && x < P.W && !(P.dbg & 8);
-                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + p) * P.Co;
+                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - p)) * P.Co;
                 for (int c0 = 0; c0 < P.Co; c0 += 16) {
                     float acc[16];
                     tc_ld16(t_row + c0, acc);
@@ -593,7 +641,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         // accumulators per tile: two sets must fit the 512 TMEM columns, the haloed box must leave room for
         // two stages in shared memory, and NACC divides the band count (no plane is computed for nothing)
         int cap = 256 / op.Co;
-        if (cap > 4) cap = 4;
+        if (cap > 8) cap = 8;
         P.NACC = 1;
         for (int c = 2; c <= cap; c *= 2)
             if (op.N % c == 0) P.NACC = c;
@@ -624,7 +672,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.dbg = env_int("TMD_UMMA_DEBUG", 0);
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
     P.b_tile_bytes = op.Co * P.row_bytes;
-    P.b_tile_stride = (P.b_tile_bytes + 1023u) & ~1023u;
+    P.b_tile_stride = ((P.mode ? 3 : 1) * P.b_tile_bytes + 1023u) & ~1023u;    // REUSE: a weight stage holds the 3 dz taps of a (dy,dx)
     int cols = 2 * P.NACC * op.Co;
     P.tmem_cols = 32;
     while ((int)P.tmem_cols < cols) P.tmem_cols *= 2;
@@ -634,10 +682,10 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     // ring depths from the shared-memory budget
     const size_t budget = 220 * 1024;
     P.SA = P.mode ? 2 : 4;
-    if ((size_t)P.SA * P.a_stage_stride > budget * 3 / 4) P.SA = 1;
+    while (P.SA > 1 && (size_t)P.SA * P.a_stage_stride + 2 * (size_t)P.b_tile_stride > budget) --P.SA;
     size_t left = budget - (size_t)P.SA * P.a_stage_stride;
     P.SB = (int)(left / P.b_tile_stride);
-    const int want_sb = P.mode ? 12 : P.SA;
+    const int want_sb = P.mode ? 6 : P.SA;
     if (P.SB > want_sb) P.SB = want_sb;
     if (P.SB > kMaxSB) P.SB = kMaxSB;
     if (P.SB < 2 || P.SA < 1) { delete plan; return nullptr; }
@@ -674,13 +722,16 @@ void conv_umma_plan_destroy(UmmaPlan* p) { delete p; }
 
 namespace {
 typedef void (*KernelFn)(const UmmaParams);
+// the three dz taps that share an activation view are issued as one MMA when N = 3*Co fits an instruction
+bool merged(const UmmaParams& p) { return p.mode && p.NACC > 1 && 3 * p.Co <= 256; }
 KernelFn pick_kernel(const UmmaParams& p) {
     if (p.mode) {
-        if (p.NACC == 4) return conv_umma_kernel<1, 4, 2>;
-        if (p.NACC == 2) return conv_umma_kernel<1, 2, 2>;
-        return conv_umma_kernel<1, 1, 2>;
+        if (p.NACC == 8) return conv_umma_kernel<1, 8, 2, true>;
+        if (p.NACC == 4) return conv_umma_kernel<1, 4, 2, true>;
+        if (p.NACC == 2) return merged(p) ? conv_umma_kernel<1, 2, 2, true> : conv_umma_kernel<1, 2, 2, false>;
+        return conv_umma_kernel<1, 1, 2, false>;
     }
-    return p.KC == 64 ? conv_umma_kernel<0, 1, 4> : conv_umma_kernel<0, 1, 2>;
+    return p.KC == 64 ? conv_umma_kernel<0, 1, 4, false> : conv_umma_kernel<0, 1, 2, false>;
 }
 }  // namespace
 
@@ -688,8 +739,9 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
     (void)op;
     static bool attr_set = false;
     if (!attr_set) {
-        KernelFn all[5] = {conv_umma_kernel<1, 4, 2>, conv_umma_kernel<1, 2, 2>, conv_umma_kernel<1, 1, 2>, conv_umma_kernel<0, 1, 4>,
-                           conv_umma_kernel<0, 1, 2>};
+        KernelFn all[7] = {conv_umma_kernel<1, 8, 2, true>, conv_umma_kernel<1, 4, 2, true>, conv_umma_kernel<1, 2, 2, true>,
+                           conv_umma_kernel<1, 2, 2, false>, conv_umma_kernel<1, 1, 2, false>, conv_umma_kernel<0, 1, 4, false>,
+                           conv_umma_kernel<0, 1, 2, false>};
         for (KernelFn f : all) {
             cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
             if (e != cudaSuccess) return e;
