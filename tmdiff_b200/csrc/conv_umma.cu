@@ -37,7 +37,7 @@ namespace tmd {
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;          // 4 role warps + 8 epilogue warps
 constexpr int kMaxSA = 4, kMaxSB = 16;
 
 struct UmmaParams {
@@ -163,17 +163,47 @@ __device__ __forceinline__ void load8_f32(const float* p, float v[8]) {
 
 // v = accumulator + bias for channels [co, co+8) of one output voxel: residual adds, raw view and
 // the activated views (same contract as epilogue_store4 in conv_op.h).
-__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8]) {
+__device__ __forceinline__ void unpack8_bf16(const uint4& t, float v[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+
+// Residual operands of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
+struct Resid { uint4 a0[2], a1[2]; };
+__device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, bool valid, Resid& r) {
+    typedef __nv_bfloat16 T;
+    r.a0[0] = r.a0[1] = r.a1[0] = r.a1[1] = make_uint4(0, 0, 0, 0);
+    if (!valid) return;
+    if (e.add0) {
+        const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co);
+        r.a0[0] = q[0]; r.a0[1] = q[1];
+    }
+    if (e.add1) {
+        const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co);
+        r.a1[0] = q[0]; r.a1[1] = q[1];
+    }
+}
+
+template <bool kPre>
+__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8], const uint4* pre0 = nullptr,
+                                             const uint4* pre1 = nullptr) {
     typedef __nv_bfloat16 T;
     if (e.add0) {
         float a[8];
-        load8_bf16(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, a);
+        if (kPre) unpack8_bf16(*pre0, a);
+        else load8_bf16(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, a);
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] += a[i];
     }
     if (e.add1) {
         float a[8];
-        load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
+        if (kPre) unpack8_bf16(*pre1, a);
+        else load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] += a[i];
     }
@@ -198,7 +228,7 @@ __device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_
 
 // One 16-channel slab of one accumulator row.  All 32 lanes of the warp call this together (the
 // POOL mode exchanges rows through shuffles); `valid` guards the stores only.
-__device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int n, int y, int x, bool valid) {
+__device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int n, int y, int x, bool valid, const Resid& pre) {
     const ConvEpilogue& e = P.epi;
     float bias[16];
     if (e.bias) {
@@ -218,7 +248,7 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
-            store_views8(e, b, ovox, hvox, co + 8 * h, v);
+            store_views8<true>(e, b, ovox, hvox, co + 8 * h, v, &pre.a0[h], &pre.a1[h]);
         }
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
@@ -243,7 +273,7 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
                 store8_bf16(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co + 8 * h, hl + 8 * h);
                 store8_bf16(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co + 8 * h, hh + 8 * h);
             }
-            store_views8(e, b, ovox, 0, co + 8 * h, ll + 8 * h);
+            store_views8<false>(e, b, ovox, 0, co + 8 * h, ll + 8 * h);
         }
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
@@ -255,7 +285,7 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
                 float v[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
-                store_views8(e, b, ovox, 0, co + 8 * h, v);
+                store_views8<false>(e, b, ovox, 0, co + 8 * h, v);
             }
         }
     }
@@ -318,7 +348,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     if (threadIdx.x == 0) {
         for (int s = 0; s < P.SA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
         for (int s = 0; s < P.SB; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 4); }
+        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 3) {
@@ -499,6 +529,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     } else if (warp >= 4) {
         // ================= epilogue =================
         const int q = warp & 3;                           // TMEM lane quarter this warp may read
+        const int sub = (warp - 4) >> 2;                  // which of the quarter's two warps
         const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
         uint32_t lt = 0;
         long long tw_full = 0, t_all0 = clock64(), tq = 0;
@@ -520,15 +551,38 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 b = tc.b0 + t;
             }
             x += tc.x0; y += tc.y0;
-            for (int p = 0; p < NACC; ++p) {
-                const int n = tc.n0 + n_off + p;
-                const bool valid = b < P.B && n < P.N && y < P.H && x < P.W && !(P.dbg & 8);
-                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - p)) * P.Co;
-                for (int c0 = 0; c0 < P.Co; c0 += 16) {
-                    float acc[16];
-                    tc_ld16(t_row + c0, acc);
-                    epilogue16(P, acc, c0, b, n, y, x, valid);
+            // work items = (plane, 16-channel slab); the two warps of a lane quarter take alternate items and
+            // fetch the residual operands of their next item before touching the current accumulator slab
+            const int nslab = P.Co >> 4, nitems = NACC * nslab;
+            const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
+            const bool normal = P.epi.mode == CONV_NORMAL;
+            auto item_vox = [&](int it, int& n, size_t& ovox, size_t& hvox, bool& valid) {
+                n = tc.n0 + n_off + it / nslab;
+                valid = in_tile && n < P.N;
+                const size_t bn = (size_t)b * P.N + n;
+                ovox = (bn * P.H + y) * P.W + x;
+                hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+            };
+            Resid cur, nxt;
+            {
+                int n; size_t ov, hv; bool vl;
+                item_vox(sub, n, ov, hv, vl);
+                if (normal && sub < nitems) load_resid(P.epi, ov, hv, (sub % nslab) * 16, vl, cur);
+            }
+            for (int it = sub; it < nitems; it += 2) {
+                if (normal && it + 2 < nitems) {
+                    int n; size_t ov, hv; bool vl;
+                    item_vox(it + 2, n, ov, hv, vl);
+                    load_resid(P.epi, ov, hv, ((it + 2) % nslab) * 16, vl, nxt);
                 }
+                int n; size_t ov, hv; bool valid;
+                item_vox(it, n, ov, hv, valid);
+                const int p = it / nslab, c0 = (it % nslab) * 16;
+                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - p)) * P.Co;
+                float acc[16];
+                tc_ld16(t_row + c0, acc);
+                epilogue16(P, acc, c0, b, n, y, x, valid, cur);
+                cur = nxt;
             }
             tc_fence_before();
             __syncwarp();
