@@ -37,6 +37,7 @@ struct ConvEpilogue {
     const float* tb[2]; int ld_tb;   // [B][ld_tb] fp32 (already offset to this module's slice) or null
     const float* sc[2]; int ld_sc;   // [B][ld_sc] fp32 or null
     void* hf_out[3]; int ld_hf;      // POOL only: LH, HL, HH
+    int dbg;                         // diagnostics of the tcgen05 kernel (TMD_UMMA_DEBUG), 0 in production
 };
 
 struct ConvOp {

@@ -37,7 +37,8 @@ namespace tmd {
 
 namespace {
 
-constexpr int kThreads = 384;          // 4 role warps + 8 epilogue warps
+constexpr int kEpiPerQuarter = 3;      // epilogue warps per TMEM lane quarter
+constexpr int kThreads = 128 + 128 * kEpiPerQuarter;   // 4 role warps + 16 epilogue warps
 constexpr int kMaxSA = 4, kMaxSB = 16;
 
 struct UmmaParams {
@@ -174,24 +175,28 @@ __device__ __forceinline__ void unpack8_bf16(const uint4& t, float v[8]) {
 }
 
 // Residual operands of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
-struct Resid { uint4 a0[2], a1[2]; };
-__device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, bool valid, Resid& r) {
+struct Resid { uint4 a0[2]; };
+__device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, int co, bool valid, Resid& r) {
     typedef __nv_bfloat16 T;
-    r.a0[0] = r.a0[1] = r.a1[0] = r.a1[1] = make_uint4(0, 0, 0, 0);
-    if (!valid) return;
+    r.a0[0] = r.a0[1] = make_uint4(0, 0, 0, 0);
+    if (!valid || (e.dbg & 32)) return;
     if (e.add0) {
         const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co);
         r.a0[0] = q[0]; r.a0[1] = q[1];
     }
-    if (e.add1) {
-        const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co);
-        r.a1[0] = q[0]; r.a1[1] = q[1];
-    }
+}
+
+// Swish through the hardware tanh: x*sigmoid(x) = h + h*tanh(h), h = x/2 (one MUFU op; its 2^-11 relative
+// error is below the bf16 rounding of the stored activation).
+__device__ __forceinline__ float swish_tanh(float x) {
+    const float h = 0.5f * x;
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
 }
 
 template <bool kPre>
-__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8], const uint4* pre0 = nullptr,
-                                             const uint4* pre1 = nullptr) {
+__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8], const uint4* pre0 = nullptr) {
     typedef __nv_bfloat16 T;
     if (e.add0) {
         float a[8];
@@ -202,12 +207,11 @@ __device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_
     }
     if (e.add1) {
         float a[8];
-        if (kPre) unpack8_bf16(*pre1, a);
-        else load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
+        load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] += a[i];
     }
-    if (e.raw_out) store8_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
+    if (e.raw_out && !(e.dbg & 64)) store8_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         if (!e.act_out[k]) continue;
@@ -218,11 +222,11 @@ __device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_
         for (int i = 0; i < 8; ++i) {
             float x = v[i];
             if (e.tb[k]) x += t[i];
-            x = swish<true>(x);
+            if (!(e.dbg & 16)) x = swish_tanh(x);
             if (e.sc[k]) x *= s[i];
             u[i] = x;
         }
-        store8_bf16(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, u);
+        if (!(e.dbg & 128)) store8_bf16(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, u);
     }
 }
 
@@ -248,32 +252,34 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
-            store_views8<true>(e, b, ovox, hvox, co + 8 * h, v, &pre.a0[h], &pre.a1[h]);
+            store_views8<true>(e, b, ovox, hvox, co + 8 * h, v, &pre.a0[h]);
         }
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
-        float ll[16], lh[16], hl[16], hh[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const float t = __shfl_xor_sync(0xffffffffu, acc[i], 1);
-            const float L = acc[i] + t, D = acc[i] - t;                 // a+b, a-b   (on the even-x lane)
-            const float u = __shfl_xor_sync(0xffffffffu, L, P.TW), w = __shfl_xor_sync(0xffffffffu, D, P.TW);
-            ll[i] = (L + u) * 0.25f + bias[i];                           // LL/2 == 2x2 average (:396)
-            hl[i] = (L - u) * 0.5f;                                      // (a+b)-(c+d)
-            lh[i] = (D + w) * 0.5f;                                      // (a-b)+(c-d)
-            hh[i] = (D - w) * 0.5f;                                      // (a-b)-(c-d)
-        }
-        if (!valid || (x & 1) || (y & 1)) return;
+        const bool writer = valid && !(x & 1) && !(y & 1);
         const size_t ovox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
+            float ll[8], lh[8], hl[8], hh[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float a = acc[8 * h + i];
+                const float t = __shfl_xor_sync(0xffffffffu, a, 1);
+                const float L = a + t, D = a - t;                           // a+b, a-b   (on the even-x lane)
+                const float u = __shfl_xor_sync(0xffffffffu, L, P.TW), w = __shfl_xor_sync(0xffffffffu, D, P.TW);
+                ll[i] = (L + u) * 0.25f + bias[8 * h + i];                   // LL/2 == 2x2 average (:396)
+                hl[i] = (L - u) * 0.5f;                                      // (a+b)-(c+d)
+                lh[i] = (D + w) * 0.5f;                                      // (a-b)+(c-d)
+                hh[i] = (D - w) * 0.5f;                                      // (a-b)-(c-d)
+            }
+            if (!writer) continue;
             if (e.hf_out[0]) {
                 typedef __nv_bfloat16 T;
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co + 8 * h, lh + 8 * h);
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co + 8 * h, hl + 8 * h);
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co + 8 * h, hh + 8 * h);
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co + 8 * h, lh);
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co + 8 * h, hl);
+                store8_bf16(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co + 8 * h, hh);
             }
-            store_views8<false>(e, b, ovox, 0, co + 8 * h, ll + 8 * h);
+            store_views8<false>(e, b, ovox, 0, co + 8 * h, ll);
         }
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
@@ -348,7 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     if (threadIdx.x == 0) {
         for (int s = 0; s < P.SA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
         for (int s = 0; s < P.SB; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 8); }
+        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 4 * kEpiPerQuarter); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 3) {
@@ -529,7 +535,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     } else if (warp >= 4) {
         // ================= epilogue =================
         const int q = warp & 3;                           // TMEM lane quarter this warp may read
-        const int sub = (warp - 4) >> 2;                  // which of the quarter's two warps
+        const int sub = (warp - 4) >> 2;                  // which of the quarter's warps
         const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
         uint32_t lt = 0;
         long long tw_full = 0, t_all0 = clock64(), tq = 0;
@@ -551,7 +557,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 b = tc.b0 + t;
             }
             x += tc.x0; y += tc.y0;
-            // work items = (plane, 16-channel slab); the two warps of a lane quarter take alternate items and
+            // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin and
             // fetch the residual operands of their next item before touching the current accumulator slab
             const int nslab = P.Co >> 4, nitems = NACC * nslab;
             const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
@@ -567,13 +573,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             {
                 int n; size_t ov, hv; bool vl;
                 item_vox(sub, n, ov, hv, vl);
-                if (normal && sub < nitems) load_resid(P.epi, ov, hv, (sub % nslab) * 16, vl, cur);
+                if (normal && sub < nitems) load_resid(P.epi, ov, (sub % nslab) * 16, vl, cur);
             }
-            for (int it = sub; it < nitems; it += 2) {
-                if (normal && it + 2 < nitems) {
+            for (int it = sub; it < nitems; it += kEpiPerQuarter) {
+                if (normal && it + kEpiPerQuarter < nitems) {
                     int n; size_t ov, hv; bool vl;
-                    item_vox(it + 2, n, ov, hv, vl);
-                    load_resid(P.epi, ov, hv, ((it + 2) % nslab) * 16, vl, nxt);
+                    item_vox(it + kEpiPerQuarter, n, ov, hv, vl);
+                    load_resid(P.epi, ov, ((it + kEpiPerQuarter) % nslab) * 16, vl, nxt);
                 }
                 int n; size_t ov, hv; bool valid;
                 item_vox(it, n, ov, hv, valid);
@@ -724,6 +730,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.a_piece_bytes = boxA[1] * boxA[2] * boxA[3] * boxA[4] * P.row_bytes;
     P.a_stage_bytes = P.mode ? P.a_piece_bytes * P.a_planes * P.a_ysplit : P.a_piece_bytes;
     P.dbg = env_int("TMD_UMMA_DEBUG", 0);
+    P.epi.dbg = P.dbg;
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
     P.b_tile_bytes = op.Co * P.row_bytes;
     P.b_tile_stride = ((P.mode ? 3 : 1) * P.b_tile_bytes + 1023u) & ~1023u;    // REUSE: a weight stage holds the 3 dz taps of a (dy,dx)
