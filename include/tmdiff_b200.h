@@ -52,11 +52,21 @@ typedef struct {
     float   sigma_t;       /* marginal_std(t)                                                  */
 } tmd_eval;
 
-/* dst = (c1*x - c2*m) [+ c3*(m1 - m)] -- the dpmsolver++ update family
- * (core/dpm_solver_pytorch.py:589-592, :648-658, :744-760), evaluated in that order in fp32. */
+/* One solver update, evaluated in fp32 in the reference's order of operations.
+ *   form 0 (singlestep family, core/dpm_solver_pytorch.py:589-592, :648-658, :744-760):
+ *       dst = (c1*x - c2*m) [+ c3*(m1 - m)]                       (m1 < 0 => no third term)
+ *   form 1 (multistep_dpm_solver_second_update, :817-873, dpmsolver++ / 'dpmsolver'):
+ *       D1_0 = k[0]*(m - m1);  dst = c1*x - c2*m - c3*D1_0        (k[0] = 1/r0, c3 = 0.5*(alpha_t*phi_1))
+ *   form 2 (multistep_dpm_solver_third_update, :875-927):
+ *       D1_0 = k[0]*(m - m1); D1_1 = k[1]*(m1 - m2); D1 = D1_0 + k[2]*(D1_0 - D1_1); D2 = k[3]*(D1_0 - D1_1)
+ *       dst = c1*x - c2*m + c3*D1 - k[4]*D2                       (c3 = alpha_t*phi_2, k[4] = alpha_t*phi_3)
+ * m = newest model value (model_prev_0), m1 the one before, m2 the oldest. */
 typedef struct {
-    int32_t dst, x, m, m1; /* slots; m1 < 0 => no third term                                   */
+    int32_t dst, x, m, m1; /* slots                                                            */
     float   c1, c2, c3;
+    int32_t form;          /* 0 / 1 / 2 as above                                               */
+    int32_t m2;            /* slot (form 2 only)                                               */
+    float   k[5];
 } tmd_update;
 
 typedef struct {
@@ -67,6 +77,8 @@ typedef struct {
 
 enum { TMD_NUM_SLOTS = 8 };  /* slot 0 holds x_T on entry; the result is read from `result_slot` */
 
+enum { TMD_MODEL_X_START = 0, TMD_MODEL_NOISE = 1 };   /* model_wrapper(model_type=...) (:296-306) */
+
 typedef struct {
     const tmd_step* steps; /* host array                                                       */
     int32_t n_steps;
@@ -74,6 +86,12 @@ typedef struct {
     float   q_weight;      /* torch.quantile(|x0|, 0.995): rank = q*(n-1); q_lo = floor(rank), */
     int32_t q_lo;          /*   q_weight = rank - q_lo (fp32, as ATen computes them)  (:436)   */
     float   max_val;       /* thresholding_max_val (1.0)                              (:437)   */
+    int32_t model_type;    /* TMD_MODEL_X_START (sample_by_dpmsolver) or TMD_MODEL_NOISE
+                              (sample_by_dpmsolver_noise / _guidance, diffusion_general.py:257-335) */
+    int32_t cfg;           /* 1 = classifier-free guidance (model_wrapper :336-344): the condition bound by
+                              tmd_precompute_condition holds 2B patches [unconditional | conditional], x is
+                              evaluated against both halves and eps = eps_u + guidance_scale*(eps_c - eps_u) */
+    float   guidance_scale;
 } tmd_plan;
 
 const char* tmd_last_error(void);
@@ -108,7 +126,7 @@ int tmd_denoise(tmd_handle h, const float* x_t_dev, const float* t_input_dev, fl
 /* DPM_Solver.sample(x_T, ...) (core/dpm_solver_pytorch.py:1081-1289) as a straight-line program of
  * evaluations and updates prepared by the host (tmdiff_b200/dpm_solver.py).  x_T / out: device fp32
  * [B,bands,H,W].  trace_dev (optional, may be NULL): receives the raw network output of every
- * evaluation, [n_eval, B, bands, H, W]. */
+ * evaluation, [n_eval, B, bands, H, W] ([n_eval, 2B, ...] when plan->cfg). */
 int tmd_sample(tmd_handle h, const float* x_T_dev, const tmd_plan* plan, float* out_dev, float* trace_dev,
                void* stream);
 

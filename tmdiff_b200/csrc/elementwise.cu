@@ -398,6 +398,17 @@ __global__ void gather_rows_kernel(const float* __restrict__ table, const int* _
     if (j < width) out[(size_t)b * width + j] = table[(size_t)ids[b] * width + j];
 }
 
+__global__ void broadcast_rows_kernel(const float* __restrict__ row, float* __restrict__ out, int width) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < width) out[(size_t)blockIdx.y * width + j] = row[j];
+}
+
+cudaError_t broadcast_rows(const float* row, float* out, int B, int width, cudaStream_t s) {
+    dim3 grid(cdiv(width, 256), B);
+    broadcast_rows_kernel<<<grid, 256, 0, s>>>(row, out, width);
+    return cudaGetLastError();
+}
+
 cudaError_t gather_rows(const float* table, const int* ids, float* out, int B, int width, cudaStream_t s) {
     dim3 grid(cdiv(width, 256), B);
     gather_rows_kernel<<<grid, 256, 0, s>>>(table, ids, out, width);

@@ -76,6 +76,8 @@ struct Launch {       // one kernel launch of the plan + what it costs algorithm
 
 }  // namespace
 
+constexpr int kMaxPlanEvals = 256;   // evaluations per tmd_sample plan whose time tables are precomputed in one launch
+
 struct tmd_engine {
     tmd_config cfg{};
     int dtype = 0;
@@ -115,6 +117,11 @@ struct tmd_engine {
     float cur_t_scalar = 0.f;
     float* slots[TMD_NUM_SLOTS] = {};
     float* d_out = nullptr;
+    float* d_xdup = nullptr;            // [x | x] for classifier-free-guidance plans (x evaluated against both condition halves)
+    // tmd_sample: the time tables of every evaluation of a plan are computed by ONE launch up front
+    // (t is a host scalar per evaluation and shared by the batch); each evaluation then broadcasts its row.
+    float *d_tb_all = nullptr, *d_tin_all = nullptr;
+    const float* tb_bcast_src = nullptr;
     int64_t launches = 0;
     bool profiling = false;
     std::vector<ProfSpan> prof_events;
@@ -382,7 +389,8 @@ extern "C" int tmd_finalize_weights(tmd_handle h) {
         CK(cudaMemset(h->d_text, 0, (size_t)TMD_NUM_SENSORS * 768 * sizeof(float)));
     }
     if (h->dmalloc(&h->d_sc_sensor, (size_t)TMD_NUM_SENSORS * h->text_rows) || h->dmalloc(&h->d_tb, (size_t)MB * h->time_rows) ||
-        h->dmalloc(&h->d_sc, (size_t)MB * h->text_rows))
+        h->dmalloc(&h->d_sc, (size_t)MB * h->text_rows) || h->dmalloc(&h->d_tb_all, (size_t)kMaxPlanEvals * h->time_rows) ||
+        h->dmalloc(&h->d_tin_all, (size_t)kMaxPlanEvals))
         return 1;
     h->text_dirty = true;
     h->finalized = true;
@@ -564,7 +572,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         CK(cudaMalloc((void**)&e->arena, e->arena_size));
         for (int i = 0; i < TMD_NUM_SLOTS; ++i)
             if (e->dmalloc(&e->slots[i], v0)) return 1;
-        if (e->dmalloc(&e->d_out, v0)) return 1;
+        if (e->dmalloc(&e->d_out, v0) || e->dmalloc(&e->d_xdup, v0)) return 1;
     }
     Planner P{e, &e->pre_ops, B, N, H, W};
     const int dt = e->dtype;
@@ -635,6 +643,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     {
         const int E = e->cfg.embed_dim;
         P.push(TMD_K_COND, 0, ((double)tr * E + (double)B * tr) * 4, [=](cudaStream_t s) {
+            if (e->tb_bcast_src) return broadcast_rows(e->tb_bcast_src, e->d_tb, B, tr, s);
             return time_table(e->cur_t_dev, e->cur_t_scalar, e->d_freqs, e->cfg.inter_dim, e->d_e_w1, e->d_e_b1, e->d_e_w2, e->d_e_b2,
                               e->d_Wt, e->d_bt, e->d_embed, e->d_tb, B, E, tr, s);
         });
@@ -822,10 +831,32 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
     if (h->B == 0 || h->step_ops.empty()) return fail("tmd_sample: call tmd_precompute_condition first");
     cudaStream_t s = (cudaStream_t)stream;
     CK(cudaSetDevice(h->device));
-    const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * h->B;
+    const bool cfg = plan->cfg != 0;
+    if (cfg && (h->B % 2)) return fail("tmd_sample: a classifier-free-guidance plan needs 2B bound patches [uncond | cond], got %d", h->B);
+    if (plan->model_type != TMD_MODEL_X_START && plan->model_type != TMD_MODEL_NOISE) return fail("tmd_sample: bad model_type %d", plan->model_type);
+    const bool noise_type = plan->model_type == TMD_MODEL_NOISE;
+    const int Bx = cfg ? h->B / 2 : h->B;      // patches being sampled
+    const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * Bx, n_net = n_per * h->B;
     if (n_per > 51200) return fail("tmd_sample: %zu values per patch exceeds the in-shared-memory quantile select (51200)", n_per);
     auto slot_ok = [](int i) { return i >= 0 && i < TMD_NUM_SLOTS; };
     if (!slot_ok(plan->result_slot)) return fail("tmd_sample: bad result slot");
+
+    // every evaluation's time table in one launch (one CTA per evaluation), broadcast per evaluation below
+    std::vector<float> tin;
+    for (int i = 0; i < plan->n_steps; ++i)
+        if (plan->steps[i].kind == 0) tin.push_back(plan->steps[i].eval.t_input);
+    const bool pre_tb = !tin.empty() && (int)tin.size() <= kMaxPlanEvals;
+    if (pre_tb) {
+        CK(cudaMemcpyAsync(h->d_tin_all, tin.data(), tin.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+        if (prof_mark(h, TMD_K_COND, 0, ((double)h->time_rows * h->cfg.embed_dim + (double)tin.size() * h->time_rows) * 4, s, true, "time_table_all"))
+            return 1;
+        CK(time_table(h->d_tin_all, 0.f, h->d_freqs, h->cfg.inter_dim, h->d_e_w1, h->d_e_b1, h->d_e_w2, h->d_e_b2, h->d_Wt, h->d_bt,
+                      nullptr, h->d_tb_all, (int)tin.size(), h->cfg.embed_dim, h->time_rows, s));
+        if (prof_mark(h, TMD_K_COND, 0, 0, s, false)) return 1;
+        ++h->launches;
+    }
+    struct Unbind { tmd_engine* e; ~Unbind() { e->tb_bcast_src = nullptr; } } unbind{h};
+
     CK(cudaMemcpyAsync(h->slots[0], x_T, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
     int n_eval = 0;
     for (int i = 0; i < plan->n_steps; ++i) {
@@ -833,19 +864,33 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
         if (st.kind == 0) {
             const tmd_eval& ev = st.eval;
             if (!slot_ok(ev.src) || !slot_ok(ev.dst)) return fail("tmd_sample: bad slot in step %d", i);
-            float* net_out = trace ? trace + (size_t)n_eval * n : h->d_out;
-            if (denoise_impl(h, h->slots[ev.src], nullptr, ev.t_input, net_out, s)) return 1;
-            if (prof_mark(h, TMD_K_SOLVER, 0, 5.0 * n * 4, s, true)) return 1;   // x, out in; x0 written, re-read, re-written
-            CK(x0_threshold(h->slots[ev.src], net_out, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, h->B, (int)n_per, plan->q_lo,
-                            plan->q_weight, plan->max_val, s));
+            float* net_out = trace ? trace + (size_t)n_eval * n_net : h->d_out;
+            const float* net_in = h->slots[ev.src];
+            if (cfg) {   // x_in = cat([x] * 2)  (:338)
+                CK(cudaMemcpyAsync(h->d_xdup, net_in, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+                CK(cudaMemcpyAsync(h->d_xdup + n, net_in, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+                net_in = h->d_xdup;
+            }
+            h->tb_bcast_src = pre_tb ? h->d_tb_all + (size_t)n_eval * h->time_rows : nullptr;
+            if (denoise_impl(h, net_in, nullptr, ev.t_input, net_out, s)) return 1;
+            if (prof_mark(h, TMD_K_SOLVER, 0, (cfg ? 6.0 : 5.0) * n * 4, s, true, "x0_threshold")) return 1;   // x, out in; x0 written, re-read, re-written
+            CK(x0_threshold(h->slots[ev.src], net_out, cfg ? net_out + n : nullptr, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, noise_type,
+                            plan->guidance_scale, Bx, (int)n_per, plan->q_lo, plan->q_weight, plan->max_val, s));
             if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             ++h->launches;
             ++n_eval;
         } else {
             const tmd_update& u = st.update;
             if (!slot_ok(u.dst) || !slot_ok(u.x) || !slot_ok(u.m) || u.m1 >= TMD_NUM_SLOTS) return fail("tmd_sample: bad slot in step %d", i);
-            if (prof_mark(h, TMD_K_SOLVER, 0, (u.m1 >= 0 ? 4.0 : 3.0) * n * 4, s, true)) return 1;
-            CK(solver_update(h->slots[u.dst], h->slots[u.x], h->slots[u.m], u.m1 >= 0 ? h->slots[u.m1] : nullptr, u.c1, u.c2, u.c3, n, s));
+            if (u.form < 0 || u.form > 2 || (u.form >= 1 && !slot_ok(u.m1)) || (u.form == 2 && !slot_ok(u.m2)))
+                return fail("tmd_sample: bad update form / slots in step %d", i);
+            const double tensors = u.form == 2 ? 5.0 : (u.m1 >= 0 ? 4.0 : 3.0);
+            if (prof_mark(h, TMD_K_SOLVER, 0, tensors * n * 4, s, true, "solver_update")) return 1;
+            if (u.form == 0)
+                CK(solver_update(h->slots[u.dst], h->slots[u.x], h->slots[u.m], u.m1 >= 0 ? h->slots[u.m1] : nullptr, u.c1, u.c2, u.c3, n, s));
+            else
+                CK(solver_update_multistep(u.form, h->slots[u.dst], h->slots[u.x], h->slots[u.m], h->slots[u.m1],
+                                           u.form == 2 ? h->slots[u.m2] : nullptr, u.c1, u.c2, u.c3, u.k, n, s));
             if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             ++h->launches;
         }

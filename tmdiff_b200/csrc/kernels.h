@@ -50,13 +50,18 @@ cudaError_t time_table(const float* t_input, float t_scalar, const float* freqs,
 cudaError_t dense_rows(const float* x, const float* W, const float* b, float* y, int rows, int in_dim, int out_dim, int act,
                        cudaStream_t s);
 cudaError_t gather_rows(const float* table, const int* ids, float* out, int B, int width, cudaStream_t s);
+// out[b][:] = row[:]  (one evaluation's time table shared by the whole batch)
+cudaError_t broadcast_rows(const float* row, float* out, int B, int width, cudaStream_t s);
 
 // ---- solver (solver.cu) ----
 // eps = (x - a*out)/s ; x0 = (x - s*eps)/a ; dynamic threshold (quantile 0.995, max 1) -> dst
-cudaError_t x0_threshold(const float* x, const float* out, float* dst, float alpha, float sigma, int B, int n, int q_lo,
-                         float q_w, float max_val, cudaStream_t s);
+// out_c (optional): conditional half for classifier-free guidance, eps = eps_u + g*(eps_c - eps_u); noise_type: out is eps
+cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
+                         float g, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s);
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s);
 cudaError_t solver_update(float* dst, const float* x, const float* m, const float* m1, float c1, float c2, float c3, size_t n,
                           cudaStream_t s);
+cudaError_t solver_update_multistep(int form, float* dst, const float* x, const float* m, const float* m1, const float* m2, float c1,
+                                    float c2, float c3, const float* k, size_t n, cudaStream_t s);
 
 }  // namespace tmd

@@ -11,9 +11,12 @@ namespace tmd {
 
 constexpr int TH_THREADS = 1024;
 
-__device__ __forceinline__ float x0_of(float x, float out, float alpha, float sigma) {
-    const float eps = __fdiv_rn(__fsub_rn(x, __fmul_rn(alpha, out)), sigma);   // model_wrapper x_start -> noise
-    return __fdiv_rn(__fsub_rn(x, __fmul_rn(sigma, eps)), alpha);              // data_prediction_fn
+// noise_pred_fn (:296-306): the network output as eps.  noise_type: the output already is eps.
+__device__ __forceinline__ float eps_of(float x, float out, float alpha, float sigma, bool noise_type) {
+    return noise_type ? out : __fdiv_rn(__fsub_rn(x, __fmul_rn(alpha, out)), sigma);
+}
+__device__ __forceinline__ float x0_of_eps(float x, float eps, float alpha, float sigma) {
+    return __fdiv_rn(__fsub_rn(x, __fmul_rn(sigma, eps)), alpha);              // data_prediction_fn (:447-456)
 }
 
 // In-block bitonic sort, descending, P = power of two.
@@ -40,10 +43,13 @@ __device__ void bitonic_desc(float* v, int P) {
 // n-q_lo-1 values exceed max_val; otherwise both neighbours are <= max_val and s == max_val.
 // In the needed case only the values > max_val take part: they are gathered into shared memory
 // and sorted there (worst case all n of them).
+//
+// out_c != nullptr: classifier-free guidance (model_wrapper :336-344) -- `out` is the unconditional
+// half, `out_c` the conditional one, eps = eps_u + g*(eps_c - eps_u).
 template <bool kFromModel>
-__global__ void __launch_bounds__(TH_THREADS) x0_threshold_kernel(const float* x, const float* out,
-                                                                   float* dst, float alpha, float sigma, int n,
-                                                                   int q_lo, float q_w, float max_val) {
+__global__ void __launch_bounds__(TH_THREADS) x0_threshold_kernel(const float* x, const float* out, const float* out_c,
+                                                                   float* dst, float alpha, float sigma, bool noise_type,
+                                                                   float g, int n, int q_lo, float q_w, float max_val) {
     extern __shared__ float big[];
     __shared__ int s_count;
     __shared__ float s_red[32];
@@ -58,7 +64,10 @@ __global__ void __launch_bounds__(TH_THREADS) x0_threshold_kernel(const float* x
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         float v;
         if (kFromModel) {
-            v = x0_of(x[base + i], out[base + i], alpha, sigma);
+            const float xv = x[base + i];
+            float eps = eps_of(xv, out[base + i], alpha, sigma, noise_type);
+            if (out_c) eps = __fadd_rn(eps, __fmul_rn(g, __fsub_rn(eps_of(xv, out_c[base + i], alpha, sigma, noise_type), eps)));
+            v = x0_of_eps(xv, eps, alpha, sigma);
             dst[base + i] = v;
         } else {
             v = dst[base + i];
@@ -118,28 +127,29 @@ __global__ void __launch_bounds__(TH_THREADS) x0_threshold_kernel(const float* x
     }
 }
 
-static cudaError_t launch_threshold(bool from_model, const float* x, const float* out, float* dst, float alpha, float sigma, int B,
-                                    int n, int q_lo, float q_w, float max_val, cudaStream_t s) {
+static cudaError_t launch_threshold(bool from_model, const float* x, const float* out, const float* out_c, float* dst, float alpha,
+                                    float sigma, bool noise_type, float g, int B, int n, int q_lo, float q_w, float max_val,
+                                    cudaStream_t s) {
     int P = 1;
     while (P < n) P <<= 1;
     const size_t smem = (size_t)P * sizeof(float);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;  // > 51200 values per sample: not supported by the in-smem select
     if (from_model) {
         cudaFuncSetAttribute(x0_threshold_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        x0_threshold_kernel<true><<<B, TH_THREADS, smem, s>>>(x, out, dst, alpha, sigma, n, q_lo, q_w, max_val);
+        x0_threshold_kernel<true><<<B, TH_THREADS, smem, s>>>(x, out, out_c, dst, alpha, sigma, noise_type, g, n, q_lo, q_w, max_val);
     } else {
         cudaFuncSetAttribute(x0_threshold_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        x0_threshold_kernel<false><<<B, TH_THREADS, smem, s>>>(nullptr, nullptr, dst, 1.f, 1.f, n, q_lo, q_w, max_val);
+        x0_threshold_kernel<false><<<B, TH_THREADS, smem, s>>>(nullptr, nullptr, nullptr, dst, 1.f, 1.f, false, 0.f, n, q_lo, q_w, max_val);
     }
     return cudaGetLastError();
 }
 
-cudaError_t x0_threshold(const float* x, const float* out, float* dst, float alpha, float sigma, int B, int n, int q_lo, float q_w,
-                         float max_val, cudaStream_t s) {
-    return launch_threshold(true, x, out, dst, alpha, sigma, B, n, q_lo, q_w, max_val, s);
+cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
+                         float g, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s) {
+    return launch_threshold(true, x, out, out_c, dst, alpha, sigma, noise_type, g, B, n, q_lo, q_w, max_val, s);
 }
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s) {
-    return launch_threshold(false, nullptr, nullptr, x0, 1.f, 1.f, B, n, q_lo, q_w, max_val, s);
+    return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, s);
 }
 
 // dst = (c1*x - c2*m) [+ c3*(m1 - m)], 128-bit vectorised; dst may alias x.
@@ -163,6 +173,51 @@ cudaError_t solver_update(float* dst, const float* x, const float* m, const floa
                           cudaStream_t s) {
     const size_t n4 = n / 4;
     solver_update_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(dst, x, m, m1, c1, c2, c3, n4);
+    return cudaGetLastError();
+}
+
+// Multistep updates (:817-927), dpmsolver++ / solver_type 'dpmsolver'; `m` newest model value.
+//   form 1: D1_0 = k0*(m - m1);                      dst = c1*x - c2*m - c3*D1_0
+//   form 2: D1_0 = k0*(m - m1); D1_1 = k1*(m1 - m2); D1 = D1_0 + k2*(D1_0 - D1_1); D2 = k3*(D1_0 - D1_1)
+//           dst = c1*x - c2*m + c3*D1 - k4*D2
+struct MultiCoef { float c1, c2, c3, k[5]; };
+template <int kForm>
+__global__ void solver_update_multistep_kernel(float* dst, const float* x, const float* m, const float* m1, const float* m2,
+                                               MultiCoef q, size_t n4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 X4 = reinterpret_cast<const float4*>(x)[i], M4 = reinterpret_cast<const float4*>(m)[i];
+    const float4 N4 = reinterpret_cast<const float4*>(m1)[i];
+    float4 O4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (kForm == 2) O4 = reinterpret_cast<const float4*>(m2)[i];
+    const float X[4] = {X4.x, X4.y, X4.z, X4.w}, M[4] = {M4.x, M4.y, M4.z, M4.w}, N[4] = {N4.x, N4.y, N4.z, N4.w},
+                O[4] = {O4.x, O4.y, O4.z, O4.w};
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float d10 = __fmul_rn(q.k[0], __fsub_rn(M[j], N[j]));
+        const float base = __fsub_rn(__fmul_rn(q.c1, X[j]), __fmul_rn(q.c2, M[j]));
+        if (kForm == 1) {
+            r[j] = __fsub_rn(base, __fmul_rn(q.c3, d10));
+        } else {
+            const float d11 = __fmul_rn(q.k[1], __fsub_rn(N[j], O[j]));
+            const float dd = __fsub_rn(d10, d11);
+            const float D1 = __fadd_rn(d10, __fmul_rn(q.k[2], dd));
+            const float D2 = __fmul_rn(q.k[3], dd);
+            r[j] = __fsub_rn(__fadd_rn(base, __fmul_rn(q.c3, D1)), __fmul_rn(q.k[4], D2));
+        }
+    }
+    reinterpret_cast<float4*>(dst)[i] = make_float4(r[0], r[1], r[2], r[3]);
+}
+
+cudaError_t solver_update_multistep(int form, float* dst, const float* x, const float* m, const float* m1, const float* m2, float c1,
+                                    float c2, float c3, const float* k, size_t n, cudaStream_t s) {
+    const size_t n4 = n / 4;
+    MultiCoef q{c1, c2, c3, {k[0], k[1], k[2], k[3], k[4]}};
+    const unsigned grid = (unsigned)((n4 + 255) / 256);
+    if (form == 1) solver_update_multistep_kernel<1><<<grid, 256, 0, s>>>(dst, x, m, m1, nullptr, q, n4);
+    else if (form == 2) solver_update_multistep_kernel<2><<<grid, 256, 0, s>>>(dst, x, m, m1, m2, q, n4);
+    else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
 
