@@ -88,16 +88,30 @@ class Sampler:
     """DPM_Solver(model_fn, ns, 'dpmsolver++', 'dynamic_thresholding') over a raw x0-predicting
     network ``net(x, t_input) -> out`` wrapped the way model_wrapper does (:184-348)."""
 
-    def __init__(self, net, ns: ScheduleVP, trace=None):
+    def __init__(self, net, ns: ScheduleVP, trace=None, model_type="x_start", guidance_scale=None):
+        """model_type 'x_start' | 'noise' (:296-306).  guidance_scale not None: classifier-free guidance
+        (:336-344) -- `net` is then called on cat([x]*2) and must return [uncond | cond] halves."""
         self.net, self.ns, self.trace = net, ns, trace
+        self.model_type, self.guidance_scale = model_type, guidance_scale
+
+    def _noise_pred(self, x, tB):
+        ns = self.ns
+        t_input = (tB - 1.0 / ns.total_N) * 1000.0                  # :291-292
+        out = self.net(x, t_input)
+        if self.model_type == "noise":
+            return out, out, t_input
+        a, s = ns.alpha(tB), ns.sigma(tB)
+        return (x - a[:, None, None, None] * out) / s[:, None, None, None], out, t_input   # x_start -> noise  :304-306
 
     def data_prediction(self, x, t):
         ns = self.ns
         tB = t.expand(x.shape[0])                                   # :418
-        t_input = (tB - 1.0 / ns.total_N) * 1000.0                  # :291-292
-        out = self.net(x, t_input)
-        a, s = ns.alpha(tB), ns.sigma(tB)
-        eps = (x - a[:, None, None, None] * out) / s[:, None, None, None]   # x_start -> noise  :304-306
+        if self.guidance_scale is None:
+            eps, out, t_input = self._noise_pred(x, tB)
+        else:                                                       # :338-344
+            e2, out, t_input = self._noise_pred(torch.cat([x] * 2), torch.cat([tB] * 2))
+            e_u, e_c = e2.chunk(2)
+            eps = e_u + self.guidance_scale * (e_c - e_u)
         a1, s1 = ns.alpha(t), ns.sigma(t)
         x0 = dynamic_threshold((x - s1 * eps) / a1)                 # :447-456
         if self.trace is not None:
@@ -149,6 +163,55 @@ class Sampler:
         x_s2 = (sig_s2 / sig_s) * x - (a_s2 * phi_12) * m_s + r2 / r1 * (a_s2 * phi_22) * (m_s1 - m_s)
         m_s2 = f(x_s2, s2)
         return (sig_t / sig_s) * x - (a_t * phi_1) * m_s + (1.0 / r2) * (a_t * phi_2) * (m_s2 - m_s)
+
+    def _multistep_update(self, x, m_list, t_list, t, order):
+        """multistep_dpm_solver_update (:929-956 dispatch; :563-608, :817-927), dpmsolver++ / 'dpmsolver'."""
+        ns = self.ns
+        t0 = t_list[-1]
+        lam_0, lam_t = ns.lam(t0), ns.lam(t)
+        sig_0, sig_t, a_t = ns.sigma(t0), ns.sigma(t), torch.exp(ns.log_alpha(t))
+        h = lam_t - lam_0
+        phi_1 = torch.expm1(-h)
+        if order == 1:
+            return sig_t / sig_0 * x - a_t * phi_1 * m_list[-1]
+        m1, m0 = m_list[-2], m_list[-1]
+        h_0 = lam_0 - ns.lam(t_list[-2])
+        r0 = h_0 / h
+        D1_0 = (1.0 / r0) * (m0 - m1)
+        if order == 2:
+            return (sig_t / sig_0) * x - (a_t * phi_1) * m0 - 0.5 * (a_t * phi_1) * D1_0
+        m2 = m_list[-3]
+        h_1 = ns.lam(t_list[-2]) - ns.lam(t_list[-3])
+        r1 = h_1 / h
+        D1_1 = (1.0 / r1) * (m1 - m2)
+        D1 = D1_0 + (r0 / (r0 + r1)) * (D1_0 - D1_1)
+        D2 = (1.0 / (r0 + r1)) * (D1_0 - D1_1)
+        phi_2 = phi_1 / h + 1.0
+        phi_3 = phi_2 / h - 0.5
+        return (sig_t / sig_0) * x - (a_t * phi_1) * m0 + (a_t * phi_2) * D1 - (a_t * phi_3) * D2
+
+    @torch.no_grad()
+    def sample_multistep(self, x, steps=50, order=3, skip_type="logSNR", denoise_to_zero=False, lower_order_final=True):
+        """DPM_Solver.sample(method='multistep') (:1208-1252)."""
+        ns = self.ns
+        t_0, t_T = 1.0 / ns.total_N, ns.T
+        ts = self.time_steps(skip_type, t_T, t_0, steps)
+        t_list, m_list = [ts[0]], [self.data_prediction(x, ts[0])]
+        for step in range(1, order):
+            x = self._multistep_update(x, m_list, t_list, ts[step], step)
+            t_list.append(ts[step])
+            m_list.append(self.data_prediction(x, ts[step]))
+        for step in range(order, steps + 1):
+            step_order = min(order, steps + 1 - step) if (lower_order_final and steps < 10) else order
+            x = self._multistep_update(x, m_list, t_list, ts[step], step_order)
+            t_list = t_list[1:] + [ts[step]]
+            if step < steps:
+                m_list = m_list[1:] + [self.data_prediction(x, ts[step])]
+            else:
+                m_list = m_list[1:] + [m_list[-1]]
+        if denoise_to_zero:
+            x = self.data_prediction(x, torch.ones(1) * t_0)
+        return x
 
     @torch.no_grad()
     def sample(self, x, steps=20, order=3, skip_type="logSNR", denoise_to_zero=True):

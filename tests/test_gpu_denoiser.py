@@ -176,3 +176,55 @@ def test_reference_call_surface(model_fp32):
     assert rel_l2(eps, want) < FP32_TOL
     x1 = G.p_sample(x_T.cuda(), 0, condition_x={"PAN": pan.cuda(), "MS": ms.cuda()}, prompt="QB")
     assert x1.shape == x_T.shape and torch.isfinite(x1).all()
+
+
+@pytest.mark.parametrize("tag", ["ms3_noise_12", "ms2_cfg_8", "ms3_xstart_9"])
+@pytest.mark.parametrize("dtype,tol", [("fp32", FP32_TOL), ("bf16", BF16_TOL)])
+def test_sampler_variants(golden_samplers, model_fp32, model_bf16, tag, dtype, tol):
+    """sample_by_dpmsolver_noise / _guidance call shapes (multistep orders 2/3, model_type 'noise', classifier-free
+    guidance as one 2B batch) and multistep over the x_start wrapper, against the reference's own runs."""
+    from conftest import SAMPLER_CASES
+    from tmdiff_b200 import DPM_Solver, NoiseScheduleVP, model_wrapper
+    N, HW, sensor, steps, order, mtype, g, dtz = SAMPLER_CASES[tag]
+    model = model_fp32 if dtype == "fp32" else model_bf16
+    pan, ms, x_T = [t.cuda() for t in make_inputs(1, N, HW, HW)]
+    G = _diffusion(model)
+    ns = NoiseScheduleVP("discrete", betas=G.betas)
+    if g is None:
+        fn = model_wrapper(model, ns, model_type=mtype, model_kwargs={"PAN": pan, "MS": ms, "prompt": sensor})
+    else:
+        fn = model_wrapper(model, ns, model_type=mtype, model_kwargs={"MS": torch.cat([torch.zeros_like(ms), ms]), "prompt": sensor},
+                           guidance_type="classifier-free", condition=pan, unconditional_condition=torch.zeros_like(pan),
+                           guidance_scale=g)
+    sol = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+    got, trace = sol.sample(x_T, steps=steps, order=order, skip_type="logSNR", method="multistep", denoise_to_zero=dtz,
+                            return_trace=True)
+    n_eval = golden_samplers[tag + "_t_input"].shape[0]
+    assert trace.shape[0] == n_eval and trace.shape[1] == (2 if g is not None else 1)
+    worst = max(rel_l2(trace[i], torch.from_numpy(golden_samplers["%s_out_%d" % (tag, i)])) for i in range(n_eval))
+    assert worst < tol, worst
+    final = torch.from_numpy(golden_samplers[tag + "_final"])
+    assert psnr(got.cpu() + ms.cpu(), final + ms.cpu()) >= 45.0
+    if dtype == "fp32":
+        assert rel_l2(got, final) < tol
+
+
+def test_sampler_entry_points(model_fp32):
+    """The GeneralDiffusion methods themselves: shapes, finiteness, and guidance == 1 equals the conditional run."""
+    pan, ms, x_T = [t.cuda() for t in make_inputs(2, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    x_in = {"PAN": pan, "MS": ms, "Res": x_T}
+    a = G.sample_by_dpmsolver_noise(x_in, "QB", steps=6, x_T=x_T)
+    b = G.sample_by_dpmsolver_guidance(x_in, "QB", 1.0, steps=6, x_T=x_T)
+    c = G.sample_by_dpmsolver_guidance(x_in, "QB", 3.0, steps=6, x_T=x_T)
+    r = G.sample_by_regression(x_in, "QB")
+    for t in (a, b, c, r):
+        assert t.shape == ms.shape and bool(torch.isfinite(t).all())
+    # guidance_scale == 1 -> noise_pred_fn(x, t, cond=condition) only (dpm_solver_pytorch.py:336-337)
+    from tmdiff_b200 import DPM_Solver, NoiseScheduleVP, model_wrapper
+    ns = NoiseScheduleVP("discrete", betas=G.betas)
+    fn = model_wrapper(model_fp32, ns, model_type="noise", model_kwargs={"PAN": pan, "MS": ms, "prompt": "QB"})
+    want = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding").sample(
+        x_T, steps=6, order=2, skip_type="logSNR", method="multistep") + ms
+    assert rel_l2(b, want) < 1e-6
+    assert rel_l2(c, want) > 1e-4

@@ -11,6 +11,7 @@ import torch
 
 from oracle import dpm_ref
 from tmdiff_b200 import _lib, diffusion, dpm_solver, networks, ops, parallel
+from util import run_plan_on_cpu
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
@@ -63,22 +64,54 @@ def test_plan_reproduces_oracle_trajectory_on_a_toy_model():
     for steps in (10, 20, 11):
         want = dpm_ref.Sampler(net, dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000))).sample(xT, steps=steps, order=3)
         plan = sol.build_plan(steps=steps, order=3, skip_type="logSNR", method="singlestep", denoise_to_zero=True)
-        slots = {0: xT.clone()}
-        for s in plan.steps:
-            if s[0] == "eval":
-                _, src, dst, t_in, a, sg = s
-                x = slots[src]
-                out = net(x, torch.tensor([t_in]))
-                a, sg = torch.tensor(a), torch.tensor(sg)
-                eps = (x - a * out) / sg
-                slots[dst] = dpm_ref.dynamic_threshold((x - sg * eps) / a)
-            else:
-                _, dst, x, m, m1, c1, c2, c3 = s
-                r = torch.tensor(c1) * slots[x] - torch.tensor(c2) * slots[m]
-                if m1 >= 0:
-                    r = r + torch.tensor(c3) * (slots[m1] - slots[m])
-                slots[dst] = r
-        assert torch.equal(slots[plan.result_slot], want), steps
+        got = run_plan_on_cpu(plan, net, xT)
+        assert torch.equal(got, want), steps
+
+
+@pytest.mark.parametrize("steps,order,mtype,g,dtz", [(12, 3, "noise", None, True), (8, 2, "noise", 2.0, False),
+                                                     (9, 3, "x_start", None, True), (50, 3, "noise", None, True),
+                                                     (5, 3, "x_start", 1.5, True), (3, 1, "noise", None, False)])
+def test_multistep_plan_reproduces_oracle_on_a_toy_model(steps, order, mtype, g, dtz):
+    """The multistep / noise-type / classifier-free-guidance programs (sample_by_dpmsolver_noise, _guidance) against
+    the oracle's restatement of DPM_Solver.sample(method='multistep'), bit for bit."""
+    betas = torch.tensor(diffusion.make_beta_schedule("cosine", 1000), dtype=torch.float32)
+    ns = dpm_solver.NoiseScheduleVP("discrete", betas=betas)
+    fn = dpm_solver.model_wrapper(_FakeModel(), ns, model_type=mtype, model_kwargs={})
+    sol = dpm_solver.DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+
+    def net(x, t_in):
+        y = torch.tanh(x * 0.3) * (1.0 - t_in.reshape(-1, 1, 1, 1) / 2000.0)
+        if g is not None:                       # the two halves of a guidance batch see different conditions
+            y = torch.cat([y[: x.shape[0] // 2] * 0.5, y[x.shape[0] // 2:]])
+        return y
+
+    xT = torch.randn(2, 4, 8, 8, generator=torch.Generator().manual_seed(2))
+    want = dpm_ref.Sampler(net, dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000)), model_type=mtype,
+                           guidance_scale=g).sample_multistep(xT, steps=steps, order=order, denoise_to_zero=dtz)
+    plan = sol.build_plan(steps=steps, order=order, skip_type="logSNR", method="multistep", denoise_to_zero=dtz)
+    assert plan.n_eval == steps + (1 if dtz else 0)
+    assert all(0 <= v < _lib.NUM_SLOTS for st in plan.steps if st[0] == "update" for v in (st[1], st[2], st[3]))
+    got = run_plan_on_cpu(plan, net, xT, model_type=mtype, guidance_scale=g)
+    assert torch.equal(got, want)
+    cp = plan.to_c(4 * 8 * 8, model_type=mtype, cfg=g is not None, guidance_scale=g or 1.0)
+    assert cp.n_steps == len(plan.steps) and cp.model_type == (1 if mtype == "noise" else 0) and cp.cfg == (g is not None)
+
+
+def test_model_wrapper_rejects_what_the_reference_samplers_never_use():
+    betas = torch.tensor(diffusion.make_beta_schedule("cosine", 1000), dtype=torch.float32)
+    ns = dpm_solver.NoiseScheduleVP("discrete", betas=betas)
+    with pytest.raises(NotImplementedError):
+        dpm_solver.model_wrapper(_FakeModel(), ns, model_type="v")
+    with pytest.raises(NotImplementedError):
+        dpm_solver.model_wrapper(_FakeModel(), ns, model_type="noise", guidance_type="classifier")
+    with pytest.raises(AssertionError):
+        dpm_solver.model_wrapper(_FakeModel(), ns, model_type="bogus")
+    fn = dpm_solver.model_wrapper(_FakeModel(), ns, model_type="noise")
+    sol = dpm_solver.DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+    with pytest.raises(NotImplementedError):
+        sol.build_plan(steps=10, order=3, method="adaptive")
+    with pytest.raises(AssertionError):
+        sol.build_plan(steps=2, order=3, method="multistep")        # `assert steps >= order` (:1210)
 
 
 def test_quantile_position_matches_torch_quantile():

@@ -84,3 +84,24 @@ def test_trajectory_against_reference(golden, sd):
         assert np.array_equal(tr["t_input"].numpy(), t_ref[i])
         assert rel_l2(tr["out"], torch.from_numpy(golden["traj_qb32_20_out_%d" % i])) < 5e-6, i
     assert rel_l2(x, torch.from_numpy(golden["traj_qb32_20_final"])) < 5e-6
+
+
+@pytest.mark.parametrize("tag", ["ms3_noise_12", "ms2_cfg_8", "ms3_xstart_9"])
+def test_sampler_variants_against_reference(golden_samplers, sd, tag):
+    """Multistep DPM-Solver++ (orders 2/3), model_type 'noise' and classifier-free guidance: the oracle restatement
+    against the reference's own DPM_Solver / model_wrapper run (committed vectors)."""
+    from conftest import SAMPLER_CASES
+    N, HW, sensor, steps, order, mtype, g, dtz = SAMPLER_CASES[tag]
+    pan, ms, x_T = make_inputs(1, N, HW, HW)
+    emb = wavbest_ref.seeded_text_embeddings()[sensor]
+    if g is not None:
+        pan, ms = torch.cat([torch.zeros_like(pan), pan]), torch.cat([torch.zeros_like(ms), ms])
+    trace = []
+    smp = dpm_ref.Sampler(lambda x, t: wavbest_ref.wavbest_forward(sd, x, t, pan, ms, emb, faithful=True),
+                          dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000)), trace=trace, model_type=mtype, guidance_scale=g)
+    got = smp.sample_multistep(x_T, steps=steps, order=order, denoise_to_zero=dtz)
+    assert len(trace) == golden_samplers[tag + "_t_input"].shape[0]
+    for i, tr in enumerate(trace):
+        assert np.array_equal(tr["t_input"].numpy(), golden_samplers[tag + "_t_input"][i])
+        assert rel_l2(tr["out"], torch.from_numpy(golden_samplers["%s_out_%d" % (tag, i)])) < 2e-6
+    assert rel_l2(got, torch.from_numpy(golden_samplers[tag + "_final"])) < 2e-6

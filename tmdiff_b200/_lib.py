@@ -24,7 +24,8 @@ class Eval(C.Structure):
 
 class Update(C.Structure):
     _fields_ = [("dst", C.c_int32), ("x", C.c_int32), ("m", C.c_int32), ("m1", C.c_int32),
-                ("c1", C.c_float), ("c2", C.c_float), ("c3", C.c_float)]
+                ("c1", C.c_float), ("c2", C.c_float), ("c3", C.c_float), ("form", C.c_int32), ("m2", C.c_int32),
+                ("k", C.c_float * 5)]
 
 
 class Step(C.Structure):
@@ -33,7 +34,11 @@ class Step(C.Structure):
 
 class Plan(C.Structure):
     _fields_ = [("steps", C.POINTER(Step)), ("n_steps", C.c_int32), ("result_slot", C.c_int32),
-                ("q_weight", C.c_float), ("q_lo", C.c_int32), ("max_val", C.c_float)]
+                ("q_weight", C.c_float), ("q_lo", C.c_int32), ("max_val", C.c_float), ("model_type", C.c_int32),
+                ("cfg", C.c_int32), ("guidance_scale", C.c_float)]
+
+
+MODEL_X_START, MODEL_NOISE = 0, 1
 
 
 KIND_NAMES = ("conv3x3x3", "conv1x1x1", "elementwise", "solver", "conditioning")

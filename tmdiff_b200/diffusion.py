@@ -114,5 +114,51 @@ class GeneralDiffusion(nn.Module):
             return res2img(res[0], x_in["MS"]), res[1]
         return res2img(res, x_in["MS"])
 
+    @torch.no_grad()
+    def sample_by_dpmsolver_noise(self, x_in, prompt, steps=50, x_T=None, return_trace=False):
+        """:257-286 -- model_type 'noise', multistep order 3, logSNR, denoise_to_zero.  The reference also puts
+        x_in['wav'] into model_kwargs, which `WavBEST.forward` (:600) does not accept; it is ignored here."""
+        device = self.betas.device
+        if x_T is None:
+            x_T = torch.randn(x_in["Res"].shape, device=device)
+        ns = NoiseScheduleVP(schedule="discrete", betas=self.betas)
+        fn = model_wrapper(self.denoise_fn, ns, model_type="noise",
+                           model_kwargs={"PAN": x_in["PAN"], "MS": x_in["MS"], "prompt": prompt})
+        solver = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+        res = solver.sample(x_T, steps=steps, order=3, skip_type="logSNR", method="multistep", denoise_to_zero=True,
+                            return_trace=return_trace)
+        if return_trace:
+            return res2img(res[0], x_in["MS"]), res[1]
+        return res2img(res, x_in["MS"])
+
+    @torch.no_grad()
+    def sample_by_regression(self, x_in, prompt):
+        """:288-297 -- one denoiser evaluation at time_in = 1001 on noise (the reference's extra `wav` positional
+        argument is dropped, as above)."""
+        device = self.betas.device
+        x_T = torch.randn(x_in["Res"].shape, device=device)
+        B = x_T.shape[0]
+        time_in = torch.tensor([1000 + 1] * B, device=device).view(B, -1)
+        return res2img(self.denoise_fn(x_T, time_in, x_in["PAN"], x_in["MS"], prompt), x_in["MS"])
+
+    @torch.no_grad()
+    def sample_by_dpmsolver_guidance(self, x_in, prompt, guidance, steps=50, x_T=None, return_trace=False):
+        """:299-335 -- classifier-free guidance: condition = PAN, unconditional = zeros (PAN and MS), model_type
+        'noise', multistep order 2, logSNR, no denoise_to_zero.  Both halves run as one 2B batch per evaluation."""
+        device = self.betas.device
+        if x_T is None:
+            x_T = torch.randn(x_in["Res"].shape, device=device)
+        condition = x_in["PAN"]
+        ns = NoiseScheduleVP(schedule="discrete", betas=self.betas)
+        fn = model_wrapper(self.denoise_fn, ns, model_type="noise",
+                           model_kwargs={"MS": torch.cat([torch.zeros_like(x_in["MS"]), x_in["MS"]]), "prompt": prompt},
+                           guidance_type="classifier-free", condition=condition,
+                           unconditional_condition=torch.zeros_like(condition), guidance_scale=guidance)
+        solver = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+        res = solver.sample(x_T, steps=steps, order=2, skip_type="logSNR", method="multistep", return_trace=return_trace)
+        if return_trace:
+            return res2img(res[0], x_in["MS"]), res[1]
+        return res2img(res, x_in["MS"])
+
     def forward(self, x, *args, **kwargs):
         raise NotImplementedError("training loss (p_losses_dynamic) is outside the sampling hot path")

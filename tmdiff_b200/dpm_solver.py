@@ -72,23 +72,51 @@ class NoiseScheduleVP:
 
 def model_wrapper(model, noise_schedule, model_type="noise", model_kwargs={}, guidance_type="uncond", condition=None,
                   unconditional_condition=None, guidance_scale=1.0, classifier_fn=None, classifier_kwargs={}):
-    """:184-348.  Returns `model_fn(x, t_continuous)`; the returned callable also carries what
-    `DPM_Solver.sample` needs to run the whole trajectory on the device."""
-    if model_type != "x_start" or guidance_type != "uncond":
-        raise NotImplementedError("tmdiff_b200 implements the reference's sample_by_dpmsolver configuration: "
-                                  "model_type='x_start', guidance_type='uncond'")
+    """:184-348.  Returns `model_fn(x, t_continuous)` (the noise prediction); the returned callable also
+    carries what `DPM_Solver.sample` needs to run the whole trajectory on the device.
 
-    def model_fn(x, t_continuous):
+    Implemented: model_type 'x_start' (sample_by_dpmsolver) and 'noise' (sample_by_dpmsolver_noise /
+    _guidance, diffusion_general.py:257-335); guidance_type 'uncond' and 'classifier-free' (:336-344; the
+    condition is the PAN tensor, passed to the denoiser as its third positional argument, :299-302)."""
+    assert model_type in ["noise", "x_start", "v", "score"]
+    assert guidance_type in ["uncond", "classifier", "classifier-free"]
+    if model_type not in ("x_start", "noise"):
+        raise NotImplementedError("tmdiff_b200 implements model_type 'x_start' and 'noise' (the reference's samplers)")
+    if guidance_type == "classifier":
+        raise NotImplementedError("classifier guidance needs a backward pass; the reference's samplers do not use it")
+    cfg_active = guidance_type == "classifier-free" and not (guidance_scale == 1.0 or unconditional_condition is None)
+
+    def noise_pred_fn(x, t_continuous, cond=None):
         t_input = (t_continuous - 1.0 / noise_schedule.total_N) * 1000.0           # :291-292
-        output = model(x, t_input, **model_kwargs)
+        output = model(x, t_input, **model_kwargs) if cond is None else model(x, t_input, cond, **model_kwargs)
+        if model_type == "noise":
+            return output
         B = x.shape[0]
-        alpha_t = noise_schedule.marginal_alpha(t_continuous).reshape(B, 1, 1, 1)   # the reference broadcasts [B] over W (:304-306) and only runs at B=1
+        # the reference broadcasts a [B] alpha over W (:304-306) and therefore only runs at B=1
+        alpha_t = noise_schedule.marginal_alpha(t_continuous).reshape(B, 1, 1, 1)
         sigma_t = noise_schedule.marginal_std(t_continuous).reshape(B, 1, 1, 1)
         return (x - alpha_t * output) / sigma_t
+
+    def model_fn(x, t_continuous):
+        if guidance_type == "uncond":
+            return noise_pred_fn(x, t_continuous)
+        if not cfg_active:
+            return noise_pred_fn(x, t_continuous, cond=condition)
+        x_in = torch.cat([x] * 2)
+        t_in = torch.cat([t_continuous] * 2)
+        c_in = torch.cat([unconditional_condition, condition])
+        noise_uncond, noise = noise_pred_fn(x_in, t_in, cond=c_in).chunk(2)
+        return noise_uncond + guidance_scale * (noise - noise_uncond)
 
     model_fn.model = model
     model_fn.noise_schedule = noise_schedule
     model_fn.model_kwargs = dict(model_kwargs)
+    model_fn.model_type = model_type
+    model_fn.guidance_type = guidance_type
+    model_fn.condition = condition
+    model_fn.unconditional_condition = unconditional_condition
+    model_fn.guidance_scale = float(guidance_scale)
+    model_fn.cfg_active = cfg_active
     return model_fn
 
 
@@ -124,9 +152,10 @@ class SamplePlan:
         t_input = (t - 1.0 / ns.total_N) * 1000.0
         self.steps.append(("eval", src, dst, t_input.item(), ns.marginal_alpha(t).item(), ns.marginal_std(t).item()))
 
-    def update(self, dst, x, m, c1, c2, m1=-1, c3=0.0):
+    def update(self, dst, x, m, c1, c2, m1=-1, c3=0.0, form=0, m2=-1, k=()):
         f = lambda v: float(v.item()) if torch.is_tensor(v) else float(v)
-        self.steps.append(("update", dst, x, m, m1, f(c1), f(c2), f(c3)))
+        k = [f(v) for v in k] + [0.0] * (5 - len(k))
+        self.steps.append(("update", dst, x, m, m1, f(c1), f(c2), f(c3), int(form), m2, k))
 
     @property
     def n_eval(self):
@@ -135,7 +164,7 @@ class SamplePlan:
     def t_inputs(self):
         return [s[3] for s in self.steps if s[0] == "eval"]
 
-    def to_c(self, n_per_sample, ratio=0.995, max_val=1.0):
+    def to_c(self, n_per_sample, ratio=0.995, max_val=1.0, model_type="x_start", cfg=False, guidance_scale=1.0):
         arr = (_lib.Step * len(self.steps))()
         for i, s in enumerate(self.steps):
             if s[0] == "eval":
@@ -143,9 +172,11 @@ class SamplePlan:
                 arr[i].eval = _lib.Eval(s[1], s[2], s[3], s[4], s[5])
             else:
                 arr[i].kind = 1
-                arr[i].update = _lib.Update(*s[1:])
+                arr[i].update = _lib.Update(*s[1:10], (C.c_float * 5)(*s[10]))
         q_lo, q_w = quantile_position(n_per_sample, ratio)
-        plan = _lib.Plan(C.cast(arr, C.POINTER(_lib.Step)), len(self.steps), self.result_slot, q_w, q_lo, max_val)
+        plan = _lib.Plan(C.cast(arr, C.POINTER(_lib.Step)), len(self.steps), self.result_slot, q_w, q_lo, max_val,
+                         _lib.MODEL_NOISE if model_type == "noise" else _lib.MODEL_X_START, 1 if cfg else 0,
+                         float(guidance_scale))
         plan._keepalive = arr
         return plan
 
@@ -190,23 +221,86 @@ class DPM_Solver:
             outer = self.get_time_steps(skip_type, t_T, t_0, steps)[torch.cumsum(torch.tensor([0] + orders), 0)]
         return outer, orders
 
+    def _plan_multistep(self, P, steps, order, skip_type, t_T, t_0, lower_order_final):
+        """`sample`'s multistep branch (:1208-1252) + multistep_dpm_solver_{second,third}_update (:817-927) and
+        dpm_solver_first_update (:563-608), dpmsolver++ / solver_type 'dpmsolver'.  The rotating
+        model_prev_list becomes a rotation of three slots."""
+        ns = self.noise_schedule
+        assert steps >= order
+        ts = self.get_time_steps(skip_type, t_T, t_0, steps)
+        assert ts.shape[0] - 1 == steps
+        X = P.X
+        free = [P.M0, P.M1, P.M2]
+        prev = []   # [(slot, t)] oldest first
+
+        def eval_into_free(t):
+            slot = free.pop(0)
+            P.eval(ns, X, slot, t)
+            prev.append((slot, t))
+
+        def update(t, k):
+            (m0, t0) = prev[-1]
+            lam_0, lam_t = ns.marginal_lambda(t0), ns.marginal_lambda(t)
+            sigma_0, sigma_t = ns.marginal_std(t0), ns.marginal_std(t)
+            alpha_t = torch.exp(ns.marginal_log_mean_coeff(t))
+            h = lam_t - lam_0
+            phi_1 = torch.expm1(-h)
+            if k == 1:
+                P.update(X, X, m0, sigma_t / sigma_0, alpha_t * phi_1)
+                return
+            (m1, t1) = prev[-2]
+            h_0 = lam_0 - ns.marginal_lambda(t1)
+            r0 = h_0 / h
+            if k == 2:
+                P.update(X, X, m0, sigma_t / sigma_0, alpha_t * phi_1, m1, 0.5 * (alpha_t * phi_1), form=1, k=[1.0 / r0])
+                return
+            assert len(prev) == 3                                  # model_prev_2, model_prev_1, model_prev_0 = model_prev_list
+            (m2, t2) = prev[-3]
+            h_1 = ns.marginal_lambda(t1) - ns.marginal_lambda(t2)
+            r1 = h_1 / h
+            phi_2 = phi_1 / h + 1.0
+            phi_3 = phi_2 / h - 0.5
+            P.update(X, X, m0, sigma_t / sigma_0, alpha_t * phi_1, m1, alpha_t * phi_2, form=2, m2=m2,
+                     k=[1.0 / r0, 1.0 / r1, r0 / (r0 + r1), 1.0 / (r0 + r1), alpha_t * phi_3])
+
+        eval_into_free(ts[0])
+        for step in range(1, order):
+            update(ts[step], step)
+            eval_into_free(ts[step])
+        for step in range(order, steps + 1):
+            step_order = min(order, steps + 1 - step) if (lower_order_final and steps < 10) else order
+            update(ts[step], step_order)
+            if len(prev) == order:
+                free.append(prev.pop(0)[0])
+            if step < steps:                                       # "We do not need to evaluate the final model value." (:1247)
+                eval_into_free(ts[step])
+        return free
+
     def build_plan(self, steps=20, order=3, skip_type="logSNR", method="singlestep", denoise_to_zero=False, t_start=None,
-                   t_end=None):
+                   t_end=None, lower_order_final=True):
         """The scalar program of `sample` (:1253-1281) + the singlestep updates (:563-815, dpmsolver++ /
         solver_type 'dpmsolver' branches)."""
         ns = self.noise_schedule
         t_0 = 1.0 / ns.total_N if t_end is None else t_end
         t_T = ns.T if t_start is None else t_start
         assert t_0 > 0 and t_T > 0
+        P = SamplePlan()
+        X, M0, M1, M2, XS = P.X, P.M0, P.M1, P.M2, P.XS
+        if method == "multistep":
+            free = self._plan_multistep(P, steps, order, skip_type, t_T, t_0, lower_order_final)
+            P.result_slot = X
+            if denoise_to_zero:
+                P.eval(ns, X, free[0] if free else XS, torch.ones((1,)) * t_0)
+                P.result_slot = P.steps[-1][2]
+            return P
         if method == "singlestep":
             outer, orders = self.get_orders_and_timesteps_for_singlestep_solver(steps, order, skip_type, t_T, t_0)
         elif method == "singlestep_fixed":
             orders = [order] * (steps // order)
             outer = self.get_time_steps(skip_type, t_T, t_0, len(orders))
         else:
-            raise NotImplementedError("method %r: tmdiff_b200 implements the singlestep solvers" % (method,))
-        P = SamplePlan()
-        X, M0, M1, M2, XS = P.X, P.M0, P.M1, P.M2, P.XS
+            raise NotImplementedError("method %r: tmdiff_b200 implements 'singlestep', 'singlestep_fixed' and 'multistep' "
+                                      "(the adaptive solver is not used by the reference's samplers)" % (method,))
         for k, o in enumerate(orders):
             s, t = outer[k], outer[k + 1]
             inner = self.get_time_steps(skip_type, s.item(), t.item(), o)
@@ -258,18 +352,32 @@ class DPM_Solver:
             raise NotImplementedError("solver_type must be 'dpmsolver'")
         if return_intermediate:
             raise NotImplementedError("return_intermediate: use return_trace for the per-evaluation network outputs")
-        plan = self.build_plan(steps, order, skip_type, method, denoise_to_zero, t_start, t_end)
-        model = self.model_fn_.model
-        kw = self.model_fn_.model_kwargs
+        plan = self.build_plan(steps, order, skip_type, method, denoise_to_zero, t_start, t_end, lower_order_final)
+        fn = self.model_fn_
+        model, kw = fn.model, fn.model_kwargs
         if not x.is_cuda:
             raise RuntimeError("x must be a CUDA tensor (no CPU path)")
-        h = model.bind_condition(kw["PAN"], kw["MS"], kw["prompt"])
         xT = x.contiguous().float()
         B = xT.shape[0]
+        MS = kw["MS"]
+        cfg = bool(getattr(fn, "cfg_active", False))
+        if fn.guidance_type == "uncond":
+            PAN = kw["PAN"]
+        elif cfg:                                   # c_in = cat([unconditional_condition, condition]) (:340)
+            PAN = torch.cat([fn.unconditional_condition, fn.condition])
+            if MS.shape[0] != 2 * B:
+                raise ValueError("classifier-free guidance: model_kwargs['MS'] must hold 2B patches [unconditional | conditional] "
+                                 "(diffusion_general.py:308)")
+        else:                                       # guidance_scale == 1: conditional half only (:336-337)
+            PAN = fn.condition
+            if MS.shape[0] == 2 * B:
+                MS = MS[B:]
+        h = model.bind_condition(PAN, MS, kw["prompt"])
         n_per = xT[0].numel()
-        cplan = plan.to_c(n_per, self.dynamic_thresholding_ratio, self.thresholding_max_val)
+        cplan = plan.to_c(n_per, self.dynamic_thresholding_ratio, self.thresholding_max_val, fn.model_type, cfg, fn.guidance_scale)
         out = torch.empty_like(xT)
-        trace = torch.empty((plan.n_eval,) + tuple(xT.shape), device=xT.device) if return_trace else None
+        nB = 2 * B if cfg else B
+        trace = torch.empty((plan.n_eval, nB) + tuple(xT.shape[1:]), device=xT.device) if return_trace else None
         with torch.cuda.device(xT.device):
             _lib.check(_lib.load().tmd_sample(h, _lib.ptr(xT), C.byref(cplan), _lib.ptr(out), _lib.ptr(trace), _lib.stream_ptr()))
         out = out.to(x.dtype)
