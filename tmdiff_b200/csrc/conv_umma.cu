@@ -162,28 +162,47 @@ __device__ __forceinline__ void load8_f32(const float* p, float v[8]) {
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
 
-// v = accumulator + bias for channels [co, co+8) of one output voxel: residual adds, raw view and
-// the activated views (same contract as epilogue_store4 in conv_op.h).
-__device__ __forceinline__ void unpack8_bf16(const uint4& t, float v[8]) {
-    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+// 256-bit global accesses (sm_100): one lane moves 16 bf16 channels = one full 32-byte sector per instruction.
+// The epilogue's accesses are one voxel per lane, i.e. scattered with the channel pitch, so each instruction costs one
+// L1 wavefront per distinct line; the L1 data pipe is shared with the tensor core's shared-memory operand reads, which
+// makes wavefronts (not bytes) the budget: 32-byte pieces halve them against 16-byte ones.
+__device__ __forceinline__ void st_global_v8(void* p, const uint32_t w[8]) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
+                 "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+}
+__device__ __forceinline__ void ld_global_v8(const void* p, uint32_t w[8]) {
+    asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ void add_bf16x16(float v[16], const uint32_t w[8]) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
         const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
-        v[2 * i] = __low2float(h);
-        v[2 * i + 1] = __high2float(h);
+        v[2 * i] += __low2float(h);
+        v[2 * i + 1] += __high2float(h);
     }
 }
+__device__ __forceinline__ void store16_bf16(__nv_bfloat16* p, const float v[16]) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+    st_global_v8(p, w);
+}
 
-// Residual operands of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
-struct Resid { uint4 a0[2]; };
+// Residual operand of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
+struct Resid { uint32_t a0[8]; };
 __device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, int co, bool valid, Resid& r) {
     typedef __nv_bfloat16 T;
-    r.a0[0] = r.a0[1] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r.a0[i] = 0u;
     if (!valid || (e.dbg & 32)) return;
-    if (e.add0) {
-        const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co);
-        r.a0[0] = q[0]; r.a0[1] = q[1];
-    }
+    if (e.add0) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
 }
 
 // Swish through the hardware tanh: x*sigmoid(x) = h + h*tanh(h), h = x/2 (one MUFU op; its 2^-11 relative
@@ -195,38 +214,47 @@ __device__ __forceinline__ float swish_tanh(float x) {
     return fmaf(h, t, h);
 }
 
+// v = accumulator + bias for channels [co, co+16) of one output voxel: residual adds, raw view and the activated
+// views (same contract as epilogue_store4 in conv_op.h).
 template <bool kPre>
-__device__ __forceinline__ void store_views8(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[8], const uint4* pre0 = nullptr) {
+__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[16],
+                                              const uint32_t* pre0 = nullptr) {
     typedef __nv_bfloat16 T;
     if (e.add0) {
-        float a[8];
-        if (kPre) unpack8_bf16(*pre0, a);
-        else load8_bf16(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, a);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] += a[i];
+        if (kPre) add_bf16x16(v, pre0);
+        else {
+            uint32_t w[8];
+            ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, w);
+            add_bf16x16(v, w);
+        }
     }
     if (e.add1) {
-        float a[8];
-        load8_bf16(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, a);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] += a[i];
+        uint32_t w[8];
+        ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
+        add_bf16x16(v, w);
     }
-    if (e.raw_out && !(e.dbg & 64)) store8_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
+    if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         if (!e.act_out[k]) continue;
-        float u[8], t[8], s[8];
-        if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co, t);
-        if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co, s);
+        uint32_t w[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float x = v[i];
-            if (e.tb[k]) x += t[i];
-            if (!(e.dbg & 16)) x = swish_tanh(x);
-            if (e.sc[k]) x *= s[i];
-            u[i] = x;
+        for (int h = 0; h < 2; ++h) {
+            float t[8], s[8], u[8];
+            if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co + 8 * h, t);
+            if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co + 8 * h, s);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float x = v[8 * h + i];
+                if (e.tb[k]) x += t[i];
+                if (!(e.dbg & 16)) x = swish_tanh(x);
+                if (e.sc[k]) x *= s[i];
+                u[i] = x;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) w[4 * h + i] = pack_bf16x2(u[2 * i], u[2 * i + 1]);
         }
-        if (!(e.dbg & 128)) store8_bf16(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, u);
+        if (!(e.dbg & 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, w);
     }
 }
 
@@ -248,51 +276,54 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         const size_t ovox = (bn * P.H + y) * P.W + x;
         const size_t hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
-            store_views8<true>(e, b, ovox, hvox, co + 8 * h, v, &pre.a0[h]);
-        }
+        for (int i = 0; i < 16; ++i) acc[i] += bias[i];
+        store_views16<true>(e, b, ovox, hvox, co, acc, pre.a0);
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
         const bool writer = valid && !(x & 1) && !(y & 1);
         const size_t ovox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+        const bool want_hf = e.hf_out[0] != nullptr;
+        float ll[16];
+        uint32_t lh[8], hl[8], hh[8];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            float ll[8], lh[8], hl[8], hh[8];
+        for (int i = 0; i < 16; i += 2) {
+            float o[2][3];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float a = acc[8 * h + i];
+            for (int j = 0; j < 2; ++j) {
+                const float a = acc[i + j];
                 const float t = __shfl_xor_sync(0xffffffffu, a, 1);
                 const float L = a + t, D = a - t;                           // a+b, a-b   (on the even-x lane)
                 const float u = __shfl_xor_sync(0xffffffffu, L, P.TW), w = __shfl_xor_sync(0xffffffffu, D, P.TW);
-                ll[i] = (L + u) * 0.25f + bias[8 * h + i];                   // LL/2 == 2x2 average (:396)
-                hl[i] = (L - u) * 0.5f;                                      // (a+b)-(c+d)
-                lh[i] = (D + w) * 0.5f;                                      // (a-b)+(c-d)
-                hh[i] = (D - w) * 0.5f;                                      // (a-b)-(c-d)
+                ll[i + j] = (L + u) * 0.25f + bias[i + j];                   // LL/2 == 2x2 average (:396)
+                o[j][0] = (D + w) * 0.5f;                                    // LH: (a-b)+(c-d)
+                o[j][1] = (L - u) * 0.5f;                                    // HL: (a+b)-(c+d)
+                o[j][2] = (D - w) * 0.5f;                                    // HH: (a-b)-(c-d)
             }
-            if (!writer) continue;
-            if (e.hf_out[0]) {
-                typedef __nv_bfloat16 T;
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co + 8 * h, lh);
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co + 8 * h, hl);
-                store8_bf16(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co + 8 * h, hh);
+            if (want_hf) {
+                lh[i >> 1] = pack_bf16x2(o[0][0], o[1][0]);
+                hl[i >> 1] = pack_bf16x2(o[0][1], o[1][1]);
+                hh[i >> 1] = pack_bf16x2(o[0][2], o[1][2]);
             }
-            store_views8<false>(e, b, ovox, 0, co + 8 * h, ll);
         }
+        if (!writer) return;
+        if (want_hf) {
+            typedef __nv_bfloat16 T;
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co, lh);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co, hl);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co, hh);
+        }
+        store_views16<false>(e, b, ovox, 0, co, ll);
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
 #pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] += bias[i];
+#pragma unroll
         for (int r = 0; r < 4; ++r) {
             const size_t ovox = (bn * (2 * P.H) + 2 * y + (r >> 1)) * (2 * P.W) + 2 * x + (r & 1);
+            float v[16];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                float v[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v[i] = acc[8 * h + i] + bias[8 * h + i];
-                store_views8<false>(e, b, ovox, 0, co + 8 * h, v);
-            }
+            for (int i = 0; i < 16; ++i) v[i] = acc[i];
+            store_views16<false>(e, b, ovox, 0, co, v);
         }
     }
 }
@@ -377,21 +408,31 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         uint32_t s = 0, ph = 1;                            // ring slot, parity of its "empty" phase
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
             const TileCoord tc = decode_tile(P, tile);
+            // band planes outside [0, N) are zero padding: neither loaded nor multiplied (see the MMA warp)
+            int planes_in = 0;
+            if (MODE) {
+#pragma unroll
+                for (int pl = 0; pl < NACC + 2; ++pl) planes_in += (unsigned)(tc.n0 - 1 + pl) < (unsigned)P.N;
+            }
             for (int g = 0; g < ngroups; ++g) {
                 int cx = tc.x0, cy = tc.y0, cn = tc.n0;
                 if (MODE) { cx += g - 1; cy -= 1; cn -= 1; }
-                else if (P.taps == 27) { cx += g % 3 - 1; cy += (g / 3) % 3 - 1; cn += g / 9 - 1; }
+                else if (P.taps == 27) {
+                    cx += g % 3 - 1; cy += (g / 3) % 3 - 1; cn += g / 9 - 1;
+                    if (cn + P.TN <= 0 || cn >= P.N) continue;            // the whole box is padding
+                }
                 for (int kc = 0; kc < nkc; ++kc) {
                     mbar_wait(a_empty(s), ph);
                     if (elect_one()) {
                         if (P.dbg & 2) mbar_arrive(a_full(s));
                         else {
-                            mbar_expect_tx(a_full(s), P.a_stage_bytes);
+                            mbar_expect_tx(a_full(s), MODE ? P.a_piece_bytes * (uint32_t)planes_in : P.a_stage_bytes);
                             uint32_t dst = a_base + s * P.a_stage_stride;
                             if (MODE) {
 #pragma unroll
                                 for (int pl = 0; pl < NACC + 2; ++pl, dst += P.a_piece_bytes)
-                                    tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn + pl, tc.b0);
+                                    if ((unsigned)(cn + pl) < (unsigned)P.N)
+                                        tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn + pl, tc.b0);
                             } else {
                                 tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn, tc.b0);
                             }
@@ -406,7 +447,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         // ================= weight tiles =================
         uint32_t s = 0, ph = 1;
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
-            for (int g = 0; g < ngroups; ++g)
+            const TileCoord tc = decode_tile(P, tile);
+            for (int g = 0; g < ngroups; ++g) {
+                if (!MODE && P.taps == 27) {
+                    const int cn = tc.n0 + g / 9 - 1;
+                    if (cn + P.TN <= 0 || cn >= P.N) continue;
+                }
                 for (int kc = 0; kc < nkc; ++kc)
 #pragma unroll 1
                     for (int t = 0; t < b_stages_per_a; ++t) {           // REUSE: t = dy
@@ -429,6 +475,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                         __syncwarp();
                         if (++s == (uint32_t)P.SB) { s = 0; ph ^= 1; }
                     }
+            }
         }
     } else if (warp == 2) {
         // ================= MMA issue =================
@@ -456,7 +503,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             tc_fence_after();
             const uint32_t d0 = tmem_base + ab * NACC * Co;
             uint32_t fresh = 0;                                   // 0 for the first MMA into each accumulator of this tile
-            for (int g = 0; g < ngroups; ++g)
+            const int n0 = decode_tile(P, tile).n0;
+            const unsigned NB = (unsigned)P.N;                    // band planes outside [0, NB) are zero padding: skipped
+            for (int g = 0; g < ngroups; ++g) {
+                if (!MODE && P.taps == 27) {
+                    const int cn = n0 + g / 9 - 1;
+                    if (cn + P.TN <= 0 || cn >= P.N) continue;
+                }
                 for (int kc = 0; kc < nkc; ++kc) {
                     if (tr) tq = clock64();
                     mbar_wait(a_full(sa), pha);
@@ -477,7 +530,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                     for (int k = 0; k < KMMA; ++k)
                                         tc_mma_bf16(d0, ((uint64_t)desc_hi << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
                                                     k == 0 ? fresh : 1u);
-                                } else if (MERGE) {
+                                } else if (MERGE && fresh) {
                                     // One MMA per input plane q (box plane q+1) and K=16 slice: its A view feeds the output planes
                                     // q+1, q, q-1 through the taps dz = 0, 1, 2, whose weights are consecutive row blocks of the
                                     // stage and whose accumulators are consecutive TMEM column blocks (planes in decreasing order).
@@ -486,6 +539,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 #pragma unroll
                                     for (int i = 0; i < NACC + 2; ++i) {
                                         const int q = merge_order<NACC>(i);                  // -1 .. NACC
+                                        if ((unsigned)(n0 + q) >= NB) continue;
                                         const int dz_lo = q + 1 > NACC - 1 ? q + 1 - (NACC - 1) : 0;   // p = q+1-dz <= NACC-1
                                         const int dz_hi = q + 1 < 2 ? q + 1 : 2;                         // p >= 0
                                         const int nblk = dz_hi - dz_lo + 1;
@@ -496,21 +550,24 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
 #pragma unroll
                                         for (int k = 0; k < KMMA; ++k)
-                                            tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id,
-                                                        (k == 0 && i < merge_fresh<NACC>()) ? fresh : 1u);
+                                            tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id, 1u);
                                     }
                                 } else {
+                                    // one MMA per (output plane pp, dz).  Also the first stage of a tile in the merged kernels:
+                                    // the first valid dz of each plane overwrites its accumulator.
 #pragma unroll
                                     for (int dz = 0; dz < 3; ++dz)
 #pragma unroll
                                         for (int pp = 0; pp < NACC; ++pp) {
+                                            if ((unsigned)(n0 + pp + dz - 1) >= NB) continue;
+                                            const int dz_first = (n0 + pp == 0) ? 1 : 0;
                                             const uint32_t a_view = a_lo + (uint32_t)(pp + dz) * plane16 + (uint32_t)t * line16;
                                             const uint32_t b_view = b_lo + (uint32_t)dz * co16;
                                             const uint32_t d = d0 + (uint32_t)(NACC - 1 - pp) * Co;
 #pragma unroll
                                             for (int k = 0; k < KMMA; ++k)
                                                 tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
-                                                            (k == 0 && dz == 0) ? fresh : 1u);
+                                                            (k == 0 && dz == dz_first) ? fresh : 1u);
                                         }
                                 }
                             }
@@ -525,6 +582,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     __syncwarp();
                     if (++sa == (uint32_t)P.SA) { sa = 0; pha ^= 1; }
                 }
+            }
             if (elect_one()) tc_commit(acc_full(ab));
             __syncwarp();
         }
@@ -670,10 +728,15 @@ bool conv_umma_supported(const ConvOp& op) {
     if (op.Ci % 32 || op.Co % 16 || op.Co < 16 || op.Co > 256) return false;
     if (op.ld_in % 8 || (reinterpret_cast<uintptr_t>(op.src) & 15)) return false;
     const ConvEpilogue& e = op.epi;
-    // 16-byte vector accesses in the epilogue
-    if ((e.raw_out && e.ld_raw % 8) || (e.add0 && e.ld_add0 % 8) || (e.add1 && e.ld_add1 % 8) || (e.hf_out[0] && e.ld_hf % 8)) return false;
+    // 32-byte vector accesses in the epilogue
+    if ((e.raw_out && e.ld_raw % 16) || (e.add0 && e.ld_add0 % 16) || (e.add1 && e.ld_add1 % 16) || (e.hf_out[0] && e.ld_hf % 16)) return false;
     for (int k = 0; k < 2; ++k)
-        if (e.act_out[k] && e.ld_act[k] % 8) return false;
+        if (e.act_out[k] && e.ld_act[k] % 16) return false;
+    {
+        const void* wide[] = {e.add0, e.add1, e.raw_out, e.act_out[0], e.act_out[1], e.hf_out[0], e.hf_out[1], e.hf_out[2]};
+        for (const void* q : wide)
+            if (reinterpret_cast<uintptr_t>(q) & 31) return false;
+    }
     if ((e.tb[0] || e.tb[1]) && e.ld_tb % 4) return false;
     if ((e.sc[0] || e.sc[1]) && e.ld_sc % 4) return false;
     const void* ptrs[] = {e.bias, e.add0, e.add1, e.raw_out, e.act_out[0], e.act_out[1], e.tb[0], e.tb[1], e.sc[0], e.sc[1],
@@ -714,6 +777,9 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.TW = floor_pow2(op.W < 16 ? op.W : 16);
         P.TH = floor_pow2(op.H < 128 / P.TW ? op.H : 128 / P.TW);
         P.TN = floor_pow2(op.N < 128 / (P.TW * P.TH) ? op.N : 128 / (P.TW * P.TH));
+        // 3x3x3 on small planes: one band plane per box (batch folded into M instead), so the dz taps that fall on the
+        // zero padding of the band axis are skipped outright
+        if (op.taps == 27 && op.B >= 128 / (P.TW * P.TH)) P.TN = 1;
         P.TB = 128 / (P.TW * P.TH * P.TN);
         P.NACC = 1;
         boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH; boxA[3] = P.TN; boxA[4] = P.TB;
