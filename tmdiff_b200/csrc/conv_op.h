@@ -16,6 +16,7 @@
 //     POOL     2x2 Haar analysis in (H,W): LL/2 (= average) goes through the path above at
 //              half resolution; the three un-halved high bands optionally go to hf_out
 //              (WaveletUPorDown down branch, Hyper_unet_general.py:389-396)
+//              (tcgen05 kernel: pool_out additionally receives the 2x2 average of v at half resolution)
 //     UPSAMPLE every v is replicated to the 2x2 block of the double-resolution grid before
 //              add0 (IDWT of (2h, HF) == nearest-upsample(h) + IDWT(0, HF), :383-386)
 #pragma once
@@ -37,6 +38,7 @@ struct ConvEpilogue {
     const float* tb[2]; int ld_tb;   // [B][ld_tb] fp32 (already offset to this module's slice) or null
     const float* sc[2]; int ld_sc;   // [B][ld_sc] fp32 or null
     void* hf_out[3]; int ld_hf;      // POOL only: LH, HL, HH
+    void* pool_out; int ld_pool;     // NORMAL only (tcgen05 kernel): 2x2 average of v at half resolution
     int dbg;                         // diagnostics of the tcgen05 kernel (TMD_UMMA_DEBUG), 0 in production
 };
 
@@ -48,6 +50,12 @@ struct ConvOp {
     int taps;                   // 27 (3x3x3, pad 1) or 1
     const float* w_f32;         // [taps][Ci][Co]
     const __nv_bfloat16* w_bf16;  // [Co][taps*Ci], K-major (tcgen05 B operand)
+    // Optional fused 1x1x1 convolution of a second tensor at the same resolution, accumulated into the same output
+    // (tcgen05 kernel only):  v += sum_ci W2[ci][co] * src2[voxel][ci].  This is how the ResBlock skip `res_conv(x)`
+    // (Hyper_unet_general.py:247-249) and the wavelet block's `Conv_2` path (:372, with the 2x2 average commuted in
+    // front of the 1x1x1 conv) ride in the K loop of the block's last 3x3x3 conv instead of being separate launches.
+    const void* src2; int Ci2, ld_in2;
+    const __nv_bfloat16* w2_bf16;  // [Co][Ci2]
     ConvEpilogue epi;
 };
 

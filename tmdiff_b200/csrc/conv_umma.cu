@@ -43,6 +43,9 @@ constexpr int kMaxSA = 4, kMaxSB = 16;
 
 struct UmmaParams {
     CUtensorMap tmA, tmB;
+    CUtensorMap tmA2, tmB2;     // fused 1x1x1 second source (ConvOp::src2): nkc2 extra K chunks after the taps
+    int nkc2;
+    uint32_t a2_piece_bytes;    // REUSE: one un-haloed band plane [TH][TW][KC] of the second source
     ConvEpilogue epi;
     int B, N, H, W, Ci, Co, taps;
     int mode;                   // 0 = SIMPLE, 1 = REUSE
@@ -217,8 +220,7 @@ __device__ __forceinline__ float swish_tanh(float x) {
 // v = accumulator + bias for channels [co, co+16) of one output voxel: residual adds, raw view and the activated
 // views (same contract as epilogue_store4 in conv_op.h).
 template <bool kPre>
-__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, size_t hvox, int co, float v[16],
-                                              const uint32_t* pre0 = nullptr) {
+__device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, float v[16], const uint32_t* pre0 = nullptr) {
     typedef __nv_bfloat16 T;
     if (e.add0) {
         if (kPre) add_bf16x16(v, pre0);
@@ -233,6 +235,10 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
         ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
         add_bf16x16(v, w);
     }
+}
+
+__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16]) {
+    typedef __nv_bfloat16 T;
     if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
@@ -272,12 +278,30 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
     }
     const size_t bn = (size_t)b * P.N + n;
     if (e.mode == CONV_NORMAL) {
-        if (!valid) return;
+        const bool pooled = e.pool_out != nullptr;           // warp-uniform
+        if (!valid && !pooled) return;
         const size_t ovox = (bn * P.H + y) * P.W + x;
         const size_t hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] += bias[i];
-        store_views16<true>(e, b, ovox, hvox, co, acc, pre.a0);
+        if (valid) add_residuals16<true>(e, ovox, hvox, co, acc, pre.a0);
+        if (pooled) {
+            // 2x2 average of v for the consumer's fused Conv_2 path; a quad is wholly inside or outside the tensor
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) {
+                float o[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const float L = acc[i + j] + __shfl_xor_sync(0xffffffffu, acc[i + j], 1);
+                    o[j] = (L + __shfl_xor_sync(0xffffffffu, L, P.TW)) * 0.25f;
+                }
+                w[i >> 1] = pack_bf16x2(o[0], o[1]);
+            }
+            if (valid && !(x & 1) && !(y & 1))
+                st_global_v8(reinterpret_cast<__nv_bfloat16*>(e.pool_out) + hvox * e.ld_pool + co, w);
+        }
+        if (valid) store_views16(e, b, ovox, co, acc);
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
         const bool writer = valid && !(x & 1) && !(y & 1);
@@ -312,7 +336,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co, hl);
             st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co, hh);
         }
-        store_views16<false>(e, b, ovox, 0, co, ll);
+        add_residuals16<false>(e, ovox, 0, co, ll);
+        store_views16(e, b, ovox, co, ll);
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
 #pragma unroll
@@ -323,7 +348,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            store_views16<false>(e, b, ovox, 0, co, v);
+            add_residuals16<false>(e, ovox, 0, co, v);
+            store_views16(e, b, ovox, co, v);
         }
     }
 }
@@ -442,6 +468,28 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     if (++s == (uint32_t)P.SA) { s = 0; ph ^= 1; }
                 }
             }
+            if (P.nkc2) {   // second source: un-haloed planes of the tile, centre tap only
+                int planes2 = 0;
+#pragma unroll
+                for (int pl = 0; pl < NACC; ++pl) planes2 += (tc.n0 + pl) < P.N;
+                for (int kc = 0; kc < P.nkc2; ++kc) {
+                    mbar_wait(a_empty(s), ph);
+                    if (elect_one()) {
+                        uint32_t dst = a_base + s * P.a_stage_stride;
+                        if (MODE) {
+                            mbar_expect_tx(a_full(s), P.a2_piece_bytes * (uint32_t)planes2);
+#pragma unroll
+                            for (int pl = 0; pl < NACC; ++pl, dst += P.a2_piece_bytes)
+                                if (tc.n0 + pl < P.N) tma_load_5d(dst, &P.tmA2, a_full(s), kc * KC, tc.x0, tc.y0, tc.n0 + pl, tc.b0);
+                        } else {
+                            mbar_expect_tx(a_full(s), P.a_stage_bytes);
+                            tma_load_5d(dst, &P.tmA2, a_full(s), kc * KC, tc.x0, tc.y0, tc.n0, tc.b0);
+                        }
+                    }
+                    __syncwarp();
+                    if (++s == (uint32_t)P.SA) { s = 0; ph ^= 1; }
+                }
+            }
         }
     } else if (warp == 1) {
         // ================= weight tiles =================
@@ -475,6 +523,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                         __syncwarp();
                         if (++s == (uint32_t)P.SB) { s = 0; ph ^= 1; }
                     }
+            }
+            for (int kc = 0; kc < P.nkc2; ++kc) {
+                mbar_wait(b_empty(s), ph);
+                if (elect_one()) {
+                    mbar_expect_tx(b_full(s), P.b_tile_bytes);
+                    tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB2, b_full(s), kc * KC, 0);
+                }
+                __syncwarp();
+                if (++s == (uint32_t)P.SB) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 2) {
@@ -582,6 +639,31 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     __syncwarp();
                     if (++sa == (uint32_t)P.SA) { sa = 0; pha ^= 1; }
                 }
+            }
+            for (int kc = 0; kc < P.nkc2; ++kc) {   // fused 1x1x1 second source: one MMA group per output plane, K = KC
+                mbar_wait(a_full(sa), pha);
+                mbar_wait(b_full(sb), phb);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t a_lo = a_lo0 + sa * a_stride16, b_lo = b_lo0 + sb * b_stride16;
+                    const uint32_t plane2_16 = P.a2_piece_bytes >> 4;
+                    if (do_mma) {
+#pragma unroll
+                        for (int pp = 0; pp < NACC; ++pp) {
+                            if (MODE && (unsigned)(n0 + pp) >= NB) continue;
+                            const uint32_t a_view = a_lo + (uint32_t)pp * plane2_16;
+                            const uint32_t d = d0 + (uint32_t)(NACC - 1 - pp) * Co;
+#pragma unroll
+                            for (int k = 0; k < KMMA; ++k)
+                                tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc, 1u);
+                        }
+                    }
+                    tc_commit(b_empty(sb));
+                    tc_commit(a_empty(sa));
+                }
+                __syncwarp();
+                if (++sb == (uint32_t)P.SB) { sb = 0; phb ^= 1; }
+                if (++sa == (uint32_t)P.SA) { sa = 0; pha ^= 1; }
             }
             if (elect_one()) tc_commit(acc_full(ab));
             __syncwarp();
@@ -743,7 +825,12 @@ bool conv_umma_supported(const ConvOp& op) {
                           e.hf_out[0], e.hf_out[1], e.hf_out[2], op.w_bf16};
     for (const void* q : ptrs)
         if (reinterpret_cast<uintptr_t>(q) & 15) return false;
-    if (e.mode == CONV_POOL && (op.H % 2 || op.W % 2)) return false;
+    if ((e.mode == CONV_POOL || e.pool_out) && (op.H % 2 || op.W % 2)) return false;
+    if (e.pool_out && (e.mode != CONV_NORMAL || e.ld_pool % 16 || (reinterpret_cast<uintptr_t>(e.pool_out) & 31))) return false;
+    if (op.src2) {
+        const int kc = (op.taps == 27 && op.H >= 16 && op.W >= 8) ? 32 : ((op.Ci % 64 == 0) ? 64 : 32);   // KC of the plan below
+        if (op.Ci2 % kc || op.ld_in2 % 8 || (reinterpret_cast<uintptr_t>(op.src2) & 15) || (reinterpret_cast<uintptr_t>(op.w2_bf16) & 15)) return false;
+    }
     if (op.W < 2 || op.H < 2) return false;
     return true;
 }
@@ -836,6 +923,26 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         cuuint32_t box[2] = {(cuuint32_t)P.KC, (cuuint32_t)op.Co};
         cuuint32_t estr[2] = {1, 1};
         if (enc(&P.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(op.w_bf16), dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+            delete plan;
+            return nullptr;
+        }
+    }
+    if (op.src2) {
+        P.nkc2 = op.Ci2 / P.KC;
+        cuuint32_t box2[5] = {boxA[0], boxA[1], boxA[2], boxA[3], boxA[4]};
+        if (P.mode) box2[2] = P.TH;                      // no halo: the 1x1x1 conv only reads the tile's own voxels
+        P.a2_piece_bytes = box2[1] * box2[2] * box2[3] * box2[4] * P.row_bytes;
+        cuuint64_t dims[5] = {(cuuint64_t)op.Ci2, (cuuint64_t)op.W, (cuuint64_t)op.H, (cuuint64_t)op.N, (cuuint64_t)op.B};
+        const cuuint64_t e = 2ull * op.ld_in2;
+        cuuint64_t strides[4] = {e, e * op.W, e * op.W * op.H, e * op.W * op.H * op.N};
+        cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+        cuuint64_t dimsB[2] = {(cuuint64_t)op.Ci2, (cuuint64_t)op.Co};
+        cuuint64_t stridesB[1] = {2ull * op.Ci2};
+        cuuint32_t boxB[2] = {(cuuint32_t)P.KC, (cuuint32_t)op.Co};
+        if (enc(&P.tmA2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(op.src2), dims, strides, box2, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS ||
+            enc(&P.tmB2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(op.w2_bf16), dimsB, stridesB, boxB, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
             delete plan;
             return nullptr;

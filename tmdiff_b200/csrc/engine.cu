@@ -47,6 +47,7 @@ struct ActSpec {
 struct OutSpec {
     View raw;
     ActSpec act[2];
+    View pool;   // 2x2 average of the result at the next level (consumed by a fused Conv_2, see ConvOp::src2)
 };
 struct ConvW {
     float* w_f32 = nullptr;
@@ -450,12 +451,23 @@ struct Planner {
         return e->d_sc + it->second;
     }
 
+    // bf16 mode: the 1x1x1 convs that are summed with a 3x3x3 conv's result (ResBlock res_conv, wavelet-down Conv_2)
+    // run as extra K chunks of that conv (ConvOp::src2) instead of as launches of their own
+    bool fuse = false;
+
     void conv(const std::string& wname, View src, int lvl, int mode, const OutSpec& out, View add0 = View{}, View add1 = View{},
-              View* hf = nullptr) {
+              View* hf = nullptr, const std::string& w2name = "", View src2 = View{}) {
         auto it = e->convs.find(wname);
         if (it == e->convs.end()) { err = "missing conv weights"; return; }
         const ConvW& cw = it->second;
         if (cw.Ci != src.C) { err = "conv input channel mismatch"; return; }
+        const ConvW* cw2 = nullptr;
+        if (!w2name.empty()) {
+            auto it2 = e->convs.find(w2name);
+            if (it2 == e->convs.end()) { err = "missing conv weights (fused 1x1x1)"; return; }
+            cw2 = &it2->second;
+            if (cw2->taps != 1 || cw2->Co != cw.Co || cw2->Ci != src2.C || (cw.bias && cw2->bias)) { err = "fused 1x1x1 conv mismatch"; return; }
+        }
         ConvOp op{};
         op.B = B; op.N = N; op.H = H >> lvl; op.W = W >> lvl;
         op.Ci = cw.Ci; op.ld_in = src.ld; op.src = src.p;
@@ -464,6 +476,11 @@ struct Planner {
         ConvEpilogue& ep = op.epi;
         ep.mode = mode;
         ep.bias = cw.bias;
+        if (cw2) {
+            op.src2 = src2.p; op.Ci2 = cw2->Ci; op.ld_in2 = src2.ld; op.w2_bf16 = cw2->w_bf16;
+            if (cw2->bias) ep.bias = cw2->bias;
+        }
+        ep.pool_out = out.pool.p; ep.ld_pool = out.pool.ld;
         ep.add0 = add0.p; ep.ld_add0 = add0.ld;
         ep.add1 = add1.p; ep.ld_add1 = add1.ld;
         ep.raw_out = out.raw.p; ep.ld_raw = out.raw.ld;
@@ -475,18 +492,21 @@ struct Planner {
         if (hf) { for (int i = 0; i < 3; ++i) ep.hf_out[i] = hf[i].p; ep.ld_hf = hf[0].ld; }
         // algorithmic cost of this launch: 2*MACs; every operand/result tensor touched once
         const double nv = (double)vox(lvl);
-        const double flops = 2.0 * nv * cw.Ci * cw.taps * cw.Co;
+        const double flops = 2.0 * nv * cw.Ci * cw.taps * cw.Co + (cw2 ? 2.0 * nv * cw2->Ci * cw.Co : 0.0);
         const double ovox = mode == CONV_POOL ? nv / 4 : (mode == CONV_UPSAMPLE ? nv * 4 : nv);
         int n_out = (out.raw.p ? 1 : 0) + (out.act[0].dst.p ? 1 : 0) + (out.act[1].dst.p ? 1 : 0);
         double bytes = nv * cw.Ci * e->esize + ovox * cw.Co * e->esize * n_out + (double)cw.Ci * cw.taps * cw.Co * e->esize;
         if (add0.p) bytes += ovox * cw.Co * e->esize;
         if (add1.p) bytes += ovox / 4 * cw.Co * e->esize;
         if (hf) bytes += 3 * ovox * cw.Co * e->esize;
+        if (cw2) bytes += nv * cw2->Ci * e->esize + (double)cw2->Ci * cw.Co * e->esize;
+        if (out.pool.p) bytes += nv / 4 * cw.Co * e->esize;
         const int kind = cw.taps == 27 ? TMD_K_CONV3 : TMD_K_CONV1;
         char lb[160];
         snprintf(lb, sizeof(lb), "%s Ci=%d Co=%d L%d %s", wname.c_str(), cw.Ci, cw.Co, lvl,
                  mode == CONV_POOL ? "pool" : (mode == CONV_UPSAMPLE ? "up" : "same"));
-        const std::string label(lb);
+        const std::string label = std::string(lb) + (cw2 ? " +" + w2name.substr(w2name.rfind('.') + 1) : "") + (out.pool.p ? " +pool" : "");
+        if ((cw2 || out.pool.p) && (e->dtype == TMD_F32 || !conv_umma_supported(op))) { err = "fused conv outside the tcgen05 envelope"; return; }
         if (e->dtype == TMD_F32) {
             push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); }, label);
         } else if (conv_umma_supported(op)) {
@@ -507,6 +527,10 @@ struct Planner {
         o1.act[0] = ActSpec{a2, nullptr, sc(p + ".dense2")};
         conv(p + ".conv20", in_act, lvl, CONV_NORMAL, o1);
         View res = in_raw;
+        if (fuse && e->convs.count(p + ".res_conv")) {
+            conv(p + ".conv21", a2, lvl, CONV_NORMAL, out, View{}, View{}, nullptr, p + ".res_conv", in_raw);
+            return;
+        }
         if (e->convs.count(p + ".res_conv")) {
             View r = buf("r@" + std::to_string(lvl), lvl, cmax(lvl));
             r.C = Co;
@@ -519,18 +543,24 @@ struct Planner {
     }
 
     // WaveletUPorDown.forward, down=True (:369-414); lvl = input level, outputs at lvl+1
-    void wavelet_down(const std::string& p, View in_act, View in_raw, int C, int lvl, bool flag, View* hf, const OutSpec& out) {
-        View xp = buf("xp@" + std::to_string(lvl + 1), lvl + 1, cmax(lvl + 1));
-        xp.C = C;
-        OutSpec o1;
-        o1.raw = xp;
-        conv(p + ".Conv_2", in_raw, lvl, CONV_POOL, o1);
+    // in_pool (fused plans): 2x2 average of in_raw, emitted by its producer; Conv_2(pool(x)) == pool(Conv_2(x)).
+    void wavelet_down(const std::string& p, View in_act, View in_raw, int C, int lvl, bool flag, View* hf, const OutSpec& out,
+                      View in_pool = View{}) {
+        View xp;
+        if (!in_pool.p) {
+            xp = buf("xp@" + std::to_string(lvl + 1), lvl + 1, cmax(lvl + 1));
+            xp.C = C;
+            OutSpec o1;
+            o1.raw = xp;
+            conv(p + ".Conv_2", in_raw, lvl, CONV_POOL, o1);
+        }
         View ac1 = buf("ac1@" + std::to_string(lvl + 1), lvl + 1, cmax(lvl + 1));
         ac1.C = C;
         OutSpec o2;
         o2.act[0] = ActSpec{ac1, flag ? nullptr : tb(p + ".Dense_0"), sc(p + ".dense1")};
         conv(p + ".Conv_0", in_act, lvl, CONV_POOL, o2, View{}, View{}, hf);
-        conv(p + ".Conv_1", ac1, lvl + 1, CONV_NORMAL, out, xp);
+        if (in_pool.p) conv(p + ".Conv_1", ac1, lvl + 1, CONV_NORMAL, out, View{}, View{}, nullptr, p + ".Conv_2", in_pool);
+        else conv(p + ".Conv_1", ac1, lvl + 1, CONV_NORMAL, out, xp);
     }
 
     // WaveletUPorDown.forward, up=True; lvl = input (low) level, outputs at lvl-1.  T = IDWT(0, skipH').
@@ -566,7 +596,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         const int cm[4] = {c[1], c[2], c[3], c[3]};
         for (int l = 0; l < 4; ++l) {
             const size_t v = v0 >> (2 * l);
-            elems += v * (size_t)(2 * 3 * c[l] + 8 * cm[l] + 8 * c[l]);
+            elems += v * (size_t)(2 * 3 * c[l] + 8 * cm[l] + 8 * c[l]) + v / 4 * (size_t)cm[l];
         }
         e->arena_size = elems * e->esize + ((size_t)64 << 20);
         CK(cudaMalloc((void**)&e->arena, e->arena_size));
@@ -575,6 +605,13 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         if (e->dmalloc(&e->d_out, v0) || e->dmalloc(&e->d_xdup, v0)) return 1;
     }
     Planner P{e, &e->pre_ops, B, N, H, W};
+    {
+        bool ok = e->dtype == TMD_BF16 && !getenv("TMD_NO_FUSE_1X1");
+        for (int l = 0; l < 4; ++l) ok = ok && c[l] % 32 == 0;
+        ConvOp probe{};
+        probe.B = B; probe.N = N; probe.H = H >> 2; probe.W = W >> 2; probe.Ci = probe.ld_in = 32; probe.Co = 32; probe.taps = 27;
+        P.fuse = ok && conv_umma_supported(probe);
+    }
     const int dt = e->dtype;
     const int tr = e->time_rows, sr = e->text_rows;
     const int HW = H * W;
@@ -610,6 +647,8 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             OutSpec ro;
             ro.raw = y;
             ro.act[0] = ActSpec{ay, nullptr, nullptr};
+            View yq;
+            if (P.fuse) ro.pool = yq = P.buf("yq@" + L(l + 1), l + 1, c[l + 1]);
             P.resblock(nm + ".conv20", in_act, in_raw, c[l + 1], l, ro);
             View hf[3];
             for (int g = 0; g < 3; ++g) hf[g] = P.buf("S" + L(g) + "@" + L(l + 1), l + 1, c[l + 1]);
@@ -617,7 +656,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             OutSpec wo;
             wo.raw = P.slice(cat_raw[l + 1], c[l + 1], c[l + 1]);
             if (l < 2) wo.act[0] = ActSpec{nxt, nullptr, nullptr};
-            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, true, hf, wo);
+            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, true, hf, wo, yq);
             in_act = nxt;
             in_raw = wo.raw;
             // convH_0 of the matching up block consumes only these skips (:381): hoist it here
@@ -678,6 +717,8 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             OutSpec ro;
             ro.raw = y;
             ro.act[0] = ActSpec{ay, nullptr, nullptr};
+            View yq;
+            if (P.fuse) ro.pool = yq = P.buf("yq@" + L(l + 1), l + 1, c[l + 1]);
             P.resblock(nm + ".conv20", in_act, in_raw, c[l + 1], l, ro);
             View nxt = P.buf("in_act@" + L(l + 1), l + 1, c[l + 1]);
             OutSpec wo;
@@ -685,7 +726,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             wo.act[0] = ActSpec{nxt, P.tb(std::string(next_res[l]) + ".dense1"), nullptr};
             wo.act[1] = ActSpec{P.slice(cat_act[l + 1], 2 * c[l + 1], c[l + 1]),
                                 P.tb(std::string(consumer[l + 1]) + ".dense1", 2 * c[l + 1]), nullptr};
-            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, false, nullptr, wo);  // high bands of the main branch are never read (:620-627)
+            P.wavelet_down(nm + ".down", ay, y, c[l + 1], l, false, nullptr, wo, yq);  // high bands of the main branch are never read (:620-627)
             in_act = nxt;
             in_raw = wo.raw;
         }
