@@ -999,6 +999,7 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
                 mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9]);
         return cudaGetLastError();
     }
+    // (programmatic dependent launch was measured: no gain -- one CTA per SM leaves nothing for the next kernel to overlap)
     kern<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
     return cudaGetLastError();
 }

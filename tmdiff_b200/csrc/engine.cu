@@ -123,6 +123,15 @@ struct tmd_engine {
     // (t is a host scalar per evaluation and shared by the batch); each evaluation then broadcasts its row.
     float *d_tb_all = nullptr, *d_tin_all = nullptr;
     const float* tb_bcast_src = nullptr;
+    // tmd_sample: the launch sequence of a plan is captured once into a CUDA graph (on a private stream) and replayed,
+    // which removes the per-launch gaps of ~1000 dependent kernels.  Keyed by the plan's contents; dropped on re-plan.
+    struct SampleGraph { uint64_t key; cudaGraphExec_t exec; int64_t launches; };
+    std::vector<SampleGraph> graphs;
+    cudaStream_t cap_stream = nullptr;
+    void drop_graphs() {
+        for (auto& g : graphs) cudaGraphExecDestroy(g.exec);
+        graphs.clear();
+    }
     int64_t launches = 0;
     bool profiling = false;
     std::vector<ProfSpan> prof_events;
@@ -249,6 +258,8 @@ extern "C" int tmd_destroy(tmd_handle h) {
     for (void* p : h->allocs) cudaFree(p);
     for (auto& sp : h->prof_events) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     if (h->arena) cudaFree(h->arena);
+    h->drop_graphs();
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     delete h;
     return 0;
 }
@@ -393,6 +404,7 @@ extern "C" int tmd_finalize_weights(tmd_handle h) {
         h->dmalloc(&h->d_sc, (size_t)MB * h->text_rows) || h->dmalloc(&h->d_tb_all, (size_t)kMaxPlanEvals * h->time_rows) ||
         h->dmalloc(&h->d_tin_all, (size_t)kMaxPlanEvals))
         return 1;
+    h->drop_graphs();
     h->text_dirty = true;
     h->finalized = true;
     h->B = 0;  // force a re-plan
@@ -585,6 +597,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     const int* c = e->cfg.channels;
     for (auto* p : e->plans) conv_umma_plan_destroy(p);
     e->plans.clear();
+    e->drop_graphs();
     e->pre_ops.clear();
     e->step_ops.clear();
     e->bufs.clear();
@@ -867,38 +880,24 @@ extern "C" int tmd_denoise(tmd_handle h, const float* x_t, const float* t_input_
     return denoise_impl(h, x_t, t_input_dev, 0.f, out, s);
 }
 
-extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, float* out, float* trace, void* stream) {
-    if (!h || !x_T || !plan || !out || !plan->steps) return fail("tmd_sample: null argument");
-    if (h->B == 0 || h->step_ops.empty()) return fail("tmd_sample: call tmd_precompute_condition first");
-    cudaStream_t s = (cudaStream_t)stream;
-    CK(cudaSetDevice(h->device));
+// The launch sequence of one plan: every evaluation's time table in one launch, then per step either one denoiser
+// evaluation + x0 conversion / dynamic threshold, or one solver update.  Touches engine-owned buffers only (unless a
+// trace is requested), so it can be captured into a CUDA graph.
+static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, int n_evals, bool pre_tb, cudaStream_t s) {
     const bool cfg = plan->cfg != 0;
-    if (cfg && (h->B % 2)) return fail("tmd_sample: a classifier-free-guidance plan needs 2B bound patches [uncond | cond], got %d", h->B);
-    if (plan->model_type != TMD_MODEL_X_START && plan->model_type != TMD_MODEL_NOISE) return fail("tmd_sample: bad model_type %d", plan->model_type);
     const bool noise_type = plan->model_type == TMD_MODEL_NOISE;
     const int Bx = cfg ? h->B / 2 : h->B;      // patches being sampled
     const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * Bx, n_net = n_per * h->B;
-    if (n_per > 51200) return fail("tmd_sample: %zu values per patch exceeds the in-shared-memory quantile select (51200)", n_per);
     auto slot_ok = [](int i) { return i >= 0 && i < TMD_NUM_SLOTS; };
-    if (!slot_ok(plan->result_slot)) return fail("tmd_sample: bad result slot");
-
-    // every evaluation's time table in one launch (one CTA per evaluation), broadcast per evaluation below
-    std::vector<float> tin;
-    for (int i = 0; i < plan->n_steps; ++i)
-        if (plan->steps[i].kind == 0) tin.push_back(plan->steps[i].eval.t_input);
-    const bool pre_tb = !tin.empty() && (int)tin.size() <= kMaxPlanEvals;
     if (pre_tb) {
-        CK(cudaMemcpyAsync(h->d_tin_all, tin.data(), tin.size() * sizeof(float), cudaMemcpyHostToDevice, s));
-        if (prof_mark(h, TMD_K_COND, 0, ((double)h->time_rows * h->cfg.embed_dim + (double)tin.size() * h->time_rows) * 4, s, true, "time_table_all"))
+        if (prof_mark(h, TMD_K_COND, 0, ((double)h->time_rows * h->cfg.embed_dim + (double)n_evals * h->time_rows) * 4, s, true, "time_table_all"))
             return 1;
         CK(time_table(h->d_tin_all, 0.f, h->d_freqs, h->cfg.inter_dim, h->d_e_w1, h->d_e_b1, h->d_e_w2, h->d_e_b2, h->d_Wt, h->d_bt,
-                      nullptr, h->d_tb_all, (int)tin.size(), h->cfg.embed_dim, h->time_rows, s));
+                      nullptr, h->d_tb_all, n_evals, h->cfg.embed_dim, h->time_rows, s));
         if (prof_mark(h, TMD_K_COND, 0, 0, s, false)) return 1;
         ++h->launches;
     }
     struct Unbind { tmd_engine* e; ~Unbind() { e->tb_bcast_src = nullptr; } } unbind{h};
-
-    CK(cudaMemcpyAsync(h->slots[0], x_T, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
     int n_eval = 0;
     for (int i = 0; i < plan->n_steps; ++i) {
         const tmd_step& st = plan->steps[i];
@@ -935,6 +934,75 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
             if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             ++h->launches;
         }
+    }
+    return 0;
+}
+
+static uint64_t fnv1a(uint64_t hsh, const void* p, size_t n) {
+    const unsigned char* c = (const unsigned char*)p;
+    for (size_t i = 0; i < n; ++i) { hsh ^= c[i]; hsh *= 1099511628211ull; }
+    return hsh;
+}
+
+extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, float* out, float* trace, void* stream) {
+    if (!h || !x_T || !plan || !out || !plan->steps) return fail("tmd_sample: null argument");
+    if (h->B == 0 || h->step_ops.empty()) return fail("tmd_sample: call tmd_precompute_condition first");
+    cudaStream_t s = (cudaStream_t)stream;
+    CK(cudaSetDevice(h->device));
+    const bool cfg = plan->cfg != 0;
+    if (cfg && (h->B % 2)) return fail("tmd_sample: a classifier-free-guidance plan needs 2B bound patches [uncond | cond], got %d", h->B);
+    if (plan->model_type != TMD_MODEL_X_START && plan->model_type != TMD_MODEL_NOISE) return fail("tmd_sample: bad model_type %d", plan->model_type);
+    const int Bx = cfg ? h->B / 2 : h->B;
+    const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * Bx;
+    if (n_per > 51200) return fail("tmd_sample: %zu values per patch exceeds the in-shared-memory quantile select (51200)", n_per);
+    if (plan->result_slot < 0 || plan->result_slot >= TMD_NUM_SLOTS) return fail("tmd_sample: bad result slot");
+
+    // every evaluation's t_input -> device (the time tables are then computed by one launch inside sample_body)
+    int n_evals = 0;
+    for (int i = 0; i < plan->n_steps; ++i) n_evals += plan->steps[i].kind == 0;
+    const bool pre_tb = n_evals > 0 && n_evals <= kMaxPlanEvals;
+    if (pre_tb) {
+        std::vector<float> tin;     // pageable: the async copy stages it before returning
+        for (int i = 0; i < plan->n_steps; ++i)
+            if (plan->steps[i].kind == 0) tin.push_back(plan->steps[i].eval.t_input);
+        CK(cudaMemcpyAsync(h->d_tin_all, tin.data(), tin.size() * sizeof(float), cudaMemcpyHostToDevice, s));
+    }
+    CK(cudaMemcpyAsync(h->slots[0], x_T, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+
+    static const bool graphs_on = !getenv("TMD_NO_GRAPH");
+    cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(s, &capturing);
+    if (graphs_on && pre_tb && !trace && !h->profiling && capturing == cudaStreamCaptureStatusNone) {
+        uint64_t key = fnv1a(1469598103934665603ull, plan->steps, (size_t)plan->n_steps * sizeof(tmd_step));
+        const int32_t scal[6] = {plan->n_steps, plan->result_slot, plan->q_lo, plan->model_type, plan->cfg, h->B};
+        const float fsc[3] = {plan->q_weight, plan->max_val, plan->guidance_scale};
+        key = fnv1a(fnv1a(key, scal, sizeof(scal)), fsc, sizeof(fsc));
+        tmd_engine::SampleGraph* g = nullptr;
+        for (auto& c : h->graphs)
+            if (c.key == key) g = &c;
+        if (!g) {
+            if (!h->cap_stream) CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+            const int64_t l0 = h->launches;
+            CK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
+            const int rc = sample_body(h, plan, nullptr, n_evals, pre_tb, h->cap_stream);
+            cudaGraph_t graph = nullptr;
+            const cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
+            const int64_t counted = h->launches - l0;
+            h->launches = l0;
+            if (rc) { if (graph) cudaGraphDestroy(graph); return 1; }
+            if (ce != cudaSuccess) return fail("tmd_sample: graph capture failed: %s", cudaGetErrorString(ce));
+            cudaGraphExec_t exec = nullptr;
+            const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ie != cudaSuccess) return fail("tmd_sample: graph instantiation failed: %s", cudaGetErrorString(ie));
+            if (h->graphs.size() >= 8) { cudaGraphExecDestroy(h->graphs.front().exec); h->graphs.erase(h->graphs.begin()); }
+            h->graphs.push_back({key, exec, counted});
+            g = &h->graphs.back();
+        }
+        CK(cudaGraphLaunch(g->exec, s));
+        h->launches += g->launches;
+    } else if (sample_body(h, plan, trace, n_evals, pre_tb, s)) {
+        return 1;
     }
     CK(cudaMemcpyAsync(out, h->slots[plan->result_slot], n * sizeof(float), cudaMemcpyDeviceToDevice, s));
     return 0;
