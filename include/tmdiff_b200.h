@@ -145,6 +145,26 @@ int tmd_conv3d_mod(const float* x, const float* w, const float* s, const float* 
 /* DPM_Solver.dynamic_thresholding_fn (core/dpm_solver_pytorch.py:430-439) in place on x0 [B, n] */
 int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream);
 
+/* ---- operators the north star names that the reference's sampling path never executes;
+ * device fp32, reference layouts ---------------------------------------------------------------- */
+/* torch.nn.GroupNorm(G, C, eps) over x [B, C, S] (S = product of the trailing dims), then y = gamma*x_hat + beta and an
+ * optional Swish.  per_sample_affine = 0: gamma/beta [C] (core/Attention.py:108-109 Normalize; AttnBlockpp.GroupNorm_0,
+ * Hyper_unet_general.py:487); = 1: gamma/beta [B, C] from the style vector (AdaptiveGroupNorm, :311-331).  gamma/beta
+ * may be NULL (affine=False). */
+int tmd_groupnorm(const float* x, float* y, const float* gamma, const float* beta, int32_t per_sample_affine, int32_t B,
+                  int32_t C, int64_t S, int32_t G, float eps, int32_t swish, void* stream);
+/* out[bh,i,:] = softmax_j(scale * q[bh,i,:].k[bh,j,:]) v[bh,j,:]; q/out [BH,Lq,D], k/v [BH,Lk,D], D <= 2048.
+ * The core of SpatialSelfAttention (core/Attention.py:140-159), CrossAttention (:185-214) and AttnBlockpp
+ * (Hyper_unet_general.py:500-506) as one fused pass (no [Lq,Lk] matrix in HBM). */
+int tmd_attention(const float* q, const float* k, const float* v, float* out, int32_t BH, int32_t Lq, int32_t Lk, int32_t D,
+                  float scale, void* stream);
+/* Dynamic_conv3d.forward (core/dynamic_conv.py:244-268; groups=1, stride 1, 'same' padding, k in {1,3}):
+ * x [B,Ci,N,H,W], weight [K,Co,Ci,k,k,k], bias [K,Co] or NULL, fc1 [hidden,Ci], fc2 [K,hidden] (attention3d's 1x1x1 convs,
+ * :194-218) -> y [B,Co,N,H,W]. */
+int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2, float* y,
+                       int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K,
+                       int32_t hidden, float temperature, int32_t dtype, void* stream);
+
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);
 

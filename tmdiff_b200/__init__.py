@@ -8,3 +8,4 @@ from .networks import WavBEST, define_General  # noqa: F401
 from .diffusion import GeneralDiffusion  # noqa: F401
 from .dpm_solver import DPM_Solver, NoiseScheduleVP, model_wrapper  # noqa: F401
 from . import ops  # noqa: F401
+from . import operators  # noqa: F401

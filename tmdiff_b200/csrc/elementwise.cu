@@ -380,8 +380,8 @@ __global__ void dense_rows_kernel(const float* __restrict__ x, const float* __re
     for (int k = lane; k < in_dim; k += 32) a = fmaf(W[(size_t)j * in_dim + k], x[(size_t)r * in_dim + k], a);
     a = warp_sum(a);
     if (lane == 0) {
-        a += bias[j];
-        y[(size_t)r * out_dim + j] = act ? swish<false>(a) : a;
+        if (bias) a += bias[j];
+        y[(size_t)r * out_dim + j] = act == 1 ? swish<false>(a) : (act == 2 ? fmaxf(a, 0.f) : a);
     }
 }
 

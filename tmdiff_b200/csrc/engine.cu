@@ -1127,3 +1127,99 @@ extern "C" int tmd_conv3d_mod(const float* x, const float* w, const float* sc, c
     cudaFreeAsync(xin, s); cudaFreeAsync(yout, s); cudaFreeAsync(pf, s); cudaFreeAsync(pb, s);
     return rc;
 }
+
+// ---------------------------------------------------------------------------------------------
+// operators named by the north star outside the sampling path
+// ---------------------------------------------------------------------------------------------
+extern "C" int tmd_groupnorm(const float* x, float* y, const float* gamma, const float* beta, int32_t per_sample_affine, int32_t B,
+                             int32_t C, int64_t S, int32_t G, float eps, int32_t swish, void* stream) {
+    if (!x || !y) return fail("tmd_groupnorm: null argument");
+    if (B <= 0 || C <= 0 || S <= 0 || G <= 0 || C % G) return fail("tmd_groupnorm: C=%d must be a positive multiple of num_groups=%d", C, G);
+    cudaStream_t s = (cudaStream_t)stream;
+    // enough CTAs per group to fill the machine at small B*G, slices of at least 4096 values
+    const size_t n = (size_t)(C / G) * (size_t)S;
+    int split = (int)((4 * 148 + (size_t)B * G - 1) / ((size_t)B * G));
+    const int max_split = (int)((n + 4095) / 4096);
+    if (split > max_split) split = max_split;
+    if (split > 64) split = 64;
+    if (split < 1) split = 1;
+    float* partial = nullptr;
+    CK(cudaMallocAsync((void**)&partial, (size_t)B * G * split * 3 * sizeof(float), s));
+    const cudaError_t err = groupnorm_affine(x, y, partial, gamma, beta, per_sample_affine ? C : 0, B, C, (size_t)S, G, split, eps, swish, s);
+    cudaFreeAsync(partial, s);
+    if (err != cudaSuccess) return fail("tmd_groupnorm: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_attention(const float* q, const float* k, const float* v, float* out, int32_t BH, int32_t Lq, int32_t Lk, int32_t D,
+                             float scale, void* stream) {
+    if (!q || !k || !v || !out) return fail("tmd_attention: null argument");
+    if (BH <= 0 || Lq <= 0 || Lk <= 0 || D <= 0) return fail("tmd_attention: empty problem");
+    if (D > 2048) return fail("tmd_attention: head width %d exceeds 2048", D);
+    if (BH > 65535) return fail("tmd_attention: batch*heads %d exceeds 65535", BH);
+    const cudaError_t err = attention_f32(q, k, v, out, BH, Lq, Lk, D, scale, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_attention: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2, float* y,
+                                  int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K,
+                                  int32_t hidden, float temperature, int32_t dtype, void* stream) {
+    if (!x || !weight || !fc1 || !fc2 || !y) return fail("tmd_dynamic_conv3d: null argument");
+    if (k != 1 && k != 3) return fail("tmd_dynamic_conv3d: kernel size must be 1 or 3");
+    if (Ci % 4 || Co % 4) return fail("tmd_dynamic_conv3d: Ci and Co must be multiples of 4");
+    if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_dynamic_conv3d: bad dtype");
+    if (B <= 0 || K <= 0 || hidden <= 0) return fail("tmd_dynamic_conv3d: empty problem");
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
+    const int taps = k * k * k;
+    const size_t wn = (size_t)Co * Ci * taps;
+    float *pooled = nullptr, *hid = nullptr, *alpha = nullptr, *aw = nullptr, *ab = nullptr, *pf = nullptr;
+    __nv_bfloat16* pb = nullptr;
+    void *xin = nullptr, *yout = nullptr;
+    CK(cudaMallocAsync((void**)&pooled, (size_t)B * Ci * 4, s));
+    CK(cudaMallocAsync((void**)&hid, (size_t)B * hidden * 4, s));
+    CK(cudaMallocAsync((void**)&alpha, (size_t)B * K * 4, s));
+    CK(cudaMallocAsync((void**)&aw, (size_t)B * wn * 4, s));
+    CK(cudaMallocAsync((void**)&ab, (size_t)B * Co * 4, s));
+    CK(cudaMallocAsync((void**)&pf, wn * 4, s));
+    CK(cudaMallocAsync((void**)&pb, wn * 2, s));
+    CK(cudaMallocAsync(&xin, (size_t)B * nhw * Ci * es, s));
+    CK(cudaMallocAsync(&yout, (size_t)B * nhw * Co * es, s));
+    // attention3d (:194-218): avgpool -> fc1 -> relu -> fc2 -> softmax(. / temperature)
+    CK(spatial_mean(x, pooled, (size_t)B * Ci, nhw, s));
+    CK(dense_rows(pooled, fc1, nullptr, hid, B, Ci, hidden, 2, s));
+    CK(dense_rows(hid, fc2, nullptr, alpha, B, hidden, K, 0, s));
+    CK(softmax_temperature(alpha, B, K, temperature, s));
+    // aggregate_weight / aggregate_bias (:251-257)
+    CK(mix_experts(alpha, weight, aw, B, K, wn, s));
+    if (bias) CK(mix_experts(alpha, bias, ab, B, K, (size_t)Co, s));
+    CK(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s));
+    int rc = 0;
+    for (int b = 0; b < B && !rc; ++b) {       // groups = batch conv (:258-263): one shared-geometry conv per sample with its own weights
+        pack_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, s>>>(aw + (size_t)b * wn, pf, pb, Co, Ci, taps);
+        CK(cudaGetLastError());
+        ConvOp op{};
+        op.B = 1; op.N = N; op.H = H; op.W = W; op.Ci = Ci; op.ld_in = Ci; op.Co = Co; op.taps = taps;
+        op.src = (const char*)xin + (size_t)b * nhw * Ci * es;
+        op.w_f32 = pf; op.w_bf16 = pb;
+        op.epi.mode = CONV_NORMAL; op.epi.bias = bias ? ab + (size_t)b * Co : nullptr;
+        op.epi.raw_out = (char*)yout + (size_t)b * nhw * Co * es; op.epi.ld_raw = Co;
+        if (dtype == TMD_F32) {
+            CK(conv_simt_f32(op, s));
+        } else if (conv_umma_supported(op)) {
+            UmmaPlan* plan = conv_umma_plan_create(op);
+            if (!plan) rc = fail("tmd_dynamic_conv3d: tensor map creation failed");
+            else {
+                const cudaError_t err = conv_umma_bf16(op, plan, s);
+                conv_umma_plan_destroy(plan);
+                if (err != cudaSuccess) rc = fail("tmd_dynamic_conv3d: %s", cudaGetErrorString(err));
+            }
+        } else {
+            CK(conv_simt_bf16(op, s));
+        }
+    }
+    if (!rc) CK(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s));
+    for (void* p : {(void*)pooled, (void*)hid, (void*)alpha, (void*)aw, (void*)ab, (void*)pf, (void*)pb, xin, yout}) cudaFreeAsync(p, s);
+    return rc;
+}

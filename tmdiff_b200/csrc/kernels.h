@@ -46,7 +46,7 @@ cudaError_t cl_to_ncdhw(int dtype, const void* x, float* out, int B, int C, size
 cudaError_t time_table(const float* t_input, float t_scalar, const float* freqs, int inter_dim, const float* w1, const float* b1, const float* w2,
                        const float* b2, const float* Wt, const float* bt, float* embed_out, float* table, int B, int E, int rows,
                        cudaStream_t s);
-// y[r][j] = act(W[j].x[r] + b[j])  small dense layer (rows r), act: 0 none, 1 swish
+// y[r][j] = act(W[j].x[r] + b[j])  small dense layer (rows r), act: 0 none, 1 swish, 2 relu; b may be null
 cudaError_t dense_rows(const float* x, const float* W, const float* b, float* y, int rows, int in_dim, int out_dim, int act,
                        cudaStream_t s);
 cudaError_t gather_rows(const float* table, const int* ids, float* out, int B, int width, cudaStream_t s);
@@ -63,5 +63,19 @@ cudaError_t solver_update(float* dst, const float* x, const float* m, const floa
                           cudaStream_t s);
 cudaError_t solver_update_multistep(int form, float* dst, const float* x, const float* m, const float* m1, const float* m2, float c1,
                                     float c2, float c3, const float* k, size_t n, cudaStream_t s);
+
+// ---- stand-alone operators outside the sampling path (operators.cu) ----
+// GroupNorm(G, C, eps) over x [B, C, S] + affine gamma/beta[b * gb_stride + c] (null: none) + optional Swish.
+// partial: workspace of B*G*split*3 floats.
+cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const float* gamma, const float* beta, int gb_stride, int B,
+                             int C, size_t S, int G, int split, float eps, int act, cudaStream_t s);
+// out[bh,i,:] = softmax_j(scale * q[bh,i,:].k[bh,j,:]) v[bh,j,:];  q/out [BH,Lq,D], k/v [BH,Lk,D] fp32, D <= 2048
+cudaError_t attention_f32(const float* q, const float* k, const float* v, float* out, int BH, int Lq, int Lk, int D, float scale,
+                          cudaStream_t s);
+
+// Dynamic_conv3d pieces (core/dynamic_conv.py:194-268): channel means, expert softmax, per-sample expert mix
+cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s);                       // out[r] = mean(x[r, :])
+cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cudaStream_t s);                      // in place over K
+cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, int K, size_t n, cudaStream_t s);    // out[b,:] = sum_k alpha[b,k] w[k,:]
 
 }  // namespace tmd

@@ -1,0 +1,285 @@
+// Stand-alone operators named by the north star but not executed on the reference's sampling path (SURVEY.md 8(a)
+// n1-n4): group normalisation with (adaptive) affine + Swish, and fused softmax attention.  fp32 in the reference
+// layout; these are the per-operator sweep's kernels, not part of patches/s.
+//
+//   GroupNorm / AdaptiveGroupNorm:  torch.nn.GroupNorm(G, C, eps) over [B, C, S] followed by
+//       y = gamma[b?, c] * x_hat + beta[b?, c]   (+ Swish)
+//     core/Attention.py:108-109 (Normalize), GeneralModel/Hyper_unet_general.py:311-331 (AdaptiveGroupNorm),
+//     :487-488 (AttnBlockpp.GroupNorm_0).  Memory-bound: one statistics pass + one apply pass, each group split over
+//     several CTAs so small batches still fill the machine; warp-shuffle reductions, Chan's merge of the partials.
+//
+//   attention:  out[bh, i, :] = softmax_j(scale * q[bh, i, :] . k[bh, j, :]) v[bh, j, :]
+//     core/Attention.py:140-159 (SpatialSelfAttention: one head of width C), :185-214 (CrossAttention: 8 heads of 64
+//     against 77 text tokens), Hyper_unet_general.py:500-506 (AttnBlockpp).  One pass over the keys with a running
+//     row maximum / sum (no [Lq, Lk] matrix in HBM), any head width up to 2048.
+#include <float.h>
+
+#include "kernels.h"
+
+namespace tmd {
+
+namespace {
+
+__device__ __forceinline__ float warp_sum_f(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// group norm
+// ------------------------------------------------------------------------------------------------
+constexpr int GN_THREADS = 256;
+
+// partial[(bg * split + s)] = {count, mean, M2} of slice s of group bg  (group = n contiguous floats)
+__global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const float* __restrict__ x, float* __restrict__ partial, size_t n, int split) {
+    const size_t bg = blockIdx.x;
+    const int s = blockIdx.y;
+    const size_t per = ((n + split - 1) / split + 3) & ~(size_t)3;
+    const size_t lo = (size_t)s * per, hi = lo + per < n ? lo + per : n;
+    const float* p = x + bg * n;
+    __shared__ float red[2][GN_THREADS / 32];
+    float cnt = 0.f, mean = 0.f, m2 = 0.f;
+    if (lo < hi) {
+        const float shift = p[lo];                      // shifted sums: no cancellation for data with a large mean
+        float a = 0.f, q = 0.f;
+        if ((n & 3) == 0) {
+            for (size_t i = lo + 4 * threadIdx.x; i < hi; i += 4 * GN_THREADS) {
+                const float4 v = *reinterpret_cast<const float4*>(p + i);
+                const float d0 = v.x - shift, d1 = v.y - shift, d2 = v.z - shift, d3 = v.w - shift;
+                a += (d0 + d1) + (d2 + d3);
+                q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+            }
+        } else {
+            for (size_t i = lo + threadIdx.x; i < hi; i += GN_THREADS) {
+                const float d = p[i] - shift;
+                a += d;
+                q += d * d;
+            }
+        }
+        a = warp_sum_f(a);
+        q = warp_sum_f(q);
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = q; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float A = 0.f, Q = 0.f;
+            for (int w = 0; w < GN_THREADS / 32; ++w) { A += red[0][w]; Q += red[1][w]; }
+            cnt = (float)(hi - lo);
+            mean = shift + A / cnt;
+            m2 = fmaxf(Q - A * A / cnt, 0.f);
+        }
+    }
+    if (threadIdx.x == 0) {
+        float* o = partial + (bg * split + s) * 3;
+        o[0] = cnt; o[1] = mean; o[2] = m2;
+    }
+}
+
+// y = gamma * (x - mean) * rstd + beta (+ swish);  gamma/beta indexed [b * gb_stride + c] (gb_stride = 0: shared affine)
+__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                              const float* __restrict__ partial, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, int gb_stride, int G, int cpg, size_t S,
+                                                              int split, float eps, int act) {
+    const size_t bg = blockIdx.x;
+    const int s = blockIdx.y;
+    const size_t n = (size_t)cpg * S;
+    // Chan's pairwise merge of the slices' (count, mean, M2)
+    float cnt = 0.f, mean = 0.f, m2 = 0.f;
+    for (int i = 0; i < split; ++i) {
+        const float* q = partial + (bg * split + i) * 3;
+        const float nb = q[0];
+        if (nb == 0.f) continue;
+        const float d = q[1] - mean, tot = cnt + nb;
+        mean += d * nb / tot;
+        m2 += q[2] + d * d * cnt * nb / tot;
+        cnt = tot;
+    }
+    const float rstd = rsqrtf(m2 / cnt + eps);
+    const int b = (int)(bg / G), g = (int)(bg % G);
+    const size_t per = ((n + split - 1) / split + 3) & ~(size_t)3;
+    const size_t lo = (size_t)s * per, hi = lo + per < n ? lo + per : n;
+    const float* p = x + bg * n;
+    float* o = y + bg * n;
+    auto one = [&](size_t i, float v) {
+        const int c = g * cpg + (int)(i / S);
+        float r = (v - mean) * rstd;
+        const float ga = gamma ? gamma[(size_t)b * gb_stride + c] : 1.f, be = beta ? beta[(size_t)b * gb_stride + c] : 0.f;
+        r = ga * r + be;
+        if (act) r = r * (1.f / (1.f + expf(-r)));
+        return r;
+    };
+    if ((S & 3) == 0) {
+        for (size_t i = lo + 4 * threadIdx.x; i < hi; i += 4 * GN_THREADS) {
+            const float4 v = *reinterpret_cast<const float4*>(p + i);
+            *reinterpret_cast<float4*>(o + i) = make_float4(one(i, v.x), one(i + 1, v.y), one(i + 2, v.z), one(i + 3, v.w));
+        }
+    } else {
+        for (size_t i = lo + threadIdx.x; i < hi; i += GN_THREADS) o[i] = one(i, p[i]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused softmax attention (fp32): 8 queries per CTA (one per warp for the row statistics), keys in tiles of 32,
+// the head dimension in chunks of 64 for q.k and striped over the 256 threads for p.v
+// ------------------------------------------------------------------------------------------------
+constexpr int AT_BQ = 8, AT_BK = 32, AT_DC = 64, AT_THREADS = 256, AT_MAXDPT = 8;   // head width <= 2048
+
+template <int DPT>
+__global__ void __launch_bounds__(AT_THREADS) attention_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                               const float* __restrict__ v, float* __restrict__ out, int Lq, int Lk,
+                                                               int D, float scale) {
+    __shared__ float Qs[AT_BQ][AT_DC];
+    __shared__ float Ks[AT_BK][AT_DC + 1];
+    __shared__ float Ps[AT_BQ][AT_BK];
+    __shared__ float alpha_s[AT_BQ], l_s[AT_BQ];
+    const int bh = blockIdx.y, q0 = blockIdx.x * AT_BQ;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const float* qb = q + ((size_t)bh * Lq + q0) * D;
+    const float* kb = k + (size_t)bh * Lk * D;
+    const float* vb = v + (size_t)bh * Lk * D;
+    float acc[AT_BQ][DPT];
+#pragma unroll
+    for (int i = 0; i < AT_BQ; ++i)
+#pragma unroll
+        for (int c = 0; c < DPT; ++c) acc[i][c] = 0.f;
+    float m_run = -FLT_MAX, l_run = 0.f;            // row w's statistics (replicated across the warp)
+    for (int j0 = 0; j0 < Lk; j0 += AT_BK) {
+        // ---- s[w][lane] = scale * q[q0+w] . k[j0+lane]
+        float sacc = 0.f;
+        for (int d0 = 0; d0 < D; d0 += AT_DC) {
+            __syncthreads();
+            for (int e = tid; e < AT_BQ * AT_DC; e += AT_THREADS) {
+                const int i = e / AT_DC, d = e % AT_DC;
+                Qs[i][d] = (q0 + i < Lq && d0 + d < D) ? qb[(size_t)i * D + d0 + d] : 0.f;
+            }
+            for (int e = tid; e < AT_BK * AT_DC; e += AT_THREADS) {
+                const int j = e / AT_DC, d = e % AT_DC;
+                Ks[j][d] = (j0 + j < Lk && d0 + d < D) ? kb[(size_t)(j0 + j) * D + d0 + d] : 0.f;
+            }
+            __syncthreads();
+#pragma unroll 16
+            for (int d = 0; d < AT_DC; ++d) sacc = fmaf(Qs[w][d], Ks[lane][d], sacc);
+        }
+        const bool live = j0 + lane < Lk;
+        const float sv = live ? sacc * scale : -FLT_MAX;
+        float mx = sv;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        const float m_new = fmaxf(m_run, mx);
+        const float pv = live ? expf(sv - m_new) : 0.f;
+        const float a = expf(m_run - m_new);
+        l_run = l_run * a + warp_sum_f(pv);
+        m_run = m_new;
+        Ps[w][lane] = pv;
+        if (lane == 0) alpha_s[w] = a;
+        __syncthreads();
+        // ---- acc[i][:] = acc[i][:] * alpha[i] + sum_j P[i][j] * v[j0+j][:]
+#pragma unroll
+        for (int i = 0; i < AT_BQ; ++i) {
+            const float al = alpha_s[i];
+#pragma unroll
+            for (int c = 0; c < DPT; ++c) acc[i][c] *= al;
+        }
+        const int jn = Lk - j0 < AT_BK ? Lk - j0 : AT_BK;
+        for (int j = 0; j < jn; ++j) {
+            float vv[DPT];
+#pragma unroll
+            for (int c = 0; c < DPT; ++c) {
+                const int d = tid + c * AT_THREADS;
+                vv[c] = d < D ? vb[(size_t)(j0 + j) * D + d] : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < AT_BQ; ++i) {
+                const float pj = Ps[i][j];
+#pragma unroll
+                for (int c = 0; c < DPT; ++c) acc[i][c] = fmaf(pj, vv[c], acc[i][c]);
+            }
+        }
+    }
+    if (lane == 0) l_s[w] = l_run;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < AT_BQ; ++i) {
+        if (q0 + i >= Lq) break;
+        const float inv = 1.f / l_s[i];
+#pragma unroll
+        for (int c = 0; c < DPT; ++c) {
+            const int d = tid + c * AT_THREADS;
+            if (d < D) out[((size_t)bh * Lq + q0 + i) * D + d] = acc[i][c] * inv;
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t attention_f32(const float* q, const float* k, const float* v, float* out, int BH, int Lq, int Lk, int D, float scale,
+                          cudaStream_t s) {
+    if (D > AT_MAXDPT * AT_THREADS) return cudaErrorInvalidValue;
+    dim3 grid((unsigned)((Lq + AT_BQ - 1) / AT_BQ), (unsigned)BH);
+    const int dpt = (D + AT_THREADS - 1) / AT_THREADS;
+    if (dpt <= 1) attention_kernel<1><<<grid, AT_THREADS, 0, s>>>(q, k, v, out, Lq, Lk, D, scale);
+    else if (dpt <= 2) attention_kernel<2><<<grid, AT_THREADS, 0, s>>>(q, k, v, out, Lq, Lk, D, scale);
+    else if (dpt <= 4) attention_kernel<4><<<grid, AT_THREADS, 0, s>>>(q, k, v, out, Lq, Lk, D, scale);
+    else attention_kernel<8><<<grid, AT_THREADS, 0, s>>>(q, k, v, out, Lq, Lk, D, scale);
+    return cudaGetLastError();
+}
+
+namespace {
+__global__ void __launch_bounds__(256) spatial_mean_kernel(const float* __restrict__ x, float* __restrict__ out, size_t S) {
+    const float* p = x + (size_t)blockIdx.x * S;
+    __shared__ float red[8];
+    float a = 0.f;
+    for (size_t i = threadIdx.x; i < S; i += 256) a += p[i];
+    a = warp_sum_f(a);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = a;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        out[blockIdx.x] = t / (float)S;
+    }
+}
+__global__ void softmax_temperature_kernel(float* x, int rows, int K, float temperature) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    float* p = x + (size_t)r * K;
+    float mx = -FLT_MAX;
+    for (int k = 0; k < K; ++k) { p[k] = p[k] / temperature; mx = fmaxf(mx, p[k]); }
+    float sum = 0.f;
+    for (int k = 0; k < K; ++k) { p[k] = expf(p[k] - mx); sum += p[k]; }
+    for (int k = 0; k < K; ++k) p[k] /= sum;
+}
+__global__ void mix_experts_kernel(const float* __restrict__ alpha, const float* __restrict__ w, float* __restrict__ out, int K, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int b = blockIdx.y;
+    float a = 0.f;
+    for (int k = 0; k < K; ++k) a = fmaf(alpha[b * K + k], w[(size_t)k * n + i], a);    // torch.mm(softmax_attention, weight)
+    out[(size_t)b * n + i] = a;
+}
+}  // namespace
+
+cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s) {
+    spatial_mean_kernel<<<(unsigned)rows, 256, 0, s>>>(x, out, S);
+    return cudaGetLastError();
+}
+cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cudaStream_t s) {
+    softmax_temperature_kernel<<<(rows + 127) / 128, 128, 0, s>>>(x, rows, K, temperature);
+    return cudaGetLastError();
+}
+cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, int K, size_t n, cudaStream_t s) {
+    dim3 grid((unsigned)((n + 255) / 256), (unsigned)B);
+    mix_experts_kernel<<<grid, 256, 0, s>>>(alpha, w, out, K, n);
+    return cudaGetLastError();
+}
+
+cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const float* gamma, const float* beta, int gb_stride, int B,
+                             int C, size_t S, int G, int split, float eps, int act, cudaStream_t s) {
+    const int cpg = C / G;
+    dim3 grid((unsigned)((size_t)B * G), (unsigned)split);
+    gn_stats_kernel<<<grid, GN_THREADS, 0, s>>>(x, partial, (size_t)cpg * S, split);
+    gn_apply_kernel<<<grid, GN_THREADS, 0, s>>>(x, y, partial, gamma, beta, gb_stride, G, cpg, S, split, eps, act);
+    return cudaGetLastError();
+}
+
+}  // namespace tmd

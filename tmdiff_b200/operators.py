@@ -1,0 +1,198 @@
+"""The operators the north star names that the reference's sampling path never executes, with
+the reference's class names, constructor arguments and state-dict keys, backed by the CUDA library:
+
+    AdaptiveGroupNorm       GeneralModel/Hyper_unet_general.py:311-331  (+ optional fused Swish)
+    AttnBlockpp, NIN        GeneralModel/Hyper_unet_general.py:471-515
+    SpatialSelfAttention    core/Attention.py:112-162
+    CrossAttention          core/Attention.py:165-214
+    Dynamic_conv3d          core/dynamic_conv.py:194-268
+
+Normalisation, the softmax-attention core and the expert mixing are hand-written kernels (csrc/operators.cu); the
+1x1 projections run through the library's convolution operator (tcgen05 in bf16 mode, fp32 CUDA cores otherwise).
+Forward only, CUDA tensors only.  torch is used for parameter storage and layout views.
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .ops import _cuda_f32, modulated_conv3d
+
+
+def group_norm(x, num_groups, weight=None, bias=None, eps=1e-6, swish=False):
+    """F.group_norm(x, G, weight, bias, eps) [+ Swish]; weight/bias [C] shared or [B, C] per sample."""
+    x = _cuda_f32(x, "x")
+    B, Cc = x.shape[0], x.shape[1]
+    S = x[0, 0].numel()
+    per_sample = weight is not None and weight.dim() == 2
+    w = None if weight is None else _cuda_f32(weight, "weight")
+    b = None if bias is None else _cuda_f32(bias, "bias")
+    y = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().tmd_groupnorm(_lib.ptr(x), _lib.ptr(y), _lib.ptr(w), _lib.ptr(b), int(per_sample), B, Cc, S,
+                                             int(num_groups), float(eps), int(bool(swish)), _lib.stream_ptr()))
+    return y
+
+
+def attention(q, k, v, scale):
+    """softmax(scale * q k^T) v for q [BH, Lq, D], k/v [BH, Lk, D] in one fused pass."""
+    q, k, v = _cuda_f32(q, "q"), _cuda_f32(k, "k"), _cuda_f32(v, "v")
+    BH, Lq, D = q.shape
+    if k.shape[0] != BH or k.shape[2] != D or v.shape != k.shape:
+        raise ValueError("attention: q [BH,Lq,D], k and v [BH,Lk,D] expected")
+    out = torch.empty_like(q)
+    with torch.cuda.device(q.device):
+        _lib.check(_lib.load().tmd_attention(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), BH, Lq, k.shape[1], D,
+                                             float(scale), _lib.stream_ptr()))
+    return out
+
+
+def _conv1x1(x, weight, bias, dtype):
+    """1x1 conv of x [B, C, *spatial] with weight [Co, Ci] through the library's conv operator."""
+    B, Ci = x.shape[:2]
+    sp = x.shape[2:]
+    n = int(torch.tensor(sp).prod())
+    w2 = next(d for d in (8, 4, 2, 1) if n % d == 0)
+    y = modulated_conv3d(x.reshape(B, Ci, 1, n // w2, w2), weight.reshape(weight.shape[0], Ci, 1, 1, 1), bias=bias, dtype=dtype)
+    return y.reshape(B, weight.shape[0], *sp)
+
+
+def _linear_tokens(x, weight, bias, dtype):
+    """nn.Linear over the last dim of x [B, L, Cin] (tokens are the voxels of a 1x1 conv)."""
+    B, L, Cin = x.shape
+    y = _conv1x1(x.reshape(1, B * L, Cin).transpose(1, 2).contiguous(), weight, bias, dtype)
+    return y.reshape(weight.shape[0], B * L).t().reshape(B, L, weight.shape[0])
+
+
+class AdaptiveGroupNorm(nn.Module):
+    def __init__(self, num_groups, in_channel, style_dim):
+        super().__init__()
+        self.num_groups, self.in_channel = num_groups, in_channel
+        self.style = nn.Linear(style_dim, in_channel * 2)
+        nn.init.zeros_(self.style.bias)
+        self.style.bias.data[:in_channel] = 1
+        self.style.bias.data[in_channel:] = 0
+
+    @torch.no_grad()
+    def forward(self, input, style, swish=False):
+        """input [B, C, N, H, W], style [B, style_dim]; swish=True fuses the activation that follows the norm."""
+        gb = _linear_tokens(style[None].float(), self.style.weight, self.style.bias, "fp32")[0]     # [B, 2C]
+        gamma, beta = gb[:, :self.in_channel].contiguous(), gb[:, self.in_channel:].contiguous()
+        return group_norm(input, self.num_groups, gamma, beta, eps=1e-6, swish=swish)
+
+
+class NIN(nn.Module):
+    def __init__(self, in_dim, num_units, init_scale=0.1):
+        super().__init__()
+        bound = math.sqrt(3.0 * max(init_scale, 1e-10) / ((in_dim + num_units) / 2.0))
+        self.W = nn.Parameter(torch.empty(in_dim, num_units).uniform_(-bound, bound), requires_grad=False)
+        self.b = nn.Parameter(torch.zeros(num_units), requires_grad=False)
+
+
+class AttnBlockpp(nn.Module):
+    def __init__(self, channels, skip_rescale=True, init_scale=0.0, dtype="fp32"):
+        super().__init__()
+        self.channels, self.skip_rescale, self.compute_dtype = channels, skip_rescale, dtype
+        self.GroupNorm_0 = nn.GroupNorm(num_groups=min(channels // 4, 32), num_channels=channels, eps=1e-6)
+        self.NIN_0, self.NIN_1, self.NIN_2 = NIN(channels, channels), NIN(channels, channels), NIN(channels, channels)
+        self.NIN_3 = NIN(channels, channels, init_scale=init_scale)
+
+    @torch.no_grad()
+    def forward(self, x):
+        """x [B, C, N, H, W] with C*N == channels; the logits are scaled by C^-0.5 (the feature C, :500)."""
+        B, Cf, N, H, W = x.shape
+        x2 = x.reshape(B, Cf * N, H, W)
+        h = group_norm(x2, self.GroupNorm_0.num_groups, self.GroupNorm_0.weight, self.GroupNorm_0.bias, eps=1e-6)
+        q, k, v = (_conv1x1(h, n.W.t().contiguous(), n.b, self.compute_dtype) for n in (self.NIN_0, self.NIN_1, self.NIN_2))
+        tok = lambda t: t.reshape(B, Cf * N, H * W).transpose(1, 2).contiguous()
+        o = attention(tok(q), tok(k), tok(v), int(Cf) ** (-0.5))
+        o = o.transpose(1, 2).reshape(B, Cf * N, H, W)
+        o = _conv1x1(o, self.NIN_3.W.t().contiguous(), self.NIN_3.b, self.compute_dtype)
+        out = (x2 + o).reshape(B, Cf, N, H, W)
+        return out / math.sqrt(2.0) if self.skip_rescale else out
+
+
+class SpatialSelfAttention(nn.Module):
+    def __init__(self, in_channels, dtype="fp32"):
+        super().__init__()
+        self.in_channels, self.compute_dtype = in_channels, dtype
+        self.norm = nn.GroupNorm(num_groups=32, num_channels=in_channels, eps=1e-6, affine=True)
+        self.q, self.k, self.v, self.proj_out = (nn.Conv2d(in_channels, in_channels, 1) for _ in range(4))
+
+    @torch.no_grad()
+    def forward(self, x):
+        B, Cc, H, W = x.shape
+        h = group_norm(x, 32, self.norm.weight, self.norm.bias, eps=1e-6)
+        q, k, v = (_conv1x1(h, m.weight.reshape(Cc, Cc), m.bias, self.compute_dtype) for m in (self.q, self.k, self.v))
+        tok = lambda t: t.reshape(B, Cc, H * W).transpose(1, 2).contiguous()
+        o = attention(tok(q), tok(k), tok(v), int(Cc) ** (-0.5)).transpose(1, 2).reshape(B, Cc, H, W)
+        return x + _conv1x1(o, self.proj_out.weight.reshape(Cc, Cc), self.proj_out.bias, self.compute_dtype)
+
+
+class CrossAttention(nn.Module):
+    def __init__(self, query_dim, context_dim=None, heads=8, dim_head=64, dropout=0.0, dtype="fp32"):
+        super().__init__()
+        inner = dim_head * heads
+        context_dim = query_dim if context_dim is None else context_dim
+        self.scale, self.heads, self.compute_dtype = dim_head ** -0.5, heads, dtype
+        self.to_q = nn.Linear(query_dim, inner, bias=False)
+        self.to_k = nn.Linear(context_dim, inner, bias=False)
+        self.to_v = nn.Linear(context_dim, inner, bias=False)
+        self.to_out = nn.Sequential(nn.Linear(inner, query_dim), nn.Dropout(dropout))
+
+    @torch.no_grad()
+    def forward(self, x, context=None, mask=None):
+        if mask is not None:
+            raise NotImplementedError("attention masks are not used anywhere in the reference")
+        context = x if context is None else context
+        B, L, _ = x.shape
+        h = self.heads
+        q = _linear_tokens(x.float(), self.to_q.weight, None, self.compute_dtype)
+        k = _linear_tokens(context.float(), self.to_k.weight, None, self.compute_dtype)
+        v = _linear_tokens(context.float(), self.to_v.weight, None, self.compute_dtype)
+        split = lambda t: t.reshape(B, t.shape[1], h, -1).permute(0, 2, 1, 3).reshape(B * h, t.shape[1], -1).contiguous()
+        o = attention(split(q), split(k), split(v), self.scale)               # logits always in fp32 (:194-197)
+        o = o.reshape(B, h, L, -1).permute(0, 2, 1, 3).reshape(B, L, -1)
+        return _linear_tokens(o, self.to_out[0].weight, self.to_out[0].bias, self.compute_dtype)
+
+
+class _Attention3d(nn.Module):
+    def __init__(self, in_planes, ratios, K, temperature):
+        super().__init__()
+        assert temperature % 3 == 1
+        hidden = int(in_planes * ratios) + 1 if in_planes != 3 else K
+        self.fc1 = nn.Conv3d(in_planes, hidden, 1, bias=False)
+        self.fc2 = nn.Conv3d(hidden, K, 1, bias=False)
+        self.temperature = temperature
+
+
+class Dynamic_conv3d(nn.Module):
+    def __init__(self, in_planes, out_planes, kernel_size, ratio=0.25, stride=1, padding=0, dilation=1, groups=1, bias=True, K=4,
+                 temperature=34, dtype="fp32"):
+        super().__init__()
+        assert in_planes % groups == 0
+        if groups != 1 or stride != 1 or dilation != 1 or kernel_size not in (1, 3) or padding != kernel_size // 2:
+            raise ValueError("Dynamic_conv3d: groups=1, stride=1, dilation=1 and 'same' padding with k in {1,3} are implemented")
+        self.in_planes, self.out_planes, self.kernel_size, self.K, self.compute_dtype = in_planes, out_planes, kernel_size, K, dtype
+        self.attention = _Attention3d(in_planes, ratio, K, temperature)
+        self.weight = nn.Parameter(torch.randn(K, out_planes, in_planes // groups, kernel_size, kernel_size, kernel_size),
+                                   requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(K, out_planes), requires_grad=False) if bias else None
+
+    @torch.no_grad()
+    def forward(self, x):
+        x = _cuda_f32(x, "x")
+        B, Ci, N, H, W = x.shape
+        hidden = self.attention.fc1.weight.shape[0]
+        y = torch.empty(B, self.out_planes, N, H, W, device=x.device)
+        w = _cuda_f32(self.weight, "weight")
+        b = None if self.bias is None else _cuda_f32(self.bias, "bias")
+        f1 = _cuda_f32(self.attention.fc1.weight, "fc1").reshape(hidden, Ci)
+        f2 = _cuda_f32(self.attention.fc2.weight, "fc2").reshape(self.K, hidden)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.load().tmd_dynamic_conv3d(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), _lib.ptr(y),
+                                                      B, Ci, self.out_planes, N, H, W, self.kernel_size, self.K, hidden,
+                                                      float(self.attention.temperature), _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16,
+                                                      _lib.stream_ptr()))
+        return y
