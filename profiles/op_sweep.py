@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""Per-operator sweep (BASELINE config 5): the memory-bound operators at the UNet's level shapes against the measured
+HBM copy bandwidth, the attention core against its FLOPs.  CUDA events on the launching stream, inputs larger than L2
+or an L2 flush between iterations.
+
+    python profiles/op_sweep.py > gpurun_out/op_sweep.md
+"""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from tmdiff_b200 import ops, operators  # noqa: E402
+
+PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+    os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else 6650.0
+FLUSH = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+
+def timed(fn, iters=5):
+    fn(); fn()
+    ts = []
+    for _ in range(iters):
+        FLUSH.zero_()                       # evict L2 (126 MB) between iterations
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return sorted(ts)[len(ts) // 2]
+
+
+def row(name, shape, ms, nbytes=None, flops=None):
+    gbs = nbytes / ms / 1e6 if nbytes else None
+    print("| %s | %s | %.3f | %s | %s | %s |" % (name, shape, ms, "%.0f" % gbs if gbs else "", "%.0f%%" % (100 * gbs / PEAK) if gbs else "",
+                                                 "%.1f" % (flops / ms / 1e9) if flops else ""))
+
+
+def main():
+    print("# per-operator sweep (median of 5, L2 flushed between iterations); HBM peak = %.0f GB/s (measured copy)\n" % PEAK)
+    print("| operator | shape | ms | GB/s (algorithmic) | of HBM peak | TFLOP/s |")
+    print("|---|---|---:|---:|---:|---:|")
+    dwt, idwt = ops.DWT_2D("haar"), ops.IDWT_2D("haar")
+    for B in (1, 16, 64, 256, 1024):
+        for (CN, HW) in ((128, 64), (256, 32), (512, 16)):         # 4-band level shapes (C*N, H)
+            x = torch.randn(B, CN, HW, HW, device="cuda")
+            row("DWT_2D", tuple(x.shape), timed(lambda: dwt(x)), 2 * x.numel() * 4)
+            row("DWT_2D LL-only", tuple(x.shape), timed(lambda: dwt(x, ll_only=True)), 1.25 * x.numel() * 4)
+            bands = dwt(x)
+            row("IDWT_2D", tuple(x.shape), timed(lambda: idwt(*bands)), 2 * x.numel() * 4)
+    for B in (1, 16, 64, 256, 1024):
+        for (C, HW) in ((32, 64), (64, 32), (128, 16), (256, 8)):
+            x = torch.randn(B, C, 4, HW, HW, device="cuda")
+            ga, be = torch.randn(B, C, device="cuda"), torch.randn(B, C, device="cuda")
+            row("GroupNorm(8)+FiLM+Swish", tuple(x.shape), timed(lambda: operators.group_norm(x, 8, ga, be, swish=True)), 2 * x.numel() * 4)
+    for B in (16, 64, 256):
+        x0 = torch.randn(B, 4, 64, 64, device="cuda") * 1.2
+        row("dynamic_thresholding", tuple(x0.shape), timed(lambda: ops.dynamic_thresholding(x0)), 2 * x0.numel() * 4)
+    for (BH, Lq, Lk, D) in ((64, 64, 64, 1024), (16, 256, 256, 512), (8, 1024, 1024, 256), (2, 4096, 4096, 128), (128, 1024, 77, 64),
+                            (512, 256, 77, 64)):
+        q, k, v = (torch.randn(BH, L, D, device="cuda") for L in (Lq, Lk, Lk))
+        row("attention core (fp32)", (BH, Lq, Lk, D), timed(lambda: operators.attention(q, k, v, D ** -0.5), 3), flops=4.0 * BH * Lq * Lk * D)
+
+
+if __name__ == "__main__":
+    main()

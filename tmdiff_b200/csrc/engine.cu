@@ -1071,6 +1071,19 @@ extern "C" int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_
 }
 
 namespace {
+// The stand-alone operators take their scratch from the stream-ordered pool; keep freed blocks cached instead of
+// returning them to the driver at every synchronisation (the default release threshold is 0).
+void keep_pool_warm() {
+    static bool done[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        uint64_t keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    done[dev] = true;
+}
 __global__ void pack_weights_kernel(const float* __restrict__ w, float* __restrict__ pf, __nv_bfloat16* __restrict__ pb, int Co, int Ci,
                                     int taps) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1092,6 +1105,7 @@ extern "C" int tmd_conv3d_mod(const float* x, const float* w, const float* sc, c
     if (Ci % 4 || Co % 4) return fail("tmd_conv3d_mod: Ci and Co must be multiples of 4");
     if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_conv3d_mod: bad dtype");
     cudaStream_t s = (cudaStream_t)stream;
+    keep_pool_warm();
     const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
     const int taps = k * k * k;
     void *xin = nullptr, *yout = nullptr;
@@ -1136,6 +1150,7 @@ extern "C" int tmd_groupnorm(const float* x, float* y, const float* gamma, const
     if (!x || !y) return fail("tmd_groupnorm: null argument");
     if (B <= 0 || C <= 0 || S <= 0 || G <= 0 || C % G) return fail("tmd_groupnorm: C=%d must be a positive multiple of num_groups=%d", C, G);
     cudaStream_t s = (cudaStream_t)stream;
+    keep_pool_warm();
     // enough CTAs per group to fill the machine at small B*G, slices of at least 4096 values
     const size_t n = (size_t)(C / G) * (size_t)S;
     int split = (int)((4 * 148 + (size_t)B * G - 1) / ((size_t)B * G));
@@ -1171,6 +1186,7 @@ extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const flo
     if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_dynamic_conv3d: bad dtype");
     if (B <= 0 || K <= 0 || hidden <= 0) return fail("tmd_dynamic_conv3d: empty problem");
     cudaStream_t s = (cudaStream_t)stream;
+    keep_pool_warm();
     const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
     const int taps = k * k * k;
     const size_t wn = (size_t)Co * Ci * taps;

@@ -12,9 +12,12 @@
 //     core/Attention.py:140-159 (SpatialSelfAttention: one head of width C), :185-214 (CrossAttention: 8 heads of 64
 //     against 77 text tokens), Hyper_unet_general.py:500-506 (AttnBlockpp).  One pass over the keys with a running
 //     row maximum / sum (no [Lq, Lk] matrix in HBM), any head width up to 2048.
+#include <cooperative_groups.h>
 #include <float.h>
 
 #include "kernels.h"
+
+namespace cg = cooperative_groups;
 
 namespace tmd {
 
@@ -116,6 +119,82 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const float* __res
     } else {
         for (size_t i = lo + threadIdx.x; i < hi; i += GN_THREADS) o[i] = one(i, p[i]);
     }
+}
+
+// Single-read variant: a thread-block cluster owns one group, every CTA keeps its slice of the group in shared memory
+// between the statistics and the apply phase, and the slices' (count, mean, M2) are exchanged through distributed
+// shared memory.  HBM traffic = one read + one write (the algorithmic bytes).  Needs n % 4 == 0 and S % 4 == 0.
+__global__ void __launch_bounds__(GN_THREADS) gn_cluster_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                int gb_stride, int G, int cpg, size_t S, size_t slice, float eps, int act) {
+    extern __shared__ __align__(16) float buf[];
+    __shared__ float part[3];
+    __shared__ float red[2][GN_THREADS / 32];
+    __shared__ float stat[2];
+    cg::cluster_group cl = cg::this_cluster();
+    const unsigned r = cl.block_rank(), CS = cl.num_blocks();
+    const size_t bg = blockIdx.x / CS;
+    const size_t n = (size_t)cpg * S;
+    const size_t lo = (size_t)r * slice, hi = lo + slice < n ? lo + slice : n;
+    const float* p = x + bg * n;
+    float a = 0.f, q = 0.f;
+    const float shift = lo < hi ? p[lo] : 0.f;
+    for (size_t i = lo + 4 * threadIdx.x; i < hi; i += 4 * GN_THREADS) {
+        const float4 v = *reinterpret_cast<const float4*>(p + i);
+        *reinterpret_cast<float4*>(buf + (i - lo)) = v;
+        const float d0 = v.x - shift, d1 = v.y - shift, d2 = v.z - shift, d3 = v.w - shift;
+        a += (d0 + d1) + (d2 + d3);
+        q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+    }
+    a = warp_sum_f(a);
+    q = warp_sum_f(q);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = q; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float A = 0.f, Q = 0.f;
+        for (int w = 0; w < GN_THREADS / 32; ++w) { A += red[0][w]; Q += red[1][w]; }
+        const float cnt = lo < hi ? (float)(hi - lo) : 0.f;
+        part[0] = cnt;
+        part[1] = cnt > 0.f ? shift + A / cnt : 0.f;
+        part[2] = cnt > 0.f ? fmaxf(Q - A * A / cnt, 0.f) : 0.f;
+    }
+    cl.sync();
+    if (threadIdx.x == 0) {          // every CTA merges the same partials in the same order: identical statistics
+        float cnt = 0.f, mean = 0.f, m2 = 0.f;
+        for (unsigned i = 0; i < CS; ++i) {
+            const float* pq = cl.map_shared_rank(part, i);
+            const float nb = pq[0];
+            if (nb == 0.f) continue;
+            const float d = pq[1] - mean, tot = cnt + nb;
+            mean += d * nb / tot;
+            m2 += pq[2] + d * d * cnt * nb / tot;
+            cnt = tot;
+        }
+        stat[0] = mean;
+        stat[1] = rsqrtf(m2 / cnt + eps);
+    }
+    __syncthreads();
+    const float mean = stat[0], rstd = stat[1];
+    const int b = (int)(bg / G), g = (int)(bg % G);
+    float* o = y + bg * n;
+    // 32-bit indices inside the group (n < 2^31): the channel of a float4 costs one 32-bit division
+    const unsigned lo32 = (unsigned)lo, cnt32 = (unsigned)(hi - lo), S32 = (unsigned)S;
+    const float* gp = gamma ? gamma + (size_t)b * gb_stride + g * cpg : nullptr;
+    const float* bp = beta ? beta + (size_t)b * gb_stride + g * cpg : nullptr;
+    for (unsigned i = 4 * threadIdx.x; i < cnt32; i += 4 * GN_THREADS) {
+        const float4 v = *reinterpret_cast<const float4*>(buf + i);
+        const unsigned c = (lo32 + i) / S32;            // S % 4 == 0: the four values share a channel
+        const float ga = (gp ? gp[c] : 1.f) * rstd, be = (bp ? bp[c] : 0.f);
+        float rr[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float t = fmaf(ga, rr[j] - mean, be);
+            if (act) t = __fdividef(t, 1.f + __expf(-t));
+            rr[j] = t;
+        }
+        *reinterpret_cast<float4*>(o + lo + i) = make_float4(rr[0], rr[1], rr[2], rr[3]);
+    }
+    cl.sync();                       // a peer may still be reading this CTA's `part`
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -276,6 +355,33 @@ cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, i
 cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const float* gamma, const float* beta, int gb_stride, int B,
                              int C, size_t S, int G, int split, float eps, int act, cudaStream_t s) {
     const int cpg = C / G;
+    const size_t n = (size_t)cpg * S;
+    if ((n & 3) == 0 && (S & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
+        // smallest cluster whose slices fit in shared memory, widened until the grid covers the machine
+        const size_t max_slice = 40 * 1024;            // floats per CTA (160 KB)
+        int cs = 1;
+        const size_t want_slice = 8 * 1024;            // 32 KB slices: several CTAs per SM keep enough loads in flight
+        while (cs < 8 && ((n + cs - 1) / cs > want_slice || (size_t)B * G * cs < 2 * 148)) cs *= 2;
+        const size_t slice = (((n + cs - 1) / cs) + 3) & ~(size_t)3;
+        if (slice <= max_slice && slice >= 4) {
+            static bool attr = false;
+            if (!attr) {
+                cudaFuncSetAttribute(gn_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(max_slice * sizeof(float)));
+                attr = true;
+            }
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)((size_t)B * G * cs));
+            cfg.blockDim = dim3(GN_THREADS);
+            cfg.dynamicSmemBytes = slice * sizeof(float);
+            cfg.stream = s;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            return cudaLaunchKernelEx(&cfg, gn_cluster_kernel, x, y, gamma, beta, gb_stride, G, cpg, S, slice, eps, act);
+        }
+    }
     dim3 grid((unsigned)((size_t)B * G), (unsigned)split);
     gn_stats_kernel<<<grid, GN_THREADS, 0, s>>>(x, partial, (size_t)cpg * S, split);
     gn_apply_kernel<<<grid, GN_THREADS, 0, s>>>(x, y, partial, gamma, beta, gb_stride, G, cpg, S, split, eps, act);
