@@ -66,6 +66,15 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def conv_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per conv launch from the committed ncu capture
+    (profiles/capture.sh -> profiles/traffic_from_ncu.py), or None when no capture is committed."""
+    p = os.path.join(ROOT, "profiles", "conv_traffic.json")
+    if not os.path.exists(p):
+        return None
+    return json.load(open(p)).get("traffic_bytes_per_launch")
+
+
 # ------------------------------------------------------------------------------------------------
 # clocks during the timed region
 # ------------------------------------------------------------------------------------------------
@@ -287,7 +296,7 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"kernel": "conv3d 3x3x3 implicit GEMM (all %d launches of one step)" % c3["launches"],
                          "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "traffic": None, "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peaks["source"],
+                         "traffic": conv_traffic(), "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peaks["source"],
                          "share_of_step": c3["ms"] / prof_total if prof_total else None,
                          "how": "CUDA events around every launch on the launching stream, one extra step after the timed region"},
             "end_to_end_tensor_frac": value / world * gflop_patch * 1e9 / (peak * 1e12),

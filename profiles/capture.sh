@@ -13,7 +13,10 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/b
 timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches_$tag.csv \
   python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_bench_$tag.log 2>&1; echo "ncu list exit $?"
 # full capture of the conv kernel on one denoiser evaluation (second evaluation: warm)
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:conv_umma --launch-skip 73 -c 16 \
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:conv_umma --launch-skip 60 -c 14 \
   -o gpurun_out/conv_umma_$tag -f python profiles/_one_eval.py 64 > gpurun_out/ncu_full_$tag.log 2>&1; echo "ncu full exit $?"
+# DRAM traffic of every conv launch of one warm evaluation (the `traffic` of bench.py's roofline object)
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:conv_umma --launch-skip 60 -c 38 --csv \
+  --log-file gpurun_out/conv_traffic_$tag.csv python profiles/_one_eval.py 64 > gpurun_out/ncu_traffic_$tag.log 2>&1; echo "ncu traffic exit $?"
 ncu -i gpurun_out/conv_umma_$tag.ncu-rep --page raw --csv > gpurun_out/conv_umma_${tag}_raw.csv 2>/dev/null
 ls -la gpurun_out

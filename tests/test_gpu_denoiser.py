@@ -228,3 +228,16 @@ def test_sampler_entry_points(model_fp32):
         x_T, steps=6, order=2, skip_type="logSNR", method="multistep") + ms
     assert rel_l2(b, want) < 1e-6
     assert rel_l2(c, want) > 1e-4
+
+
+def test_mixed_sensor_batch(model_fp32):
+    """BASELINE config 3: per-sample prompts inside one band bucket equal the single-prompt runs of each patch."""
+    pan, ms, x_T = [t.cuda() for t in make_inputs(3, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    prompts = ["QB", "GF2", "WV2"]
+    joint = G.sample_by_dpmsolver({"PAN": pan, "MS": ms, "Res": x_T}, prompts, steps=6, x_T=x_T)
+    for i, p in enumerate(prompts):
+        one = G.sample_by_dpmsolver({"PAN": pan[i:i + 1], "MS": ms[i:i + 1], "Res": x_T[i:i + 1]}, p, steps=6, x_T=x_T[i:i + 1])
+        assert rel_l2(joint[i:i + 1], one) < 1e-6, p
+    same = G.sample_by_dpmsolver({"PAN": pan, "MS": ms, "Res": x_T}, "QB", steps=6, x_T=x_T)
+    assert rel_l2(joint[1:2], same[1:2]) > 1e-4          # the text modulation really differs between sensors

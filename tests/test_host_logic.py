@@ -196,3 +196,23 @@ def test_two_rank_gather_gloo(n_total):
     for p in procs:
         p.join(60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_bucket_by_bands_and_sample_mixed_order():
+    g = torch.Generator().manual_seed(0)
+    patches = []
+    for i, (n, s) in enumerate([(8, "WV3"), (4, "QB"), (4, "GF2"), (8, "WV3"), (4, "QB")]):
+        patches.append((torch.rand(1, 8, 8, generator=g), torch.rand(n, 8, 8, generator=g), s))
+    b = parallel.bucket_by_bands(patches)
+    assert sorted(b) == [4, 8] and b[4][0] == [1, 2, 4] and b[8][0] == [0, 3] and b[4][3] == ["QB", "GF2", "QB"]
+    assert b[8][2].shape == (2, 8, 8, 8) and b[4][1].shape == (3, 1, 8, 8)
+
+    class Fake:
+        def sample_by_dpmsolver(self, x_in, prompt, steps=20, x_T=None):
+            assert len(prompt) == x_in["MS"].shape[0]
+            return x_in["MS"] + x_in["PAN"] + x_T
+
+    noise = [torch.randn(p[1].shape, generator=g) for p in patches]
+    out = parallel.sample_mixed(Fake(), patches, steps=3, x_T=noise)
+    for o, (pan, ms, _), z in zip(out, patches, noise):
+        assert torch.equal(o, ms + pan + z)

@@ -58,6 +58,7 @@ struct UmmaParams {
     uint32_t row_bytes, layout_type, sbo16;
     uint32_t tmem_cols, idesc;
     int a_planes, a_ysplit;     // REUSE: the haloed box is fetched as a_planes x a_ysplit TMA instructions (more requests in flight)
+    int pl_off;                 // REUSE: 1 when a tile spans the whole band axis (both halo planes are padding and get no slot in the stage)
     uint32_t a_piece_bytes;
     long long* trace;           // diagnostics (TMD_UMMA_TRACE=1): per-role cycle counters of CTA 0
     int dbg;                    // diagnostics (TMD_UMMA_DEBUG): 1 no MMA, 2 no activation loads, 4 no weight loads, 8 no epilogue stores
@@ -456,9 +457,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                             uint32_t dst = a_base + s * P.a_stage_stride;
                             if (MODE) {
 #pragma unroll
-                                for (int pl = 0; pl < NACC + 2; ++pl, dst += P.a_piece_bytes)
+                                for (int pl = 0; pl < NACC + 2; ++pl)
                                     if ((unsigned)(cn + pl) < (unsigned)P.N)
-                                        tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn + pl, tc.b0);
+                                        tma_load_5d(dst + (uint32_t)(pl - P.pl_off) * P.a_piece_bytes, &P.tmA, a_full(s), kc * KC, cx, cy, cn + pl, tc.b0);
                             } else {
                                 tma_load_5d(dst, &P.tmA, a_full(s), kc * KC, cx, cy, cn, tc.b0);
                             }
@@ -544,6 +545,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const uint32_t a_stride16 = P.a_stage_stride >> 4, b_stride16 = P.b_tile_stride >> 4;
         const uint32_t plane16 = ((uint32_t)(P.TH + 2) * P.TW * P.row_bytes) >> 4;   // one haloed band plane
         const uint32_t line16 = ((uint32_t)P.TW * P.row_bytes) >> 4;                  // one line of 8 voxels = one swizzle atom
+        const int pl_off = P.pl_off;
         const uint32_t idesc = P.idesc;
         const uint32_t idesc_base = P.idesc & ~(0x3Fu << 17);
         const uint32_t Co = P.Co;
@@ -602,7 +604,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         const int nblk = dz_hi - dz_lo + 1;
                                         const int p_top = q + 1 - dz_lo;
                                         const uint32_t id = idesc_base | ((uint32_t)((nblk * Co) >> 3) << 17);
-                                        const uint32_t a_view = a_lo + (uint32_t)(q + 1) * plane16 + (uint32_t)t * line16;
+                                        const uint32_t a_view = a_lo + (uint32_t)(q + 1 - pl_off) * plane16 + (uint32_t)t * line16;
                                         const uint32_t b_view = b_lo + (uint32_t)dz_lo * co16;
                                         const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
 #pragma unroll
@@ -618,7 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         for (int pp = 0; pp < NACC; ++pp) {
                                             if ((unsigned)(n0 + pp + dz - 1) >= NB) continue;
                                             const int dz_first = (n0 + pp == 0) ? 1 : 0;
-                                            const uint32_t a_view = a_lo + (uint32_t)(pp + dz) * plane16 + (uint32_t)t * line16;
+                                            const uint32_t a_view = a_lo + (uint32_t)(pp + dz - pl_off) * plane16 + (uint32_t)t * line16;
                                             const uint32_t b_view = b_lo + (uint32_t)dz * co16;
                                             const uint32_t d = d0 + (uint32_t)(NACC - 1 - pp) * Co;
 #pragma unroll
@@ -855,7 +857,8 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.NACC = 1;
         for (int c = 2; c <= cap; c *= 2)
             if (op.N % c == 0) P.NACC = c;
-        P.a_planes = P.NACC + 2;
+        P.pl_off = (P.NACC == op.N) ? 1 : 0;
+        P.a_planes = P.NACC + 2 - 2 * P.pl_off;
         P.a_ysplit = 1;
         boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH + 2; boxA[3] = 1; boxA[4] = 1;   // one TMA instruction per haloed plane
         P.tiles_n = (op.N + P.NACC - 1) / P.NACC;
@@ -895,11 +898,13 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
 
     // ring depths from the shared-memory budget
     const size_t budget = 220 * 1024;
-    P.SA = P.mode ? 2 : 4;
+    // activation stages first (their TMA round trip is the long one), at least four weight stages behind them
+    const int want_sb = P.mode ? 6 : 4;
+    P.SA = P.mode ? env_int("TMD_UMMA_SA", 2) : 4;
+    while (P.SA > 2 && (size_t)P.SA * P.a_stage_stride + 4 * (size_t)P.b_tile_stride > budget) --P.SA;
     while (P.SA > 1 && (size_t)P.SA * P.a_stage_stride + 2 * (size_t)P.b_tile_stride > budget) --P.SA;
     size_t left = budget - (size_t)P.SA * P.a_stage_stride;
     P.SB = (int)(left / P.b_tile_stride);
-    const int want_sb = P.mode ? 6 : P.SA;
     if (P.SB > want_sb) P.SB = want_sb;
     if (P.SB > kMaxSB) P.SB = kMaxSB;
     if (P.SB < 2 || P.SA < 1) { delete plan; return nullptr; }

@@ -25,3 +25,40 @@ def gather_tiles(local, n_total, group=None):
     out = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(out, pad, group=group)
     return torch.cat([o[: e - s] for o, (s, e) in zip(out, sizes)], dim=0)
+
+
+def bucket_by_bands(patches):
+    """Mixed-sensor batches (BASELINE config 3): stacked tensors need equal band counts, and zero-padding 4 -> 8 bands
+    is not equivalent (biases and pad-1 convolutions leak into padded bands), so a joint batch is split
+    into one bucket per band count.  `patches`: sequence of (PAN [1,H,W], MS [N,H,W], prompt).  Returns
+    {N: (indices, PAN [b,1,H,W], MS [b,N,H,W], prompts)}; per-sample prompts inside a bucket are free (the text
+    modulation is a per-sample scale table)."""
+    buckets = {}
+    for i, (pan, ms, prompt) in enumerate(patches):
+        buckets.setdefault(int(ms.shape[0]), []).append(i)
+    out = {}
+    for n, idx in sorted(buckets.items()):
+        out[n] = (idx, torch.stack([patches[i][0] for i in idx]), torch.stack([patches[i][1] for i in idx]),
+                  [patches[i][2] for i in idx])
+    return out
+
+
+@torch.no_grad()
+def sample_mixed(diffusion, patches, steps=20, x_T=None, group=None):
+    """Sample a joint WV3/QB/GF2 batch: bucket by band count, shard every bucket contiguously over the ranks (equal
+    FLOPs per rank: an 8-band patch costs twice a 4-band one), one all-gather per bucket.  Returns the fused images
+    in input order (list of [N_i, H, W])."""
+    on = dist.is_available() and dist.is_initialized()
+    rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
+    result = [None] * len(patches)
+    for n, (idx, pan, ms, prompts) in bucket_by_bands(patches).items():
+        lo, hi = shard_range(len(idx), rank, world)
+        if hi > lo:
+            noise = torch.randn_like(ms[lo:hi]) if x_T is None else torch.stack([x_T[i] for i in idx[lo:hi]]).to(ms.device)
+            local = diffusion.sample_by_dpmsolver({"PAN": pan[lo:hi], "MS": ms[lo:hi], "Res": noise}, prompts[lo:hi], steps=steps, x_T=noise)
+        else:
+            local = ms.new_zeros((0,) + tuple(ms.shape[1:]))
+        full = gather_tiles(local, len(idx), group) if world > 1 else local
+        for j, i in enumerate(idx):
+            result[i] = full[j]
+    return result
