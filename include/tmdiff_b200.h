@@ -41,7 +41,7 @@ typedef struct {
     int32_t dtype;         /* TMD_F32: fp32 SIMT convs (parity mode); TMD_BF16: tcgen05 convs  */
 } tmd_config;
 
-/* One network evaluation of the sampler = DPM_Solver.model_fn(x, t) for model_type "x_start",
+/* One network evaluation of the sampler = DPM_Solver.model_fn(x, t) (model_type and guidance from the plan),
  * algorithm "dpmsolver++", dynamic thresholding (core/dpm_solver_pytorch.py:296-306, 430-465).
  * The scalars are the fp32 values the reference computes on the host side of each call. */
 typedef struct {
@@ -164,6 +164,12 @@ int tmd_attention(const float* q, const float* k, const float* v, float* out, in
 int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2, float* y,
                        int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K,
                        int32_t hidden, float temperature, int32_t dtype, void* stream);
+
+/* Full-reference quality of fused images, one fused reduction per image (no host gather): out[b] = {SAM in degrees
+ * (SAM_numpy, core/metrics.py:88-111), ERGAS (ERGAS_numpy, :221-241, ratio = 0.25), mean per-band universal quality
+ * index (UIQC_numpy / QIndex_numpy, :244-284)} of img[b] against ref[b]; ref/img device fp32 [B, C, H, W], C <= 8. */
+int tmd_quality_metrics(const float* ref, const float* img, float* out, int32_t B, int32_t C, int32_t H, int32_t W, float ratio,
+                        void* stream);
 
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);

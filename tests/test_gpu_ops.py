@@ -126,3 +126,26 @@ def test_dynamic_threshold_boundary_counts(ops):
         want = dpm_ref.dynamic_threshold(x)
         got = ops.dynamic_thresholding(x.cuda()).cpu()
         assert torch.allclose(got, want, rtol=0, atol=1e-6), k
+
+
+@pytest.mark.gpu
+def test_quality_metrics_match_reference(ops):
+    """On-device SAM / ERGAS / Q against the reference's numpy functions (committed vectors) and the oracle restatement."""
+    import numpy as np
+    import os
+    from oracle import metrics_ref
+    vec = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scene_vectors.npz"))
+    a, b = vec["metric_a"], vec["metric_b"]                       # [H, W, C]
+    to_nchw = lambda t: torch.from_numpy(t).permute(2, 0, 1)[None].float().cuda()
+    got = ops.quality_metrics(to_nchw(a), to_nchw(b)).cpu().double().numpy()[0]
+    assert np.allclose(got, vec["metric_values"], rtol=2e-5)
+    g = torch.Generator().manual_seed(4)
+    x = torch.rand(5, 8, 64, 64, generator=g) * 0.9 + 0.05
+    y = (x + 0.03 * torch.randn(x.shape, generator=g)).clamp(0.01, 1)
+    got = ops.quality_metrics(x.cuda(), y.cuda()).cpu().double().numpy()
+    for i in range(5):
+        hwc = lambda t: t[i].permute(1, 2, 0).double().numpy()
+        want = [metrics_ref.sam(hwc(x), hwc(y)), metrics_ref.ergas(hwc(x), hwc(y)), metrics_ref.uiqc(hwc(x), hwc(y))]
+        assert np.allclose(got[i], want, rtol=2e-5), i
+    with pytest.raises(RuntimeError):
+        ops.quality_metrics(torch.rand(1, 9, 8, 8).cuda(), torch.rand(1, 9, 8, 8).cuda())

@@ -1239,3 +1239,12 @@ extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const flo
     for (void* p : {(void*)pooled, (void*)hid, (void*)alpha, (void*)aw, (void*)ab, (void*)pf, (void*)pb, xin, yout}) cudaFreeAsync(p, s);
     return rc;
 }
+
+extern "C" int tmd_quality_metrics(const float* ref, const float* img, float* out, int32_t B, int32_t C, int32_t H, int32_t W, float ratio,
+                                   void* stream) {
+    if (!ref || !img || !out) return fail("tmd_quality_metrics: null argument");
+    if (B <= 0 || C <= 0 || C > 8 || H <= 0 || W <= 0) return fail("tmd_quality_metrics: need 1..8 bands and a non-empty image");
+    const cudaError_t err = quality_metrics(ref, img, out, B, C, H * W, ratio, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_quality_metrics: %s", cudaGetErrorString(err));
+    return 0;
+}

@@ -73,6 +73,8 @@ cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const flo
 cudaError_t attention_f32(const float* q, const float* k, const float* v, float* out, int BH, int Lq, int Lk, int D, float scale,
                           cudaStream_t s);
 
+// out[b] = {SAM (degrees), ERGAS, mean per-band Q index} of img[b] against ref[b]; [B, C, HW] fp32, C <= 8
+cudaError_t quality_metrics(const float* ref, const float* img, float* out, int B, int C, int HW, float ratio, cudaStream_t s);
 // Dynamic_conv3d pieces (core/dynamic_conv.py:194-268): channel means, expert softmax, per-sample expert mix
 cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s);                       // out[r] = mean(x[r, :])
 cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cudaStream_t s);                      // in place over K

@@ -338,6 +338,73 @@ __global__ void mix_experts_kernel(const float* __restrict__ alpha, const float*
 }
 }  // namespace
 
+// ------------------------------------------------------------------------------------------------
+// full-reference quality metrics as one fused reduction per image:
+// SAM_numpy (core/metrics.py:88-111), ERGAS_numpy (:221-241), UIQC_numpy / QIndex_numpy (:244-284)
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr int QM_MAXC = 8, QM_THREADS = 256;
+__global__ void __launch_bounds__(QM_THREADS) quality_metrics_kernel(const float* __restrict__ ref, const float* __restrict__ img,
+                                                                     float* __restrict__ out, int C, int HW, float ratio) {
+    __shared__ double acc[QM_MAXC][5];     // per band: sum a, sum b, sum a^2, sum b^2, sum ab   (a = ref, b = img)
+    __shared__ double sam_acc;
+    const int b = blockIdx.x;
+    const float* A = ref + (size_t)b * C * HW;
+    const float* Bm = img + (size_t)b * C * HW;
+    for (int i = threadIdx.x; i < QM_MAXC * 5; i += QM_THREADS) (&acc[0][0])[i] = 0.0;
+    if (threadIdx.x == 0) sam_acc = 0.0;
+    __syncthreads();
+    double loc[QM_MAXC][5];
+#pragma unroll
+    for (int c = 0; c < QM_MAXC; ++c)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) loc[c][k] = 0.0;
+    double sam = 0.0;
+    for (int p = threadIdx.x; p < HW; p += QM_THREADS) {
+        float dot = 0.f, na = 0.f, nb = 0.f;
+#pragma unroll
+        for (int c = 0; c < QM_MAXC; ++c) {
+            if (c >= C) break;
+            const float a = A[(size_t)c * HW + p], v = Bm[(size_t)c * HW + p];
+            dot = fmaf(a, v, dot); na = fmaf(a, a, na); nb = fmaf(v, v, nb);
+            loc[c][0] += a; loc[c][1] += v; loc[c][2] += (double)a * a; loc[c][3] += (double)v * v; loc[c][4] += (double)a * v;
+        }
+        const float cs = dot / sqrtf(nb) / sqrtf(na);
+        const float ang = acosf(cs);                       // |cs| > 1 or 0/0 -> NaN, counted as 0 like the reference
+        if (ang == ang) sam += ang;
+    }
+#pragma unroll
+    for (int c = 0; c < QM_MAXC; ++c) {
+        if (c >= C) break;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) atomicAdd(&acc[c][k], loc[c][k]);
+    }
+    atomicAdd(&sam_acc, sam);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double n = (double)HW;
+        double erg = 0.0, q = 0.0;
+        for (int c = 0; c < C; ++c) {
+            const double sa = acc[c][0], sb = acc[c][1], saa = acc[c][2], sbb = acc[c][3], sab = acc[c][4];
+            const double mse = (saa - 2.0 * sab + sbb) / n;                 // RMSE_numpy^2 of the band
+            const double m1 = sa / n, m2 = sb / n;
+            erg += mse / (m2 * m2);                                         // / mean(ps_band)^2, ps = the second argument
+            const double d1 = (saa - n * m1 * m1) / (n - 1.0), d2 = (sbb - n * m2 * m2) / (n - 1.0), cov = (sab - n * m1 * m2) / (n - 1.0);
+            q += 4.0 * cov * m1 * m2 / (d1 + d2) / (m1 * m1 + m2 * m2);
+        }
+        out[b * 3 + 0] = (float)(sam_acc / n * 180.0 / 3.14159265358979323846);
+        out[b * 3 + 1] = (float)(100.0 * ratio * sqrt(erg / C));
+        out[b * 3 + 2] = (float)(q / C);
+    }
+}
+}  // namespace
+
+cudaError_t quality_metrics(const float* ref, const float* img, float* out, int B, int C, int HW, float ratio, cudaStream_t s) {
+    if (C > QM_MAXC) return cudaErrorInvalidValue;
+    quality_metrics_kernel<<<B, QM_THREADS, 0, s>>>(ref, img, out, C, HW, ratio);
+    return cudaGetLastError();
+}
+
 cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s) {
     spatial_mean_kernel<<<(unsigned)rows, 256, 0, s>>>(x, out, S);
     return cudaGetLastError();

@@ -94,3 +94,16 @@ def quantile_position(n, q):
     rank = torch.tensor(q, dtype=torch.float32) * (n - 1)
     lo = torch.floor(rank)
     return int(lo.item()), float((rank - lo).item())
+
+
+def quality_metrics(ref, img, ratio=0.25):
+    """Per-image [SAM (degrees), ERGAS, Q] of img against ref ([B, C, H, W], C <= 8) as one fused device reduction
+    (core/metrics.py SAM_numpy / ERGAS_numpy / UIQC_numpy semantics); returns a [B, 3] CUDA tensor."""
+    a, b = _cuda_f32(ref, "ref"), _cuda_f32(img, "img")
+    if a.shape != b.shape or a.dim() != 4:
+        raise ValueError("ref and img must both be [B, C, H, W]")
+    B, Cc, H, W = a.shape
+    out = torch.empty(B, 3, device=a.device)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.load().tmd_quality_metrics(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), B, Cc, H, W, float(ratio), _lib.stream_ptr()))
+    return out
