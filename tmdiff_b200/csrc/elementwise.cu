@@ -33,9 +33,106 @@ __global__ void stem_expand_kernel(const float* __restrict__ x, const float* __r
     store4<T>(out + vox * C + c, o);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// bf16 fast paths of the three per-evaluation glue kernels: 8 channels (16 bytes) per thread, 32-bit index
+// arithmetic, Swish through tanh.approx (as in the conv epilogue).  HBM-bound.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float swish_tanh_f(float x) {
+    const float h = 0.5f * x;
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
+}
+__device__ __forceinline__ uint4 pack8_bf16(const float v[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ void unpack8_bf16f(const uint4& t, float v[8]) {
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
+        v[2 * i] = __low2float(h);
+        v[2 * i + 1] = __high2float(h);
+    }
+}
+__device__ __forceinline__ void ldg8(const float* p, float v[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
+__global__ void __launch_bounds__(256) stem_expand_bf16_kernel(const float* __restrict__ x, const float* __restrict__ pan,
+                                                               const float* __restrict__ w, const float* __restrict__ bias,
+                                                               const float* __restrict__ sc, int ld_sc, __nv_bfloat16* __restrict__ out,
+                                                               int C, unsigned NHW, unsigned HW, unsigned total8) {
+    const unsigned i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= total8) return;
+    const unsigned c8 = (unsigned)C >> 3;
+    const unsigned vox = i / c8, c = (i % c8) * 8u;
+    const unsigned b = vox / NHW;
+    float v = x[vox];
+    if (pan) v = pan[b * HW + vox % HW] - v;
+    float ww[8], bb[8], ss[8], o[8];
+    ldg8(w + c, ww); ldg8(bias + c, bb); ldg8(sc + (size_t)b * ld_sc + c, ss);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = swish_tanh_f(fmaf(ww[k], v, bb[k])) * ss[k];
+    *reinterpret_cast<uint4*>(out + (size_t)vox * C + c) = pack8_bf16(o);
+}
+
+__global__ void __launch_bounds__(256) slice_activate_bf16_kernel(const __nv_bfloat16* __restrict__ src, int ld_src,
+                                                                  __nv_bfloat16* __restrict__ dst, int ld_dst, const float* __restrict__ tb,
+                                                                  int ld_tb, int C, unsigned vps, unsigned total8) {
+    const unsigned i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= total8) return;
+    const unsigned c8 = (unsigned)C >> 3;
+    const unsigned vox = i / c8, c = (i % c8) * 8u;
+    const unsigned b = vox / vps;
+    float v[8], t[8];
+    unpack8_bf16f(*reinterpret_cast<const uint4*>(src + (size_t)vox * ld_src + c), v);
+    if (tb) {
+        ldg8(tb + (size_t)b * ld_tb + c, t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] += t[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = swish_tanh_f(v[k]);
+    *reinterpret_cast<uint4*>(dst + (size_t)vox * ld_dst + c) = pack8_bf16(v);
+}
+
+// C <= 64: (C/8) lanes per voxel, one 16-byte load each, shuffle reduce
+__global__ void __launch_bounds__(256) project_to_band_bf16_kernel(const __nv_bfloat16* __restrict__ a, int ld, const float* __restrict__ w,
+                                                                   float* __restrict__ out, int C, unsigned nvox) {
+    const unsigned c8 = (unsigned)C >> 3;                     // 1, 2, 4 or 8 lanes per voxel
+    const unsigned g = blockIdx.x * 256u + threadIdx.x;
+    const unsigned vox = g / c8, l = g % c8;
+    float acc = 0.f;
+    if (vox < nvox) {
+        float v[8], ww[8];
+        unpack8_bf16f(*reinterpret_cast<const uint4*>(a + (size_t)vox * ld + l * 8u), v);
+        ldg8(w + l * 8u, ww);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc = fmaf(v[k], ww[k], acc);
+    }
+    for (unsigned o = 1; o < c8; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (vox < nvox && l == 0) out[vox] = acc;
+}
+
 cudaError_t stem_expand(int dtype, const float* x, const float* pan, const float* w, const float* bias, const float* sc,
                         int ld_sc, void* out, int C, int B, int N, int HW, cudaStream_t s) {
     const size_t total4 = (size_t)B * N * HW * (C / 4);
+    if (dtype != 0 && C % 8 == 0 && ld_sc % 4 == 0 && total4 / 2 < 0xffffffffull &&
+        ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(sc) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0) {
+        const unsigned total8 = (unsigned)(total4 / 2);
+        stem_expand_bf16_kernel<<<cdiv(total8, 256), 256, 0, s>>>(x, pan, w, bias, sc, ld_sc, (__nv_bfloat16*)out, C, (unsigned)(N * HW),
+                                                                  (unsigned)HW, total8);
+        return cudaGetLastError();
+    }
     if (dtype == 0)
         stem_expand_kernel<float><<<cdiv(total4, 256), 256, 0, s>>>(x, pan, w, bias, sc, ld_sc, (float*)out, C, N, HW, total4);
     else
@@ -66,6 +163,13 @@ __global__ void slice_activate_kernel(const T* __restrict__ src, int ld_src, T* 
 cudaError_t slice_activate(int dtype, const void* src, int ld_src, void* dst, int ld_dst, const float* tb, int ld_tb, int C,
                            int B, size_t vps, cudaStream_t s) {
     const size_t total4 = (size_t)B * vps * (C / 4);
+    if (dtype != 0 && C % 8 == 0 && ld_src % 8 == 0 && ld_dst % 8 == 0 && ld_tb % 4 == 0 && total4 / 2 < 0xffffffffull &&
+        ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(tb)) & 15) == 0) {
+        const unsigned total8 = (unsigned)(total4 / 2);
+        slice_activate_bf16_kernel<<<cdiv(total8, 256), 256, 0, s>>>((const __nv_bfloat16*)src, ld_src, (__nv_bfloat16*)dst, ld_dst, tb, ld_tb,
+                                                                     C, (unsigned)vps, total8);
+        return cudaGetLastError();
+    }
     if (dtype == 0)
         slice_activate_kernel<float, false><<<cdiv(total4, 256), 256, 0, s>>>((const float*)src, ld_src, (float*)dst, ld_dst, tb, ld_tb, C, vps, total4);
     else
@@ -100,6 +204,11 @@ __global__ void project_to_band_kernel(const T* __restrict__ a, int ld, const fl
 
 cudaError_t project_to_band(int dtype, const void* a, int ld, const float* w, float* out, int C, size_t nvox, cudaStream_t s) {
     const size_t threads = nvox * 8;
+    if (dtype != 0 && (C == 8 || C == 16 || C == 32 || C == 64) && ld % 8 == 0 && nvox * (C / 8) < 0xffffffffull &&
+        (reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0) {
+        project_to_band_bf16_kernel<<<cdiv(nvox * (C / 8), 256), 256, 0, s>>>((const __nv_bfloat16*)a, ld, w, out, C, (unsigned)nvox);
+        return cudaGetLastError();
+    }
     if (dtype == 0)
         project_to_band_kernel<float><<<cdiv(threads, 256), 256, 0, s>>>((const float*)a, ld, w, out, C, nvox);
     else
