@@ -426,8 +426,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     const uint32_t tmem_base = tmem_base_slot;
 
     constexpr int KC = KMMA * 16;
-    const int ngroups = MODE ? 3 : P.taps;              // tap groups that need their own activation box
-    constexpr int b_stages_per_a = MODE ? 3 : 1;        // weight stages consumed per activation stage
+    const int ngroups = MODE ? 1 : P.taps;              // activation boxes per K chunk (REUSE: ONE haloed box serves all 27 taps)
+    constexpr int b_stages_per_a = MODE ? 9 : 1;        // weight stages consumed per activation stage (REUSE: the 9 (dy,dx) taps)
     const int nkc = P.nkc;
 
     if (warp == 0) {
@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             }
             for (int g = 0; g < ngroups; ++g) {
                 int cx = tc.x0, cy = tc.y0, cn = tc.n0;
-                if (MODE) { cx += g - 1; cy -= 1; cn -= 1; }
+                if (MODE) { cx -= 1; cy -= 1; cn -= 1; }
                 else if (P.taps == 27) {
                     cx += g % 3 - 1; cy += (g / 3) % 3 - 1; cn += g / 9 - 1;
                     if (cn + P.TN <= 0 || cn >= P.N) continue;            // the whole box is padding
@@ -513,8 +513,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                 if (MODE) {
                                     mbar_expect_tx(b_full(s), 3 * P.b_tile_bytes);
 #pragma unroll
-                                    for (int dz = 0; dz < 3; ++dz)       // tap = (dz*3+dy)*3+dx; rows [dz*Co, (dz+1)*Co) of the stage
-                                        tma_load_2d(dst + dz * P.b_tile_bytes, &P.tmB, b_full(s), ((dz * 3 + t) * 3 + g) * P.Ci + kc * KC, 0);
+                                    for (int dz = 0; dz < 3; ++dz)       // tap = (dz*3+dy)*3+dx, t = dy*3+dx; rows [dz*Co, (dz+1)*Co) of the stage
+                                        tma_load_2d(dst + dz * P.b_tile_bytes, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, 0);
                                 } else {
                                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
                                     tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, 0);
@@ -539,12 +539,18 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         // ================= MMA issue =================
         // Descriptors differ only in their 14-bit start-address field, so the loops below just add
         // 16-byte-unit offsets to the low word.
-        const uint32_t desc_hi = P.sbo16 | (1u << 14) | (P.layout_type << 29);
+        const uint32_t desc_hi = P.sbo16 | (1u << 14) | (P.layout_type << 29);                  // weights, SIMPLE boxes, second source
+        // REUSE: the haloed box is [planes][TH+2 lines][TW+2 voxels]; an 8-voxel line segment is one 8-row group, the
+        // groups of a view are one line pitch apart (SBO), and a tap is a start-address offset of dy lines + dx voxels.
+        // The swizzle is a function of the absolute shared-memory address for TMA and UMMA alike, so views that start
+        // inside a swizzle atom read back exactly what TMA wrote (profiles/micro/shifted_view.cu).
+        const uint32_t line16 = ((uint32_t)(P.TW + 2) * P.row_bytes) >> 4;
+        const uint32_t desc_hi_a = MODE ? (line16 | (1u << 14) | (P.layout_type << 29)) : desc_hi;
         const uint32_t a_lo0 = ((a_base & 0x3FFFFu) >> 4) | (1u << 16);
         const uint32_t b_lo0 = ((b_base & 0x3FFFFu) >> 4) | (1u << 16);
         const uint32_t a_stride16 = P.a_stage_stride >> 4, b_stride16 = P.b_tile_stride >> 4;
-        const uint32_t plane16 = ((uint32_t)(P.TH + 2) * P.TW * P.row_bytes) >> 4;   // one haloed band plane
-        const uint32_t line16 = ((uint32_t)P.TW * P.row_bytes) >> 4;                  // one line of 8 voxels = one swizzle atom
+        const uint32_t plane16 = (uint32_t)(P.TH + 2) * line16;                      // one haloed band plane
+        const uint32_t vox16 = P.row_bytes >> 4;                                     // one voxel
         const int pl_off = P.pl_off;
         const uint32_t idesc = P.idesc;
         const uint32_t idesc_base = P.idesc & ~(0x3Fu << 17);
@@ -583,11 +589,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                         tc_fence_after();
                         if (elect_one()) {
                             const uint32_t b_lo = b_lo0 + sb * b_stride16;
+                            const uint32_t tap16 = (uint32_t)(t / 3) * line16 + (uint32_t)(t % 3) * vox16;   // REUSE: t = dy*3 + dx
                             if (do_mma) {
                                 if (!MODE) {
 #pragma unroll
                                     for (int k = 0; k < KMMA; ++k)
-                                        tc_mma_bf16(d0, ((uint64_t)desc_hi << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
+                                        tc_mma_bf16(d0, ((uint64_t)desc_hi_a << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
                                                     k == 0 ? fresh : 1u);
                                 } else if (MERGE && fresh) {
                                     // One MMA per input plane q (box plane q+1) and K=16 slice: its A view feeds the output planes
@@ -604,12 +611,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         const int nblk = dz_hi - dz_lo + 1;
                                         const int p_top = q + 1 - dz_lo;
                                         const uint32_t id = idesc_base | ((uint32_t)((nblk * Co) >> 3) << 17);
-                                        const uint32_t a_view = a_lo + (uint32_t)(q + 1 - pl_off) * plane16 + (uint32_t)t * line16;
+                                        const uint32_t a_view = a_lo + (uint32_t)(q + 1 - pl_off) * plane16 + tap16;
                                         const uint32_t b_view = b_lo + (uint32_t)dz_lo * co16;
                                         const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
 #pragma unroll
                                         for (int k = 0; k < KMMA; ++k)
-                                            tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id, 1u);
+                                            tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id, 1u);
                                     }
                                 } else {
                                     // one MMA per (output plane pp, dz).  Also the first stage of a tile in the merged kernels:
@@ -620,12 +627,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         for (int pp = 0; pp < NACC; ++pp) {
                                             if ((unsigned)(n0 + pp + dz - 1) >= NB) continue;
                                             const int dz_first = (n0 + pp == 0) ? 1 : 0;
-                                            const uint32_t a_view = a_lo + (uint32_t)(pp + dz - pl_off) * plane16 + (uint32_t)t * line16;
+                                            const uint32_t a_view = a_lo + (uint32_t)(pp + dz - pl_off) * plane16 + tap16;
                                             const uint32_t b_view = b_lo + (uint32_t)dz * co16;
                                             const uint32_t d = d0 + (uint32_t)(NACC - 1 - pp) * Co;
 #pragma unroll
                                             for (int k = 0; k < KMMA; ++k)
-                                                tc_mma_bf16(d, ((uint64_t)desc_hi << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
+                                                tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
                                                             (k == 0 && dz == dz_first) ? fresh : 1u);
                                         }
                                 }
@@ -860,7 +867,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.pl_off = (P.NACC == op.N) ? 1 : 0;
         P.a_planes = P.NACC + 2 - 2 * P.pl_off;
         P.a_ysplit = 1;
-        boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH + 2; boxA[3] = 1; boxA[4] = 1;   // one TMA instruction per haloed plane
+        boxA[0] = P.KC; boxA[1] = P.TW + 2; boxA[2] = P.TH + 2; boxA[3] = 1; boxA[4] = 1;   // one TMA instruction per haloed plane
         P.tiles_n = (op.N + P.NACC - 1) / P.NACC;
     } else {
         P.KC = (op.Ci % 64 == 0) ? 64 : 32;
@@ -936,7 +943,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     if (op.src2) {
         P.nkc2 = op.Ci2 / P.KC;
         cuuint32_t box2[5] = {boxA[0], boxA[1], boxA[2], boxA[3], boxA[4]};
-        if (P.mode) box2[2] = P.TH;                      // no halo: the 1x1x1 conv only reads the tile's own voxels
+        if (P.mode) { box2[1] = P.TW; box2[2] = P.TH; }   // no halo: the 1x1x1 conv only reads the tile's own voxels
         P.a2_piece_bytes = box2[1] * box2[2] * box2[3] * box2[4] * P.row_bytes;
         cuuint64_t dims[5] = {(cuuint64_t)op.Ci2, (cuuint64_t)op.W, (cuuint64_t)op.H, (cuuint64_t)op.N, (cuuint64_t)op.B};
         const cuuint64_t e = 2ull * op.ld_in2;
