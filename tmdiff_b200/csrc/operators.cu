@@ -14,6 +14,7 @@
 //     row maximum / sum (no [Lq, Lk] matrix in HBM), any head width up to 2048.
 #include <cooperative_groups.h>
 #include <float.h>
+#include <stdlib.h>
 
 #include "kernels.h"
 
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(GN_THREADS) gn_cluster_kernel(const float* __r
                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                 int gb_stride, int G, int cpg, size_t S, size_t slice, float eps, int act) {
     extern __shared__ __align__(16) float buf[];
-    __shared__ float part[3];
+    __shared__ float part_all[8][4];      // every rank's (count, mean, M2), pushed here by the owners
     __shared__ float red[2][GN_THREADS / 32];
     __shared__ float stat[2];
     cg::cluster_group cl = cg::this_cluster();
@@ -139,35 +140,53 @@ __global__ void __launch_bounds__(GN_THREADS) gn_cluster_kernel(const float* __r
     const float* p = x + bg * n;
     float a = 0.f, q = 0.f;
     const float shift = lo < hi ? p[lo] : 0.f;
-    for (size_t i = lo + 4 * threadIdx.x; i < hi; i += 4 * GN_THREADS) {
-        const float4 v = *reinterpret_cast<const float4*>(p + i);
-        *reinterpret_cast<float4*>(buf + (i - lo)) = v;
-        const float d0 = v.x - shift, d1 = v.y - shift, d2 = v.z - shift, d3 = v.w - shift;
-        a += (d0 + d1) + (d2 + d3);
-        q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+    {
+        // four 16-byte loads in flight per thread before the first use
+        const unsigned cnt = lo < hi ? (unsigned)(hi - lo) : 0u;
+        const float* ps = p + lo;
+        unsigned i = 4 * threadIdx.x;
+        for (; i + 12 * GN_THREADS < cnt; i += 16 * GN_THREADS) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = __ldcs(reinterpret_cast<const float4*>(ps + i + u * 4 * GN_THREADS));
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                *reinterpret_cast<float4*>(buf + i + u * 4 * GN_THREADS) = v[u];
+                const float d0 = v[u].x - shift, d1 = v[u].y - shift, d2 = v[u].z - shift, d3 = v[u].w - shift;
+                a += (d0 + d1) + (d2 + d3);
+                q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+            }
+        }
+        for (; i < cnt; i += 4 * GN_THREADS) {
+            const float4 v = __ldcs(reinterpret_cast<const float4*>(ps + i));
+            *reinterpret_cast<float4*>(buf + i) = v;
+            const float d0 = v.x - shift, d1 = v.y - shift, d2 = v.z - shift, d3 = v.w - shift;
+            a += (d0 + d1) + (d2 + d3);
+            q += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+        }
     }
     a = warp_sum_f(a);
     q = warp_sum_f(q);
     if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = q; }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < CS) {               // thread t pushes this CTA's partial into rank t's shared memory (DSMEM store)
         float A = 0.f, Q = 0.f;
         for (int w = 0; w < GN_THREADS / 32; ++w) { A += red[0][w]; Q += red[1][w]; }
         const float cnt = lo < hi ? (float)(hi - lo) : 0.f;
-        part[0] = cnt;
-        part[1] = cnt > 0.f ? shift + A / cnt : 0.f;
-        part[2] = cnt > 0.f ? fmaxf(Q - A * A / cnt, 0.f) : 0.f;
+        float* dst = cl.map_shared_rank(&part_all[r][0], threadIdx.x);
+        dst[0] = cnt;
+        dst[1] = cnt > 0.f ? shift + A / cnt : 0.f;
+        dst[2] = cnt > 0.f ? fmaxf(Q - A * A / cnt, 0.f) : 0.f;
     }
-    cl.sync();
-    if (threadIdx.x == 0) {          // every CTA merges the same partials in the same order: identical statistics
+    cl.sync();                            // release/acquire at cluster scope: all partials are now local
+    if (threadIdx.x == 0) {               // every CTA merges the same partials in the same order: identical statistics
         float cnt = 0.f, mean = 0.f, m2 = 0.f;
         for (unsigned i = 0; i < CS; ++i) {
-            const float* pq = cl.map_shared_rank(part, i);
-            const float nb = pq[0];
+            const float nb = part_all[i][0];
             if (nb == 0.f) continue;
-            const float d = pq[1] - mean, tot = cnt + nb;
+            const float d = part_all[i][1] - mean, tot = cnt + nb;
             mean += d * nb / tot;
-            m2 += pq[2] + d * d * cnt * nb / tot;
+            m2 += part_all[i][2] + d * d * cnt * nb / tot;
             cnt = tot;
         }
         stat[0] = mean;
@@ -192,9 +211,9 @@ __global__ void __launch_bounds__(GN_THREADS) gn_cluster_kernel(const float* __r
             if (act) t = __fdividef(t, 1.f + __expf(-t));
             rr[j] = t;
         }
-        *reinterpret_cast<float4*>(o + lo + i) = make_float4(rr[0], rr[1], rr[2], rr[3]);
+        __stcs(reinterpret_cast<float4*>(o + lo + i), make_float4(rr[0], rr[1], rr[2], rr[3]));
     }
-    cl.sync();                       // a peer may still be reading this CTA's `part`
+    // no trailing cluster barrier: after the one above nobody touches a peer's shared memory again
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -427,7 +446,7 @@ cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const flo
         // smallest cluster whose slices fit in shared memory, widened until the grid covers the machine
         const size_t max_slice = 40 * 1024;            // floats per CTA (160 KB)
         int cs = 1;
-        const size_t want_slice = 8 * 1024;            // 32 KB slices: several CTAs per SM keep enough loads in flight
+        static const size_t want_slice = getenv("TMD_GN_SLICE") ? (size_t)atoi(getenv("TMD_GN_SLICE")) : 8 * 1024;   // 32 KB slices: several CTAs per SM keep enough loads in flight
         while (cs < 8 && ((n + cs - 1) / cs > want_slice || (size_t)B * G * cs < 2 * 148)) cs *= 2;
         const size_t slice = (((n + cs - 1) / cs) + 3) & ~(size_t)3;
         if (slice <= max_slice && slice >= 4) {
