@@ -40,6 +40,8 @@ namespace {
 constexpr int kEpiPerQuarter = 3;      // epilogue warps per TMEM lane quarter
 constexpr int kThreads = 128 + 128 * kEpiPerQuarter;   // 4 role warps + 16 epilogue warps
 constexpr int kMaxSA = 4, kMaxSB = 16;
+constexpr int kMaxCo = 256;
+constexpr int kCstPerThread = (5 * kMaxCo + 128 * kEpiPerQuarter - 1) / (128 * kEpiPerQuarter);
 
 struct UmmaParams {
     CUtensorMap tmA, tmB;
@@ -54,6 +56,7 @@ struct UmmaParams {
     int NACC;                   // accumulators (band planes) per tile
     int tiles_x, tiles_y, tiles_n, tiles_b, num_tiles;
     int SA, SB;
+    int b_taps;                 // REUSE: (dy,dx) taps per weight stage (1, 3 or 9): fewer, larger stages amortise the per-stage handshake
     uint32_t a_stage_bytes, a_stage_stride, b_tile_bytes, b_tile_stride;
     uint32_t row_bytes, layout_type, sbo16;
     uint32_t tmem_cols, idesc;
@@ -238,7 +241,10 @@ __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ov
     }
 }
 
-__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16]) {
+// kS: the per-sample vectors come from the tile's staged copy in shared memory, cs = [bias | tb0 | tb1 | sc0 | sc1][Co]
+// (absent tb reads as 0, absent sc as 1), instead of global memory.
+template <bool kS>
+__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16], const float* cs = nullptr, int Co = 0) {
     typedef __nv_bfloat16 T;
     if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
 #pragma unroll
@@ -248,15 +254,29 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             float t[8], s[8], u[8];
-            if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co + 8 * h, t);
-            if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co + 8 * h, s);
+            if (kS) {
+                const float4* pt = reinterpret_cast<const float4*>(cs + (1 + k) * Co + co + 8 * h);
+                const float4* ps = reinterpret_cast<const float4*>(cs + (3 + k) * Co + co + 8 * h);
+                const float4 t0 = pt[0], t1 = pt[1], s0 = ps[0], s1 = ps[1];
+                t[0] = t0.x; t[1] = t0.y; t[2] = t0.z; t[3] = t0.w; t[4] = t1.x; t[5] = t1.y; t[6] = t1.z; t[7] = t1.w;
+                s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                float x = v[8 * h + i];
-                if (e.tb[k]) x += t[i];
-                if (!(e.dbg & 16)) x = swish_tanh(x);
-                if (e.sc[k]) x *= s[i];
-                u[i] = x;
+                for (int i = 0; i < 8; ++i) {
+                    float x = v[8 * h + i] + t[i];
+                    if (!(e.dbg & 16)) x = swish_tanh(x);
+                    u[i] = x * s[i];
+                }
+            } else {
+                if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co + 8 * h, t);
+                if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co + 8 * h, s);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float x = v[8 * h + i];
+                    if (e.tb[k]) x += t[i];
+                    if (!(e.dbg & 16)) x = swish_tanh(x);
+                    if (e.sc[k]) x *= s[i];
+                    u[i] = x;
+                }
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) w[4 * h + i] = pack_bf16x2(u[2 * i], u[2 * i + 1]);
@@ -266,23 +286,29 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 }
 
 // One 16-channel slab of one accumulator row.  All 32 lanes of the warp call this together (the
-// POOL mode exchanges rows through shuffles); `valid` guards the stores only.
-__device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int n, int y, int x, bool valid, const Resid& pre) {
+// POOL mode exchanges rows through shuffles); `valid` guards the stores only.  ovox / hvox are the row's voxel index at
+// the convolution's resolution and at half of it.
+template <bool kS>
+__device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int y, int x, size_t ovox, size_t hvox, bool valid,
+                                           const Resid& pre, const float* cs) {
     const ConvEpilogue& e = P.epi;
     float bias[16];
-    if (e.bias) {
+    if (kS) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 t = reinterpret_cast<const float4*>(cs + co)[i];
+            bias[4 * i] = t.x; bias[4 * i + 1] = t.y; bias[4 * i + 2] = t.z; bias[4 * i + 3] = t.w;
+        }
+    } else if (e.bias) {
         load8_f32(e.bias + co, bias);
         load8_f32(e.bias + co + 8, bias + 8);
     } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) bias[i] = 0.f;
     }
-    const size_t bn = (size_t)b * P.N + n;
     if (e.mode == CONV_NORMAL) {
         const bool pooled = e.pool_out != nullptr;           // warp-uniform
         if (!valid && !pooled) return;
-        const size_t ovox = (bn * P.H + y) * P.W + x;
-        const size_t hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] += bias[i];
         if (valid) add_residuals16<true>(e, ovox, hvox, co, acc, pre.a0);
@@ -302,11 +328,10 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             if (valid && !(x & 1) && !(y & 1))
                 st_global_v8(reinterpret_cast<__nv_bfloat16*>(e.pool_out) + hvox * e.ld_pool + co, w);
         }
-        if (valid) store_views16(e, b, ovox, co, acc);
+        if (valid) store_views16<kS>(e, b, ovox, co, acc, cs, P.Co);
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
         const bool writer = valid && !(x & 1) && !(y & 1);
-        const size_t ovox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
         const bool want_hf = e.hf_out[0] != nullptr;
         float ll[16];
         uint32_t lh[8], hl[8], hh[8];
@@ -333,24 +358,25 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         if (!writer) return;
         if (want_hf) {
             typedef __nv_bfloat16 T;
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[0]) + ovox * e.ld_hf + co, lh);
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + ovox * e.ld_hf + co, hl);
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + ovox * e.ld_hf + co, hh);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[0]) + hvox * e.ld_hf + co, lh);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + hvox * e.ld_hf + co, hl);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + hvox * e.ld_hf + co, hh);
         }
-        add_residuals16<false>(e, ovox, 0, co, ll);
-        store_views16(e, b, ovox, co, ll);
+        add_residuals16<false>(e, hvox, 0, co, ll);
+        store_views16<kS>(e, b, hvox, co, ll, cs, P.Co);
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] += bias[i];
+        const size_t up0 = 4 * ovox - 2 * (size_t)x;         // voxel (2y, 2x) of the double-resolution plane
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const size_t ovox = (bn * (2 * P.H) + 2 * y + (r >> 1)) * (2 * P.W) + 2 * x + (r & 1);
+            const size_t uvox = up0 + (size_t)(r >> 1) * (2 * P.W) + (r & 1);
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            add_residuals16<false>(e, ovox, 0, co, v);
-            store_views16(e, b, ovox, co, v);
+            add_residuals16<false>(e, uvox, 0, co, v);
+            store_views16<kS>(e, b, uvox, co, v, cs, P.Co);
         }
     }
 }
@@ -396,6 +422,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 4];
     __shared__ uint32_t tmem_base_slot;
+    __shared__ __align__(16) float cst[MODE ? 2 : 1][MODE ? 5 * kMaxCo : 4];   // REUSE: per-tile epilogue vectors (see the epilogue warps)
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
@@ -427,7 +454,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 
     constexpr int KC = KMMA * 16;
     const int ngroups = MODE ? 1 : P.taps;              // activation boxes per K chunk (REUSE: ONE haloed box serves all 27 taps)
-    constexpr int b_stages_per_a = MODE ? 9 : 1;        // weight stages consumed per activation stage (REUSE: the 9 (dy,dx) taps)
+    const int b_taps = MODE ? P.b_taps : 1;             // (dy,dx) taps held by one weight stage
+    const int b_stages_per_a = MODE ? 9 / b_taps : 1;   // weight stages consumed per activation stage (REUSE: the 9 (dy,dx) taps)
     const int nkc = P.nkc;
 
     if (warp == 0) {
@@ -504,17 +532,18 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 }
                 for (int kc = 0; kc < nkc; ++kc)
 #pragma unroll 1
-                    for (int t = 0; t < b_stages_per_a; ++t) {           // REUSE: t = dy
+                    for (int ts = 0; ts < b_stages_per_a; ++ts) {
                         mbar_wait(b_empty(s), ph);
                         if (elect_one()) {
                             if (P.dbg & 4) mbar_arrive(b_full(s));
                             else {
-                                const uint32_t dst = b_base + s * P.b_tile_stride;
+                                uint32_t dst = b_base + s * P.b_tile_stride;
                                 if (MODE) {
-                                    mbar_expect_tx(b_full(s), 3 * P.b_tile_bytes);
+                                    mbar_expect_tx(b_full(s), 3 * P.b_tile_bytes * (uint32_t)b_taps);
+                                    for (int t = ts * b_taps; t < (ts + 1) * b_taps; ++t)    // t = dy*3+dx
 #pragma unroll
-                                    for (int dz = 0; dz < 3; ++dz)       // tap = (dz*3+dy)*3+dx, t = dy*3+dx; rows [dz*Co, (dz+1)*Co) of the stage
-                                        tma_load_2d(dst + dz * P.b_tile_bytes, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, 0);
+                                        for (int dz = 0; dz < 3; ++dz, dst += P.b_tile_bytes)   // tap = dz*9+t; rows [dz*Co, (dz+1)*Co) of the tap's block
+                                            tma_load_2d(dst, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, 0);
                                 } else {
                                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
                                     tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, 0);
@@ -582,21 +611,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     tc_fence_after();
                     const uint32_t a_lo = a_lo0 + sa * a_stride16;
 #pragma unroll 1
-                    for (int t = 0; t < b_stages_per_a; ++t) {           // REUSE: t = dy
+                    for (int ts = 0; ts < b_stages_per_a; ++ts) {
                         if (tr) tq = clock64();
                         mbar_wait(b_full(sb), phb);
                         if (tr) { tw_b += clock64() - tq; tq = clock64(); }
                         tc_fence_after();
                         if (elect_one()) {
-                            const uint32_t b_lo = b_lo0 + sb * b_stride16;
-                            const uint32_t tap16 = (uint32_t)(t / 3) * line16 + (uint32_t)(t % 3) * vox16;   // REUSE: t = dy*3 + dx
+#pragma unroll 1
+                          for (int tt = 0; tt < b_taps; ++tt) {
+                            const int t = ts * b_taps + tt;                    // REUSE: t = dy*3 + dx
+                            const uint32_t fr = fresh | (uint32_t)(tt > 0);    // 0: first MMAs of the tile (overwrite)
+                            const uint32_t b_lo = b_lo0 + sb * b_stride16 + (uint32_t)tt * 3u * co16;
+                            const uint32_t tap16 = (uint32_t)(t / 3) * line16 + (uint32_t)(t % 3) * vox16;
                             if (do_mma) {
                                 if (!MODE) {
 #pragma unroll
                                     for (int k = 0; k < KMMA; ++k)
                                         tc_mma_bf16(d0, ((uint64_t)desc_hi_a << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
-                                                    k == 0 ? fresh : 1u);
-                                } else if (MERGE && fresh) {
+                                                    k == 0 ? fr : 1u);
+                                } else if (MERGE && fr) {
                                     // One MMA per input plane q (box plane q+1) and K=16 slice: its A view feeds the output planes
                                     // q+1, q, q-1 through the taps dz = 0, 1, 2, whose weights are consecutive row blocks of the
                                     // stage and whose accumulators are consecutive TMEM column blocks (planes in decreasing order).
@@ -633,10 +666,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 #pragma unroll
                                             for (int k = 0; k < KMMA; ++k)
                                                 tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
-                                                            (k == 0 && dz == dz_first) ? fresh : 1u);
+                                                            (k == 0 && dz == dz_first) ? fr : 1u);
                                         }
                                 }
                             }
+                          }
                             tc_commit(b_empty(sb));              // weight stage free once these MMAs retire
                         }
                         __syncwarp();
@@ -687,15 +721,42 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const int sub = (warp - 4) >> 2;                  // which of the quarter's warps
         const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
         uint32_t lt = 0;
-        long long tw_full = 0, t_all0 = clock64(), tq = 0;
+        long long tw_full = 0, tw_ld = 0, tw_bar = 0, t_all0 = clock64(), tq = 0;
         const bool tr = P.trace && blockIdx.x == 0 && threadIdx.x == 128;
+        const size_t plane_vox = (size_t)P.H * P.W, hplane_vox = (size_t)(P.H / 2) * (P.W / 2);
+        // REUSE kernels: a tile lies in one sample, so its per-sample epilogue vectors [bias | tb0 | tb1 | sc0 | sc1][Co]
+        // are staged in shared memory once per tile (double-buffered, fetched one tile ahead by the 384 epilogue threads)
+        // instead of being re-read from global memory by every lane for every slab.
+        const int e_tid = (int)threadIdx.x - 128, n_cst = 5 * P.Co;
+        float pre_c[kCstPerThread];
+        auto load_consts = [&](int bb) {
+            const ConvEpilogue& e = P.epi;
+#pragma unroll
+            for (int j = 0; j < kCstPerThread; ++j) {
+                const int idx = e_tid + j * 128 * kEpiPerQuarter;
+                if (idx >= n_cst) continue;
+                const int v = idx / P.Co, c = idx - v * P.Co;
+                float val;
+                if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
+                else if (v < 3) val = e.tb[v - 1] ? __ldg(e.tb[v - 1] + (size_t)bb * e.ld_tb + c) : 0.f;
+                else val = e.sc[v - 3] ? __ldg(e.sc[v - 3] + (size_t)bb * e.ld_sc + c) : 1.f;
+                pre_c[j] = val;
+            }
+        };
+        auto store_consts = [&](float* dst) {
+#pragma unroll
+            for (int j = 0; j < kCstPerThread; ++j) {
+                const int idx = e_tid + j * 128 * kEpiPerQuarter;
+                if (idx < n_cst) dst[idx] = pre_c[j];
+            }
+        };
+        if (MODE && (int)blockIdx.x < P.num_tiles) {
+            load_consts(decode_tile(P, blockIdx.x).b0);
+            store_consts(&cst[0][0]);
+        }
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
             const TileCoord tc = decode_tile(P, tile);
             const int ab = lt & 1;
-            if (tr) tq = clock64();
-            mbar_wait(acc_full(ab), (lt >> 1) & 1);
-            if (tr) tw_full += clock64() - tq;
-            tc_fence_after();
             int b, n_off, y, x;
             if (MODE) { x = r % P.TW; y = r / P.TW; n_off = 0; b = tc.b0; }
             else {
@@ -711,39 +772,47 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             const int nslab = P.Co >> 4, nitems = NACC * nslab;
             const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
             const bool normal = P.epi.mode == CONV_NORMAL;
-            auto item_vox = [&](int it, int& n, size_t& ovox, size_t& hvox, bool& valid) {
-                n = tc.n0 + n_off + it / nslab;
-                valid = in_tile && n < P.N;
-                const size_t bn = (size_t)b * P.N + n;
-                ovox = (bn * P.H + y) * P.W + x;
-                hvox = (bn * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
-            };
+            const size_t bn0 = (size_t)b * P.N + tc.n0 + n_off;
+            const size_t vox0 = (bn0 * P.H + y) * P.W + x, hvox0 = (bn0 * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+            const float* cs = nullptr;
+            if (MODE) {
+                // this tile's per-sample vectors were staged by the previous iteration; fetch the next tile's
+                cs = &cst[lt & 1][0];
+                const int nt = tile + gridDim.x;
+                if (nt < P.num_tiles) load_consts(decode_tile(P, nt).b0);
+                if (tr) tq = clock64();
+                asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
+                if (tr) tw_bar += clock64() - tq;
+            }
+            if (tr) tq = clock64();
+            mbar_wait(acc_full(ab), (lt >> 1) & 1);
+            if (tr) tw_full += clock64() - tq;
+            tc_fence_after();
+            int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
+            while (sl >= nslab) { sl -= nslab; ++pl; }
             Resid cur, nxt;
-            {
-                int n; size_t ov, hv; bool vl;
-                item_vox(sub, n, ov, hv, vl);
-                if (normal && sub < nitems) load_resid(P.epi, ov, (sub % nslab) * 16, vl, cur);
-            }
+            if (normal && pl < NACC) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
-                if (normal && it + kEpiPerQuarter < nitems) {
-                    int n; size_t ov, hv; bool vl;
-                    item_vox(it + kEpiPerQuarter, n, ov, hv, vl);
-                    load_resid(P.epi, ov, ((it + kEpiPerQuarter) % nslab) * 16, vl, nxt);
-                }
-                int n; size_t ov, hv; bool valid;
-                item_vox(it, n, ov, hv, valid);
-                const int p = it / nslab, c0 = (it % nslab) * 16;
-                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - p)) * P.Co;
+                int pl2 = pl, sl2 = sl + kEpiPerQuarter;
+                while (sl2 >= nslab) { sl2 -= nslab; ++pl2; }
+                if (normal && pl2 < NACC)
+                    load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, sl2 * 16, in_tile && tc.n0 + n_off + pl2 < P.N, nxt);
+                const bool valid = in_tile && tc.n0 + n_off + pl < P.N;
+                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - pl)) * P.Co;
                 float acc[16];
-                tc_ld16(t_row + c0, acc);
-                epilogue16(P, acc, c0, b, n, y, x, valid, cur);
+                if (tr) tq = clock64();
+                tc_ld16(t_row + sl * 16, acc);
+                if (tr) tw_ld += clock64() - tq;
+                epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs);
                 cur = nxt;
+                pl = pl2; sl = sl2;
             }
+            if (MODE && tile + (int)gridDim.x < P.num_tiles) store_consts(&cst[(lt + 1) & 1][0]);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty(ab));
         }
-        if (tr) { P.trace[8] = clock64() - t_all0; P.trace[9] = tw_full; }
+        if (tr) { P.trace[8] = clock64() - t_all0; P.trace[9] = tw_full; P.trace[10] = tw_ld; P.trace[11] = tw_bar; }
     }
 
     tc_fence_before();
@@ -896,7 +965,13 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.epi.dbg = P.dbg;
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
     P.b_tile_bytes = op.Co * P.row_bytes;
-    P.b_tile_stride = ((P.mode ? 3 : 1) * P.b_tile_bytes + 1023u) & ~1023u;    // REUSE: a weight stage holds the 3 dz taps of a (dy,dx)
+    // REUSE: a weight stage holds the 3 dz taps of b_taps (dy,dx) taps.  Small Co: three taps per stage, so that a stage
+    // carries enough MMA work to hide the issue warp's per-stage wait / commit round.
+    P.b_taps = 1;
+    if (P.mode) {
+        P.b_taps = env_int("TMD_UMMA_BTAPS", op.Co <= 64 ? 3 : 1);
+        if (P.b_taps != 1 && P.b_taps != 3 && P.b_taps != 9) P.b_taps = 1;
+    }
     int cols = 2 * P.NACC * op.Co;
     P.tmem_cols = 32;
     while ((int)P.tmem_cols < cols) P.tmem_cols *= 2;
@@ -904,16 +979,20 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(op.Co >> 3) << 17) | ((128u >> 4) << 24);
 
     // ring depths from the shared-memory budget
-    const size_t budget = 220 * 1024;
-    // activation stages first (their TMA round trip is the long one), at least four weight stages behind them
-    const int want_sb = P.mode ? 6 : 4;
-    P.SA = P.mode ? env_int("TMD_UMMA_SA", 2) : 4;
-    while (P.SA > 2 && (size_t)P.SA * P.a_stage_stride + 4 * (size_t)P.b_tile_stride > budget) --P.SA;
-    while (P.SA > 1 && (size_t)P.SA * P.a_stage_stride + 2 * (size_t)P.b_tile_stride > budget) --P.SA;
-    size_t left = budget - (size_t)P.SA * P.a_stage_stride;
-    P.SB = (int)(left / P.b_tile_stride);
-    if (P.SB > want_sb) P.SB = want_sb;
-    if (P.SB > kMaxSB) P.SB = kMaxSB;
+    const size_t budget = 215 * 1024;              // 227 KB less the kernel's static shared memory (barriers, epilogue vectors)
+    for (;; P.b_taps /= 3) {
+        P.b_tile_stride = ((P.mode ? 3 * P.b_taps : 1) * P.b_tile_bytes + 1023u) & ~1023u;
+        // activation stages first (their TMA round trip is the long one), at least four weight stages behind them
+        const int want_sb = P.mode ? (P.b_taps == 1 ? 6 : (P.b_taps == 3 ? 4 : 2)) : 4;
+        P.SA = P.mode ? env_int("TMD_UMMA_SA", 2) : 4;
+        while (P.SA > 2 && (size_t)P.SA * P.a_stage_stride + 4 * (size_t)P.b_tile_stride > budget) --P.SA;
+        while (P.SA > 1 && (size_t)P.SA * P.a_stage_stride + 2 * (size_t)P.b_tile_stride > budget) --P.SA;
+        size_t left = budget - (size_t)P.SA * P.a_stage_stride;
+        P.SB = (int)(left / P.b_tile_stride);
+        if (P.SB > want_sb) P.SB = want_sb;
+        if (P.SB > kMaxSB) P.SB = kMaxSB;
+        if (P.b_taps == 1 || (P.SA >= 2 && P.SB >= (P.b_taps == 3 ? 3 : 2))) break;   // else: fewer taps per stage
+    }
     if (P.SB < 2 || P.SA < 1) { delete plan; return nullptr; }
     plan->smem = (size_t)P.SA * P.a_stage_stride + (size_t)P.SB * P.b_tile_stride + 1024;
 
@@ -989,7 +1068,10 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
                            conv_umma_kernel<1, 2, 2, false>, conv_umma_kernel<1, 1, 2, false>, conv_umma_kernel<0, 1, 4, false>,
                            conv_umma_kernel<0, 1, 2, false>};
         for (KernelFn f : all) {
-            cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+            cudaFuncAttributes fa;
+            cudaError_t e = cudaFuncGetAttributes(&fa, f);
+            if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);   // static + dynamic <= 227 KB
             if (e != cudaSuccess) return e;
         }
         attr_set = true;
@@ -1006,9 +1088,9 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
         cudaFree(p.trace);
         const long long mmas = t[6] * (p.mode ? 27 : p.taps) * p.nkc * p.NACC * (p.KC / 16);
         fprintf(stderr, "[umma trace] Ci=%d Co=%d %dx%dx%d mode=%d NACC=%d tiles=%d grid=%d | mma warp: total %lld cyc, wait acc %lld, wait A %lld, "
-                "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld\n",
+                "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld, tmem ld %lld, bar %lld\n",
                 p.Ci, p.Co, p.N, p.H, p.W, p.mode, p.NACC, p.num_tiles, plan->grid, t[0], t[1], t[2], t[3], t[4],
-                mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9]);
+                mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9], t[10], t[11]);
         return cudaGetLastError();
     }
     // (programmatic dependent launch was measured: no gain -- one CTA per SM leaves nothing for the next kernel to overlap)
