@@ -4,7 +4,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libtmdiff_b200.so")
+# TMDIFF_B200_LIB: load another build of the same library (A/B runs of kernel variants on one box, profiles/_variant.py)
+LIB_PATH = os.environ.get("TMDIFF_B200_LIB") or os.path.join(_HERE, "lib", "libtmdiff_b200.so")
 
 F32, BF16 = 0, 1
 SENSOR_IDS = {"QB": 0, "WV3": 1, "GF2": 2, "WV2": 3, "WV4": 4}

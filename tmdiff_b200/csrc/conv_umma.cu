@@ -49,7 +49,8 @@ struct UmmaParams {
     int nkc2;
     uint32_t a2_piece_bytes;    // REUSE: one un-haloed band plane [TH][TW][KC] of the second source
     ConvEpilogue epi;
-    int B, N, H, W, Ci, Co, taps;
+    int B, N, H, W, Ci, Co, taps;   // Co: output channels of ONE tile (= the layer's Co / co_split)
+    int co_split;               // REUSE: channel groups the layer's Co is split into (a tile = voxels x planes x one group)
     int mode;                   // 0 = SIMPLE, 1 = REUSE
     int KC, nkc;                // channels per chunk, chunks per tap
     int TW, TH, TN, TB;         // output tile (voxels per accumulator = 128)
@@ -82,10 +83,15 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 // Spin on the phase parity; a wait that lasts ~4 s means a broken pipeline: trap instead of hanging the GPU.
+#ifndef TMD_PRODUCER_SLEEP
+#define TMD_PRODUCER_SLEEP 0
+#endif
+template <int kSleepNs = 0>
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
     long long t0 = 0;
     for (uint32_t spins = 0;; ++spins) {
+        if (kSleepNs && spins) __nanosleep(kSleepNs);
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -187,7 +193,37 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<const uint32_t*>(&h);
 }
+// Packed fp32 pairs (sm_100 FADD2 / FMUL2 / FFMA2): same IEEE results as the scalar instructions at half the issue slots,
+// which is what the epilogue warps are short of.
+__device__ __forceinline__ uint64_t pk2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
 __device__ __forceinline__ void add_bf16x16(float v[16], const uint32_t w[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const uint64_t r = add2(pk2(v[2 * i], v[2 * i + 1]), pk2(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u)));
+        upk2(r, v[2 * i], v[2 * i + 1]);
+    }
+}
+__device__ __forceinline__ void add_bf16x16_scalar(float v[16], const uint32_t w[8]) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[i]);
@@ -242,11 +278,13 @@ __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ov
 }
 
 // kS: the per-sample vectors come from the tile's staged copy in shared memory, cs = [bias | tb0 | tb1 | sc0 | sc1][Co]
-// (absent tb reads as 0, absent sc as 1), instead of global memory.
+// (tb halved; absent tb reads as 0, absent sc as 1), instead of global memory.
 template <bool kS>
-__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16], const float* cs = nullptr, int Co = 0) {
+__device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16], const float* cs = nullptr, int Co = 0,
+                                              int cb = 0) {
     typedef __nv_bfloat16 T;
-    if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + co, v);
+    const int cg = co + cb;          // channel in the tensors (co: channel of this tile's group, the index into cs)
+    if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         if (!e.act_out[k]) continue;
@@ -255,20 +293,28 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
         for (int h = 0; h < 2; ++h) {
             float t[8], s[8], u[8];
             if (kS) {
-                const float4* pt = reinterpret_cast<const float4*>(cs + (1 + k) * Co + co + 8 * h);
-                const float4* ps = reinterpret_cast<const float4*>(cs + (3 + k) * Co + co + 8 * h);
-                const float4 t0 = pt[0], t1 = pt[1], s0 = ps[0], s1 = ps[1];
-                t[0] = t0.x; t[1] = t0.y; t[2] = t0.z; t[3] = t0.w; t[4] = t1.x; t[5] = t1.y; t[6] = t1.z; t[7] = t1.w;
-                s[0] = s0.x; s[1] = s0.y; s[2] = s0.z; s[3] = s0.w; s[4] = s1.x; s[5] = s1.y; s[6] = s1.z; s[7] = s1.w;
+                // cs holds tb/2: h = (v + tb)/2 is one FFMA, swish = h + h*tanh(h) another, then the modulation scale
+                const ulonglong2* pt = reinterpret_cast<const ulonglong2*>(cs + (1 + k) * Co + co + 8 * h);
+                const ulonglong2* ps = reinterpret_cast<const ulonglong2*>(cs + (3 + k) * Co + co + 8 * h);
+                const ulonglong2 t0 = pt[0], t1 = pt[1], s0 = ps[0], s1 = ps[1];
+                const uint64_t tt[4] = {t0.x, t0.y, t1.x, t1.y}, ss[4] = {s0.x, s0.y, s1.x, s1.y};
+                const uint64_t half2 = pk2(0.5f, 0.5f);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    float x = v[8 * h + i] + t[i];
-                    if (!(e.dbg & 16)) x = swish_tanh(x);
-                    u[i] = x * s[i];
+                for (int i = 0; i < 4; ++i) {
+                    uint64_t x = fma2(pk2(v[8 * h + 2 * i], v[8 * h + 2 * i + 1]), half2, tt[i]);
+                    if (!(e.dbg & 16)) {
+                        float a, b2, ta, tb2;
+                        upk2(x, a, b2);
+                        asm("tanh.approx.f32 %0, %1;" : "=f"(ta) : "f"(a));
+                        asm("tanh.approx.f32 %0, %1;" : "=f"(tb2) : "f"(b2));
+                        x = fma2(x, pk2(ta, tb2), x);
+                    } else x = add2(x, x);
+                    x = mul2(x, ss[i]);
+                    upk2(x, u[2 * i], u[2 * i + 1]);
                 }
             } else {
-                if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + co + 8 * h, t);
-                if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + co + 8 * h, s);
+                if (e.tb[k]) load8_f32(e.tb[k] + (size_t)b * e.ld_tb + cg + 8 * h, t);
+                if (e.sc[k]) load8_f32(e.sc[k] + (size_t)b * e.ld_sc + cg + 8 * h, s);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     float x = v[8 * h + i];
@@ -281,7 +327,7 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 #pragma unroll
             for (int i = 0; i < 4; ++i) w[4 * h + i] = pack_bf16x2(u[2 * i], u[2 * i + 1]);
         }
-        if (!(e.dbg & 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + co, w);
+        if (!(e.dbg & 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + cg, w);
     }
 }
 
@@ -290,8 +336,9 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 // the convolution's resolution and at half of it.
 template <bool kS>
 __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int y, int x, size_t ovox, size_t hvox, bool valid,
-                                           const Resid& pre, const float* cs) {
+                                           const Resid& pre, const float* cs, int cb) {
     const ConvEpilogue& e = P.epi;
+    const int cg = co + cb;
     float bias[16];
     if (kS) {
 #pragma unroll
@@ -300,8 +347,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             bias[4 * i] = t.x; bias[4 * i + 1] = t.y; bias[4 * i + 2] = t.z; bias[4 * i + 3] = t.w;
         }
     } else if (e.bias) {
-        load8_f32(e.bias + co, bias);
-        load8_f32(e.bias + co + 8, bias + 8);
+        load8_f32(e.bias + cg, bias);
+        load8_f32(e.bias + cg + 8, bias + 8);
     } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) bias[i] = 0.f;
@@ -310,8 +357,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         const bool pooled = e.pool_out != nullptr;           // warp-uniform
         if (!valid && !pooled) return;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) acc[i] += bias[i];
-        if (valid) add_residuals16<true>(e, ovox, hvox, co, acc, pre.a0);
+        for (int i = 0; i < 16; i += 2) upk2(add2(pk2(acc[i], acc[i + 1]), pk2(bias[i], bias[i + 1])), acc[i], acc[i + 1]);
+        if (valid) add_residuals16<true>(e, ovox, hvox, cg, acc, pre.a0);
         if (pooled) {
             // 2x2 average of v for the consumer's fused Conv_2 path; a quad is wholly inside or outside the tensor
             uint32_t w[8];
@@ -326,9 +373,9 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
                 w[i >> 1] = pack_bf16x2(o[0], o[1]);
             }
             if (valid && !(x & 1) && !(y & 1))
-                st_global_v8(reinterpret_cast<__nv_bfloat16*>(e.pool_out) + hvox * e.ld_pool + co, w);
+                st_global_v8(reinterpret_cast<__nv_bfloat16*>(e.pool_out) + hvox * e.ld_pool + cg, w);
         }
-        if (valid) store_views16<kS>(e, b, ovox, co, acc, cs, P.Co);
+        if (valid) store_views16<kS>(e, b, ovox, co, acc, cs, P.Co, cb);
     } else if (e.mode == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
         const bool writer = valid && !(x & 1) && !(y & 1);
@@ -358,12 +405,12 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         if (!writer) return;
         if (want_hf) {
             typedef __nv_bfloat16 T;
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[0]) + hvox * e.ld_hf + co, lh);
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + hvox * e.ld_hf + co, hl);
-            st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + hvox * e.ld_hf + co, hh);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[0]) + hvox * e.ld_hf + cg, lh);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + hvox * e.ld_hf + cg, hl);
+            st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + hvox * e.ld_hf + cg, hh);
         }
-        add_residuals16<false>(e, hvox, 0, co, ll);
-        store_views16<kS>(e, b, hvox, co, ll, cs, P.Co);
+        add_residuals16<false>(e, hvox, 0, cg, ll);
+        store_views16<kS>(e, b, hvox, co, ll, cs, P.Co, cb);
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
 #pragma unroll
@@ -375,15 +422,18 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            add_residuals16<false>(e, uvox, 0, co, v);
-            store_views16<kS>(e, b, uvox, co, v, cs, P.Co);
+            add_residuals16<false>(e, uvox, 0, cg, v);
+            store_views16<kS>(e, b, uvox, co, v, cs, P.Co, cb);
         }
     }
 }
 
-struct TileCoord { int b0, n0, y0, x0; };
+struct TileCoord { int b0, n0, y0, x0, ch; };
 __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int t) {
     TileCoord c;
+    // the channel groups of one voxel tile are neighbours in the tile order: they run at the same time on different SMs
+    // and share the activation boxes through L2
+    c.ch = t % P.co_split; t /= P.co_split;
     c.x0 = (t % P.tiles_x) * P.TW; t /= P.tiles_x;
     c.y0 = (t % P.tiles_y) * P.TH; t /= P.tiles_y;
     c.n0 = (t % P.tiles_n) * (P.mode ? P.NACC : P.TN); t /= P.tiles_n;
@@ -477,7 +527,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     if (cn + P.TN <= 0 || cn >= P.N) continue;            // the whole box is padding
                 }
                 for (int kc = 0; kc < nkc; ++kc) {
-                    mbar_wait(a_empty(s), ph);
+                    mbar_wait<TMD_PRODUCER_SLEEP>(a_empty(s), ph);
                     if (elect_one()) {
                         if (P.dbg & 2) mbar_arrive(a_full(s));
                         else {
@@ -502,7 +552,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 #pragma unroll
                 for (int pl = 0; pl < NACC; ++pl) planes2 += (tc.n0 + pl) < P.N;
                 for (int kc = 0; kc < P.nkc2; ++kc) {
-                    mbar_wait(a_empty(s), ph);
+                    mbar_wait<TMD_PRODUCER_SLEEP>(a_empty(s), ph);
                     if (elect_one()) {
                         uint32_t dst = a_base + s * P.a_stage_stride;
                         if (MODE) {
@@ -533,7 +583,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 for (int kc = 0; kc < nkc; ++kc)
 #pragma unroll 1
                     for (int ts = 0; ts < b_stages_per_a; ++ts) {
-                        mbar_wait(b_empty(s), ph);
+                        mbar_wait<TMD_PRODUCER_SLEEP>(b_empty(s), ph);
                         if (elect_one()) {
                             if (P.dbg & 4) mbar_arrive(b_full(s));
                             else {
@@ -543,10 +593,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                     for (int t = ts * b_taps; t < (ts + 1) * b_taps; ++t)    // t = dy*3+dx
 #pragma unroll
                                         for (int dz = 0; dz < 3; ++dz, dst += P.b_tile_bytes)   // tap = dz*9+t; rows [dz*Co, (dz+1)*Co) of the tap's block
-                                            tma_load_2d(dst, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, 0);
+                                            tma_load_2d(dst, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, tc.ch * P.Co);
                                 } else {
                                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
-                                    tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, 0);
+                                    tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, tc.ch * P.Co);
                                 }
                             }
                         }
@@ -555,10 +605,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     }
             }
             for (int kc = 0; kc < P.nkc2; ++kc) {
-                mbar_wait(b_empty(s), ph);
+                mbar_wait<TMD_PRODUCER_SLEEP>(b_empty(s), ph);
                 if (elect_one()) {
                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
-                    tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB2, b_full(s), kc * KC, 0);
+                    tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB2, b_full(s), kc * KC, tc.ch * P.Co);
                 }
                 __syncwarp();
                 if (++s == (uint32_t)P.SB) { s = 0; ph ^= 1; }
@@ -629,12 +679,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                     for (int k = 0; k < KMMA; ++k)
                                         tc_mma_bf16(d0, ((uint64_t)desc_hi_a << 32) | (a_lo + k * 2), ((uint64_t)desc_hi << 32) | (b_lo + k * 2), idesc,
                                                     k == 0 ? fr : 1u);
-                                } else if (MERGE && fr) {
+                                } else if (MERGE) {
                                     // One MMA per input plane q (box plane q+1) and K=16 slice: its A view feeds the output planes
                                     // q+1, q, q-1 through the taps dz = 0, 1, 2, whose weights are consecutive row blocks of the
                                     // stage and whose accumulators are consecutive TMEM column blocks (planes in decreasing order).
-                                    // Order: first the MMAs whose column spans tile the accumulators (they overwrite at the
-                                    // start of a tile), then the rest.
+                                    // The first tap of a tile has to overwrite: `init` tracks which accumulators already hold
+                                    // this tile's data; an MMA whose span is all-fresh overwrites, all-initialised accumulates,
+                                    // and a mixed span (first tap only) is issued plane by plane.
+                                    uint32_t init = fr ? 0xffffffffu : 0u;
 #pragma unroll
                                     for (int i = 0; i < NACC + 2; ++i) {
                                         const int q = merge_order<NACC>(i);                  // -1 .. NACC
@@ -643,17 +695,33 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                         const int dz_hi = q + 1 < 2 ? q + 1 : 2;                         // p >= 0
                                         const int nblk = dz_hi - dz_lo + 1;
                                         const int p_top = q + 1 - dz_lo;
-                                        const uint32_t id = idesc_base | ((uint32_t)((nblk * Co) >> 3) << 17);
+                                        const uint32_t mask = ((1u << nblk) - 1u) << (p_top - nblk + 1);
+                                        const uint32_t have = init & mask;
+                                        init |= mask;
                                         const uint32_t a_view = a_lo + (uint32_t)(q + 1 - pl_off) * plane16 + tap16;
-                                        const uint32_t b_view = b_lo + (uint32_t)dz_lo * co16;
-                                        const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
+                                        if (have == mask || have == 0u) {
+                                            const uint32_t id = idesc_base | ((uint32_t)((nblk * Co) >> 3) << 17);
+                                            const uint32_t b_view = b_lo + (uint32_t)dz_lo * co16;
+                                            const uint32_t d = d0 + (uint32_t)(NACC - 1 - p_top) * Co;
 #pragma unroll
-                                        for (int k = 0; k < KMMA; ++k)
-                                            tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id, 1u);
+                                            for (int k = 0; k < KMMA; ++k)
+                                                tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), id,
+                                                            (k == 0 && have == 0u) ? 0u : 1u);
+                                        } else {
+#pragma unroll
+                                            for (int j = 0; j < nblk; ++j) {                 // plane p_top - j through dz_lo + j
+                                                const uint32_t b_view = b_lo + (uint32_t)(dz_lo + j) * co16;
+                                                const uint32_t d = d0 + (uint32_t)(NACC - 1 - (p_top - j)) * Co;
+                                                const uint32_t acc_on = (have >> (p_top - j)) & 1u;
+#pragma unroll
+                                                for (int k = 0; k < KMMA; ++k)
+                                                    tc_mma_bf16(d, ((uint64_t)desc_hi_a << 32) | (a_view + k * 2), ((uint64_t)desc_hi << 32) | (b_view + k * 2), idesc,
+                                                                k == 0 ? acc_on : 1u);
+                                            }
+                                        }
                                     }
                                 } else {
-                                    // one MMA per (output plane pp, dz).  Also the first stage of a tile in the merged kernels:
-                                    // the first valid dz of each plane overwrites its accumulator.
+                                    // one MMA per (output plane pp, dz); the first valid dz of each plane overwrites its accumulator
 #pragma unroll
                                     for (int dz = 0; dz < 3; ++dz)
 #pragma unroll
@@ -729,16 +797,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         // instead of being re-read from global memory by every lane for every slab.
         const int e_tid = (int)threadIdx.x - 128, n_cst = 5 * P.Co;
         float pre_c[kCstPerThread];
-        auto load_consts = [&](int bb) {
+        auto load_consts = [&](int bb, int cb) {
             const ConvEpilogue& e = P.epi;
 #pragma unroll
             for (int j = 0; j < kCstPerThread; ++j) {
                 const int idx = e_tid + j * 128 * kEpiPerQuarter;
                 if (idx >= n_cst) continue;
-                const int v = idx / P.Co, c = idx - v * P.Co;
+                const int v = idx / P.Co, c = idx - v * P.Co + cb;
                 float val;
                 if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
-                else if (v < 3) val = e.tb[v - 1] ? __ldg(e.tb[v - 1] + (size_t)bb * e.ld_tb + c) : 0.f;
+                else if (v < 3) val = e.tb[v - 1] ? 0.5f * __ldg(e.tb[v - 1] + (size_t)bb * e.ld_tb + c) : 0.f;   // stored halved (store_views16)
                 else val = e.sc[v - 3] ? __ldg(e.sc[v - 3] + (size_t)bb * e.ld_sc + c) : 1.f;
                 pre_c[j] = val;
             }
@@ -751,7 +819,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             }
         };
         if (MODE && (int)blockIdx.x < P.num_tiles) {
-            load_consts(decode_tile(P, blockIdx.x).b0);
+            const TileCoord t0 = decode_tile(P, blockIdx.x);
+            load_consts(t0.b0, t0.ch * P.Co);
             store_consts(&cst[0][0]);
         }
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
@@ -772,6 +841,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             const int nslab = P.Co >> 4, nitems = NACC * nslab;
             const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
             const bool normal = P.epi.mode == CONV_NORMAL;
+            const int cb = tc.ch * P.Co;                    // first channel of this tile's group
             const size_t bn0 = (size_t)b * P.N + tc.n0 + n_off;
             const size_t vox0 = (bn0 * P.H + y) * P.W + x, hvox0 = (bn0 * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
             const float* cs = nullptr;
@@ -779,7 +849,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 // this tile's per-sample vectors were staged by the previous iteration; fetch the next tile's
                 cs = &cst[lt & 1][0];
                 const int nt = tile + gridDim.x;
-                if (nt < P.num_tiles) load_consts(decode_tile(P, nt).b0);
+                if (nt < P.num_tiles) {
+                    const TileCoord tn = decode_tile(P, nt);
+                    load_consts(tn.b0, tn.ch * P.Co);
+                }
                 if (tr) tq = clock64();
                 asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
                 if (tr) tw_bar += clock64() - tq;
@@ -791,20 +864,28 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
             Resid cur, nxt;
-            if (normal && pl < NACC) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
+#ifndef TMD_EXP_NOPREF
+            if (normal && pl < NACC) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
+#endif
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
                 int pl2 = pl, sl2 = sl + kEpiPerQuarter;
                 while (sl2 >= nslab) { sl2 -= nslab; ++pl2; }
+#ifdef TMD_EXP_NOPREF
+                if (normal) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
+#else
                 if (normal && pl2 < NACC)
-                    load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, sl2 * 16, in_tile && tc.n0 + n_off + pl2 < P.N, nxt);
+                    load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && tc.n0 + n_off + pl2 < P.N, nxt);
+#endif
                 const bool valid = in_tile && tc.n0 + n_off + pl < P.N;
                 const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - pl)) * P.Co;
                 float acc[16];
                 if (tr) tq = clock64();
                 tc_ld16(t_row + sl * 16, acc);
                 if (tr) tw_ld += clock64() - tq;
-                epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs);
+                epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs, cb);
+#ifndef TMD_EXP_NOPREF
                 cur = nxt;
+#endif
                 pl = pl2; sl = sl2;
             }
             if (MODE && tile + (int)gridDim.x < P.num_tiles) store_consts(&cst[(lt + 1) & 1][0]);
@@ -921,6 +1002,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     memset(&P, 0, sizeof(P));
     P.epi = op.epi;
     P.B = op.B; P.N = op.N; P.H = op.H; P.W = op.W; P.Ci = op.Ci; P.Co = op.Co; P.taps = op.taps;
+    P.co_split = 1;
     P.mode = (op.taps == 27 && op.H >= 16 && op.W >= 8) ? 1 : 0;
     cuuint32_t boxA[5];
     if (P.mode) {
@@ -928,7 +1010,10 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.TW = 8; P.TH = 16; P.TN = 1; P.TB = 1;
         // accumulators per tile: two sets must fit the 512 TMEM columns, the haloed box must leave room for
         // two stages in shared memory, and NACC divides the band count (no plane is computed for nothing)
-        int cap = 256 / op.Co;
+        // Co = 256: a tile computes half of the output channels for two band planes instead of all of them for one, so a
+        // weight stage (the dominant L2 -> shared-memory stream of these layers) feeds twice the MMA work
+        if (op.Co == 256 && op.N % 2 == 0 && env_int("TMD_UMMA_COSPLIT", 1)) { P.co_split = 2; P.Co = 128; }
+        int cap = 256 / P.Co;
         if (cap > 8) cap = 8;
         P.NACC = 1;
         for (int c = 2; c <= cap; c *= 2)
@@ -955,7 +1040,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.tiles_x = (op.W + P.TW - 1) / P.TW;
     P.tiles_y = (op.H + P.TH - 1) / P.TH;
     P.tiles_b = (op.B + P.TB - 1) / P.TB;
-    P.num_tiles = P.tiles_x * P.tiles_y * P.tiles_n * P.tiles_b;
+    P.num_tiles = P.tiles_x * P.tiles_y * P.tiles_n * P.tiles_b * P.co_split;
     P.row_bytes = P.KC * 2;
     P.layout_type = P.KC == 64 ? 2u : 4u;           // SWIZZLE_128B : SWIZZLE_64B
     P.sbo16 = (8 * P.row_bytes) >> 4;               // 8-row swizzle atoms are contiguous
@@ -964,19 +1049,19 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.dbg = env_int("TMD_UMMA_DEBUG", 0);
     P.epi.dbg = P.dbg;
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
-    P.b_tile_bytes = op.Co * P.row_bytes;
+    P.b_tile_bytes = P.Co * P.row_bytes;
     // REUSE: a weight stage holds the 3 dz taps of b_taps (dy,dx) taps.  Small Co: three taps per stage, so that a stage
     // carries enough MMA work to hide the issue warp's per-stage wait / commit round.
     P.b_taps = 1;
     if (P.mode) {
-        P.b_taps = env_int("TMD_UMMA_BTAPS", op.Co <= 64 ? 3 : 1);
+        P.b_taps = env_int("TMD_UMMA_BTAPS", P.Co <= 64 ? 3 : 1);
         if (P.b_taps != 1 && P.b_taps != 3 && P.b_taps != 9) P.b_taps = 1;
     }
-    int cols = 2 * P.NACC * op.Co;
+    int cols = 2 * P.NACC * P.Co;
     P.tmem_cols = 32;
     while ((int)P.tmem_cols < cols) P.tmem_cols *= 2;
     // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
-    P.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(op.Co >> 3) << 17) | ((128u >> 4) << 24);
+    P.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(P.Co >> 3) << 17) | ((128u >> 4) << 24);
 
     // ring depths from the shared-memory budget
     const size_t budget = 215 * 1024;              // 227 KB less the kernel's static shared memory (barriers, epilogue vectors)
@@ -1011,7 +1096,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     {   // weights [Co][taps*Ci] bf16
         cuuint64_t dims[2] = {(cuuint64_t)op.taps * op.Ci, (cuuint64_t)op.Co};
         cuuint64_t strides[1] = {2ull * op.taps * op.Ci};
-        cuuint32_t box[2] = {(cuuint32_t)P.KC, (cuuint32_t)op.Co};
+        cuuint32_t box[2] = {(cuuint32_t)P.KC, (cuuint32_t)P.Co};
         cuuint32_t estr[2] = {1, 1};
         if (enc(&P.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(op.w_bf16), dims, strides, box, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
@@ -1030,7 +1115,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         cuuint32_t estr[5] = {1, 1, 1, 1, 1};
         cuuint64_t dimsB[2] = {(cuuint64_t)op.Ci2, (cuuint64_t)op.Co};
         cuuint64_t stridesB[1] = {2ull * op.Ci2};
-        cuuint32_t boxB[2] = {(cuuint32_t)P.KC, (cuuint32_t)op.Co};
+        cuuint32_t boxB[2] = {(cuuint32_t)P.KC, (cuuint32_t)P.Co};
         if (enc(&P.tmA2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(op.src2), dims, strides, box2, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS ||
             enc(&P.tmB2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(op.w2_bf16), dimsB, stridesB, boxB, estr,
