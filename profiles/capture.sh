@@ -19,4 +19,6 @@ timeout 1500 ncu --set full --clock-control none --import-source on -k regex:con
 timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:conv_umma --launch-skip 60 -c 38 --csv \
   --log-file gpurun_out/conv_traffic_$tag.csv python profiles/_one_eval.py 64 > gpurun_out/ncu_traffic_$tag.log 2>&1; echo "ncu traffic exit $?"
 ncu -i gpurun_out/conv_umma_$tag.ncu-rep --page raw --csv > gpurun_out/conv_umma_${tag}_raw.csv 2>/dev/null
-ls -la gpurun_out
+# the report itself is scratch (the raw CSV above is what gets summarised); keep the merge-back under its size limit
+rm -f gpurun_out/conv_umma_$tag.ncu-rep
+ls -la gpurun_out | tail -20

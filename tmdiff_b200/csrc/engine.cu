@@ -1177,9 +1177,45 @@ extern "C" int tmd_attention(const float* q, const float* k, const float* v, flo
     return 0;
 }
 
+namespace {
+// experts' k^ndim taps scattered into the centre of the k^3 layout the convolution operators take (zero elsewhere)
+__global__ void embed_taps_kernel(const float* __restrict__ w, float* __restrict__ out, size_t rows, int k, int ndim) {
+    const int st = ndim == 1 ? k : k * k, dt = k * k * k;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * (size_t)dt) return;
+    const size_t r = i / dt;
+    const int t = (int)(i - r * dt), dz = t / (k * k), dy = (t / k) % k, dx = t % k, c = k / 2;
+    float v = 0.f;
+    if (ndim == 2) { if (dz == c) v = w[r * st + dy * k + dx]; }
+    else if (dz == c && dy == c) v = w[r * st + dx];
+    out[i] = v;
+}
+}  // namespace
+
+static int dynamic_conv_impl(const char* who, const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                             const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                             int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream);
+
 extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2, float* y,
                                   int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K,
                                   int32_t hidden, float temperature, int32_t dtype, void* stream) {
+    return dynamic_conv_impl("tmd_dynamic_conv3d", x, weight, bias, fc1, fc2, nullptr, y, B, Ci, Co, N, H, W, k, 3, K, hidden, temperature, dtype,
+                             stream);
+}
+
+extern "C" int tmd_dynamic_conv(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                                const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                                int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream) {
+    if (ndim < 1 || ndim > 3) return fail("tmd_dynamic_conv: ndim must be 1, 2 or 3");
+    if ((ndim < 3 && N != 1) || (ndim < 2 && H != 1)) return fail("tmd_dynamic_conv: unused leading extents must be 1");
+    return dynamic_conv_impl("tmd_dynamic_conv", x, weight, bias, fc1, fc2, fc2_bias, y, B, Ci, Co, N, H, W, k, ndim, K, hidden, temperature, dtype,
+                             stream);
+}
+
+static int dynamic_conv_impl(const char* who, const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                             const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                             int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream) {
+    (void)who;
     if (!x || !weight || !fc1 || !fc2 || !y) return fail("tmd_dynamic_conv3d: null argument");
     if (k != 1 && k != 3) return fail("tmd_dynamic_conv3d: kernel size must be 1 or 3");
     if (Ci % 4 || Co % 4) return fail("tmd_dynamic_conv3d: Ci and Co must be multiples of 4");
@@ -1190,7 +1226,7 @@ extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const flo
     const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
     const int taps = k * k * k;
     const size_t wn = (size_t)Co * Ci * taps;
-    float *pooled = nullptr, *hid = nullptr, *alpha = nullptr, *aw = nullptr, *ab = nullptr, *pf = nullptr;
+    float *pooled = nullptr, *hid = nullptr, *alpha = nullptr, *aw = nullptr, *ab = nullptr, *pf = nullptr, *wemb = nullptr;
     __nv_bfloat16* pb = nullptr;
     void *xin = nullptr, *yout = nullptr;
     CK(cudaMallocAsync((void**)&pooled, (size_t)B * Ci * 4, s));
@@ -1205,9 +1241,16 @@ extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const flo
     // attention3d (:194-218): avgpool -> fc1 -> relu -> fc2 -> softmax(. / temperature)
     CK(spatial_mean(x, pooled, (size_t)B * Ci, nhw, s));
     CK(dense_rows(pooled, fc1, nullptr, hid, B, Ci, hidden, 2, s));
-    CK(dense_rows(hid, fc2, nullptr, alpha, B, hidden, K, 0, s));
+    CK(dense_rows(hid, fc2, fc2_bias, alpha, B, hidden, K, 0, s));          // attention1d / attention2d carry a bias here (:18, :108)
     CK(softmax_temperature(alpha, B, K, temperature, s));
     // aggregate_weight / aggregate_bias (:251-257)
+    if (ndim < 3 && k > 1) {
+        CK(cudaMallocAsync((void**)&wemb, (size_t)K * wn * 4, s));
+        const size_t tot = (size_t)K * wn;
+        embed_taps_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(weight, wemb, (size_t)K * Co * Ci, k, ndim);
+        CK(cudaGetLastError());
+        weight = wemb;
+    }
     CK(mix_experts(alpha, weight, aw, B, K, wn, s));
     if (bias) CK(mix_experts(alpha, bias, ab, B, K, (size_t)Co, s));
     CK(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s));
@@ -1237,6 +1280,7 @@ extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const flo
     }
     if (!rc) CK(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s));
     for (void* p : {(void*)pooled, (void*)hid, (void*)alpha, (void*)aw, (void*)ab, (void*)pf, (void*)pb, xin, yout}) cudaFreeAsync(p, s);
+    if (wemb) cudaFreeAsync(wemb, s);
     return rc;
 }
 
@@ -1246,5 +1290,41 @@ extern "C" int tmd_quality_metrics(const float* ref, const float* img, float* ou
     if (B <= 0 || C <= 0 || C > 8 || H <= 0 || W <= 0) return fail("tmd_quality_metrics: need 1..8 bands and a non-empty image");
     const cudaError_t err = quality_metrics(ref, img, out, B, C, H * W, ratio, (cudaStream_t)stream);
     if (err != cudaSuccess) return fail("tmd_quality_metrics: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_layernorm(const float* x, float* y, const float* gamma, const float* beta, int32_t rows, int32_t C, float eps, void* stream) {
+    if (!x || !y) return fail("tmd_layernorm: null argument");
+    if (rows <= 0 || C <= 0) return fail("tmd_layernorm: empty problem");
+    const cudaError_t err = layernorm_rows(x, y, gamma, beta, rows, C, eps, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_layernorm: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_geglu(const float* proj, float* out, int64_t rows, int32_t D, void* stream) {
+    if (!proj || !out) return fail("tmd_geglu: null argument");
+    if (rows <= 0 || D <= 0 || D % 4) return fail("tmd_geglu: D must be a positive multiple of 4");
+    const cudaError_t err = geglu_rows(proj, out, (size_t)rows, D, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_geglu: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_band_moments(const float* a, const float* b, float* out, int32_t B, int32_t Ca, int32_t Cb, int32_t H, int32_t W,
+                                int32_t highpass, void* stream) {
+    if (!a || !b || !out) return fail("tmd_band_moments: null argument");
+    if (B <= 0 || Ca < 1 || Cb < 1 || Ca > 8 || Cb > 8 || H <= 0 || W <= 0) return fail("tmd_band_moments: need 1..8 bands per image and a non-empty image");
+    if (highpass && (H < 3 || W < 3)) return fail("tmd_band_moments: the 3x3 high-pass needs H, W >= 3");
+    const cudaError_t err = band_moments(a, b, out, B, Ca, Cb, H, W, highpass != 0, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_band_moments: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_psf_downsample(const float* x, float* y, const float* param, float* psf_out, int32_t mode, int32_t B, int32_t C, int32_t H,
+                                  int32_t W, int32_t k, int32_t scale, void* stream) {
+    if (!x || !y || !param) return fail("tmd_psf_downsample: null argument");
+    if (mode != 0 && mode != 1) return fail("tmd_psf_downsample: mode 0 (softmax PSF) or 1 (Gaussian)");
+    if (B <= 0 || C <= 0 || k < 1 || k > 16 || scale < 1 || H < k || W < k) return fail("tmd_psf_downsample: need 1 <= k <= 16, scale >= 1 and an image no smaller than the kernel");
+    const cudaError_t err = psf_downsample(x, y, param, psf_out, mode, B * C, H, W, k, scale, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_psf_downsample: %s", cudaGetErrorString(err));
     return 0;
 }

@@ -80,4 +80,16 @@ cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cuda
 cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cudaStream_t s);                      // in place over K
 cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, int K, size_t n, cudaStream_t s);    // out[b,:] = sum_k alpha[b,k] w[k,:]
 
+
+// ---- operators2.cu ----
+// nn.LayerNorm(C, eps) over the rows of x [rows, C]; gamma / beta may be null
+cudaError_t layernorm_rows(const float* x, float* y, const float* gamma, const float* beta, int rows, int C, float eps, cudaStream_t s);
+// out[r, j] = p[r, j] * gelu(p[r, D + j]),  p [rows, 2D]  (GEGLU, core/Attention.py:69-76)
+cudaError_t geglu_rows(const float* p, float* out, size_t rows, int D, cudaStream_t s);
+// per image: [sum a_i | sum a_i^2 | sum b_j | sum b_j^2 | sum a_i b_j | count], optionally after the 3x3 high-pass of sobel_torch
+cudaError_t band_moments(const float* a, const float* b, float* out, int B, int Ca, int Cb, int H, int W, bool highpass, cudaStream_t s);
+// learned-PSF blur + every scale-th output (core/kernelAdaption.py:117-180); mode 0 softmax PSF, 1 Gaussian from a 2x2 parameter
+cudaError_t psf_downsample(const float* in, float* out, const float* param, float* psf_out, int mode, int planes, int H, int W, int k, int scale,
+                           cudaStream_t s);
+
 }  // namespace tmd
