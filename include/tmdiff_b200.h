@@ -171,6 +171,30 @@ int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, c
 int tmd_quality_metrics(const float* ref, const float* img, float* out, int32_t B, int32_t C, int32_t H, int32_t W, float ratio,
                         void* stream);
 
+/* Dynamic_conv1d / Dynamic_conv2d / Dynamic_conv3d.forward in one entry (core/dynamic_conv.py:45-104, 140-190, 221-268): ndim = 1, 2
+ * or 3 trailing dims carry the k^ndim kernel (x viewed as [B,Ci,N,H,W] with the unused leading extents = 1, weight
+ * [K,Co,Ci,k^ndim]); fc2_bias [K] is the bias attention1d / attention2d put on fc2 (:18, :108; attention3d has none -> NULL). */
+int tmd_dynamic_conv(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                     const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                     int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream);
+/* torch.nn.LayerNorm(C, eps) over the rows of x [rows, C] (BasicTransformerBlock.norm1-3, core/Attention.py:282-284);
+ * gamma / beta [C] or NULL. */
+int tmd_layernorm(const float* x, float* y, const float* gamma, const float* beta, int32_t rows, int32_t C, float eps, void* stream);
+/* GEGLU gate (core/Attention.py:69-76): out[r, j] = proj[r, j] * gelu(proj[r, D + j]), proj [rows, 2D] (exact erf GELU). */
+int tmd_geglu(const float* proj, float* out, int64_t rows, int32_t D, void* stream);
+/* Band-pair moments of image pairs, one fused reduction per image: a [B,Ca,H,W], b [B,Cb,H,W] (Ca, Cb <= 8) ->
+ * out [B, 2Ca + 2Cb + Ca*Cb + 1] = [sum a_i | sum a_i^2 | sum b_j | sum b_j^2 | sum a_i*b_j (i major) | pixel count].
+ * highpass != 0: both images first go through the 3x3 filter of sobel_torch (core/metrics.py:411-422; valid region).
+ * Everything QIndex_torch / D_lambda_torch / D_s_torch / SCC_torch (:425-503) and cc (utils/util.py:375-386) need. */
+int tmd_band_moments(const float* a, const float* b, float* out, int32_t B, int32_t Ca, int32_t Cb, int32_t H, int32_t W,
+                     int32_t highpass, void* stream);
+/* EntireKernel / GaussianKernel.forward (core/kernelAdaption.py:117-180): depthwise valid cross-correlation of x [B,C,H,W]
+ * with one learned k x k PSF, keeping every scale-th output -> y [B,C,(H-k)/scale+1,(W-k)/scale+1].  mode 0: PSF =
+ * softmax(param[k*k]) (EntireKernel, k = scale_factor); mode 1: the Gaussian of kernel_generator (:12-47, shift 'center')
+ * from the 2x2 parameter param[4].  psf_out [k*k] (or NULL) receives the PSF (the reference keeps it as self.psf). */
+int tmd_psf_downsample(const float* x, float* y, const float* param, float* psf_out, int32_t mode, int32_t B, int32_t C, int32_t H,
+                       int32_t W, int32_t k, int32_t scale, void* stream);
+
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);
 

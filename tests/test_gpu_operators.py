@@ -97,3 +97,90 @@ def test_attention_core(BH, Lq, Lk, D):
     assert float((attention(q, k, ones, scale) - 1).abs().max()) < 1e-5
     with pytest.raises(RuntimeError):
         attention(q[:, :, :4].contiguous().repeat(1, 1, 1024), k[:, :, :4].contiguous().repeat(1, 1, 1024), v[:, :, :4].contiguous().repeat(1, 1, 1024), 1.0)
+
+
+# ---- second batch: BasicTransformerBlock / SpatialTransformer, Dynamic_conv1d/2d, learned-PSF kernels, torch metrics
+# (tests/golden/make_golden_operators2.py) ----
+@pytest.fixture(scope="module")
+def vec2():
+    return np.load(os.path.join(ROOT, "tests", "golden", "operator_vectors2.npz"))
+
+
+def _build2(tag, dtype="fp32"):
+    from tmdiff_b200 import operators as O
+    return {"btb": lambda: O.BasicTransformerBlock(64, 4, 16, context_dim=96, checkpoint=False, dtype=dtype),
+            "st": lambda: O.SpatialTransformer(64, 4, 16, depth=2, context_dim=[96, 96], use_checkpoint=False, dtype=dtype),
+            "dyn2d": lambda: O.Dynamic_conv2d(16, 32, 3, padding=1, K=4, temperature=34, dtype=dtype),
+            "dyn1d": lambda: O.Dynamic_conv1d(16, 32, 3, padding=1, K=4, temperature=34, dtype=dtype),
+            "psf_entire": lambda: O.EntireKernel(kernel_size=4, bands=4, scale_factor=4),
+            "psf_gauss": lambda: O.GaussianKernel(kernel_size=5, bands=4, scale_factor=4)}[tag]()
+
+
+@pytest.mark.parametrize("tag", ["btb", "st", "dyn2d", "dyn1d", "psf_entire", "psf_gauss"])
+def test_state_dict_keys_match_reference_2(vec2, tag):
+    m = _build2(tag)
+    ref = _sd(vec2, tag)
+    mine = m.state_dict()
+    assert set(mine) == set(ref)
+    assert all(tuple(mine[k].shape) == tuple(ref[k].shape) for k in ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,dtype,tol", [("btb", "fp32", FP32_TOL), ("btb", "bf16", BF16_TOL), ("st", "fp32", FP32_TOL), ("st", "bf16", BF16_TOL),
+                                           ("dyn2d", "fp32", FP32_TOL), ("dyn2d", "bf16", BF16_TOL), ("dyn1d", "fp32", FP32_TOL),
+                                           ("psf_entire", "fp32", FP32_TOL), ("psf_gauss", "fp32", FP32_TOL)])
+def test_operator_against_reference_2(vec2, tag, dtype, tol):
+    m = _build2(tag, dtype)
+    m.load_state_dict(_sd(vec2, tag), strict=True)
+    m = m.cuda()
+    x = _inp(vec2, tag, "x")
+    if tag == "btb":
+        got = m(x, context=_inp(vec2, tag, "context"))
+    elif tag == "st":
+        got = m(x, context=[_inp(vec2, tag, "context"), _inp(vec2, tag, "context2")])
+    else:
+        got = m(x)
+    ref = torch.from_numpy(vec2[tag + "/out"])
+    assert got.shape == ref.shape
+    assert rel_l2(got, ref) < tol
+    if tag == "psf_entire":
+        assert rel_l2(m.psf, torch.from_numpy(vec2["psf_entire/psf"])) < FP32_TOL
+    if tag == "psf_gauss":
+        assert rel_l2(m.KernelAdaption[0, 0], torch.from_numpy(vec2["psf_gauss/psf"])) < FP32_TOL
+
+
+@pytest.mark.gpu
+def test_layer_norm_and_geglu_against_torch():
+    """plain fp32 torch references of the two row kernels, including widths off the vector path and rows that do not fill a block"""
+    from tmdiff_b200.operators import geglu, layer_norm
+    g = torch.Generator().manual_seed(5)
+    for rows, C in [(7, 64), (300, 320), (33, 1024), (5, 1280), (9, 30)]:
+        x = (torch.randn(rows, C, generator=g) * 3 + 1).cuda()
+        w, b = torch.randn(C, generator=g).cuda(), torch.randn(C, generator=g).cuda()
+        ref = torch.nn.functional.layer_norm(x, (C,), w, b, 1e-5)
+        assert rel_l2(layer_norm(x, w, b, 1e-5), ref) < FP32_TOL
+    assert rel_l2(layer_norm(x), torch.nn.functional.layer_norm(x, (C,))) < FP32_TOL
+    for rows, D in [(3, 64), (77, 256), (1000, 1280)]:
+        p = torch.randn(rows, 2 * D, generator=g).cuda()
+        a, gate = p.chunk(2, dim=-1)
+        assert rel_l2(geglu(p), a * torch.nn.functional.gelu(gate)) < FP32_TOL
+
+
+@pytest.mark.gpu
+def test_torch_metrics_match_reference(vec2):
+    """QIndex_torch / D_lambda_torch / D_s_torch / SCC_torch / cc on the device against the reference's values (north star: 0.5 %)."""
+    from tmdiff_b200 import metrics as M
+    t = {k: torch.from_numpy(vec2["metrics/in/" + k]).cuda() for k in ("ps", "lms", "pan", "lpan", "gt")}
+    close = lambda got, key: np.testing.assert_allclose(got.cpu().numpy(), vec2["metrics/" + key], rtol=5e-3, atol=1e-5)
+    close(M.QIndex_torch(t["ps"][:, 0], t["gt"][:, 0]), "QIndex")
+    close(M.D_lambda_torch(t["lms"], t["ps"]), "D_lambda")
+    close(M.D_s_torch(t["lms"], t["pan"], t["lpan"], t["ps"]), "D_s")
+    close(M.cc(t["ps"], t["gt"]), "cc")
+    np.testing.assert_allclose(np.array([float(M.SCC_torch(t["gt"][:, c:c + 1], t["ps"][:, c:c + 1])) for c in range(4)]), vec2["metrics/SCC"], rtol=5e-3)
+    np.testing.assert_allclose(float(M.SCC_torch(t["gt"], t["ps"])), float(vec2["metrics/SCC"].mean()), rtol=5e-3)
+    # full-size property: a fused image against itself is perfect (Q = 1, SCC = 1, cc = 1, D_lambda of identical inputs = 0)
+    big = torch.rand(8, 8, 256, 256, generator=torch.Generator().manual_seed(1)).cuda()
+    assert abs(float(M.SCC_torch(big, big)) - 1) < 1e-5 and float((M.cc(big, big) - 1).abs().max()) < 1e-5
+    assert float(M.D_lambda_torch(big, big)) < 1e-6
+    q = M.q_index_matrix(big, big)
+    assert float((q.diagonal(dim1=1, dim2=2) - 1).abs().max()) < 1e-4

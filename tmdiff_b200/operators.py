@@ -5,7 +5,9 @@ the reference's class names, constructor arguments and state-dict keys, backed b
     AttnBlockpp, NIN        GeneralModel/Hyper_unet_general.py:471-515
     SpatialSelfAttention    core/Attention.py:112-162
     CrossAttention          core/Attention.py:165-214
-    Dynamic_conv3d          core/dynamic_conv.py:194-268
+    Dynamic_conv1d/2d/3d    core/dynamic_conv.py:45-104, 140-190, 221-268
+    GEGLU, FeedForward, BasicTransformerBlock, SpatialTransformer     core/Attention.py:69-96, 266-362
+    EntireKernel, GaussianKernel                                      core/kernelAdaption.py:117-180
 
 Normalisation, the softmax-attention core and the expert mixing are hand-written kernels (csrc/operators.cu); the
 1x1 projections run through the library's convolution operator (tcgen05 in bf16 mode, fp32 CUDA cores otherwise).
@@ -196,3 +198,208 @@ class Dynamic_conv3d(nn.Module):
                                                       float(self.attention.temperature), _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16,
                                                       _lib.stream_ptr()))
         return y
+
+
+class _DynamicConvNd(nn.Module):
+    """Dynamic_conv1d / Dynamic_conv2d (core/dynamic_conv.py:45-104, 140-190): same expert mixing as the 3-D layer; their
+    attention carries a bias on fc2 (:18, :108)."""
+    ndim = 2
+
+    def __init__(self, in_planes, out_planes, kernel_size, ratio=0.25, stride=1, padding=0, dilation=1, groups=1, bias=True, K=4,
+                 temperature=34, dtype="fp32"):
+        super().__init__()
+        assert in_planes % groups == 0 and temperature % 3 == 1
+        if groups != 1 or stride != 1 or dilation != 1 or kernel_size not in (1, 3) or padding != kernel_size // 2:
+            raise ValueError("Dynamic_conv: groups=1, stride=1, dilation=1 and 'same' padding with k in {1,3} are implemented")
+        conv = nn.Conv1d if self.ndim == 1 else nn.Conv2d
+        hidden = int(in_planes * ratio) + 1 if in_planes != 3 else K
+        self.in_planes, self.out_planes, self.kernel_size, self.K, self.compute_dtype = in_planes, out_planes, kernel_size, K, dtype
+        self.attention = nn.Module()
+        self.attention.fc1 = conv(in_planes, hidden, 1, bias=False)
+        self.attention.fc2 = conv(hidden, K, 1, bias=True)
+        self.attention.temperature = temperature
+        self.weight = nn.Parameter(torch.randn(K, out_planes, in_planes // groups, *([kernel_size] * self.ndim)), requires_grad=False)
+        self.bias = nn.Parameter(torch.zeros(K, out_planes), requires_grad=False) if bias else None
+
+    @torch.no_grad()
+    def forward(self, x):
+        x = _cuda_f32(x, "x")
+        B, Ci = x.shape[:2]
+        sp = [1] * (3 - self.ndim) + list(x.shape[2:])
+        hidden = self.attention.fc1.weight.shape[0]
+        y = torch.empty(B, self.out_planes, *x.shape[2:], device=x.device)
+        w = _cuda_f32(self.weight, "weight")
+        b = None if self.bias is None else _cuda_f32(self.bias, "bias")
+        f1 = _cuda_f32(self.attention.fc1.weight, "fc1").reshape(hidden, Ci)
+        f2 = _cuda_f32(self.attention.fc2.weight, "fc2").reshape(self.K, hidden)
+        f2b = _cuda_f32(self.attention.fc2.bias, "fc2.bias")
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.load().tmd_dynamic_conv(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), _lib.ptr(f2b), _lib.ptr(y),
+                                                    B, Ci, self.out_planes, sp[0], sp[1], sp[2], self.kernel_size, self.ndim, self.K, hidden,
+                                                    float(self.attention.temperature), _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16,
+                                                    _lib.stream_ptr()))
+        return y
+
+
+class Dynamic_conv1d(_DynamicConvNd):
+    ndim = 1
+
+
+class Dynamic_conv2d(_DynamicConvNd):
+    ndim = 2
+
+
+def layer_norm(x, weight=None, bias=None, eps=1e-5):
+    """F.layer_norm over the last dim of x [..., C]."""
+    x = _cuda_f32(x, "x")
+    Cc = x.shape[-1]
+    y = torch.empty_like(x)
+    w = None if weight is None else _cuda_f32(weight, "weight")
+    b = None if bias is None else _cuda_f32(bias, "bias")
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().tmd_layernorm(_lib.ptr(x), _lib.ptr(y), _lib.ptr(w), _lib.ptr(b), x.numel() // Cc, Cc, float(eps), _lib.stream_ptr()))
+    return y
+
+
+def geglu(proj):
+    """proj [..., 2D] -> proj[..., :D] * gelu(proj[..., D:])."""
+    proj = _cuda_f32(proj, "proj")
+    D = proj.shape[-1] // 2
+    out = torch.empty(*proj.shape[:-1], D, device=proj.device)
+    with torch.cuda.device(proj.device):
+        _lib.check(_lib.load().tmd_geglu(_lib.ptr(proj), _lib.ptr(out), proj.numel() // (2 * D), D, _lib.stream_ptr()))
+    return out
+
+
+class GEGLU(nn.Module):
+    def __init__(self, dim_in, dim_out, dtype="fp32"):
+        super().__init__()
+        self.proj, self.compute_dtype = nn.Linear(dim_in, dim_out * 2), dtype
+
+    @torch.no_grad()
+    def forward(self, x):
+        return geglu(_linear_tokens(x, self.proj.weight, self.proj.bias, self.compute_dtype))
+
+
+class FeedForward(nn.Module):
+    def __init__(self, dim, dim_out=None, mult=4, glu=False, dropout=0.0, dtype="fp32"):
+        super().__init__()
+        if not glu:
+            raise NotImplementedError("the reference only builds the gated feed-forward (BasicTransformerBlock gated_ff=True)")
+        inner = int(dim * mult)
+        self.compute_dtype = dtype
+        self.net = nn.Sequential(GEGLU(dim, inner, dtype), nn.Dropout(dropout), nn.Linear(inner, dim if dim_out is None else dim_out))
+
+    @torch.no_grad()
+    def forward(self, x):
+        return _linear_tokens(self.net[0](x), self.net[2].weight, self.net[2].bias, self.compute_dtype)
+
+
+class BasicTransformerBlock(nn.Module):
+    def __init__(self, dim, n_heads, d_head, dropout=0.0, context_dim=None, gated_ff=True, checkpoint=True, disable_self_attn=False,
+                 dtype="fp32"):
+        super().__init__()
+        self.disable_self_attn = disable_self_attn
+        self.attn1 = CrossAttention(query_dim=dim, heads=n_heads, dim_head=d_head, dropout=dropout,
+                                    context_dim=context_dim if disable_self_attn else None, dtype=dtype)
+        self.ff = FeedForward(dim, dropout=dropout, glu=gated_ff, dtype=dtype)
+        self.attn2 = CrossAttention(query_dim=dim, context_dim=context_dim, heads=n_heads, dim_head=d_head, dropout=dropout, dtype=dtype)
+        self.norm1, self.norm2, self.norm3 = nn.LayerNorm(dim), nn.LayerNorm(dim), nn.LayerNorm(dim)
+
+    @torch.no_grad()
+    def forward(self, x, context=None):
+        ln = lambda n, t: layer_norm(t, n.weight, n.bias, n.eps)
+        x = self.attn1(ln(self.norm1, x), context=context if self.disable_self_attn else None) + x
+        x = self.attn2(ln(self.norm2, x), context=context) + x
+        return self.ff(ln(self.norm3, x)) + x
+
+
+class SpatialTransformer(nn.Module):
+    def __init__(self, in_channels, n_heads, d_head, depth=1, dropout=0.0, context_dim=None, disable_self_attn=False, use_linear=False,
+                 use_checkpoint=True, dtype="fp32"):
+        super().__init__()
+        if context_dim is not None and not isinstance(context_dim, list):
+            context_dim = [context_dim]
+        if context_dim is None:
+            context_dim = [None] * depth
+        if use_linear:
+            raise NotImplementedError("use_linear=True: the reference's proj_out has mismatched dimensions there (core/Attention.py:340)")
+        inner = n_heads * d_head
+        self.in_channels, self.compute_dtype = in_channels, dtype
+        self.norm = nn.GroupNorm(num_groups=32, num_channels=in_channels, eps=1e-6, affine=True)
+        self.proj_in = nn.Conv2d(in_channels, inner, 1)
+        self.transformer_blocks = nn.ModuleList([BasicTransformerBlock(inner, n_heads, d_head, dropout=dropout, context_dim=context_dim[d],
+                                                                       disable_self_attn=disable_self_attn, dtype=dtype) for d in range(depth)])
+        self.proj_out = nn.Conv2d(inner, in_channels, 1)
+        nn.init.zeros_(self.proj_out.weight)
+        nn.init.zeros_(self.proj_out.bias)
+
+    @torch.no_grad()
+    def forward(self, x, context=None):
+        if not isinstance(context, list):
+            context = [context]
+        B, Cc, H, W = x.shape
+        inner = self.proj_in.weight.shape[0]
+        h = group_norm(x, 32, self.norm.weight, self.norm.bias, eps=1e-6)
+        h = _conv1x1(h, self.proj_in.weight.reshape(inner, Cc), self.proj_in.bias, self.compute_dtype)
+        h = h.reshape(B, inner, H * W).transpose(1, 2).contiguous()
+        for i, blk in enumerate(self.transformer_blocks):
+            h = blk(h, context=context[i])
+        h = h.transpose(1, 2).reshape(B, inner, H, W).contiguous()
+        return _conv1x1(h, self.proj_out.weight.reshape(Cc, inner), self.proj_out.bias, self.compute_dtype) + x
+
+
+class _PSFKernel(nn.Module):
+    """Depthwise learned-PSF blur + every scale_factor-th output (core/kernelAdaption.py:117-180) as one kernel: the PSF is built
+    from the parameter inside the kernel and only the kept outputs are computed."""
+    mode = 0
+
+    def __init__(self, kernel_size, bands, scale_factor):
+        super().__init__()
+        self.kernel_size, self.bands, self.scale_factor = kernel_size, bands, scale_factor
+        self.psf = None
+
+    def _run(self, Z, param, k):
+        Z = _cuda_f32(Z, "Z")
+        B, Cc, H, W = Z.shape
+        s = self.scale_factor
+        out = torch.empty(B, Cc, (H - k) // s + 1, (W - k) // s + 1, device=Z.device)
+        psf = torch.empty(k, k, device=Z.device)
+        p = _cuda_f32(param, "param")
+        with torch.cuda.device(Z.device):
+            _lib.check(_lib.load().tmd_psf_downsample(_lib.ptr(Z), _lib.ptr(out), _lib.ptr(p), _lib.ptr(psf), self.mode, B, Cc, H, W, k, s,
+                                                      _lib.stream_ptr()))
+        return out, psf
+
+
+class EntireKernel(_PSFKernel):
+    mode = 0
+
+    def __init__(self, kernel_size, bands, scale_factor):
+        super().__init__(kernel_size, bands, scale_factor)
+        self.KernelAdaption = nn.Parameter(torch.randn(scale_factor, scale_factor), requires_grad=False)
+
+    @torch.no_grad()
+    def forward(self, Z):
+        out, self.psf = self._run(Z, self.KernelAdaption, self.scale_factor)      # the PSF is scale_factor x scale_factor (:134)
+        return out
+
+
+class GaussianKernel(_PSFKernel):
+    mode = 1
+
+    def __init__(self, kernel_size, bands, scale_factor):
+        super().__init__(kernel_size, bands, scale_factor)
+        self.KernelParam = nn.Parameter(5 * torch.eye(2, 2), requires_grad=False)
+
+    def re_init(self):
+        self.KernelParam = nn.Parameter(5 * torch.eye(2, 2), requires_grad=False)
+
+    @torch.no_grad()
+    def forward(self, Z):
+        out, psf = self._run(Z, self.KernelParam, self.kernel_size)
+        self.KernelAdaption = psf[None, None]
+        return out
+
+
+GaussianKernel_new = GaussianKernel
