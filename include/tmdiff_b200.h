@@ -130,6 +130,14 @@ int tmd_denoise(tmd_handle h, const float* x_t_dev, const float* t_input_dev, fl
 int tmd_sample(tmd_handle h, const float* x_T_dev, const tmd_plan* plan, float* out_dev, float* trace_dev,
                void* stream);
 
+/* One ancestral DDPM step after the denoiser call (GeneralDiffusion.p_sample, GeneralModel/diffusion_general.py:134-138,
+ * 155-174, 196-201): x0 = c_recip*x - c_recipm1*eps, clamped to [-1,1] when clip; out = coef1*x0 + coef2*x + sigma*z.
+ * noise (device, [n]) is the caller's z (the reference's torch.randn_like), or NULL: Philox4x32-10 normals are drawn inside the
+ * kernel from (seed, step) and never touch HBM.  sigma = 0 on the last step (t = 0).  x, eps, out: device fp32 [n]; out may
+ * alias x. */
+int tmd_ancestral_update(const float* x, const float* eps, const float* noise, float* out, float c_recip, float c_recipm1,
+                         float coef1, float coef2, float sigma, int32_t clip, uint64_t seed, uint64_t step, int64_t n, void* stream);
+
 /* ---- stand-alone operators (parity tests, per-operator sweep) -------------------------------- */
 /* DWT_2D("haar").forward (DWT_IDWT/DWT_IDWT_layer.py:321-334): x [B,C,H,W] -> 4 x [B,C,H/2,W/2].
  * lh/hl/hh may be NULL (LL-only variant). */

@@ -58,6 +58,22 @@ def main():
     for B in (16, 64, 256):
         x0 = torch.randn(B, 4, 64, 64, device="cuda") * 1.2
         row("dynamic_thresholding", tuple(x0.shape), timed(lambda: ops.dynamic_thresholding(x0)), 2 * x0.numel() * 4)
+    from tmdiff_b200 import metrics
+    for (rows, C) in ((64 * 4096, 64), (64 * 1024, 320), (16 * 4096, 512), (64 * 256, 1280)):
+        x, w, b = torch.randn(rows, C, device="cuda"), torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
+        row("LayerNorm", (rows, C), timed(lambda: operators.layer_norm(x, w, b)), 2 * x.numel() * 4)
+        p = torch.randn(rows, 2 * C, device="cuda")
+        row("GEGLU gate", (rows, 2 * C), timed(lambda: operators.geglu(p)), 1.5 * p.numel() * 4)
+    for B in (16, 64, 256):
+        a, b = torch.rand(B, 4, 256, 256, device="cuda"), torch.rand(B, 4, 256, 256, device="cuda")
+        row("band moments (4x4 pairs)", tuple(a.shape), timed(lambda: metrics.band_moments(a, b)), 2 * a.numel() * 4)
+        row("band moments + 3x3 high-pass", tuple(a.shape), timed(lambda: metrics.band_moments(a, b, highpass=True)), 2 * a.numel() * 4)
+        row("quality_metrics (SAM/ERGAS/Q)", tuple(a.shape), timed(lambda: ops.quality_metrics(a, b)), 2 * a.numel() * 4)
+        blur = operators.GaussianKernel(kernel_size=8, bands=4, scale_factor=4).cuda()
+        row("Gaussian PSF blur /4", tuple(a.shape), timed(lambda: blur(a)), (1 + 1 / 16) * a.numel() * 4)
+        e = torch.randn_like(a)
+        row("ancestral step (Philox in kernel)", tuple(a.shape), timed(lambda: ops.ancestral_update(a, e, None, 1.1, 0.4, 0.3, 0.7, 0.5, True, 1, 2)),
+            3 * a.numel() * 4)
     for (BH, Lq, Lk, D) in ((64, 64, 64, 1024), (16, 256, 256, 512), (8, 1024, 1024, 256), (2, 4096, 4096, 128), (128, 1024, 77, 64),
                             (512, 256, 77, 64)):
         q, k, v = (torch.randn(BH, L, D, device="cuda") for L in (Lq, Lk, Lk))

@@ -178,6 +178,32 @@ def test_reference_call_surface(model_fp32):
     assert x1.shape == x_T.shape and torch.isfinite(x1).all()
 
 
+def test_ancestral_step_fused(model_fp32):
+    """p_sample's fused update == the reference's torch expressions (p_mean_variance + noise * exp(0.5 log_var), :155-201) for
+    the same noise tensor, bit for bit; the in-kernel Philox draw is standard normal, differs per step and is reproducible."""
+    pan, ms, x_T = [t.cuda() for t in make_inputs(2, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    cond = {"PAN": pan, "MS": ms}
+    for t in (999, 500, 1, 0):
+        z = torch.randn(x_T.shape, generator=torch.Generator().manual_seed(t)).cuda()
+        mean, log_var = G.p_mean_variance(x=x_T, t=t, clip_denoised=True, x_in=cond, prompt="QB")
+        want = mean + (z if t > 0 else torch.zeros_like(z)) * (0.5 * log_var).exp()
+        got = G.p_sample(x_T, t, condition_x=cond, prompt="QB", noise=z)
+        assert rel_l2(got, want) < 1e-6
+    from tmdiff_b200 import ops
+    x = torch.zeros(64, 4, 64, 64).cuda()
+    a = ops.ancestral_update(x, x, None, 1.0, 0.0, 0.0, 0.0, 1.0, True, seed=7, step=3)      # out = z
+    b = ops.ancestral_update(x, x, None, 1.0, 0.0, 0.0, 0.0, 1.0, True, seed=7, step=4)
+    assert torch.equal(a, ops.ancestral_update(x, x, None, 1.0, 0.0, 0.0, 0.0, 1.0, True, seed=7, step=3))
+    assert abs(float(a.mean())) < 5e-3 and abs(float(a.var()) - 1) < 1e-2 and abs(float((a * b).mean())) < 5e-3
+    assert abs(float((a ** 4).mean()) - 3) < 0.1                                              # kurtosis of a normal
+    torch.manual_seed(0)
+    r1 = G.p_sample_loop_steps(cond, x_T, [5, 4, 3, 2, 1, 0], prompt="QB")
+    torch.manual_seed(0)
+    r2 = G.p_sample_loop_steps(cond, x_T, [5, 4, 3, 2, 1, 0], prompt="QB")
+    assert torch.equal(r1, r2) and torch.isfinite(r1).all()
+
+
 @pytest.mark.parametrize("tag", ["ms3_noise_12", "ms2_cfg_8", "ms3_xstart_9"])
 @pytest.mark.parametrize("dtype,tol", [("fp32", FP32_TOL), ("bf16", BF16_TOL)])
 def test_sampler_variants(golden_samplers, model_fp32, model_bf16, tag, dtype, tol):

@@ -1328,3 +1328,14 @@ extern "C" int tmd_psf_downsample(const float* x, float* y, const float* param, 
     if (err != cudaSuccess) return fail("tmd_psf_downsample: %s", cudaGetErrorString(err));
     return 0;
 }
+
+extern "C" int tmd_ancestral_update(const float* x, const float* eps, const float* noise, float* out, float c_recip, float c_recipm1,
+                                    float coef1, float coef2, float sigma, int32_t clip, uint64_t seed, uint64_t step, int64_t n,
+                                    void* stream) {
+    if (!x || !eps || !out) return fail("tmd_ancestral_update: null argument");
+    if (n <= 0 || n % 4) return fail("tmd_ancestral_update: element count must be a positive multiple of 4");
+    const cudaError_t err = ancestral_update(out, x, eps, noise, c_recip, c_recipm1, coef1, coef2, sigma, clip != 0, seed, step, (size_t)n,
+                                             (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_ancestral_update: %s", cudaGetErrorString(err));
+    return 0;
+}

@@ -64,6 +64,11 @@ cudaError_t solver_update(float* dst, const float* x, const float* m, const floa
 cudaError_t solver_update_multistep(int form, float* dst, const float* x, const float* m, const float* m1, const float* m2, float c1,
                                     float c2, float c3, const float* k, size_t n, cudaStream_t s);
 
+// ancestral DDPM step: out = coef1*clamp(c_recip*x - c_recipm1*eps) + coef2*x + sigma*z; z = noise or in-kernel Philox normals
+cudaError_t ancestral_update(float* out, const float* x, const float* eps, const float* noise, float c_recip, float c_recipm1, float coef1,
+                             float coef2, float sigma, bool clip, unsigned long long seed, unsigned long long step, size_t n,
+                             cudaStream_t s);
+
 // ---- stand-alone operators outside the sampling path (operators.cu) ----
 // GroupNorm(G, C, eps) over x [B, C, S] + affine gamma/beta[b * gb_stride + c] (null: none) + optional Swish.
 // partial: workspace of B*G*split*3 floats.

@@ -221,4 +221,50 @@ cudaError_t solver_update_multistep(int form, float* dst, const float* x, const 
     return cudaGetLastError();
 }
 
+
+// Ancestral DDPM step (GeneralDiffusion.p_sample, diffusion_general.py:134-138, 155-174, 196-201) fused into one pass:
+//   x0 = clamp(c_recip*x - c_recipm1*eps, -1, 1);  mean = coef1*x0 + coef2*x;  out = mean + sigma*z
+// z: the caller's noise tensor (torch.randn_like in the reference) or, when noise == nullptr, Philox4x32-10 normals drawn in
+// the kernel (counter = element index / 4, subsequence per call) -- no noise tensor in HBM.  Same operation order as the
+// reference's torch expressions.
+}  // namespace tmd
+#include <curand_kernel.h>
+namespace tmd {
+__global__ void ancestral_update_kernel(float* out, const float* x, const float* eps, const float* noise, float c_recip, float c_recipm1,
+                                        float coef1, float coef2, float sigma, int clip, unsigned long long seed,
+                                        unsigned long long step, size_t n4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 X4 = reinterpret_cast<const float4*>(x)[i], E4 = reinterpret_cast<const float4*>(eps)[i];
+    float4 Z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (sigma != 0.f) {
+        if (noise) Z4 = reinterpret_cast<const float4*>(noise)[i];
+        else {
+            curandStatePhilox4_32_10_t st;
+            curand_init(seed, /*subsequence*/ i, /*offset*/ step * 4ull, &st);
+            Z4 = curand_normal4(&st);
+        }
+    }
+    const float X[4] = {X4.x, X4.y, X4.z, X4.w}, E[4] = {E4.x, E4.y, E4.z, E4.w}, Z[4] = {Z4.x, Z4.y, Z4.z, Z4.w};
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float x0 = __fsub_rn(__fmul_rn(c_recip, X[j]), __fmul_rn(c_recipm1, E[j]));
+        if (clip) x0 = fminf(fmaxf(x0, -1.f), 1.f);
+        const float mean = __fadd_rn(__fmul_rn(coef1, x0), __fmul_rn(coef2, X[j]));
+        r[j] = __fadd_rn(mean, __fmul_rn(Z[j], sigma));
+    }
+    reinterpret_cast<float4*>(out)[i] = make_float4(r[0], r[1], r[2], r[3]);
+}
+
+cudaError_t ancestral_update(float* out, const float* x, const float* eps, const float* noise, float c_recip, float c_recipm1, float coef1,
+                             float coef2, float sigma, bool clip, unsigned long long seed, unsigned long long step, size_t n,
+                             cudaStream_t s) {
+    if (n % 4) return cudaErrorInvalidValue;
+    const size_t n4 = n / 4;
+    ancestral_update_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(out, x, eps, noise, c_recip, c_recipm1, coef1, coef2, sigma, clip ? 1 : 0,
+                                                                        seed, step, n4);
+    return cudaGetLastError();
+}
+
 }  // namespace tmd

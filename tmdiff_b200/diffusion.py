@@ -55,6 +55,10 @@ class GeneralDiffusion(nn.Module):
         self.register_buffer("posterior_log_variance_clipped", to_torch(np.log(np.maximum(pv, 1e-20))))
         self.register_buffer("posterior_mean_coef1", to_torch(betas * np.sqrt(ac_prev) / (1.0 - ac)))
         self.register_buffer("posterior_mean_coef2", to_torch((1.0 - ac_prev) * np.sqrt(alphas) / (1.0 - ac)))
+        # fp32 host copies of the per-step scalars for the fused ancestral step (no device read-back per step)
+        self._host_schedule = {k: getattr(self, k).detach().cpu().numpy() for k in
+                               ("sqrt_recip_alphas_cumprod_1", "sqrt_recipm1_alphas_cumprod_1", "posterior_mean_coef1",
+                                "posterior_mean_coef2", "posterior_log_variance_clipped")}
 
     # ---- ancestral DDPM step (:155-225): one denoiser call + element-wise torch ops -------------
     def predict_start_from_noise(self, x_t, t, noise):                     # :376-378
@@ -75,23 +79,42 @@ class GeneralDiffusion(nn.Module):
         return self.q_posterior(x_start=x_recon, x_t=x, t=t)
 
     @torch.no_grad()
-    def p_sample(self, x, t, clip_denoised=True, condition_x=None, prompt="QB", guidance=1.0):
-        mean, log_var = self.p_mean_variance(x=x, t=t, clip_denoised=clip_denoised, x_in=condition_x, prompt=prompt,
-                                             guidance=guidance)
-        noise = torch.randn_like(x) if t > 0 else torch.zeros_like(x)
-        return mean + noise * (0.5 * log_var).exp()
+    def p_sample(self, x, t, clip_denoised=True, condition_x=None, prompt="QB", guidance=1.0, noise=None, seed=None):
+        """:196-201.  One denoiser evaluation, then predict_start_from_noise + clamp + q_posterior + the noise term as ONE
+        kernel (tmd_ancestral_update) with host-side schedule scalars.  noise: the step's z (default torch.randn_like, i.e.
+        the reference's draw under the same torch seed); seed: draw z inside the kernel instead (Philox, no noise tensor)."""
+        from . import ops
+        B = x.shape[0]
+        time_in = torch.full((B, 1), t + 1, device=x.device)
+        eps = self.denoise_fn(x, time_in, condition_x["PAN"], condition_x["MS"], prompt)
+        h = self._host_schedule
+        sigma = float(np.exp(np.float32(0.5) * h["posterior_log_variance_clipped"][t])) if t > 0 else 0.0
+        if t > 0 and noise is None and seed is None:
+            noise = torch.randn_like(x)
+        return ops.ancestral_update(x, eps, noise if t > 0 else None, float(h["sqrt_recip_alphas_cumprod_1"][t]),
+                                    float(h["sqrt_recipm1_alphas_cumprod_1"][t]), float(h["posterior_mean_coef1"][t]),
+                                    float(h["posterior_mean_coef2"][t]), sigma, clip_denoised, 0 if seed is None else int(seed), t)
 
     @torch.no_grad()
-    def p_sample_loop(self, x_in, continous=False, prompt="QB", guidance=1.0):
+    def p_sample_loop(self, x_in, continous=False, prompt="QB", guidance=1.0, seed=None):
+        """:203-225.  seed=None: x_T and every step's noise come from torch's generator exactly where the reference draws
+        them; seed=int: the per-step noise is drawn inside the update kernel (nothing but x and eps is read)."""
         device = self.betas.device
         sample_inter = 1 | (self.num_timesteps // 10)
         img = torch.randn(x_in["Res"].shape, device=device)
         ret = res2img(img, x_in["MS"])
         for i in reversed(range(self.num_timesteps)):
-            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, guidance=guidance)
+            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, guidance=guidance, seed=seed)
             if i % sample_inter == 0:
                 ret = torch.cat([ret, res2img(img, x_in["MS"])], dim=0)
         return ret if continous else ret[-1]
+
+    @torch.no_grad()
+    def p_sample_loop_steps(self, x_in, img, steps, prompt="QB", seed=None):
+        """The body of p_sample_loop over an explicit list of timesteps from a given x_t (tests, truncated schedules)."""
+        for i in steps:
+            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, seed=seed)
+        return img
 
     @torch.no_grad()
     def super_resolution(self, x_in, continous, prompt, guidance):

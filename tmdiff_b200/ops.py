@@ -107,3 +107,19 @@ def quality_metrics(ref, img, ratio=0.25):
     with torch.cuda.device(a.device):
         _lib.check(_lib.load().tmd_quality_metrics(_lib.ptr(a), _lib.ptr(b), _lib.ptr(out), B, Cc, H, W, float(ratio), _lib.stream_ptr()))
     return out
+
+
+def ancestral_update(x, eps, noise, c_recip, c_recipm1, coef1, coef2, sigma, clip=True, seed=0, step=0):
+    """out = coef1 * clamp(c_recip*x - c_recipm1*eps, -1, 1) + coef2*x + sigma*z  (GeneralDiffusion.p_sample's arithmetic,
+    GeneralModel/diffusion_general.py:134-138, 155-174, 196-201) in one kernel.  z = `noise`, or Philox normals drawn in the
+    kernel from (seed, step) when noise is None."""
+    x, eps = _cuda_f32(x, "x"), _cuda_f32(eps, "eps")
+    if eps.shape != x.shape or x.numel() % 4:
+        raise ValueError("ancestral_update: x and eps must have the same shape and a multiple of 4 elements")
+    z = None if noise is None else _cuda_f32(noise, "noise")
+    out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().tmd_ancestral_update(_lib.ptr(x), _lib.ptr(eps), _lib.ptr(z), _lib.ptr(out), float(c_recip), float(c_recipm1),
+                                                    float(coef1), float(coef2), float(sigma), int(bool(clip)), int(seed), int(step),
+                                                    x.numel(), _lib.stream_ptr()))
+    return out
