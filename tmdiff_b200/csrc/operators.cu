@@ -363,11 +363,12 @@ __global__ void mix_experts_kernel(const float* __restrict__ alpha, const float*
 // ------------------------------------------------------------------------------------------------
 namespace {
 constexpr int QM_MAXC = 8, QM_THREADS = 256;
-__global__ void __launch_bounds__(QM_THREADS) quality_metrics_kernel(const float* __restrict__ ref, const float* __restrict__ img,
-                                                                     float* __restrict__ out, int C, int HW, float ratio) {
+// stage 1: every CTA reduces a pixel range of one image into ws[b] = {per band: sum a, sum b, sum a^2, sum b^2, sum ab} + {sum of angles}
+__global__ void __launch_bounds__(QM_THREADS) quality_moments_kernel(const float* __restrict__ ref, const float* __restrict__ img,
+                                                                     double* __restrict__ ws, int C, int HW) {
     __shared__ double acc[QM_MAXC][5];     // per band: sum a, sum b, sum a^2, sum b^2, sum ab   (a = ref, b = img)
     __shared__ double sam_acc;
-    const int b = blockIdx.x;
+    const int b = blockIdx.y;
     const float* A = ref + (size_t)b * C * HW;
     const float* Bm = img + (size_t)b * C * HW;
     for (int i = threadIdx.x; i < QM_MAXC * 5; i += QM_THREADS) (&acc[0][0])[i] = 0.0;
@@ -379,7 +380,7 @@ __global__ void __launch_bounds__(QM_THREADS) quality_metrics_kernel(const float
 #pragma unroll
         for (int k = 0; k < 5; ++k) loc[c][k] = 0.0;
     double sam = 0.0;
-    for (int p = threadIdx.x; p < HW; p += QM_THREADS) {
+    for (int p = blockIdx.x * QM_THREADS + threadIdx.x; p < HW; p += gridDim.x * QM_THREADS) {
         float dot = 0.f, na = 0.f, nb = 0.f;
 #pragma unroll
         for (int c = 0; c < QM_MAXC; ++c) {
@@ -400,28 +401,47 @@ __global__ void __launch_bounds__(QM_THREADS) quality_metrics_kernel(const float
     }
     atomicAdd(&sam_acc, sam);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const double n = (double)HW;
-        double erg = 0.0, q = 0.0;
-        for (int c = 0; c < C; ++c) {
-            const double sa = acc[c][0], sb = acc[c][1], saa = acc[c][2], sbb = acc[c][3], sab = acc[c][4];
-            const double mse = (saa - 2.0 * sab + sbb) / n;                 // RMSE_numpy^2 of the band
-            const double m1 = sa / n, m2 = sb / n;
-            erg += mse / (m2 * m2);                                         // / mean(ps_band)^2, ps = the second argument
-            const double d1 = (saa - n * m1 * m1) / (n - 1.0), d2 = (sbb - n * m2 * m2) / (n - 1.0), cov = (sab - n * m1 * m2) / (n - 1.0);
-            q += 4.0 * cov * m1 * m2 / (d1 + d2) / (m1 * m1 + m2 * m2);
-        }
-        out[b * 3 + 0] = (float)(sam_acc / n * 180.0 / 3.14159265358979323846);
-        out[b * 3 + 1] = (float)(100.0 * ratio * sqrt(erg / C));
-        out[b * 3 + 2] = (float)(q / C);
+    double* w = ws + (size_t)b * (QM_MAXC * 5 + 1);
+    for (int i = threadIdx.x; i < C * 5; i += QM_THREADS) atomicAdd(&w[i], (&acc[0][0])[i]);
+    if (threadIdx.x == 0) atomicAdd(&w[QM_MAXC * 5], sam_acc);
+}
+
+// stage 2: one thread per image turns the moments into {SAM, ERGAS, Q}
+__global__ void quality_finish_kernel(const double* __restrict__ ws, float* __restrict__ out, int B, int C, int HW, float ratio) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const double* w = ws + (size_t)b * (QM_MAXC * 5 + 1);
+    const double n = (double)HW;
+    double erg = 0.0, q = 0.0;
+    for (int c = 0; c < C; ++c) {
+        const double sa = w[c * 5 + 0], sb = w[c * 5 + 1], saa = w[c * 5 + 2], sbb = w[c * 5 + 3], sab = w[c * 5 + 4];
+        const double mse = (saa - 2.0 * sab + sbb) / n;                 // RMSE_numpy^2 of the band
+        const double m1 = sa / n, m2 = sb / n;
+        erg += mse / (m2 * m2);                                         // / mean(ps_band)^2, ps = the second argument
+        const double d1 = (saa - n * m1 * m1) / (n - 1.0), d2 = (sbb - n * m2 * m2) / (n - 1.0), cov = (sab - n * m1 * m2) / (n - 1.0);
+        q += 4.0 * cov * m1 * m2 / (d1 + d2) / (m1 * m1 + m2 * m2);
     }
+    out[b * 3 + 0] = (float)(w[QM_MAXC * 5] / n * 180.0 / 3.14159265358979323846);
+    out[b * 3 + 1] = (float)(100.0 * ratio * sqrt(erg / C));
+    out[b * 3 + 2] = (float)(q / C);
 }
 }  // namespace
 
 cudaError_t quality_metrics(const float* ref, const float* img, float* out, int B, int C, int HW, float ratio, cudaStream_t s) {
     if (C > QM_MAXC) return cudaErrorInvalidValue;
-    quality_metrics_kernel<<<B, QM_THREADS, 0, s>>>(ref, img, out, C, HW, ratio);
-    return cudaGetLastError();
+    int split = (2 * 148 + B - 1) / B, most = (HW + 4 * QM_THREADS - 1) / (4 * QM_THREADS);
+    if (split > most) split = most;
+    if (split < 1) split = 1;
+    double* ws = nullptr;
+    const size_t wbytes = (size_t)B * (QM_MAXC * 5 + 1) * sizeof(double);
+    cudaError_t e = cudaMallocAsync((void**)&ws, wbytes, s);
+    if (e != cudaSuccess) return e;
+    cudaMemsetAsync(ws, 0, wbytes, s);
+    quality_moments_kernel<<<dim3((unsigned)split, (unsigned)B), QM_THREADS, 0, s>>>(ref, img, ws, C, HW);
+    quality_finish_kernel<<<(B + 127) / 128, 128, 0, s>>>(ws, out, B, C, HW, ratio);
+    e = cudaGetLastError();
+    cudaFreeAsync(ws, s);
+    return e;
 }
 
 cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s) {

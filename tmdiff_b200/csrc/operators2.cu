@@ -89,10 +89,10 @@ __global__ void geglu_kernel(const float* __restrict__ p, float* __restrict__ ou
 // applied to both first.  out[b] = [sa(Ca) | saa(Ca) | sb(Cb) | sbb(Cb) | sab(Ca*Cb) | count].
 constexpr int BM_MAXC = 8, BM_THREADS = 256;
 template <bool kHighpass>
-__global__ void __launch_bounds__(BM_THREADS) band_moments_kernel(const float* __restrict__ A, const float* __restrict__ Bm, float* __restrict__ out,
+__global__ void __launch_bounds__(BM_THREADS) band_moments_kernel(const float* __restrict__ A, const float* __restrict__ Bm, double* __restrict__ ws,
                                                                   int Ca, int Cb, int H, int W) {
     __shared__ double acc[4 * BM_MAXC + BM_MAXC * BM_MAXC];
-    const int b = blockIdx.x, nacc = 2 * Ca + 2 * Cb + Ca * Cb;
+    const int b = blockIdx.y, nacc = 2 * Ca + 2 * Cb + Ca * Cb;
     const size_t HW = (size_t)H * W;
     const float* a0 = A + (size_t)b * Ca * HW;
     const float* b0 = Bm + (size_t)b * Cb * HW;
@@ -117,8 +117,8 @@ __global__ void __launch_bounds__(BM_THREADS) band_moments_kernel(const float* _
             for (int dx = 0; dx < 3; ++dx) s += p[(size_t)dy * W + dx];
         return 9.f * p[(size_t)W + 1] - s;                     // 8*centre - the eight neighbours
     };
-    // fp32 partial sums per thread over a short stride (<= count / 256 terms each), doubles across threads
-    for (int p = threadIdx.x; p < count; p += BM_THREADS) {
+    // fp32 partial sums per thread over a short stride (a few dozen terms each), doubles across threads and CTAs
+    for (int p = blockIdx.x * BM_THREADS + threadIdx.x; p < count; p += gridDim.x * BM_THREADS) {
         const int y = p / ow, x = p - y * ow;
         float va[BM_MAXC], vb[BM_MAXC];
 #pragma unroll
@@ -142,9 +142,14 @@ __global__ void __launch_bounds__(BM_THREADS) band_moments_kernel(const float* _
             if (i < Ca && j < Cb) atomicAdd(&acc[2 * Ca + 2 * Cb + i * Cb + j], (double)sab[i][j]);
     }
     __syncthreads();
-    float* o = out + (size_t)b * (nacc + 1);
-    for (int i = threadIdx.x; i < nacc; i += BM_THREADS) o[i] = (float)acc[i];
-    if (threadIdx.x == 0) o[nacc] = (float)count;
+    for (int i = threadIdx.x; i < nacc; i += BM_THREADS) atomicAdd(&ws[(size_t)b * nacc + i], acc[i]);
+}
+
+__global__ void band_moments_finish_kernel(const double* __restrict__ ws, float* __restrict__ out, int B, int nacc, float count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * (nacc + 1)) return;
+    const int b = i / (nacc + 1), k = i - b * (nacc + 1);
+    out[i] = k < nacc ? (float)ws[(size_t)b * nacc + k] : count;
 }
 
 // ---- learned PSF blur + subsample (EntireKernel / GaussianKernel forward) ----
@@ -221,11 +226,24 @@ cudaError_t geglu_rows(const float* p, float* out, size_t rows, int D, cudaStrea
 
 cudaError_t band_moments(const float* a, const float* b, float* out, int B, int Ca, int Cb, int H, int W, bool highpass, cudaStream_t s) {
     if (Ca > BM_MAXC || Cb > BM_MAXC || Ca < 1 || Cb < 1) return cudaErrorInvalidValue;
-    if (highpass) {
-        if (H < 3 || W < 3) return cudaErrorInvalidValue;
-        band_moments_kernel<true><<<B, BM_THREADS, 0, s>>>(a, b, out, Ca, Cb, H, W);
-    } else band_moments_kernel<false><<<B, BM_THREADS, 0, s>>>(a, b, out, Ca, Cb, H, W);
-    return cudaGetLastError();
+    if (highpass && (H < 3 || W < 3)) return cudaErrorInvalidValue;
+    const int nacc = 2 * Ca + 2 * Cb + Ca * Cb;
+    const int count = highpass ? (H - 2) * (W - 2) : H * W;
+    // enough CTAs for two per SM, each with at least a few pixels per thread
+    int split = (2 * 148 + B - 1) / B, most = (count + 4 * BM_THREADS - 1) / (4 * BM_THREADS);
+    if (split > most) split = most;
+    if (split < 1) split = 1;
+    double* ws = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&ws, (size_t)B * nacc * sizeof(double), s);
+    if (e != cudaSuccess) return e;
+    cudaMemsetAsync(ws, 0, (size_t)B * nacc * sizeof(double), s);
+    const dim3 grid((unsigned)split, (unsigned)B);
+    if (highpass) band_moments_kernel<true><<<grid, BM_THREADS, 0, s>>>(a, b, ws, Ca, Cb, H, W);
+    else band_moments_kernel<false><<<grid, BM_THREADS, 0, s>>>(a, b, ws, Ca, Cb, H, W);
+    band_moments_finish_kernel<<<(B * (nacc + 1) + 255) / 256, 256, 0, s>>>(ws, out, B, nacc, (float)count);
+    e = cudaGetLastError();
+    cudaFreeAsync(ws, s);
+    return e;
 }
 
 cudaError_t psf_downsample(const float* in, float* out, const float* param, float* psf_out, int mode, int planes, int H, int W, int k, int scale,
