@@ -50,6 +50,7 @@ struct UmmaParams {
     uint32_t a2_piece_bytes;    // REUSE: one un-haloed band plane [TH][TW][KC] of the second source
     ConvEpilogue epi;
     int B, N, H, W, Ci, Co, taps;   // Co: output channels of ONE tile (= the layer's Co / co_split)
+    uint32_t fd[5][2];          // {multiplier, shift} of the exact divisions by co_split, tiles_x, tiles_y, tiles_n and Co (decode_tile, staging)
     int co_split;               // REUSE: channel groups the layer's Co is split into (a tile = voxels x planes x one group)
     int mode;                   // 0 = SIMPLE, 1 = REUSE
     int KC, nkc;                // channels per chunk, chunks per tap
@@ -429,15 +430,19 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
 }
 
 struct TileCoord { int b0, n0, y0, x0, ch; };
-__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int t) {
+// n / d for n < 2^31 with the host's {multiplier, shift} (round-up method): a 32-bit multiply-high, an add and a shift instead of
+// the ~40-instruction runtime division -- the epilogue warps decode two tiles per tile and are short of issue slots.
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const uint32_t f[2]) { return (__umulhi(n, f[0]) + n) >> f[1]; }
+__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& P, int tile) {
     TileCoord c;
     // the channel groups of one voxel tile are neighbours in the tile order: they run at the same time on different SMs
     // and share the activation boxes through L2
-    c.ch = t % P.co_split; t /= P.co_split;
-    c.x0 = (t % P.tiles_x) * P.TW; t /= P.tiles_x;
-    c.y0 = (t % P.tiles_y) * P.TH; t /= P.tiles_y;
-    c.n0 = (t % P.tiles_n) * (P.mode ? P.NACC : P.TN); t /= P.tiles_n;
-    c.b0 = t * P.TB;
+    uint32_t t = (uint32_t)tile, q;
+    q = fdiv(t, P.fd[0]); c.ch = (int)(t - q * P.co_split); t = q;
+    q = fdiv(t, P.fd[1]); c.x0 = (int)(t - q * P.tiles_x) * P.TW; t = q;
+    q = fdiv(t, P.fd[2]); c.y0 = (int)(t - q * P.tiles_y) * P.TH; t = q;
+    q = fdiv(t, P.fd[3]); c.n0 = (int)(t - q * P.tiles_n) * (P.mode ? P.NACC : P.TN); t = q;
+    c.b0 = (int)t * P.TB;
     return c;
 }
 
@@ -803,7 +808,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             for (int j = 0; j < kCstPerThread; ++j) {
                 const int idx = e_tid + j * 128 * kEpiPerQuarter;
                 if (idx >= n_cst) continue;
-                const int v = idx / P.Co, c = idx - v * P.Co + cb;
+                const int v = (int)fdiv((uint32_t)idx, P.fd[4]), c = idx - v * P.Co + cb;
                 float val;
                 if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
                 else if (v < 3) val = e.tb[v - 1] ? 0.5f * __ldg(e.tb[v - 1] + (size_t)bb * e.ld_tb + c) : 0.f;   // stored halved (store_views16)
@@ -823,19 +828,19 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             load_consts(t0.b0, t0.ch * P.Co);
             store_consts(&cst[0][0]);
         }
+        // the row's place in its tile: REUSE (x, y) of the 16 x 8 plane tile; SIMPLE (x, y, band plane, sample) of the box
+        int x_in, y_in, n_in = 0, b_in = 0;
+        if (MODE) { x_in = r % P.TW; y_in = r / P.TW; }
+        else {
+            int t = r;
+            x_in = t % P.TW; t /= P.TW;
+            y_in = t % P.TH; t /= P.TH;
+            n_in = t % P.TN; b_in = t / P.TN;
+        }
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
             const TileCoord tc = decode_tile(P, tile);
             const int ab = lt & 1;
-            int b, n_off, y, x;
-            if (MODE) { x = r % P.TW; y = r / P.TW; n_off = 0; b = tc.b0; }
-            else {
-                int t = r;
-                x = t % P.TW; t /= P.TW;
-                y = t % P.TH; t /= P.TH;
-                n_off = t % P.TN; t /= P.TN;
-                b = tc.b0 + t;
-            }
-            x += tc.x0; y += tc.y0;
+            const int b = tc.b0 + b_in, n_off = n_in, y = y_in + tc.y0, x = x_in + tc.x0;
             // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin and
             // fetch the residual operands of their next item before touching the current accumulator slab
             const int nslab = P.Co >> 4, nitems = NACC * nslab;
@@ -1041,6 +1046,15 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.tiles_y = (op.H + P.TH - 1) / P.TH;
     P.tiles_b = (op.B + P.TB - 1) / P.TB;
     P.num_tiles = P.tiles_x * P.tiles_y * P.tiles_n * P.tiles_b * P.co_split;
+    {
+        const uint32_t ds[5] = {(uint32_t)P.co_split, (uint32_t)P.tiles_x, (uint32_t)P.tiles_y, (uint32_t)P.tiles_n, (uint32_t)P.Co};
+        for (int i = 0; i < 5; ++i) {          // round-up magic numbers: n / d == (umulhi(n, m) + n) >> s for n < 2^31
+            uint32_t sh = 0;
+            while ((1u << sh) < ds[i]) ++sh;
+            P.fd[i][0] = (uint32_t)((((uint64_t)1 << 32) * (((uint64_t)1 << sh) - ds[i])) / ds[i] + 1);
+            P.fd[i][1] = sh;
+        }
+    }
     P.row_bytes = P.KC * 2;
     P.layout_type = P.KC == 64 ? 2u : 4u;           // SWIZZLE_128B : SWIZZLE_64B
     P.sbo16 = (8 * P.row_bytes) >> 4;               // 8-row swizzle atoms are contiguous

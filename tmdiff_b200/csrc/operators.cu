@@ -393,13 +393,23 @@ __global__ void __launch_bounds__(QM_THREADS) quality_moments_kernel(const float
         const float ang = acosf(cs);                       // |cs| > 1 or 0/0 -> NaN, counted as 0 like the reference
         if (ang == ang) sam += ang;
     }
+    auto wsum = [](double v) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        return v;
+    };
+    const bool lead = (threadIdx.x & 31) == 0;      // one shared-memory atomic per warp and value (shared double atomics are CAS loops)
 #pragma unroll
     for (int c = 0; c < QM_MAXC; ++c) {
         if (c >= C) break;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) atomicAdd(&acc[c][k], loc[c][k]);
+        for (int k = 0; k < 5; ++k) {
+            const double u = wsum(loc[c][k]);
+            if (lead) atomicAdd(&acc[c][k], u);
+        }
     }
-    atomicAdd(&sam_acc, sam);
+    sam = wsum(sam);
+    if (lead) atomicAdd(&sam_acc, sam);
     __syncthreads();
     double* w = ws + (size_t)b * (QM_MAXC * 5 + 1);
     for (int i = threadIdx.x; i < C * 5; i += QM_THREADS) atomicAdd(&w[i], (&acc[0][0])[i]);

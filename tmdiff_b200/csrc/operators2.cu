@@ -17,6 +17,12 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
 // ---- LayerNorm(C, eps) over rows of x [rows, C]: one warp per row, the row held in registers when C <= 1024 ----
 constexpr int LN_WARPS = 8;
 template <int kVec>   // float4 pieces per lane held in registers (C <= 128 * kVec), 0: re-read the row
@@ -133,13 +139,24 @@ __global__ void __launch_bounds__(BM_THREADS) band_moments_kernel(const float* _
             for (int j = 0; j < BM_MAXC; ++j) sab[i][j] = fmaf(va[i], vb[j], sab[i][j]);
         }
     }
+    // warp reduction in double, then one shared-memory atomic per warp and value (shared double atomics are CAS loops)
+    const bool lead = (threadIdx.x & 31) == 0;
 #pragma unroll
     for (int i = 0; i < BM_MAXC; ++i) {
-        if (i < Ca) { atomicAdd(&acc[i], (double)sa[i]); atomicAdd(&acc[Ca + i], (double)saa[i]); }
-        if (i < Cb) { atomicAdd(&acc[2 * Ca + i], (double)sb[i]); atomicAdd(&acc[2 * Ca + Cb + i], (double)sbb[i]); }
+        if (i < Ca) {                                            // warp-uniform conditions
+            const double u = warp_sum_d(sa[i]), v = warp_sum_d(saa[i]);
+            if (lead) { atomicAdd(&acc[i], u); atomicAdd(&acc[Ca + i], v); }
+        }
+        if (i < Cb) {
+            const double u = warp_sum_d(sb[i]), v = warp_sum_d(sbb[i]);
+            if (lead) { atomicAdd(&acc[2 * Ca + i], u); atomicAdd(&acc[2 * Ca + Cb + i], v); }
+        }
 #pragma unroll
         for (int j = 0; j < BM_MAXC; ++j)
-            if (i < Ca && j < Cb) atomicAdd(&acc[2 * Ca + 2 * Cb + i * Cb + j], (double)sab[i][j]);
+            if (i < Ca && j < Cb) {
+                const double u = warp_sum_d(sab[i][j]);
+                if (lead) atomicAdd(&acc[2 * Ca + 2 * Cb + i * Cb + j], u);
+            }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < nacc; i += BM_THREADS) atomicAdd(&ws[(size_t)b * nacc + i], acc[i]);
