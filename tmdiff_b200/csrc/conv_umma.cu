@@ -39,7 +39,7 @@ namespace {
 
 constexpr int kEpiPerQuarter = 3;      // epilogue warps per TMEM lane quarter
 constexpr int kThreads = 128 + 128 * kEpiPerQuarter;   // 4 role warps + 16 epilogue warps
-constexpr int kMaxSA = 4, kMaxSB = 16;
+constexpr int kMaxSA = 4, kMaxSB = 16, kMaxAcc = 4;
 constexpr int kMaxCo = 256;
 constexpr int kCstPerThread = (5 * kMaxCo + 128 * kEpiPerQuarter - 1) / (128 * kEpiPerQuarter);
 
@@ -58,6 +58,7 @@ struct UmmaParams {
     int NACC;                   // accumulators (band planes) per tile
     int tiles_x, tiles_y, tiles_n, tiles_b, num_tiles;
     int SA, SB;
+    int acc_stages, acc_shift;  // accumulator sets in TMEM (2 or 4: 4 when 4*NACC*Co fits the 512 columns) and log2 of it
     int b_taps;                 // REUSE: (dy,dx) taps per weight stage (1, 3 or 9): fewer, larger stages amortise the per-stage handshake
     uint32_t a_stage_bytes, a_stage_stride, b_tile_bytes, b_tile_stride;
     uint32_t row_bytes, layout_type, sbo16;
@@ -84,6 +85,8 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 // Spin on the phase parity; a wait that lasts ~4 s means a broken pipeline: trap instead of hanging the GPU.
+// (A suspend-time hint on try_wait, meant to take the probes off the shared-memory data pipe, was measured: -4 % -- the parked
+// warps wake up later than the spinning ones.)
 #ifndef TMD_PRODUCER_SLEEP
 #define TMD_PRODUCER_SLEEP 0
 #endif
@@ -475,7 +478,7 @@ __device__ __forceinline__ uint32_t elect_one() {
 template <int MODE, int NACC, int KMMA, bool MERGE>
 __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_constant__ UmmaParams P) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 4];
+    __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc];
     __shared__ uint32_t tmem_base_slot;
     __shared__ __align__(16) float cst[MODE ? 2 : 1][MODE ? 5 * kMaxCo : 4];   // REUSE: per-tile epilogue vectors (see the epilogue warps)
 
@@ -489,12 +492,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     auto b_full = [&](int s) { return bar0 + 8u * (2 * kMaxSA + s); };
     auto b_empty = [&](int s) { return bar0 + 8u * (2 * kMaxSA + kMaxSB + s); };
     auto acc_full = [&](int s) { return bar0 + 8u * (2 * kMaxSA + 2 * kMaxSB + s); };
-    auto acc_empty = [&](int s) { return bar0 + 8u * (2 * kMaxSA + 2 * kMaxSB + 2 + s); };
+    auto acc_empty = [&](int s) { return bar0 + 8u * (2 * kMaxSA + 2 * kMaxSB + kMaxAcc + s); };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < P.SA; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
         for (int s = 0; s < P.SB; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 4 * kEpiPerQuarter); }
+        for (int s = 0; s < P.acc_stages; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), 4 * kEpiPerQuarter); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 3) {
@@ -645,9 +648,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         long long tw_acc = 0, tw_a = 0, tw_b = 0, t_issue = 0, t_all0 = clock64(), tq = 0;
         const bool tr = P.trace && blockIdx.x == 0;
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
-            const uint32_t ab = lt & 1;
+            const uint32_t ab = lt & (uint32_t)(P.acc_stages - 1);             // accumulator set (2 or 4 of them)
             if (tr) tq = clock64();
-            mbar_wait(acc_empty(ab), ((lt >> 1) & 1) ^ 1);
+            mbar_wait(acc_empty(ab), ((lt >> P.acc_shift) & 1) ^ 1);
             if (tr) tw_acc += clock64() - tq;
             tc_fence_after();
             const uint32_t d0 = tmem_base + ab * NACC * Co;
@@ -839,7 +842,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         }
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
             const TileCoord tc = decode_tile(P, tile);
-            const int ab = lt & 1;
+            const int ab = lt & (uint32_t)(P.acc_stages - 1);
             const int b = tc.b0 + b_in, n_off = n_in, y = y_in + tc.y0, x = x_in + tc.x0;
             // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin and
             // fetch the residual operands of their next item before touching the current accumulator slab
@@ -863,7 +866,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 if (tr) tw_bar += clock64() - tq;
             }
             if (tr) tq = clock64();
-            mbar_wait(acc_full(ab), (lt >> 1) & 1);
+            mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
             if (tr) tw_full += clock64() - tq;
             tc_fence_after();
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
@@ -1071,7 +1074,12 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.b_taps = env_int("TMD_UMMA_BTAPS", P.Co <= 64 ? 3 : 1);
         if (P.b_taps != 1 && P.b_taps != 3 && P.b_taps != 9) P.b_taps = 1;
     }
-    int cols = 2 * P.NACC * P.Co;
+    // accumulator sets: two overlap the epilogue of tile i with the MMAs of tile i+1.  Four (possible when 4*NACC*Co <= 512,
+    // TMD_UMMA_ACC4=1) were measured for the Co = 32 layers: no change -- the two roles do not lose time to jitter but to the
+    // shared L1 / shared-memory data pipe
+    P.acc_stages = (4 * P.NACC * P.Co <= 512 && env_int("TMD_UMMA_ACC4", 0)) ? 4 : 2;
+    P.acc_shift = P.acc_stages == 4 ? 2 : 1;
+    int cols = P.acc_stages * P.NACC * P.Co;
     P.tmem_cols = 32;
     while ((int)P.tmem_cols < cols) P.tmem_cols *= 2;
     // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
