@@ -861,20 +861,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     const TileCoord tn = decode_tile(P, nt);
                     load_consts(tn.b0, tn.ch * P.Co);
                 }
-#ifdef TMD_EXP_LEADER_WAIT
                 // one warp probes the accumulator barrier for all twelve (every probe is a wavefront on the shared-memory data
-                // pipe); the named barrier below hands the observation on, tcgen05.fence::after_thread_sync orders the TMEM loads
+                // pipe the tensor core reads through: +2.6 %); the named barrier below hands the observation on and
+                // tcgen05.fence::after_thread_sync orders the TMEM loads behind it
                 if (warp == 4) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
-#endif
                 if (tr) tq = clock64();
                 asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
                 if (tr) tw_bar += clock64() - tq;
             }
             if (tr) tq = clock64();
-#ifdef TMD_EXP_LEADER_WAIT
-            if (!MODE)
-#endif
-            mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
+            if (!MODE) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
             if (tr) tw_full += clock64() - tq;
             tc_fence_after();
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
