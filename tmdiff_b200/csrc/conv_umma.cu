@@ -432,6 +432,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
     }
 }
 
+// (back-off in the producers' waits -- nanosleep 32 / 200 ns, try_wait suspend hints 0.5-2 us -- was measured: 0 to -6 %)
+#define PRODUCER_WAIT(bar, ph) mbar_wait<TMD_PRODUCER_SLEEP>(bar, ph)
 struct TileCoord { int b0, n0, y0, x0, ch; };
 // n / d for n < 2^31 with the host's {multiplier, shift} (round-up method): a 32-bit multiply-high, an add and a shift instead of
 // the ~40-instruction runtime division -- the epilogue warps decode two tiles per tile and are short of issue slots.
@@ -535,7 +537,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     if (cn + P.TN <= 0 || cn >= P.N) continue;            // the whole box is padding
                 }
                 for (int kc = 0; kc < nkc; ++kc) {
-                    mbar_wait<TMD_PRODUCER_SLEEP>(a_empty(s), ph);
+                    PRODUCER_WAIT(a_empty(s), ph);
                     if (elect_one()) {
                         if (P.dbg & 2) mbar_arrive(a_full(s));
                         else {
@@ -560,7 +562,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 #pragma unroll
                 for (int pl = 0; pl < NACC; ++pl) planes2 += (tc.n0 + pl) < P.N;
                 for (int kc = 0; kc < P.nkc2; ++kc) {
-                    mbar_wait<TMD_PRODUCER_SLEEP>(a_empty(s), ph);
+                    PRODUCER_WAIT(a_empty(s), ph);
                     if (elect_one()) {
                         uint32_t dst = a_base + s * P.a_stage_stride;
                         if (MODE) {
@@ -591,7 +593,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 for (int kc = 0; kc < nkc; ++kc)
 #pragma unroll 1
                     for (int ts = 0; ts < b_stages_per_a; ++ts) {
-                        mbar_wait<TMD_PRODUCER_SLEEP>(b_empty(s), ph);
+                        PRODUCER_WAIT(b_empty(s), ph);
                         if (elect_one()) {
                             if (P.dbg & 4) mbar_arrive(b_full(s));
                             else {
@@ -613,7 +615,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     }
             }
             for (int kc = 0; kc < P.nkc2; ++kc) {
-                mbar_wait<TMD_PRODUCER_SLEEP>(b_empty(s), ph);
+                PRODUCER_WAIT(b_empty(s), ph);
                 if (elect_one()) {
                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
                     tma_load_2d(b_base + s * P.b_tile_stride, &P.tmB2, b_full(s), kc * KC, tc.ch * P.Co);
@@ -861,17 +863,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     const TileCoord tn = decode_tile(P, nt);
                     load_consts(tn.b0, tn.ch * P.Co);
                 }
-                // one warp probes the accumulator barrier for all twelve (every probe is a wavefront on the shared-memory data
-                // pipe the tensor core reads through: +2.6 %); the named barrier below hands the observation on and
-                // tcgen05.fence::after_thread_sync orders the TMEM loads behind it
-                if (warp == 4) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
-                if (tr) tq = clock64();
-                asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
-                if (tr) tw_bar += clock64() - tq;
             }
+            // one warp probes the accumulator barrier for all twelve (every probe is a wavefront on the shared-memory data pipe
+            // the tensor core reads through: +2.6 %); the named barrier hands the observation on (and publishes the staged
+            // vectors), tcgen05.fence::after_thread_sync orders the TMEM loads behind it
             if (tr) tq = clock64();
-            if (!MODE) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
+            if (warp == 4) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
             if (tr) tw_full += clock64() - tq;
+            asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
             tc_fence_after();
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
