@@ -305,7 +305,7 @@ def run_ours(args):
                                  "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1) if v["ms"] > 0 else 0.0}
                              for k, v in prof.items()},
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:        # the reported CPU baseline is an N = 1 item (rank 0 of a multi-rank run has peers waiting)
             threads = args.cpu_threads or os.cpu_count()
             sec = cpu_sample_seconds(N, P, args.solver_steps, args.sensor, threads)
             line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "patches/s", "cores": threads, "kind": "port",
