@@ -21,6 +21,7 @@ One JSON line on stdout (rank 0):
 `--impl reference` times that CPU path alone (rank 0 only), one patch per step.
 """
 import argparse
+import gc
 import json
 import os
 import sys
@@ -233,7 +234,17 @@ def run_ours(args):
         torch.cuda.current_stream().synchronize()        # the caller holds the host result before the next batch
 
     def timed(fn, k):
-        """k steps bracketed by barrier + synchronize; device time from CUDA events, max over ranks."""
+        """k steps bracketed by barrier + synchronize; device time from CUDA events, max over ranks.  The cyclic garbage
+        collector is held off for the k steps (as timeit does): a generation-2 pass of this process takes ~100 ms of host
+        time, which the end-to-end loop -- one host synchronisation per step -- cannot hide behind queued GPU work."""
+        gc.collect()
+        gc.disable()
+        try:
+            return _timed(fn, k)
+        finally:
+            gc.enable()
+
+    def _timed(fn, k):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -261,6 +272,7 @@ def run_ours(args):
     launches = model.launch_count() - l0
     clocks = sampler.finish()
 
+    step_e2e()
     step_e2e()
     e2e_ms = timed(step_e2e, args.steps)
 
