@@ -1072,11 +1072,12 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     P.epi.dbg = P.dbg;
     P.a_stage_stride = (P.a_stage_bytes + 1023u) & ~1023u;
     P.b_tile_bytes = P.Co * P.row_bytes;
-    // REUSE: a weight stage holds the 3 dz taps of b_taps (dy,dx) taps.  Small Co: three taps per stage, so that a stage
-    // carries enough MMA work to hide the issue warp's per-stage wait / commit round.
+    // REUSE: a weight stage holds the 3 dz taps of b_taps (dy,dx) taps.  Small Co: three or all nine taps per stage, so that a
+    // stage carries enough MMA work to hide the issue warp's per-stage wait / commit round (Co <= 32: 9 taps +1 % over 3;
+    // the ring-depth loop below falls back to fewer taps where shared memory is short).
     P.b_taps = 1;
     if (P.mode) {
-        P.b_taps = env_int("TMD_UMMA_BTAPS", P.Co <= 64 ? 3 : 1);
+        P.b_taps = env_int("TMD_UMMA_BTAPS", P.Co <= 32 ? 9 : (P.Co <= 64 ? 3 : 1));
         if (P.b_taps != 1 && P.b_taps != 3 && P.b_taps != 9) P.b_taps = 1;
     }
     // accumulator sets: two overlap the epilogue of tile i with the MMAs of tile i+1.  Four (possible when 4*NACC*Co <= 512,
