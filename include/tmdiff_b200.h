@@ -166,6 +166,13 @@ int tmd_groupnorm(const float* x, float* y, const float* gamma, const float* bet
  * (Hyper_unet_general.py:500-506) as one fused pass (no [Lq,Lk] matrix in HBM). */
 int tmd_attention(const float* q, const float* k, const float* v, float* out, int32_t BH, int32_t Lq, int32_t Lk, int32_t D,
                   float scale, void* stream);
+/* The same attention core on the tcgen05 tensor cores (bf16 operands, fp32 logits, softmax statistics and accumulation; the
+ * reference's own half-precision path keeps the logits in fp32 too, core/Attention.py:194-197).  q [BH,Lq,D] and k [BH,Lk,D]
+ * are token-major bf16, vt [BH,D,lk_pitch] is CHANNEL-major bf16 (the [B,C,HW] layout of the reference's 1x1 convs,
+ * core/Attention.py:128-131; lk_pitch >= Lk, a multiple of 8, padding never read), out [BH,Lq,D] fp32.  D must be a multiple of
+ * 64 and scale positive; anything else is an error (the fp32 entry above takes every shape). */
+int tmd_attention_bf16(const void* q, const void* k, const void* vt, float* out, int32_t BH, int32_t Lq, int32_t Lk, int32_t D,
+                       int32_t lk_pitch, float scale, void* stream);
 /* Dynamic_conv3d.forward (core/dynamic_conv.py:244-268; groups=1, stride 1, 'same' padding, k in {1,3}):
  * x [B,Ci,N,H,W], weight [K,Co,Ci,k,k,k], bias [K,Co] or NULL, fc1 [hidden,Ci], fc2 [K,hidden] (attention3d's 1x1x1 convs,
  * :194-218) -> y [B,Co,N,H,W]. */

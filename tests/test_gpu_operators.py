@@ -99,6 +99,36 @@ def test_attention_core(BH, Lq, Lk, D):
         attention(q[:, :, :4].contiguous().repeat(1, 1, 1024), k[:, :, :4].contiguous().repeat(1, 1, 1024), v[:, :, :4].contiguous().repeat(1, 1, 1024), 1.0)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("BH,Lq,Lk,D", [(4, 1024, 1024, 256), (16, 256, 77, 64), (2, 300, 333, 128), (1, 64, 64, 2048), (2, 4096, 4096, 512),
+                                        (3, 9, 1, 64), (2, 130, 200, 192)])
+def test_attention_core_bf16(BH, Lq, Lk, D):
+    """The tcgen05 attention kernel (bf16 operands, fp32 logits / statistics / accumulation) against float64 softmax attention
+    of the SAME bf16-rounded operands: level shapes of the sweep, ragged query / key counts (partial tiles, a partial key
+    block, a single key), heads wider than one 256-column accumulator.  Logits up to +-30 so that the running maximum is
+    raised (and the accumulator rescaled) in mid-sequence; constant values must come back unchanged."""
+    from tmdiff_b200.operators import attention
+    g = torch.Generator().manual_seed(2)
+    q, k, v = (torch.randn(BH, L, D, generator=g).cuda() for L in (Lq, Lk, Lk))
+    k[:, Lk // 2:] *= 3.0                  # later key blocks carry the larger logits
+    scale = 2.0 * D ** -0.5
+    r = lambda t: t.to(torch.bfloat16).double()
+    want = torch.softmax(torch.einsum("bid,bjd->bij", r(q), r(k)) * scale, -1) @ r(v)
+    got = attention(q, k, v, scale, "bf16")
+    assert got.dtype == torch.float32 and got.shape == q.shape
+    assert rel_l2(got, want) < 5e-3                       # only P's bf16 rounding and the fp32 accumulation order remain
+    exact = torch.softmax(torch.einsum("bid,bjd->bij", q.double(), k.double()) * scale, -1) @ v.double()
+    assert rel_l2(got, exact) < BF16_TOL                  # north-star bf16 gate against the unrounded fp32 inputs
+    got_cm = attention(q, k, v.transpose(1, 2).contiguous(), scale, "bf16", v_channel_major=True)
+    assert torch.equal(got_cm, got)
+    ones = torch.ones_like(v)
+    assert float((attention(q, k, ones, scale, "bf16") - 1).abs().max()) < 1e-4     # the row sum is taken over the rounded P
+    # widths the tensor-core kernel does not take run the fp32 kernel; the raw entry refuses them
+    from tmdiff_b200 import _lib
+    with pytest.raises(RuntimeError):
+        _lib.check(_lib.load().tmd_attention_bf16(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(got), BH, Lq, Lk, 48, Lk, 1.0, _lib.stream_ptr()))
+
+
 # ---- second batch: BasicTransformerBlock / SpatialTransformer, Dynamic_conv1d/2d, learned-PSF kernels, torch metrics
 # (tests/golden/make_golden_operators2.py) ----
 @pytest.fixture(scope="module")

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libtmdiff_b200.so")
-SOURCES = ["engine.cu", "elementwise.cu", "solver.cu", "conv_simt.cu", "conv_umma.cu", "operators.cu", "operators2.cu"]
+SOURCES = ["engine.cu", "elementwise.cu", "solver.cu", "conv_simt.cu", "conv_umma.cu", "attn_umma.cu", "operators.cu", "operators2.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

@@ -1,0 +1,436 @@
+// tcgen05 / TMA fused softmax attention for sm_100a (bf16 operands, fp32 logits / statistics / accumulation).
+//
+// out[bh, i, :] = softmax_j(scale * q[bh,i,:] . k[bh,j,:]) v[bh,j,:] -- the core of SpatialSelfAttention
+// (core/Attention.py:140-159: one head as wide as the channel count), CrossAttention (:185-214: 8 heads x 64, 77 text
+// keys) and AttnBlockpp (GeneralModel/Hyper_unet_general.py:500-506) in bf16 mode.  The fp32 CUDA-core kernel in
+// operators.cu stays the fp32 parity mode.
+//
+// One CTA owns 128 queries x DV <= 256 output channels of one (batch, head) and walks the keys in blocks of 128:
+//   S = Q K^T        128 x 128 fp32 in TMEM, two buffers (the logits of block j+1 are issued before the softmax of block j)
+//   P = exp2(S - m)  by the 128 softmax threads (one query row per thread = one TMEM lane: no shuffles), bf16, written to
+//                    shared memory in the 128-byte-swizzled K-major layout a TMA load would have produced
+//   O += P V         128 x DV fp32 in TMEM; the running maximum is only raised when a block exceeds it by 2^8, so the
+//                    accumulator is rescaled (tcgen05.ld / st) rarely
+// Operands: q, k token-major [BH, L, D] (K-major for S), v channel-major [BH, D, LkPad] (K-major for P V: exactly the
+// [B, C, HW] layout the reference's 1x1 convs produce).  Heads wider than 256 split their OUTPUT channels over
+// gridDim.y CTAs, each recomputing the logits; Q stays resident in shared memory when D <= 256.
+//
+// Warp roles (256 threads): 0 = TMA producer of K (and Q) chunks, 1 = TMA producer of V blocks, 2 = MMA issue,
+// 3 = TMEM allocation, 4-7 = softmax / rescale / output.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <cstdint>
+#include <cstring>
+
+#include "kernels.h"
+
+namespace tmd {
+
+namespace {
+
+constexpr int kAttnThreads = 256;
+constexpr int kStagesMax = 4;
+constexpr uint32_t kTileBytes = 128 * 128;      // [128 rows][64 bf16]: one swizzled K-major operand tile
+
+struct AttnParams {
+    CUtensorMap tmQ, tmK, tmV;
+    float* out;
+    int BH, Lq, Lk, D, DV;
+    int nkc, nkb;                 // 64-wide chunks of D; 128-key blocks
+    int q_resident, NS, NVB;
+    uint32_t stage_bytes, v_bytes;
+    uint32_t idesc_qk, idesc_pv;
+    float scale_log2;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// A wait that lasts seconds means a broken pipeline: trap instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (uint32_t spins = 0;; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+        if ((spins & 0xfff) == 0xfff) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000LL) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const float v[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+          "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])),
+          "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+          "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
+        : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// K-major, 128-byte-swizzled shared-memory matrix descriptor: start address >> 4 at [0,14), LBO = 1 at [16,30),
+// SBO = 1024 B (one 8-row swizzle atom) at [32,46), version 1 at [46,48), SWIZZLE_128B (2) at [61,64).
+__device__ __forceinline__ uint64_t sdesc(uint32_t lo) {
+    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ uint32_t sdesc_lo(uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); }
+
+__global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kStagesMax + 10];
+    __shared__ uint32_t tmem_base_slot;
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
+    const uint32_t q_base = smem_base;
+    const uint32_t st_base = q_base + (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u);
+    const uint32_t p_base = st_base + (uint32_t)P.NS * P.stage_bytes;
+    const uint32_t v_base = p_base + 2 * kTileBytes;
+    const uint32_t bar0 = smem_u32(bars);
+    auto k_full = [&](int s) { return bar0 + 8u * s; };
+    auto k_empty = [&](int s) { return bar0 + 8u * (kStagesMax + s); };
+    const uint32_t q_full = bar0 + 8u * (2 * kStagesMax);
+    auto v_full = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 1 + s); };
+    auto v_empty = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 3 + s); };
+    auto s_full = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 5 + s); };
+    const uint32_t p_full = bar0 + 8u * (2 * kStagesMax + 7);
+    const uint32_t pv_done = bar0 + 8u * (2 * kStagesMax + 8);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStagesMax; ++s) { mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); }
+        mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1); mbar_init(s_full(s), 1); }
+        mbar_init(p_full, 128);
+        mbar_init(pv_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 3) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+    const uint32_t tmem_o = tmem_base + 256u;
+
+    const int q0 = blockIdx.x * 128, dv0 = blockIdx.y * P.DV, bh = blockIdx.z;
+    const int nkc = P.nkc, nkb = P.nkb;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ================= K (and Q) chunks =================
+            if (P.q_resident) {
+                mbar_expect_tx(q_full, (uint32_t)nkc * kTileBytes);
+                for (int kc = 0; kc < nkc; ++kc) tma_load_3d(q_base + (uint32_t)kc * kTileBytes, &P.tmQ, q_full, kc * 64, q0, bh);
+            }
+            uint32_t s = 0, ph = 1;
+            for (int j = 0; j < nkb; ++j)
+                for (int kc = 0; kc < nkc; ++kc) {
+                    mbar_wait(k_empty(s), ph);
+                    mbar_expect_tx(k_full(s), P.stage_bytes);
+                    const uint32_t dst = st_base + s * P.stage_bytes;
+                    tma_load_3d(dst, &P.tmK, k_full(s), kc * 64, j * 128, bh);
+                    if (!P.q_resident) tma_load_3d(dst + kTileBytes, &P.tmQ, k_full(s), kc * 64, q0, bh);
+                    if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
+                }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ================= V blocks: [DV channels][128 keys] as two 64-key swizzle columns =================
+            const uint32_t half = (uint32_t)P.DV * 128u;
+            for (int j = 0; j < nkb; ++j) {
+                const int vb = j % P.NVB, use = j / P.NVB;
+                mbar_wait(v_empty(vb), (use & 1) ^ 1);
+                const bool second = j * 128 + 64 < P.Lk;            // a key column past the end is neither loaded nor multiplied
+                mbar_expect_tx(v_full(vb), second ? 2 * half : half);
+                const uint32_t dst = v_base + (uint32_t)vb * P.v_bytes;
+                tma_load_3d(dst, &P.tmV, v_full(vb), j * 128, dv0, bh);
+                if (second) tma_load_3d(dst + half, &P.tmV, v_full(vb), j * 128 + 64, dv0, bh);
+            }
+        }
+    } else if (warp == 2) {
+        if (lane == 0) {
+            // ================= MMA issue =================
+            const uint32_t q_lo0 = sdesc_lo(q_base), st_lo0 = sdesc_lo(st_base), p_lo0 = sdesc_lo(p_base), v_lo0 = sdesc_lo(v_base);
+            const uint32_t tile16 = kTileBytes >> 4, stage16 = P.stage_bytes >> 4, half16 = ((uint32_t)P.DV * 128u) >> 4;
+            uint32_t ks = 0, kph = 0;
+            if (P.q_resident) mbar_wait(q_full, 0);
+            auto issue_qk = [&](int j) {
+                const uint32_t d = tmem_base + (uint32_t)(j & 1) * 128u;
+                for (int kc = 0; kc < nkc; ++kc) {
+                    mbar_wait(k_full(ks), kph);
+                    tc_fence_after();
+                    const uint32_t b_lo = st_lo0 + ks * stage16;
+                    const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)kc * tile16 : b_lo + tile16;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | k));
+                    tc_commit(k_empty(ks));
+                    if (++ks == (uint32_t)P.NS) { ks = 0; kph ^= 1; }
+                }
+                tc_commit(s_full(j & 1));
+            };
+            issue_qk(0);
+            for (int j = 0; j < nkb; ++j) {
+                // the logits of the next block go out first: their buffer was last read by softmax(j-1), which had signalled
+                // p_full(j-1) before PV(j-1) was issued
+                if (j + 1 < nkb) issue_qk(j + 1);
+                const int vb = j % P.NVB, use = j / P.NVB;
+                mbar_wait(v_full(vb), use & 1);
+                mbar_wait(p_full, j & 1);
+                tc_fence_after();
+                const int keys = P.Lk - j * 128;
+                const int ksteps = keys >= 128 ? 8 : (keys + 15) >> 4;
+                const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
+                for (int k = 0; k < ksteps; ++k) {
+                    const uint32_t blk = k >> 2, kk = k & 3;
+                    tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
+                }
+                tc_commit(v_empty(vb));
+                tc_commit(pv_done);
+            }
+        }
+    } else if (warp >= 4) {
+        // ================= softmax, accumulator rescale, output =================
+        const int qtr = warp & 3;
+        const int r = qtr * 32 + lane;                                   // query row of this thread = TMEM lane
+        const uint32_t lane_addr = (uint32_t)(qtr * 32) << 16;
+        const float sl2 = P.scale_log2;
+        float m_run = -INFINITY, l_run = 0.f;
+        const uint32_t p_row = p_base + (uint32_t)r * 128u;
+        const uint32_t sw = (uint32_t)(r & 7);
+        for (int j = 0; j < nkb; ++j) {
+            mbar_wait(s_full(j & 1), (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t s_addr = tmem_base + lane_addr + (uint32_t)(j & 1) * 128u;
+            const int nvalid = P.Lk - j * 128;                               // >= 1
+            float mb = -INFINITY;
+#pragma unroll 2
+            for (int c = 0; c < 8; ++c) {
+                float v[16];
+                tc_ld16(s_addr + c * 16, v);
+                if (nvalid >= 128) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) mb = fmaxf(mb, v[i] * sl2);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (c * 16 + i < nvalid) mb = fmaxf(mb, v[i] * sl2);
+                }
+            }
+            // raise the reference maximum only when some row of the warp outgrew it by 2^8 (P stays below 256 otherwise)
+            const bool raise = __any_sync(0xffffffffu, mb > m_run + 8.f);
+            float alpha = 1.f;
+            if (raise) {
+                const float m_new = fmaxf(m_run, mb);
+                alpha = ex2(m_run - m_new);                                  // 0 on the first block
+                l_run *= alpha;
+                m_run = m_new;
+            }
+            uint32_t pk[64];
+            float lsum = 0.f;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float v[16];
+                tc_ld16(s_addr + c * 16, v);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    float p = ex2(fmaf(v[i], sl2, -m_run));
+                    if (nvalid < 128 && c * 16 + i >= nvalid) p = 0.f;
+                    v[i] = p;
+                }
+                // the row sum is taken over the ROUNDED probabilities the tensor core multiplies, so that sum_j P_ij / l_i = 1
+                // holds for what is actually accumulated (constant values come back unchanged)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const uint32_t w = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+                    pk[c * 8 + i] = w;
+                    lsum += __uint_as_float(w << 16) + __uint_as_float(w & 0xffff0000u);
+                }
+            }
+            l_run += lsum;
+            if (j > 0) {
+                mbar_wait(pv_done, (j - 1) & 1);                             // P is single-buffered; the accumulator is at rest
+                tc_fence_after();
+                if (raise) {
+                    for (int c = 0; c < P.DV / 16; ++c) {
+                        float v[16];
+                        tc_ld16(tmem_o + lane_addr + c * 16, v);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) v[i] *= alpha;
+                        tc_st16(tmem_o + lane_addr + c * 16, v);
+                    }
+                    tc_wait_st();
+                }
+            }
+            // P tile: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of its 128-byte row (SWIZZLE_128B)
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const uint32_t addr = p_row + (uint32_t)(c >> 3) * kTileBytes + ((((uint32_t)c & 7u) ^ sw) << 4);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]),
+                             "r"(pk[4 * c + 3])
+                             : "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> the tensor core's async-proxy reads
+            tc_fence_before();
+            mbar_arrive(p_full);
+        }
+        mbar_wait(pv_done, (nkb - 1) & 1);
+        tc_fence_after();
+        const float inv = 1.f / l_run;
+        const bool valid = q0 + r < P.Lq;
+        float* orow = P.out + ((size_t)bh * P.Lq + (size_t)(q0 + r)) * P.D + dv0;
+        for (int c = 0; c < P.DV / 16; ++c) {
+            float v[16];
+            tc_ld16(tmem_o + lane_addr + c * 16, v);
+            if (valid) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    reinterpret_cast<float4*>(orow + c * 16)[i] = make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 3) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn attn_encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// bf16 [batch][rows][inner] with a row pitch of `pitch` elements, boxes of [box_rows][64]
+bool make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t batch, uint64_t pitch, uint32_t box_rows) {
+    EncodeTiledFn enc = attn_encode_fn();
+    if (!enc) return false;
+    const cuuint64_t dims[3] = {inner, rows, batch};
+    const cuuint64_t strides[2] = {pitch * 2, pitch * rows * 2};
+    const cuuint32_t box[3] = {64, box_rows, 1}, es[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+bool attention_bf16_supported(int BH, int Lq, int Lk, int D, int lk_pitch) {
+    return BH > 0 && BH <= 65535 && Lq > 0 && Lk > 0 && D >= 64 && D % 64 == 0 && D <= 4096 && lk_pitch >= Lk && lk_pitch % 8 == 0;
+}
+
+cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* out, int BH, int Lq, int Lk, int D, int lk_pitch,
+                           float scale, cudaStream_t stream) {
+    if (!attention_bf16_supported(BH, Lq, Lk, D, lk_pitch)) return cudaErrorInvalidValue;
+    if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(vt) | reinterpret_cast<uintptr_t>(out)) & 15)
+        return cudaErrorMisalignedAddress;
+    AttnParams P;
+    memset(&P, 0, sizeof(P));
+    P.out = out;
+    P.BH = BH; P.Lq = Lq; P.Lk = Lk; P.D = D;
+    P.DV = D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64);
+    if (D < P.DV) P.DV = D;
+    P.nkc = D / 64;
+    P.nkb = (Lk + 127) / 128;
+    P.q_resident = D <= 256;
+    P.stage_bytes = P.q_resident ? kTileBytes : 2 * kTileBytes;
+    P.NS = P.q_resident ? 4 : 3;
+    P.v_bytes = (uint32_t)P.DV * 256u;
+    P.NVB = P.DV <= 128 ? 2 : 1;
+    // D = f32, A = B = bf16, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+    P.idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    P.idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)P.DV >> 3) << 17) | ((128u >> 4) << 24);
+    P.scale_log2 = scale * 1.4426950408889634f;
+    if (!make_map(&P.tmQ, q, D, Lq, BH, D, 128) || !make_map(&P.tmK, k, D, Lk, BH, D, 128) ||
+        !make_map(&P.tmV, vt, Lk, D, BH, lk_pitch, (uint32_t)P.DV))
+        return cudaErrorInvalidValue;
+    static int smem_limit = 0;
+    if (!smem_limit) {
+        cudaFuncAttributes fa;
+        cudaError_t e = cudaFuncGetAttributes(&fa, attn_umma_kernel);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(attn_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);
+        if (e != cudaSuccess) return e;
+        smem_limit = 227 * 1024 - (int)fa.sharedSizeBytes;
+    }
+    auto need = [&]() {
+        return 1024 + (P.q_resident ? (size_t)P.nkc * kTileBytes : 0) + (size_t)P.NS * P.stage_bytes + 2 * kTileBytes + (size_t)P.NVB * P.v_bytes;
+    };
+    while (P.NS > 2 && need() > (size_t)smem_limit) --P.NS;
+    size_t smem = need();
+    if (smem > (size_t)smem_limit) return cudaErrorInvalidConfiguration;
+    // every CTA allocates all 512 TMEM columns: keep it at one CTA per SM
+    if (smem < 120 * 1024) smem = 120 * 1024;
+    const dim3 grid((Lq + 127) / 128, D / P.DV, BH);
+    attn_umma_kernel<<<grid, kAttnThreads, smem, stream>>>(P);
+    return cudaGetLastError();
+}
+
+}  // namespace tmd

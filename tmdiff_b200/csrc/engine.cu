@@ -1177,6 +1177,18 @@ extern "C" int tmd_attention(const float* q, const float* k, const float* v, flo
     return 0;
 }
 
+extern "C" int tmd_attention_bf16(const void* q, const void* k, const void* vt, float* out, int32_t BH, int32_t Lq, int32_t Lk,
+                                  int32_t D, int32_t lk_pitch, float scale, void* stream) {
+    if (!q || !k || !vt || !out) return fail("tmd_attention_bf16: null argument");
+    if (!attention_bf16_supported(BH, Lq, Lk, D, lk_pitch))
+        return fail("tmd_attention_bf16: unsupported problem BH=%d Lq=%d Lk=%d D=%d lk_pitch=%d (D must be a multiple of 64, lk_pitch a "
+                    "multiple of 8 and >= Lk, BH <= 65535)", BH, Lq, Lk, D, lk_pitch);
+    if (!(scale > 0.f)) return fail("tmd_attention_bf16: the logit scale must be positive");
+    const cudaError_t err = attention_bf16(q, k, vt, out, BH, Lq, Lk, D, lk_pitch, scale, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_attention_bf16: %s", cudaGetErrorString(err));
+    return 0;
+}
+
 namespace {
 // experts' k^ndim taps scattered into the centre of the k^3 layout the convolution operators take (zero elsewhere)
 __global__ void embed_taps_kernel(const float* __restrict__ w, float* __restrict__ out, size_t rows, int k, int ndim) {

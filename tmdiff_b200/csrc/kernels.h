@@ -78,6 +78,12 @@ cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const flo
 cudaError_t attention_f32(const float* q, const float* k, const float* v, float* out, int BH, int Lq, int Lk, int D, float scale,
                           cudaStream_t s);
 
+// bf16 tensor-core variant (attn_umma.cu): q [BH,Lq,D], k [BH,Lk,D] token-major, vt [BH,D,lk_pitch] channel-major (lk_pitch >= Lk,
+// multiple of 8), out [BH,Lq,D] fp32; D a multiple of 64
+bool attention_bf16_supported(int BH, int Lq, int Lk, int D, int lk_pitch);
+cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* out, int BH, int Lq, int Lk, int D, int lk_pitch,
+                           float scale, cudaStream_t s);
+
 // out[b] = {SAM (degrees), ERGAS, mean per-band Q index} of img[b] against ref[b]; [B, C, HW] fp32, C <= 8
 cudaError_t quality_metrics(const float* ref, const float* img, float* out, int B, int C, int HW, float ratio, cudaStream_t s);
 // Dynamic_conv3d pieces (core/dynamic_conv.py:194-268): channel means, expert softmax, per-sample expert mix

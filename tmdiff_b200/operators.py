@@ -37,8 +37,15 @@ def group_norm(x, num_groups, weight=None, bias=None, eps=1e-6, swish=False):
     return y
 
 
-def attention(q, k, v, scale):
-    """softmax(scale * q k^T) v for q [BH, Lq, D], k/v [BH, Lk, D] in one fused pass."""
+def attention(q, k, v, scale, dtype="fp32", v_channel_major=False):
+    """softmax(scale * q k^T) v for q [BH, Lq, D], k/v [BH, Lk, D] in one fused pass (v [BH, D, Lk] when v_channel_major).
+
+    dtype "fp32": the CUDA-core kernel (1e-5 parity mode).  dtype "bf16": the tcgen05 kernel (bf16 operands, fp32 logits and
+    accumulation) whenever the head width is a multiple of 64; other widths run the fp32 kernel."""
+    if dtype == "bf16" and q.shape[-1] % 64 == 0:
+        return attention_bf16(q, k, v, scale, v_channel_major)
+    if v_channel_major:
+        v = v.transpose(1, 2)
     q, k, v = _cuda_f32(q, "q"), _cuda_f32(k, "k"), _cuda_f32(v, "v")
     BH, Lq, D = q.shape
     if k.shape[0] != BH or k.shape[2] != D or v.shape != k.shape:
@@ -47,6 +54,27 @@ def attention(q, k, v, scale):
     with torch.cuda.device(q.device):
         _lib.check(_lib.load().tmd_attention(_lib.ptr(q), _lib.ptr(k), _lib.ptr(v), _lib.ptr(out), BH, Lq, k.shape[1], D,
                                              float(scale), _lib.stream_ptr()))
+    return out
+
+
+def attention_bf16(q, k, v, scale, v_channel_major=False):
+    """The tensor-core attention core (tmd_attention_bf16).  q [BH, Lq, D], k [BH, Lk, D]; v [BH, Lk, D], or [BH, D, Lk] when
+    v_channel_major (the layout the reference's 1x1 convs produce, which is the one the kernel reads).  Returns fp32."""
+    if not (q.is_cuda and k.is_cuda and v.is_cuda):
+        raise RuntimeError("attention_bf16: CUDA tensors required (no CPU fallback)")
+    BH, Lq, D = q.shape
+    Lk = k.shape[1]
+    vt = v if v_channel_major else v.transpose(1, 2)
+    if k.shape[0] != BH or k.shape[2] != D or tuple(vt.shape) != (BH, D, Lk):
+        raise ValueError("attention: q [BH,Lq,D], k and v [BH,Lk,D] expected")
+    pitch = (Lk + 7) // 8 * 8
+    if pitch != Lk:
+        vt = torch.nn.functional.pad(vt, (0, pitch - Lk))
+    qb, kb, vb = (t.to(torch.bfloat16).contiguous() for t in (q, k, vt))
+    out = torch.empty(BH, Lq, D, device=q.device, dtype=torch.float32)
+    with torch.cuda.device(q.device):
+        _lib.check(_lib.load().tmd_attention_bf16(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), BH, Lq, Lk, D, pitch,
+                                                  float(scale), _lib.stream_ptr()))
     return out
 
 
@@ -108,7 +136,7 @@ class AttnBlockpp(nn.Module):
         h = group_norm(x2, self.GroupNorm_0.num_groups, self.GroupNorm_0.weight, self.GroupNorm_0.bias, eps=1e-6)
         q, k, v = (_conv1x1(h, n.W.t().contiguous(), n.b, self.compute_dtype) for n in (self.NIN_0, self.NIN_1, self.NIN_2))
         tok = lambda t: t.reshape(B, Cf * N, H * W).transpose(1, 2).contiguous()
-        o = attention(tok(q), tok(k), tok(v), int(Cf) ** (-0.5))
+        o = attention(tok(q), tok(k), v.reshape(B, Cf * N, H * W), int(Cf) ** (-0.5), self.compute_dtype, v_channel_major=True)
         o = o.transpose(1, 2).reshape(B, Cf * N, H, W)
         o = _conv1x1(o, self.NIN_3.W.t().contiguous(), self.NIN_3.b, self.compute_dtype)
         out = (x2 + o).reshape(B, Cf, N, H, W)
@@ -128,7 +156,8 @@ class SpatialSelfAttention(nn.Module):
         h = group_norm(x, 32, self.norm.weight, self.norm.bias, eps=1e-6)
         q, k, v = (_conv1x1(h, m.weight.reshape(Cc, Cc), m.bias, self.compute_dtype) for m in (self.q, self.k, self.v))
         tok = lambda t: t.reshape(B, Cc, H * W).transpose(1, 2).contiguous()
-        o = attention(tok(q), tok(k), tok(v), int(Cc) ** (-0.5)).transpose(1, 2).reshape(B, Cc, H, W)
+        o = attention(tok(q), tok(k), v.reshape(B, Cc, H * W), int(Cc) ** (-0.5), self.compute_dtype, v_channel_major=True)
+        o = o.transpose(1, 2).reshape(B, Cc, H, W)
         return x + _conv1x1(o, self.proj_out.weight.reshape(Cc, Cc), self.proj_out.bias, self.compute_dtype)
 
 
@@ -154,7 +183,7 @@ class CrossAttention(nn.Module):
         k = _linear_tokens(context.float(), self.to_k.weight, None, self.compute_dtype)
         v = _linear_tokens(context.float(), self.to_v.weight, None, self.compute_dtype)
         split = lambda t: t.reshape(B, t.shape[1], h, -1).permute(0, 2, 1, 3).reshape(B * h, t.shape[1], -1).contiguous()
-        o = attention(split(q), split(k), split(v), self.scale)               # logits always in fp32 (:194-197)
+        o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)   # logits always in fp32 (:194-197)
         o = o.reshape(B, h, L, -1).permute(0, 2, 1, 3).reshape(B, L, -1)
         return _linear_tokens(o, self.to_out[0].weight, self.to_out[0].bias, self.compute_dtype)
 
