@@ -104,6 +104,21 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+// 32 columns of this warp's 32 TMEM lanes; the caller waits (tc_wait_ld) once for a batch of these
+__device__ __forceinline__ void tc_ld32_nowait(uint32_t taddr, float* v) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_st16(uint32_t taddr, const float v[16]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
@@ -262,20 +277,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
             tc_fence_after();
             const uint32_t s_addr = tmem_base + lane_addr + (uint32_t)(j & 1) * 128u;
             const int nvalid = P.Lk - j * 128;                               // >= 1
-            float mb = -INFINITY;
-#pragma unroll 2
-            for (int c = 0; c < 8; ++c) {
-                float v[16];
-                tc_ld16(s_addr + c * 16, v);
-                if (nvalid >= 128) {
+            // the whole logit row of this thread comes out of TMEM once (four x32 loads in flight, one wait) and stays in registers
+            float sv[128];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) mb = fmaxf(mb, v[i] * sl2);
-                } else {
+            for (int c = 0; c < 4; ++c) tc_ld32_nowait(s_addr + c * 32, sv + c * 32);
+            tc_wait_ld();
+            if (nvalid < 128) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c * 16 + i < nvalid) mb = fmaxf(mb, v[i] * sl2);
-                }
+                for (int i = 0; i < 128; ++i)
+                    if (i >= nvalid) sv[i] = -INFINITY;
             }
+            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+            for (int i = 0; i < 128; i += 4) {
+                mx[0] = fmaxf(mx[0], sv[i]); mx[1] = fmaxf(mx[1], sv[i + 1]); mx[2] = fmaxf(mx[2], sv[i + 2]); mx[3] = fmaxf(mx[3], sv[i + 3]);
+            }
+            const float mb = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * sl2;     // scale > 0
             // raise the reference maximum only when some row of the warp outgrew it by 2^8 (P stays below 256 otherwise)
             const bool raise = __any_sync(0xffffffffu, mb > m_run + 8.f);
             float alpha = 1.f;
@@ -285,27 +302,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
                 l_run *= alpha;
                 m_run = m_new;
             }
+            // P = exp2(S * scale * log2(e) - m), rounded to bf16; masked keys (-inf) give exactly 0.  The row sum is taken over
+            // the ROUNDED probabilities the tensor core multiplies, so that sum_j P_ij / l_i = 1 holds for what is actually
+            // accumulated (constant values come back unchanged).
             uint32_t pk[64];
-            float lsum = 0.f;
+            float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                float v[16];
-                tc_ld16(s_addr + c * 16, v);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    float p = ex2(fmaf(v[i], sl2, -m_run));
-                    if (nvalid < 128 && c * 16 + i >= nvalid) p = 0.f;
-                    v[i] = p;
-                }
-                // the row sum is taken over the ROUNDED probabilities the tensor core multiplies, so that sum_j P_ij / l_i = 1
-                // holds for what is actually accumulated (constant values come back unchanged)
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const uint32_t w = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-                    pk[c * 8 + i] = w;
-                    lsum += __uint_as_float(w << 16) + __uint_as_float(w & 0xffff0000u);
-                }
+            for (int i = 0; i < 64; ++i) {
+                const float p0 = ex2(fmaf(sv[2 * i], sl2, -m_run)), p1 = ex2(fmaf(sv[2 * i + 1], sl2, -m_run));
+                const uint32_t w = pack_bf16x2(p0, p1);
+                pk[i] = w;
+                ls[i & 1] += __uint_as_float(w << 16);
+                ls[2 + (i & 1)] += __uint_as_float(w & 0xffff0000u);
             }
+            const float lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
             l_run += lsum;
             if (j > 0) {
                 mbar_wait(pv_done, (j - 1) & 1);                             // P is single-buffered; the accumulator is at rest
