@@ -39,6 +39,9 @@ struct AttnParams {
     int BH, Lq, Lk, D, DV;
     int nkc, nkb;                 // 64-wide chunks of D; 128-key blocks
     int q_resident, NS, NVB;
+    int ndv;                      // SINGLE: DV-wide output chunks one CTA walks (the other mode spreads them over gridDim.y)
+    uint32_t ab_bytes;            // shared memory of the Q / K region (SINGLE: P is written over it once the logits are complete)
+    uint32_t tmem_cols;
     uint32_t stage_bytes, v_bytes;
     uint32_t idesc_qk, idesc_pv;
     float scale_log2;
@@ -147,17 +150,23 @@ __device__ __forceinline__ uint64_t sdesc(uint32_t lo) {
 }
 __device__ __forceinline__ uint32_t sdesc_lo(uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); }
 
-__global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
+// SINGLE = the keys fit one 128-key block (Lk <= 128: the 77 text tokens of cross attention, the 8x8 level).  Then nothing is
+// carried from block to block, which removes every reason for a big footprint: P is written over the Q / K tiles (dead once the
+// logits are complete), the output accumulators sit on top of the logits in TMEM (dead once P is written), one CTA walks ALL
+// output chunks of a wide head against the same P (no logit recomputation), and two CTAs share an SM so that the loads of one
+// overlap the softmax / stores of the other -- these shapes are HBM-bound.
+template <bool SINGLE>
+__global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t bars[2 * kStagesMax + 10];
+    __shared__ __align__(8) uint64_t bars[2 * kStagesMax + 13];
     __shared__ uint32_t tmem_base_slot;
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
     const uint32_t q_base = smem_base;
     const uint32_t st_base = q_base + (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u);
-    const uint32_t p_base = st_base + (uint32_t)P.NS * P.stage_bytes;
-    const uint32_t v_base = p_base + 2 * kTileBytes;
+    const uint32_t p_base = SINGLE ? q_base : q_base + P.ab_bytes;
+    const uint32_t v_base = q_base + P.ab_bytes + (SINGLE ? 0u : 2 * kTileBytes);
     const uint32_t bar0 = smem_u32(bars);
     auto k_full = [&](int s) { return bar0 + 8u * s; };
     auto k_empty = [&](int s) { return bar0 + 8u * (kStagesMax + s); };
@@ -167,17 +176,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
     auto s_full = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 5 + s); };
     const uint32_t p_full = bar0 + 8u * (2 * kStagesMax + 7);
     const uint32_t pv_done = bar0 + 8u * (2 * kStagesMax + 8);
+    auto o_full = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 9 + s); };
+    auto o_empty = [&](int s) { return bar0 + 8u * (2 * kStagesMax + 11 + s); };
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStagesMax; ++s) { mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); }
         mbar_init(q_full, 1);
-        for (int s = 0; s < 2; ++s) { mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1); mbar_init(s_full(s), 1); }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1); mbar_init(s_full(s), 1);
+            mbar_init(o_full(s), 1); mbar_init(o_empty(s), 128);
+        }
         mbar_init(p_full, 128);
         mbar_init(pv_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 3) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(512u)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(P.tmem_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -185,10 +199,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
-    const uint32_t tmem_o = tmem_base + 256u;
+    const uint32_t tmem_o = tmem_base + (SINGLE ? 0u : 256u);
 
-    const int q0 = blockIdx.x * 128, dv0 = blockIdx.y * P.DV, bh = blockIdx.z;
-    const int nkc = P.nkc, nkb = P.nkb;
+    const int q0 = blockIdx.x * 128, dv0 = SINGLE ? 0 : blockIdx.y * P.DV, bh = blockIdx.z;
+    const int nkc = P.nkc, nkb = SINGLE ? 1 : P.nkb;
+    const int nvload = SINGLE ? P.ndv : nkb;             // V tiles this CTA consumes
 
     if (warp == 0) {
         if (lane == 0) {
@@ -210,16 +225,17 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            // ================= V blocks: [DV channels][128 keys] as two 64-key swizzle columns =================
+            // ================= V tiles: [DV channels][128 keys] as two 64-key swizzle columns =================
             const uint32_t half = (uint32_t)P.DV * 128u;
-            for (int j = 0; j < nkb; ++j) {
-                const int vb = j % P.NVB, use = j / P.NVB;
+            for (int it = 0; it < nvload; ++it) {
+                const int vb = it % P.NVB, use = it / P.NVB;
+                const int key0 = SINGLE ? 0 : it * 128, dv = SINGLE ? it * P.DV : dv0;
                 mbar_wait(v_empty(vb), (use & 1) ^ 1);
-                const bool second = j * 128 + 64 < P.Lk;            // a key column past the end is neither loaded nor multiplied
+                const bool second = key0 + 64 < P.Lk;               // a key column past the end is neither loaded nor multiplied
                 mbar_expect_tx(v_full(vb), second ? 2 * half : half);
                 const uint32_t dst = v_base + (uint32_t)vb * P.v_bytes;
-                tma_load_3d(dst, &P.tmV, v_full(vb), j * 128, dv0, bh);
-                if (second) tma_load_3d(dst + half, &P.tmV, v_full(vb), j * 128 + 64, dv0, bh);
+                tma_load_3d(dst, &P.tmV, v_full(vb), key0, dv, bh);
+                if (second) tma_load_3d(dst + half, &P.tmV, v_full(vb), key0 + 64, dv, bh);
             }
         }
     } else if (warp == 2) {
@@ -244,23 +260,42 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
                 tc_commit(s_full(j & 1));
             };
             issue_qk(0);
-            for (int j = 0; j < nkb; ++j) {
-                // the logits of the next block go out first: their buffer was last read by softmax(j-1), which had signalled
-                // p_full(j-1) before PV(j-1) was issued
-                if (j + 1 < nkb) issue_qk(j + 1);
-                const int vb = j % P.NVB, use = j / P.NVB;
-                mbar_wait(v_full(vb), use & 1);
-                mbar_wait(p_full, j & 1);
-                tc_fence_after();
-                const int keys = P.Lk - j * 128;
-                const int ksteps = keys >= 128 ? 8 : (keys + 15) >> 4;
-                const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
-                for (int k = 0; k < ksteps; ++k) {
-                    const uint32_t blk = k >> 2, kk = k & 3;
-                    tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
+            if (SINGLE) {
+                mbar_wait(p_full, 0);
+                const int ksteps = (P.Lk + 15) >> 4;
+                for (int c = 0; c < P.ndv; ++c) {
+                    const int vb = c % P.NVB, use = c / P.NVB, ob = c & 1;
+                    mbar_wait(v_full(vb), use & 1);
+                    if (c >= 2) mbar_wait(o_empty(ob), ((c >> 1) - 1) & 1);
+                    tc_fence_after();
+                    const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t blk = k >> 2, kk = k & 3;
+                        tc_mma_bf16(tmem_o + (uint32_t)ob * P.DV, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv,
+                                    (uint32_t)k);
+                    }
+                    tc_commit(v_empty(vb));
+                    tc_commit(o_full(ob));
                 }
-                tc_commit(v_empty(vb));
-                tc_commit(pv_done);
+            } else {
+                for (int j = 0; j < nkb; ++j) {
+                    // the logits of the next block go out first: their buffer was last read by softmax(j-1), which had signalled
+                    // p_full(j-1) before PV(j-1) was issued
+                    if (j + 1 < nkb) issue_qk(j + 1);
+                    const int vb = j % P.NVB, use = j / P.NVB;
+                    mbar_wait(v_full(vb), use & 1);
+                    mbar_wait(p_full, j & 1);
+                    tc_fence_after();
+                    const int keys = P.Lk - j * 128;
+                    const int ksteps = keys >= 128 ? 8 : (keys + 15) >> 4;
+                    const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t blk = k >> 2, kk = k & 3;
+                        tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
+                    }
+                    tc_commit(v_empty(vb));
+                    tc_commit(pv_done);
+                }
             }
         }
     } else if (warp >= 4) {
@@ -269,9 +304,79 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
         const int r = qtr * 32 + lane;                                   // query row of this thread = TMEM lane
         const uint32_t lane_addr = (uint32_t)(qtr * 32) << 16;
         const float sl2 = P.scale_log2;
-        float m_run = -INFINITY, l_run = 0.f;
         const uint32_t p_row = p_base + (uint32_t)r * 128u;
         const uint32_t sw = (uint32_t)(r & 7);
+        const bool valid = q0 + r < P.Lq;
+        float* orow = P.out + ((size_t)bh * P.Lq + (size_t)(q0 + r)) * P.D + dv0;
+        if (SINGLE) {
+            // one key block: two passes over the logits in 64-column halves (128 registers per thread: two CTAs per SM)
+            mbar_wait(s_full(0), 0);
+            tc_fence_after();
+            const uint32_t s_addr = tmem_base + lane_addr;
+            const int nvalid = P.Lk, nhalf = nvalid > 64 ? 2 : 1;
+            float mb = -INFINITY;
+            for (int h = 0; h < nhalf; ++h) {
+                float sv[64];
+                tc_ld32_nowait(s_addr + h * 64, sv);
+                tc_ld32_nowait(s_addr + h * 64 + 32, sv + 32);
+                tc_wait_ld();
+                float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                for (int i = 0; i < 64; ++i)
+                    if (h * 64 + i < nvalid) mx[i & 3] = fmaxf(mx[i & 3], sv[i]);
+                mb = fmaxf(mb, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])));
+            }
+            const float m = mb * sl2;                                        // scale > 0
+            float l = 0.f;
+            for (int h = 0; h < nhalf; ++h) {
+                float sv[64];
+                tc_ld32_nowait(s_addr + h * 64, sv);
+                tc_ld32_nowait(s_addr + h * 64 + 32, sv + 32);
+                tc_wait_ld();
+                // every thread's logit reads precede ITS writes below, but P overwrites the Q / K tiles, which only the completed
+                // logit MMAs (s_full) read: no further ordering is needed
+                float ls[2] = {0.f, 0.f};
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int col = c * 8 + 2 * i;
+                        float p0 = ex2(fmaf(sv[col], sl2, -m)), p1 = ex2(fmaf(sv[col + 1], sl2, -m));
+                        if (h * 64 + col >= nvalid) p0 = 0.f;
+                        if (h * 64 + col + 1 >= nvalid) p1 = 0.f;
+                        w[i] = pack_bf16x2(p0, p1);
+                        ls[0] += __uint_as_float(w[i] << 16);
+                        ls[1] += __uint_as_float(w[i] & 0xffff0000u);
+                    }
+                    const uint32_t addr = p_row + (uint32_t)h * kTileBytes + ((((uint32_t)c) ^ sw) << 4);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+                }
+                l += ls[0] + ls[1];
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tc_fence_before();
+            mbar_arrive(p_full);
+            const float inv = 1.f / l;
+            for (int c = 0; c < P.ndv; ++c) {
+                const int ob = c & 1;
+                mbar_wait(o_full(ob), (c >> 1) & 1);
+                tc_fence_after();
+                for (int cc = 0; cc < P.DV / 16; ++cc) {
+                    float v[16];
+                    tc_ld16(tmem_o + lane_addr + (uint32_t)ob * P.DV + cc * 16, v);
+                    if (valid) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            reinterpret_cast<float4*>(orow + c * P.DV + cc * 16)[i] =
+                                make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(o_empty(ob));
+            }
+        } else {
+        float m_run = -INFINITY, l_run = 0.f;
         for (int j = 0; j < nkb; ++j) {
             mbar_wait(s_full(j & 1), (j >> 1) & 1);
             tc_fence_after();
@@ -346,8 +451,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
         mbar_wait(pv_done, (nkb - 1) & 1);
         tc_fence_after();
         const float inv = 1.f / l_run;
-        const bool valid = q0 + r < P.Lq;
-        float* orow = P.out + ((size_t)bh * P.Lq + (size_t)(q0 + r)) * P.D + dv0;
         for (int c = 0; c < P.DV / 16; ++c) {
             float v[16];
             tc_ld16(tmem_o + lane_addr + c * 16, v);
@@ -357,11 +460,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attn_umma_kernel(const __grid
                     reinterpret_cast<float4*>(orow + c * 16)[i] = make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
             }
         }
+        }
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 3) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    if (warp == 3) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(P.tmem_cols) : "memory");
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -401,19 +505,60 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     if (!attention_bf16_supported(BH, Lq, Lk, D, lk_pitch)) return cudaErrorInvalidValue;
     if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(vt) | reinterpret_cast<uintptr_t>(out)) & 15)
         return cudaErrorMisalignedAddress;
+    static int smem_limit[2] = {0, 0};
+    if (!smem_limit[0]) {
+        const void* fns[2] = {(const void*)attn_umma_kernel<false>, (const void*)attn_umma_kernel<true>};
+        for (int i = 0; i < 2; ++i) {
+            cudaFuncAttributes fa;
+            cudaError_t e = cudaFuncGetAttributes(&fa, fns[i]);
+            if (e != cudaSuccess) return e;
+            e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);
+            if (e != cudaSuccess) return e;
+            smem_limit[i] = 227 * 1024 - (int)fa.sharedSizeBytes;
+        }
+    }
+    const bool single = Lk <= 128;
     AttnParams P;
     memset(&P, 0, sizeof(P));
     P.out = out;
     P.BH = BH; P.Lq = Lq; P.Lk = Lk; P.D = D;
-    P.DV = D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64);
-    if (D < P.DV) P.DV = D;
     P.nkc = D / 64;
     P.nkb = (Lk + 127) / 128;
     P.q_resident = D <= 256;
     P.stage_bytes = P.q_resident ? kTileBytes : 2 * kTileBytes;
-    P.NS = P.q_resident ? 4 : 3;
-    P.v_bytes = (uint32_t)P.DV * 256u;
-    P.NVB = P.DV <= 128 ? 2 : 1;
+    size_t smem;
+    if (single) {
+        // one key block: every output chunk against the same P, accumulators on top of the logits, P on top of Q / K
+        P.DV = D <= 256 ? D : (D % 128 == 0 ? 128 : 64);
+        P.ndv = D / P.DV;
+        P.NVB = 1;
+        P.NS = P.q_resident ? P.nkc : 2;
+        const int ocols = (P.ndv > 1 ? 2 : 1) * P.DV;
+        P.tmem_cols = ocols <= 128 ? 128 : 256;
+        P.v_bytes = (uint32_t)P.DV * 256u;
+        P.ab_bytes = (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u) + (uint32_t)P.NS * P.stage_bytes;
+        if (P.ab_bytes < 2 * kTileBytes) P.ab_bytes = 2 * kTileBytes;
+        smem = 1024 + (size_t)P.ab_bytes + (size_t)P.NVB * P.v_bytes;
+        // co-resident CTAs must find their TMEM columns: at most 512 / tmem_cols of them fit by shared memory
+        const size_t floor_bytes = P.tmem_cols == 128 ? 46 * 1024 : 76 * 1024;
+        if (smem < floor_bytes) smem = floor_bytes;
+    } else {
+        P.DV = D <= 256 ? D : (D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64));
+        P.ndv = 1;
+        P.NS = P.q_resident ? 4 : 3;
+        P.v_bytes = (uint32_t)P.DV * 256u;
+        P.NVB = P.DV <= 128 ? 2 : 1;
+        P.tmem_cols = 512;
+        auto need = [&]() {
+            P.ab_bytes = (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u) + (uint32_t)P.NS * P.stage_bytes;
+            return 1024 + (size_t)P.ab_bytes + 2 * kTileBytes + (size_t)P.NVB * P.v_bytes;
+        };
+        while (P.NS > 2 && need() > (size_t)smem_limit[0]) --P.NS;
+        smem = need();
+        // every CTA allocates all 512 TMEM columns: keep it at one CTA per SM
+        if (smem < 120 * 1024) smem = 120 * 1024;
+    }
+    if (smem > (size_t)smem_limit[single ? 1 : 0]) return cudaErrorInvalidConfiguration;
     // D = f32, A = B = bf16, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
     P.idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
     P.idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)P.DV >> 3) << 17) | ((128u >> 4) << 24);
@@ -421,25 +566,13 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     if (!make_map(&P.tmQ, q, D, Lq, BH, D, 128) || !make_map(&P.tmK, k, D, Lk, BH, D, 128) ||
         !make_map(&P.tmV, vt, Lk, D, BH, lk_pitch, (uint32_t)P.DV))
         return cudaErrorInvalidValue;
-    static int smem_limit = 0;
-    if (!smem_limit) {
-        cudaFuncAttributes fa;
-        cudaError_t e = cudaFuncGetAttributes(&fa, attn_umma_kernel);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(attn_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);
-        if (e != cudaSuccess) return e;
-        smem_limit = 227 * 1024 - (int)fa.sharedSizeBytes;
+    if (single) {
+        const dim3 grid((Lq + 127) / 128, 1, BH);
+        attn_umma_kernel<true><<<grid, kAttnThreads, smem, stream>>>(P);
+    } else {
+        const dim3 grid((Lq + 127) / 128, D / P.DV, BH);
+        attn_umma_kernel<false><<<grid, kAttnThreads, smem, stream>>>(P);
     }
-    auto need = [&]() {
-        return 1024 + (P.q_resident ? (size_t)P.nkc * kTileBytes : 0) + (size_t)P.NS * P.stage_bytes + 2 * kTileBytes + (size_t)P.NVB * P.v_bytes;
-    };
-    while (P.NS > 2 && need() > (size_t)smem_limit) --P.NS;
-    size_t smem = need();
-    if (smem > (size_t)smem_limit) return cudaErrorInvalidConfiguration;
-    // every CTA allocates all 512 TMEM columns: keep it at one CTA per SM
-    if (smem < 120 * 1024) smem = 120 * 1024;
-    const dim3 grid((Lq + 127) / 128, D / P.DV, BH);
-    attn_umma_kernel<<<grid, kAttnThreads, smem, stream>>>(P);
     return cudaGetLastError();
 }
 
