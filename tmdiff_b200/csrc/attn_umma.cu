@@ -16,7 +16,7 @@
 // gridDim.y CTAs, each recomputing the logits; Q stays resident in shared memory when D <= 256.
 //
 // Warp roles (256 threads): 0 = TMA producer of K (and Q) chunks, 1 = TMA producer of V blocks, 2 = MMA issue,
-// 3 = TMEM allocation, 4-7 = softmax / rescale / output.
+// 3 = TMEM allocation, 4-7 = softmax / rescale / output.  Keys that fit ONE block (Lk <= 128) take the SINGLE variant below.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -29,7 +29,6 @@ namespace tmd {
 
 namespace {
 
-constexpr int kAttnThreads = 256;
 constexpr int kStagesMax = 4;
 constexpr uint32_t kTileBytes = 128 * 128;      // [128 rows][64 bf16]: one swizzled K-major operand tile
 
@@ -156,7 +155,10 @@ __device__ __forceinline__ uint32_t sdesc_lo(uint32_t addr) { return ((addr & 0x
 // output chunks of a wide head against the same P (no logit recomputation), and two CTAs share an SM so that the loads of one
 // overlap the softmax / stores of the other -- these shapes are HBM-bound.
 template <bool SINGLE>
-__global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
+__global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
+    // SINGLE runs 192 threads (one producer warp for all three operands, MMA issue and TMEM allocation in one warp, softmax warps
+    // 2-5 = TMEM lane quarters 2, 3, 0, 1) at <= 85 registers, so that four CTAs fit an SM
+    constexpr int W_K = 0, W_V = SINGLE ? 0 : 1, W_MMA = SINGLE ? 1 : 2, W_ALLOC = SINGLE ? 1 : 3, W_SOFTMAX = SINGLE ? 2 : 4;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kStagesMax + 13];
     __shared__ uint32_t tmem_base_slot;
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
         mbar_init(pv_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 3) {
+    if (warp == W_ALLOC) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_slot)), "r"(P.tmem_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
     const int nkc = P.nkc, nkb = SINGLE ? 1 : P.nkb;
     const int nvload = SINGLE ? P.ndv : nkb;             // V tiles this CTA consumes
 
-    if (warp == 0) {
+    if (warp == W_K) {
         if (lane == 0) {
             // ================= K (and Q) chunks =================
             if (P.q_resident) {
@@ -223,7 +225,8 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
                     if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
                 }
         }
-    } else if (warp == 1) {
+    }
+    if (warp == W_V) {
         if (lane == 0) {
             // ================= V tiles: [DV channels][128 keys] as two 64-key swizzle columns =================
             const uint32_t half = (uint32_t)P.DV * 128u;
@@ -238,7 +241,8 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
                 if (second) tma_load_3d(dst + half, &P.tmV, v_full(vb), key0 + 64, dv, bh);
             }
         }
-    } else if (warp == 2) {
+    }
+    if (warp == W_MMA) {
         if (lane == 0) {
             // ================= MMA issue =================
             const uint32_t q_lo0 = sdesc_lo(q_base), st_lo0 = sdesc_lo(st_base), p_lo0 = sdesc_lo(p_base), v_lo0 = sdesc_lo(v_base);
@@ -298,7 +302,8 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
                 }
             }
         }
-    } else if (warp >= 4) {
+    }
+    if (warp >= W_SOFTMAX) {
         // ================= softmax, accumulator rescale, output =================
         const int qtr = warp & 3;
         const int r = qtr * 32 + lane;                                   // query row of this thread = TMEM lane
@@ -358,6 +363,29 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
             tc_fence_before();
             mbar_arrive(p_full);
             const float inv = 1.f / l;
+            if (P.ndv == 1) {
+                // the whole head in one chunk: a thread's output row is one contiguous D*4-byte piece of global memory.  Written
+                // straight from registers it costs one L1 wavefront per lane and instruction (rows are D*4 bytes apart), which is
+                // what bounded the 77-key cross-attention shape; instead the row is staged in shared memory (over the dead Q / K /
+                // P / V tiles, pitch D*4 + 16 bytes: conflict-free 16-byte stores) and leaves as ONE bulk copy per row.
+                mbar_wait(o_full(0), 0);
+                tc_fence_after();
+                const uint32_t srow = q_base + (uint32_t)r * ((uint32_t)P.DV * 4u + 16u);
+                for (int cc = 0; cc < P.DV / 16; ++cc) {
+                    float v[16];
+                    tc_ld16(tmem_o + lane_addr + cc * 16, v);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(srow + (uint32_t)cc * 64u + (uint32_t)i * 16u), "f"(v[4 * i] * inv),
+                                     "f"(v[4 * i + 1] * inv), "f"(v[4 * i + 2] * inv), "f"(v[4 * i + 3] * inv)
+                                     : "memory");
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                if (valid)
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(orow), "r"(srow), "r"((uint32_t)P.DV * 4u) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            } else
             for (int c = 0; c < P.ndv; ++c) {
                 const int ob = c & 1;
                 mbar_wait(o_full(ob), (c >> 1) & 1);
@@ -465,7 +493,7 @@ __global__ void __launch_bounds__(kAttnThreads, SINGLE ? 2 : 1) attn_umma_kernel
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 3) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(P.tmem_cols) : "memory");
+    if (warp == W_ALLOC) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(P.tmem_cols) : "memory");
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -540,7 +568,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
         if (P.ab_bytes < 2 * kTileBytes) P.ab_bytes = 2 * kTileBytes;
         smem = 1024 + (size_t)P.ab_bytes + (size_t)P.NVB * P.v_bytes;
         // co-resident CTAs must find their TMEM columns: at most 512 / tmem_cols of them fit by shared memory
-        const size_t floor_bytes = P.tmem_cols == 128 ? 46 * 1024 : 76 * 1024;
+        const size_t floor_bytes = P.tmem_cols == 128 ? 46 * 1024 : 80 * 1024;
         if (smem < floor_bytes) smem = floor_bytes;
     } else {
         P.DV = D <= 256 ? D : (D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64));
@@ -568,10 +596,10 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
         return cudaErrorInvalidValue;
     if (single) {
         const dim3 grid((Lq + 127) / 128, 1, BH);
-        attn_umma_kernel<true><<<grid, kAttnThreads, smem, stream>>>(P);
+        attn_umma_kernel<true><<<grid, 192, smem, stream>>>(P);
     } else {
         const dim3 grid((Lq + 127) / 128, D / P.DV, BH);
-        attn_umma_kernel<false><<<grid, kAttnThreads, smem, stream>>>(P);
+        attn_umma_kernel<false><<<grid, 256, smem, stream>>>(P);
     }
     return cudaGetLastError();
 }
