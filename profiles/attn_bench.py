@@ -1,6 +1,8 @@
 """Attention-core sweep on one B200 (BASELINE config 5): the tcgen05 kernel (tmd_attention_bf16) against the
 fp32 CUDA-core kernel (tmd_attention), CUDA events on the launching stream, operands already in the kernel's layout.
-Algorithmic FLOPs = 4 * BH * Lq * Lk * D (QK^T and PV).  Usage: python profiles/attn_bench.py [out.md]"""
+Algorithmic FLOPs = 4 * BH * Lq * Lk * D (QK^T and PV); algorithmic bytes = bf16 q, k, v read once + fp32 out written once.  A shape
+is judged against the roofline that bounds it: tensor when FLOPs / bytes exceeds the machine balance (measured bf16 peak / measured
+HBM copy bandwidth), HBM otherwise.  Usage: python profiles/attn_bench.py [out.md]"""
 import json
 import os
 import sys
@@ -73,13 +75,18 @@ def main():
         BH_full, BH = BH, sub
         t_f32 = time_ms(f32, 2) * BH_full / sub
         BH = BH_full
-        rows.append((what, BH, Lq, Lk, D, t_bf, flops / t_bf / 1e9, flops / t_bf / 1e9 / peak, flops / t_f32 / 1e9))
+        nbytes = 2.0 * BH * D * (Lq + 2 * Lk) + 4.0 * BH * Lq * D
+        hbm = float(PEAKS.get("hbm_gbs", 6537.6))
+        tf, gbs = flops / t_bf / 1e9, nbytes / t_bf / 1e6
+        bound = "tensor" if flops / nbytes > peak * 1e3 / hbm else "hbm"
+        rows.append((what, BH, Lq, Lk, D, t_bf, tf, gbs, bound, tf / peak if bound == "tensor" else gbs / hbm, flops / t_f32 / 1e9))
         print(rows[-1], flush=True)
     lines = ["# Attention core sweep (tcgen05 `attn_umma_kernel` vs fp32 CUDA-core kernel)", "",
-             "Peak: %.1f TFLOP/s (%s, MEASURED_PEAKS.json). FLOPs = 4*BH*Lq*Lk*D." % (peak, src), "",
-             "| shape | BH | Lq | Lk | D | bf16 ms | bf16 TFLOP/s | of peak | fp32 kernel TFLOP/s |", "|---|---|---|---|---|---|---|---|---|"]
+             "Peaks (MEASURED_PEAKS.json): %.1f TFLOP/s (%s), %.1f GB/s HBM copy. FLOPs = 4*BH*Lq*Lk*D; bytes = bf16 q,k,v + fp32 out."
+             % (peak, src, float(PEAKS.get("hbm_gbs", 6537.6))), "",
+             "| shape | BH | Lq | Lk | D | ms | TFLOP/s | GB/s | bound | frac of that roofline | fp32 kernel TFLOP/s |", "|---|---|---|---|---|---|---|---|---|---|---|"]
     for r in rows:
-        lines.append("| %s | %d | %d | %d | %d | %.3f | %.1f | %.2f | %.1f |" % r)
+        lines.append("| %s | %d | %d | %d | %d | %.3f | %.1f | %.0f | %s | %.2f | %.1f |" % r)
     text = "\n".join(lines) + "\n"
     if len(sys.argv) > 1:
         open(sys.argv[1], "w").write(text)

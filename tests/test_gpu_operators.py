@@ -101,7 +101,7 @@ def test_attention_core(BH, Lq, Lk, D):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("BH,Lq,Lk,D", [(4, 1024, 1024, 256), (16, 256, 77, 64), (2, 300, 333, 128), (1, 64, 64, 2048), (2, 4096, 4096, 512),
-                                        (3, 9, 1, 64), (2, 130, 200, 192), (2, 200, 100, 256), (2, 130, 128, 192), (3, 70, 40, 640)])
+                                        (3, 9, 1, 64), (2, 130, 200, 192), (2, 200, 100, 256), (2, 130, 128, 192), (3, 70, 40, 640), (4, 256, 256, 1024), (2, 140, 190, 320)])
 def test_attention_core_bf16(BH, Lq, Lk, D):
     """The tcgen05 attention kernel (bf16 operands, fp32 logits / statistics / accumulation) against float64 softmax attention
     of the SAME bf16-rounded operands: level shapes of the sweep, ragged query / key counts (partial tiles, a partial key

@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
     const uint32_t tmem_o = tmem_base + (SINGLE ? 0u : 256u);
 
     const int q0 = blockIdx.x * 128, dv0 = SINGLE ? 0 : blockIdx.y * P.DV, bh = blockIdx.z;
-    const int nkc = P.nkc, nkb = SINGLE ? 1 : P.nkb;
+    const int nkc = P.nkc, nkb = P.nkb;                  // SINGLE: one block, or two for a wide head (Lk <= 256)
     const int nvload = SINGLE ? P.ndv : nkb;             // V tiles this CTA consumes
 
     if (warp == W_K) {
@@ -234,11 +234,13 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
                 const int vb = it % P.NVB, use = it / P.NVB;
                 const int key0 = SINGLE ? 0 : it * 128, dv = SINGLE ? it * P.DV : dv0;
                 mbar_wait(v_empty(vb), (use & 1) ^ 1);
-                const bool second = key0 + 64 < P.Lk;               // a key column past the end is neither loaded nor multiplied
-                mbar_expect_tx(v_full(vb), second ? 2 * half : half);
+                // 64-key columns of this tile that hold keys: one past the end is neither loaded nor multiplied
+                int ncol = (P.Lk - key0 + 63) >> 6;
+                const int maxcol = SINGLE ? 2 * nkb : 2;
+                if (ncol > maxcol) ncol = maxcol;
+                mbar_expect_tx(v_full(vb), (uint32_t)ncol * half);
                 const uint32_t dst = v_base + (uint32_t)vb * P.v_bytes;
-                tma_load_3d(dst, &P.tmV, v_full(vb), key0, dv, bh);
-                if (second) tma_load_3d(dst + half, &P.tmV, v_full(vb), key0 + 64, dv, bh);
+                for (int t = 0; t < ncol; ++t) tma_load_3d(dst + (uint32_t)t * half, &P.tmV, v_full(vb), key0 + 64 * t, dv, bh);
             }
         }
     }
@@ -265,6 +267,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             };
             issue_qk(0);
             if (SINGLE) {
+                if (nkb > 1) issue_qk(1);
                 mbar_wait(p_full, 0);
                 const int ksteps = (P.Lk + 15) >> 4;
                 for (int c = 0; c < P.ndv; ++c) {
@@ -314,11 +317,12 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
         const bool valid = q0 + r < P.Lq;
         float* orow = P.out + ((size_t)bh * P.Lq + (size_t)(q0 + r)) * P.D + dv0;
         if (SINGLE) {
-            // one key block: two passes over the logits in 64-column halves (128 registers per thread: two CTAs per SM)
+            // the logits of all keys are at hand: exact softmax in two passes over 64-column pieces (few registers: four CTAs per SM)
             mbar_wait(s_full(0), 0);
+            if (nkb > 1) mbar_wait(s_full(1), 0);
             tc_fence_after();
             const uint32_t s_addr = tmem_base + lane_addr;
-            const int nvalid = P.Lk, nhalf = nvalid > 64 ? 2 : 1;
+            const int nvalid = P.Lk, nhalf = (nvalid + 63) >> 6;
             float mb = -INFINITY;
             for (int h = 0; h < nhalf; ++h) {
                 float sv[64];
@@ -545,7 +549,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
             smem_limit[i] = 227 * 1024 - (int)fa.sharedSizeBytes;
         }
     }
-    const bool single = Lk <= 128;
+    const bool single = Lk <= 128 || (Lk <= 256 && D > 256);     // all logits of a query tile fit TMEM next to nothing else
     AttnParams P;
     memset(&P, 0, sizeof(P));
     P.out = out;
@@ -557,15 +561,16 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     size_t smem;
     if (single) {
         // one key block: every output chunk against the same P, accumulators on top of the logits, P on top of Q / K
-        P.DV = D <= 256 ? D : (D % 128 == 0 ? 128 : 64);
+        P.DV = D <= 256 ? D : ((D % 128 == 0 && P.nkb == 1) ? 128 : 64);
         P.ndv = D / P.DV;
         P.NVB = 1;
         P.NS = P.q_resident ? P.nkc : 2;
-        const int ocols = (P.ndv > 1 ? 2 : 1) * P.DV;
-        P.tmem_cols = ocols <= 128 ? 128 : 256;
-        P.v_bytes = (uint32_t)P.DV * 256u;
+        int cols = (P.ndv > 1 ? 2 : 1) * P.DV;
+        if (cols < 128 * P.nkb) cols = 128 * P.nkb;
+        P.tmem_cols = cols <= 128 ? 128 : 256;
+        P.v_bytes = (uint32_t)P.DV * 256u * (uint32_t)P.nkb;
         P.ab_bytes = (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u) + (uint32_t)P.NS * P.stage_bytes;
-        if (P.ab_bytes < 2 * kTileBytes) P.ab_bytes = 2 * kTileBytes;
+        if (P.ab_bytes < 2 * kTileBytes * (uint32_t)P.nkb) P.ab_bytes = 2 * kTileBytes * (uint32_t)P.nkb;
         smem = 1024 + (size_t)P.ab_bytes + (size_t)P.NVB * P.v_bytes;
         // co-resident CTAs must find their TMEM columns: at most 512 / tmem_cols of them fit by shared memory
         const size_t floor_bytes = P.tmem_cols == 128 ? 46 * 1024 : 80 * 1024;
