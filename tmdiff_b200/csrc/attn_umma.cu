@@ -21,6 +21,8 @@
 #include <cuda_bf16.h>
 
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "kernels.h"
@@ -41,6 +43,7 @@ struct AttnParams {
     int ndv;                      // SINGLE: DV-wide output chunks one CTA walks (the other mode spreads them over gridDim.y)
     uint32_t ab_bytes;            // shared memory of the Q / K region (SINGLE: P is written over it once the logits are complete)
     uint32_t tmem_cols;
+    long long* trace;             // diagnostics (TMD_ATTN_TRACE=1): cycle counters of CTA 0's first softmax warp / MMA thread
     uint32_t stage_bytes, v_bytes;
     uint32_t idesc_qk, idesc_pv;
     float scale_log2;
@@ -409,9 +412,13 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             }
         } else {
         float m_run = -INFINITY, l_run = 0.f;
+        const bool tr = P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == W_SOFTMAX;
+        long long t_s = 0, t_ld = 0, t_math = 0, t_pv = 0, t_p = 0, t0 = clock64(), tq = 0;
         for (int j = 0; j < nkb; ++j) {
+            if (tr) tq = clock64();
             mbar_wait(s_full(j & 1), (j >> 1) & 1);
             tc_fence_after();
+            if (tr) { const long long n = clock64(); t_s += n - tq; tq = n; }
             const uint32_t s_addr = tmem_base + lane_addr + (uint32_t)(j & 1) * 128u;
             const int nvalid = P.Lk - j * 128;                               // >= 1
             // the whole logit row of this thread comes out of TMEM once (four x32 loads in flight, one wait) and stays in registers
@@ -419,6 +426,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
 #pragma unroll
             for (int c = 0; c < 4; ++c) tc_ld32_nowait(s_addr + c * 32, sv + c * 32);
             tc_wait_ld();
+            if (tr) { const long long n = clock64(); t_ld += n - tq; tq = n; }
             if (nvalid < 128) {
 #pragma unroll
                 for (int i = 0; i < 128; ++i)
@@ -454,6 +462,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             }
             const float lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
             l_run += lsum;
+            if (tr) { const long long n = clock64(); t_math += n - tq; tq = n; }
             if (j > 0) {
                 mbar_wait(pv_done, (j - 1) & 1);                             // P is single-buffered; the accumulator is at rest
                 tc_fence_after();
@@ -468,6 +477,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
                     tc_wait_st();
                 }
             }
+            if (tr) { const long long n = clock64(); t_pv += n - tq; tq = n; }
             // P tile: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of its 128-byte row (SWIZZLE_128B)
 #pragma unroll
             for (int c = 0; c < 16; ++c) {
@@ -479,6 +489,11 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> the tensor core's async-proxy reads
             tc_fence_before();
             mbar_arrive(p_full);
+            if (tr) t_p += clock64() - tq;
+        }
+        if (tr && lane == 0) {
+            P.trace[0] = clock64() - t0; P.trace[1] = t_s; P.trace[2] = t_ld; P.trace[3] = t_math; P.trace[4] = t_pv; P.trace[5] = t_p;
+            P.trace[6] = nkb;
         }
         mbar_wait(pv_done, (nkb - 1) & 1);
         tc_fence_after();
@@ -604,6 +619,20 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
         attn_umma_kernel<true><<<grid, 192, smem, stream>>>(P);
     } else {
         const dim3 grid((Lq + 127) / 128, D / P.DV, BH);
+        const char* te = getenv("TMD_ATTN_TRACE");
+        if (te && te[0] == '1') {
+            cudaMalloc((void**)&P.trace, 8 * sizeof(long long));
+            cudaMemset(P.trace, 0, 8 * sizeof(long long));
+            attn_umma_kernel<false><<<grid, 256, smem, stream>>>(P);
+            cudaDeviceSynchronize();
+            long long t[8];
+            cudaMemcpy(t, P.trace, sizeof(t), cudaMemcpyDeviceToHost);
+            cudaFree(P.trace);
+            const double n = t[6] ? (double)t[6] : 1.0;
+            fprintf(stderr, "[attn trace] Lq=%d Lk=%d D=%d | softmax warp per key block: total %.0f cyc = wait S %.0f + tmem ld %.0f + max/exp/pack %.0f + "
+                    "wait PV %.0f + P store/fence/arrive %.0f\n", Lq, Lk, D, t[0] / n, t[1] / n, t[2] / n, t[3] / n, t[4] / n, t[5] / n);
+            return cudaGetLastError();
+        }
         attn_umma_kernel<false><<<grid, 256, smem, stream>>>(P);
     }
     return cudaGetLastError();
