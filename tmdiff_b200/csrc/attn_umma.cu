@@ -15,8 +15,8 @@
 // [B, C, HW] layout the reference's 1x1 convs produce).  Heads wider than 256 split their OUTPUT channels over
 // gridDim.y CTAs, each recomputing the logits; Q stays resident in shared memory when D <= 256.
 //
-// Warp roles (256 threads): 0 = TMA producer of K (and Q) chunks, 1 = TMA producer of V blocks, 2 = MMA issue,
-// 3 = TMEM allocation, 4-7 = softmax / rescale / output.  Keys that fit ONE block (Lk <= 128) take the SINGLE variant below.
+// Warp roles (384 threads): 0 = TMA producer of K (and Q) chunks, 1 = TMA producer of V blocks, 2 = MMA issue,
+// 3 = TMEM allocation, 4-7 and 8-11 = two softmax / rescale / output warpgroups (keys 0-63 / 64-127 of every block).  Keys that fit ONE block (Lk <= 128) take the SINGLE variant below.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -158,13 +158,14 @@ __device__ __forceinline__ uint32_t sdesc_lo(uint32_t addr) { return ((addr & 0x
 // output chunks of a wide head against the same P (no logit recomputation), and two CTAs share an SM so that the loads of one
 // overlap the softmax / stores of the other -- these shapes are HBM-bound.
 template <bool SINGLE>
-__global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
+__global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_kernel(const __grid_constant__ AttnParams P) {
     // SINGLE runs 192 threads (one producer warp for all three operands, MMA issue and TMEM allocation in one warp, softmax warps
     // 2-5 = TMEM lane quarters 2, 3, 0, 1) at <= 85 registers, so that four CTAs fit an SM
     constexpr int W_K = 0, W_V = SINGLE ? 0 : 1, W_MMA = SINGLE ? 1 : 2, W_ALLOC = SINGLE ? 1 : 3, W_SOFTMAX = SINGLE ? 2 : 4;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kStagesMax + 13];
     __shared__ uint32_t tmem_base_slot;
+    __shared__ float xch[2][SINGLE ? 1 : 128];      // long sequences: row statistics exchanged between the two softmax warpgroups
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1); mbar_init(s_full(s), 1);
             mbar_init(o_full(s), 1); mbar_init(o_empty(s), 128);
         }
-        mbar_init(p_full, 128);
+        mbar_init(p_full, SINGLE ? 128 : 256);
         mbar_init(pv_done, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -411,34 +412,47 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
                 mbar_arrive(o_empty(ob));
             }
         } else {
+        // Two softmax warpgroups share every key block: warps 4-7 take keys 0-63 of the block, warps 8-11 keys 64-127 of the SAME
+        // query rows (a TMEM lane quarter is open to every warp with that index mod 4).  The block's exp2 / pack work -- which
+        // bounded head widths <= 128 with one warpgroup (TMD_ATTN_TRACE: 1610 of 2700 cycles per block) -- halves per thread; the
+        // partner threads of a row exchange their partial row maxima through shared memory (one named barrier per block), keep
+        // partial row sums that are only added at the end, write one 64-key P tile each and rescale / store one half of the
+        // output channels each.
+        const int wg = (warp - W_SOFTMAX) >> 2;
         float m_run = -INFINITY, l_run = 0.f;
         const bool tr = P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == W_SOFTMAX;
         long long t_s = 0, t_ld = 0, t_math = 0, t_pv = 0, t_p = 0, t0 = clock64(), tq = 0;
+        const int hdv = P.DV >> 1;                                           // output channels this warpgroup rescales and stores
         for (int j = 0; j < nkb; ++j) {
             if (tr) tq = clock64();
             mbar_wait(s_full(j & 1), (j >> 1) & 1);
             tc_fence_after();
             if (tr) { const long long n = clock64(); t_s += n - tq; tq = n; }
-            const uint32_t s_addr = tmem_base + lane_addr + (uint32_t)(j & 1) * 128u;
-            const int nvalid = P.Lk - j * 128;                               // >= 1
-            // the whole logit row of this thread comes out of TMEM once (four x32 loads in flight, one wait) and stays in registers
-            float sv[128];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) tc_ld32_nowait(s_addr + c * 32, sv + c * 32);
+            const uint32_t s_addr = tmem_base + lane_addr + (uint32_t)(j & 1) * 128u + (uint32_t)wg * 64u;
+            const int nvalid = P.Lk - j * 128 - wg * 64;                     // valid keys of this half (may be <= 0 in the last block)
+            float sv[64];
+            tc_ld32_nowait(s_addr, sv);
+            tc_ld32_nowait(s_addr + 32, sv + 32);
             tc_wait_ld();
             if (tr) { const long long n = clock64(); t_ld += n - tq; tq = n; }
-            if (nvalid < 128) {
+            if (nvalid < 64) {
 #pragma unroll
-                for (int i = 0; i < 128; ++i)
+                for (int i = 0; i < 64; ++i)
                     if (i >= nvalid) sv[i] = -INFINITY;
             }
             float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-            for (int i = 0; i < 128; i += 4) {
+            for (int i = 0; i < 64; i += 4) {
                 mx[0] = fmaxf(mx[0], sv[i]); mx[1] = fmaxf(mx[1], sv[i + 1]); mx[2] = fmaxf(mx[2], sv[i + 2]); mx[3] = fmaxf(mx[3], sv[i + 3]);
             }
-            const float mb = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * sl2;     // scale > 0
-            // raise the reference maximum only when some row of the warp outgrew it by 2^8 (P stays below 256 otherwise)
+            const float mpart = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+            // (one 1 KB exchange buffer, hence the second barrier: shared memory is full at D = 256)
+            xch[wg][r] = mpart;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            const float mb = fmaxf(mpart, xch[wg ^ 1][r]) * sl2;             // scale > 0; key 0 of the block is valid, so mb is finite
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            // raise the reference maximum only when some row of the warp outgrew it by 2^8 (P stays below 256 otherwise); the
+            // partner warp sees the same maxima and the same history, i.e. takes the same decision
             const bool raise = __any_sync(0xffffffffu, mb > m_run + 8.f);
             float alpha = 1.f;
             if (raise) {
@@ -450,38 +464,38 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             // P = exp2(S * scale * log2(e) - m), rounded to bf16; masked keys (-inf) give exactly 0.  The row sum is taken over
             // the ROUNDED probabilities the tensor core multiplies, so that sum_j P_ij / l_i = 1 holds for what is actually
             // accumulated (constant values come back unchanged).
-            uint32_t pk[64];
+            uint32_t pk[32];
             float ls[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int i = 0; i < 64; ++i) {
+            for (int i = 0; i < 32; ++i) {
                 const float p0 = ex2(fmaf(sv[2 * i], sl2, -m_run)), p1 = ex2(fmaf(sv[2 * i + 1], sl2, -m_run));
                 const uint32_t w = pack_bf16x2(p0, p1);
                 pk[i] = w;
                 ls[i & 1] += __uint_as_float(w << 16);
                 ls[2 + (i & 1)] += __uint_as_float(w & 0xffff0000u);
             }
-            const float lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
-            l_run += lsum;
+            l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             if (tr) { const long long n = clock64(); t_math += n - tq; tq = n; }
             if (j > 0) {
                 mbar_wait(pv_done, (j - 1) & 1);                             // P is single-buffered; the accumulator is at rest
                 tc_fence_after();
                 if (raise) {
-                    for (int c = 0; c < P.DV / 16; ++c) {
+                    for (int c = 0; c < hdv / 16; ++c) {
                         float v[16];
-                        tc_ld16(tmem_o + lane_addr + c * 16, v);
+                        const uint32_t a = tmem_o + lane_addr + (uint32_t)(wg * hdv + c * 16);
+                        tc_ld16(a, v);
 #pragma unroll
                         for (int i = 0; i < 16; ++i) v[i] *= alpha;
-                        tc_st16(tmem_o + lane_addr + c * 16, v);
+                        tc_st16(a, v);
                     }
                     tc_wait_st();
                 }
             }
             if (tr) { const long long n = clock64(); t_pv += n - tq; tq = n; }
-            // P tile: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of its 128-byte row (SWIZZLE_128B)
+            // this warpgroup's 64-key P tile: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of its 128-byte row (SWIZZLE_128B)
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const uint32_t addr = p_row + (uint32_t)(c >> 3) * kTileBytes + ((((uint32_t)c & 7u) ^ sw) << 4);
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t addr = p_row + (uint32_t)wg * kTileBytes + ((((uint32_t)c) ^ sw) << 4);
                 asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]),
                              "r"(pk[4 * c + 3])
                              : "memory");
@@ -495,16 +509,20 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 256, SINGLE ? 4 : 1) attn_umma_
             P.trace[0] = clock64() - t0; P.trace[1] = t_s; P.trace[2] = t_ld; P.trace[3] = t_math; P.trace[4] = t_pv; P.trace[5] = t_p;
             P.trace[6] = nkb;
         }
+        // the row sum is the sum of the two warpgroups' partial sums (same reference maximum on both sides)
+        xch[wg][r] = l_run;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float inv = 1.f / (l_run + xch[wg ^ 1][r]);
         mbar_wait(pv_done, (nkb - 1) & 1);
         tc_fence_after();
-        const float inv = 1.f / l_run;
-        for (int c = 0; c < P.DV / 16; ++c) {
+        for (int c = 0; c < hdv / 16; ++c) {
             float v[16];
-            tc_ld16(tmem_o + lane_addr + c * 16, v);
+            tc_ld16(tmem_o + lane_addr + (uint32_t)(wg * hdv + c * 16), v);
             if (valid) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    reinterpret_cast<float4*>(orow + c * 16)[i] = make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
+                    reinterpret_cast<float4*>(orow + wg * hdv + c * 16)[i] =
+                        make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
             }
         }
         }
@@ -623,7 +641,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
         if (te && te[0] == '1') {
             cudaMalloc((void**)&P.trace, 8 * sizeof(long long));
             cudaMemset(P.trace, 0, 8 * sizeof(long long));
-            attn_umma_kernel<false><<<grid, 256, smem, stream>>>(P);
+            attn_umma_kernel<false><<<grid, 384, smem, stream>>>(P);
             cudaDeviceSynchronize();
             long long t[8];
             cudaMemcpy(t, P.trace, sizeof(t), cudaMemcpyDeviceToHost);
@@ -633,7 +651,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
                     "wait PV %.0f + P store/fence/arrive %.0f\n", Lq, Lk, D, t[0] / n, t[1] / n, t[2] / n, t[3] / n, t[4] / n, t[5] / n);
             return cudaGetLastError();
         }
-        attn_umma_kernel<false><<<grid, 256, smem, stream>>>(P);
+        attn_umma_kernel<false><<<grid, 384, smem, stream>>>(P);
     }
     return cudaGetLastError();
 }
