@@ -203,6 +203,11 @@ def run_ours(args):
             raise SystemExit("bench.py --gpus %d must be launched with torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # libraries may write to the C-level stdout (NCCL prints its version line there under NCCL_DEBUG=VERSION): keep fd 1 clean for
+    # the ONE JSON line by pointing it at stderr until that line is printed
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -323,7 +328,10 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "patches/s", "cores": threads, "kind": "port",
                                     "sample": "1 patch of the workload (%d-band %dx%d, %d NFE), B=1, oracle faithful=True, %.1f s"
                                               % (N, P, P, args.solver_steps + 1, sec)}
+        sys.stdout.flush()
+        os.dup2(_real_stdout, 1)
         print(json.dumps(line))
+        sys.stdout.flush()
         sys.stdout.flush()
     if world > 1:
         dist.barrier()
