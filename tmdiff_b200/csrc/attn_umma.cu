@@ -244,8 +244,12 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     mbar_wait(k_empty(s), ph);
                     mbar_expect_tx(k_full(s), P.stage_bytes);
                     const uint32_t dst = st_base + s * P.stage_bytes;
-                    for (int c = 0; c < kch; ++c) tma_load_3d(dst + (uint32_t)c * kTileBytes, &P.tmK, k_full(s), (kc + c) * 64, j * 128, bh);
-                    if (!P.q_resident) tma_load_3d(dst + kTileBytes, &P.tmQ, k_full(s), kc * 64, q0, bh);      // (kch = 1 when Q is streamed)
+                    // a stage holds kch K chunks; when Q is streamed, kch (K chunk, Q chunk) pairs
+                    const uint32_t pitch = P.q_resident ? kTileBytes : 2 * kTileBytes;
+                    for (int c = 0; c < kch; ++c) {
+                        tma_load_3d(dst + (uint32_t)c * pitch, &P.tmK, k_full(s), (kc + c) * 64, j * 128, bh);
+                        if (!P.q_resident) tma_load_3d(dst + (uint32_t)c * pitch + kTileBytes, &P.tmQ, k_full(s), (kc + c) * 64, q0, bh);
+                    }
                     if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
                 }
         }
@@ -283,7 +287,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     mbar_wait(k_full(ks), kph);
                     tc_fence_after();
                     for (int c = 0; c < P.kch; ++c) {
-                        const uint32_t b_lo = st_lo0 + ks * stage16 + (uint32_t)c * tile16;
+                        const uint32_t b_lo = st_lo0 + ks * stage16 + (uint32_t)c * (P.q_resident ? tile16 : 2 * tile16);
                         const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)(kc + c) * tile16 : b_lo + tile16;
 #pragma unroll
                         for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | c | k));
@@ -639,7 +643,11 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
             P.kch = P.nkc <= 3 ? P.nkc : (P.nkc % 2 == 0 ? 2 : 1);
             P.stage_bytes = (uint32_t)P.kch * kTileBytes;
         }
-        P.NS = P.q_resident ? (6 / P.kch > 2 ? 6 / P.kch : 2) : 5;
+        else if (P.nkc % 2 == 0) {
+            P.kch = 2;
+            P.stage_bytes = 4 * kTileBytes;
+        }
+        P.NS = P.q_resident ? (6 / P.kch > 2 ? 6 / P.kch : 2) : (P.kch == 2 ? 2 : 5);
         P.v_bytes = (uint32_t)P.DV * 256u;
         P.NVB = P.DV <= 128 ? 2 : 1;
         P.tmem_cols = 512;
