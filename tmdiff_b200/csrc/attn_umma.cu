@@ -31,7 +31,7 @@ namespace tmd {
 
 namespace {
 
-constexpr int kStagesMax = 6;
+constexpr int kStagesMax = 4;
 constexpr uint32_t kTileBytes = 128 * 128;      // [128 rows][64 bf16]: one swizzled K-major operand tile
 
 struct AttnParams {
@@ -40,7 +40,6 @@ struct AttnParams {
     int BH, Lq, Lk, D, DV;
     int nkc, nkb;                 // 64-wide chunks of D; 128-key blocks
     int q_resident, NS, NVB;
-    int kch;                      // 64-wide K chunks per ring stage (one barrier round trip per stage: fewer, larger stages)
     int ndv;                      // SINGLE: DV-wide output chunks one CTA walks (the other mode spreads them over gridDim.y)
     uint32_t ab_bytes;            // shared memory of the Q / K region (SINGLE: P is written over it once the logits are complete)
     uint32_t tmem_cols;
@@ -134,24 +133,6 @@ __device__ __forceinline__ void tc_st16(uint32_t taddr, const float v[16]) {
           "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])), "r"(__float_as_uint(v[15]))
         : "memory");
 }
-// A operand from TMEM (P, packed bf16 pairs: column i of a lane holds keys 2i, 2i+1 of that query row), B from shared memory
-__device__ __forceinline__ void tc_mma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tc_st32_u(uint32_t taddr, const uint32_t* v) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
-        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
-          "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]),
-          "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-        : "memory");
-}
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) {
     float y;
@@ -191,7 +172,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
     const uint32_t q_base = smem_base;
     const uint32_t st_base = q_base + (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u);
     const uint32_t p_base = SINGLE ? q_base : q_base + P.ab_bytes;
-    const uint32_t v_base = q_base + P.ab_bytes;       // (long sequences keep P in TMEM: no shared-memory P tile)
+    const uint32_t v_base = q_base + P.ab_bytes + (SINGLE ? 0u : 2 * kTileBytes);
     const uint32_t bar0 = smem_u32(bars);
     auto k_full = [&](int s) { return bar0 + 8u * s; };
     auto k_empty = [&](int s) { return bar0 + 8u * (kStagesMax + s); };
@@ -238,18 +219,13 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 for (int kc = 0; kc < nkc; ++kc) tma_load_3d(q_base + (uint32_t)kc * kTileBytes, &P.tmQ, q_full, kc * 64, q0, bh);
             }
             uint32_t s = 0, ph = 1;
-            const int kch = P.kch;
             for (int j = 0; j < nkb; ++j)
-                for (int kc = 0; kc < nkc; kc += kch) {
+                for (int kc = 0; kc < nkc; ++kc) {
                     mbar_wait(k_empty(s), ph);
                     mbar_expect_tx(k_full(s), P.stage_bytes);
                     const uint32_t dst = st_base + s * P.stage_bytes;
-                    // a stage holds kch K chunks; when Q is streamed, kch (K chunk, Q chunk) pairs
-                    const uint32_t pitch = P.q_resident ? kTileBytes : 2 * kTileBytes;
-                    for (int c = 0; c < kch; ++c) {
-                        tma_load_3d(dst + (uint32_t)c * pitch, &P.tmK, k_full(s), (kc + c) * 64, j * 128, bh);
-                        if (!P.q_resident) tma_load_3d(dst + (uint32_t)c * pitch + kTileBytes, &P.tmQ, k_full(s), (kc + c) * 64, q0, bh);
-                    }
+                    tma_load_3d(dst, &P.tmK, k_full(s), kc * 64, j * 128, bh);
+                    if (!P.q_resident) tma_load_3d(dst + kTileBytes, &P.tmQ, k_full(s), kc * 64, q0, bh);
                     if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
                 }
         }
@@ -281,17 +257,13 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             if (P.q_resident) mbar_wait(q_full, 0);
             auto issue_qk = [&](int j) {
                 const uint32_t d = tmem_base + (uint32_t)(j & 1) * 128u;
-                // one wait / commit round trip per STAGE: at one 64-wide chunk (4 MMAs = 256 tensor cycles) per stage the round trip
-                // (~250 cycles) kept the pipe half idle -- a fixed ~1700 cycles per key block on top of the MMA time
-                for (int kc = 0; kc < nkc; kc += P.kch) {
+                for (int kc = 0; kc < nkc; ++kc) {
                     mbar_wait(k_full(ks), kph);
                     tc_fence_after();
-                    for (int c = 0; c < P.kch; ++c) {
-                        const uint32_t b_lo = st_lo0 + ks * stage16 + (uint32_t)c * (P.q_resident ? tile16 : 2 * tile16);
-                        const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)(kc + c) * tile16 : b_lo + tile16;
+                    const uint32_t b_lo = st_lo0 + ks * stage16;
+                    const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)kc * tile16 : b_lo + tile16;
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | c | k));
-                    }
+                    for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | k));
                     tc_commit(k_empty(ks));
                     if (++ks == (uint32_t)P.NS) { ks = 0; kph ^= 1; }
                 }
@@ -328,11 +300,9 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     const int keys = P.Lk - j * 128;
                     const int ksteps = keys >= 128 ? 8 : (keys + 15) >> 4;
                     const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
-                    // P(j) sits in TMEM over the logits it was computed from (first 64 columns of buffer j & 1): A operand from TMEM
-                    const uint32_t p_tm = tmem_base + (uint32_t)(j & 1) * 128u;
                     for (int k = 0; k < ksteps; ++k) {
                         const uint32_t blk = k >> 2, kk = k & 3;
-                        tc_mma_bf16_ts(tmem_o, p_tm + (uint32_t)k * 8u, sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
+                        tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
                     }
                     tc_commit(v_empty(vb));
                     tc_commit(pv_done);
@@ -506,10 +476,10 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             }
             l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
             if (tr) { const long long n = clock64(); t_math += n - tq; tq = n; }
-            if (j > 0 && raise) {
-                mbar_wait(pv_done, (j - 1) & 1);                             // the accumulator is at rest
+            if (j > 0) {
+                mbar_wait(pv_done, (j - 1) & 1);                             // P is single-buffered; the accumulator is at rest
                 tc_fence_after();
-                {
+                if (raise) {
                     for (int c = 0; c < hdv / 16; ++c) {
                         float v[16];
                         const uint32_t a = tmem_o + lane_addr + (uint32_t)(wg * hdv + c * 16);
@@ -522,12 +492,15 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 }
             }
             if (tr) { const long long n = clock64(); t_pv += n - tq; tq = n; }
-            // P goes back into TMEM over the block's logits (packed bf16 pairs: keys 2i, 2i+1 of a row in column i of its lane, this
-            // warpgroup's 64 keys in columns wg*32 .. wg*32+31): the tensor core takes its A operand from there.  Both warpgroups
-            // had their logits in registers before the exchange barrier above, so nothing still needed is overwritten.  No shared-
-            // memory P tile, no proxy fence -- and 32 KB more shared memory for the K ring (the K / V stream bounds D = 256).
-            tc_st32_u(tmem_base + lane_addr + (uint32_t)(j & 1) * 128u + (uint32_t)wg * 32u, pk);
-            tc_wait_st();
+            // this warpgroup's 64-key P tile: 16-byte chunk c of row r sits at chunk (c ^ (r & 7)) of its 128-byte row (SWIZZLE_128B)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t addr = p_row + (uint32_t)wg * kTileBytes + ((((uint32_t)c) ^ sw) << 4);
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]),
+                             "r"(pk[4 * c + 3])
+                             : "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> the tensor core's async-proxy reads
             tc_fence_before();
             mbar_arrive(p_full);
             if (tr) t_p += clock64() - tq;
@@ -617,7 +590,6 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     P.nkc = D / 64;
     P.nkb = (Lk + 127) / 128;
     P.q_resident = D <= 256;
-    P.kch = 1;
     P.stage_bytes = P.q_resident ? kTileBytes : 2 * kTileBytes;
     size_t smem;
     if (single) {
@@ -639,21 +611,13 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     } else {
         P.DV = D <= 256 ? D : (D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64));
         P.ndv = 1;
-        if (P.q_resident) {
-            P.kch = P.nkc <= 3 ? P.nkc : (P.nkc % 2 == 0 ? 2 : 1);
-            P.stage_bytes = (uint32_t)P.kch * kTileBytes;
-        }
-        else if (P.nkc % 2 == 0) {
-            P.kch = 2;
-            P.stage_bytes = 4 * kTileBytes;
-        }
-        P.NS = P.q_resident ? (6 / P.kch > 2 ? 6 / P.kch : 2) : (P.kch == 2 ? 2 : 5);
+        P.NS = P.q_resident ? 4 : 3;
         P.v_bytes = (uint32_t)P.DV * 256u;
         P.NVB = P.DV <= 128 ? 2 : 1;
         P.tmem_cols = 512;
         auto need = [&]() {
             P.ab_bytes = (P.q_resident ? (uint32_t)P.nkc * kTileBytes : 0u) + (uint32_t)P.NS * P.stage_bytes;
-            return 1024 + (size_t)P.ab_bytes + (size_t)P.NVB * P.v_bytes;
+            return 1024 + (size_t)P.ab_bytes + 2 * kTileBytes + (size_t)P.NVB * P.v_bytes;
         };
         while (P.NS > 2 && need() > (size_t)smem_limit[0]) --P.NS;
         smem = need();
