@@ -40,6 +40,7 @@ struct AttnParams {
     int BH, Lq, Lk, D, DV;
     int nkc, nkb;                 // 64-wide chunks of D; 128-key blocks
     int q_resident, NS, NVB;
+    int kch;                      // 64-wide K chunks per ring stage (one barrier round trip per stage: fewer, larger stages)
     int ndv;                      // SINGLE: DV-wide output chunks one CTA walks (the other mode spreads them over gridDim.y)
     uint32_t ab_bytes;            // shared memory of the Q / K region (SINGLE: P is written over it once the logits are complete)
     uint32_t tmem_cols;
@@ -219,13 +220,18 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 for (int kc = 0; kc < nkc; ++kc) tma_load_3d(q_base + (uint32_t)kc * kTileBytes, &P.tmQ, q_full, kc * 64, q0, bh);
             }
             uint32_t s = 0, ph = 1;
+            const int kch = P.kch;
+            // a stage holds kch K chunks; when Q is streamed, kch (K chunk, Q chunk) pairs
+            const uint32_t pitch = P.q_resident ? kTileBytes : 2 * kTileBytes;
             for (int j = 0; j < nkb; ++j)
-                for (int kc = 0; kc < nkc; ++kc) {
+                for (int kc = 0; kc < nkc; kc += kch) {
                     mbar_wait(k_empty(s), ph);
                     mbar_expect_tx(k_full(s), P.stage_bytes);
                     const uint32_t dst = st_base + s * P.stage_bytes;
-                    tma_load_3d(dst, &P.tmK, k_full(s), kc * 64, j * 128, bh);
-                    if (!P.q_resident) tma_load_3d(dst + kTileBytes, &P.tmQ, k_full(s), kc * 64, q0, bh);
+                    for (int c = 0; c < kch; ++c) {
+                        tma_load_3d(dst + (uint32_t)c * pitch, &P.tmK, k_full(s), (kc + c) * 64, j * 128, bh);
+                        if (!P.q_resident) tma_load_3d(dst + (uint32_t)c * pitch + kTileBytes, &P.tmQ, k_full(s), (kc + c) * 64, q0, bh);
+                    }
                     if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
                 }
         }
@@ -257,13 +263,17 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             if (P.q_resident) mbar_wait(q_full, 0);
             auto issue_qk = [&](int j) {
                 const uint32_t d = tmem_base + (uint32_t)(j & 1) * 128u;
-                for (int kc = 0; kc < nkc; ++kc) {
+                // one wait / commit round trip per STAGE: at one 64-wide chunk (4 MMAs = 256 tensor cycles) per stage the round trip
+                // (~250 cycles) kept the pipe half idle -- a fixed ~1700 cycles per key block on top of the MMA time
+                for (int kc = 0; kc < nkc; kc += P.kch) {
                     mbar_wait(k_full(ks), kph);
                     tc_fence_after();
-                    const uint32_t b_lo = st_lo0 + ks * stage16;
-                    const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)kc * tile16 : b_lo + tile16;
+                    for (int c = 0; c < P.kch; ++c) {
+                        const uint32_t b_lo = st_lo0 + ks * stage16 + (uint32_t)c * (P.q_resident ? tile16 : 2 * tile16);
+                        const uint32_t a_lo = P.q_resident ? q_lo0 + (uint32_t)(kc + c) * tile16 : b_lo + tile16;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | k));
+                        for (int k = 0; k < 4; ++k) tc_mma_bf16(d, sdesc(a_lo + k * 2), sdesc(b_lo + k * 2), P.idesc_qk, (uint32_t)(kc | c | k));
+                    }
                     tc_commit(k_empty(ks));
                     if (++ks == (uint32_t)P.NS) { ks = 0; kph ^= 1; }
                 }
@@ -590,6 +600,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     P.nkc = D / 64;
     P.nkb = (Lk + 127) / 128;
     P.q_resident = D <= 256;
+    P.kch = 1;
     P.stage_bytes = P.q_resident ? kTileBytes : 2 * kTileBytes;
     size_t smem;
     if (single) {
@@ -611,7 +622,17 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     } else {
         P.DV = D <= 256 ? D : (D % 256 == 0 ? 256 : (D % 128 == 0 ? 128 : 64));
         P.ndv = 1;
-        P.NS = P.q_resident ? 4 : 3;
+        if (P.q_resident) {
+            P.kch = P.nkc <= 3 ? P.nkc : (P.nkc % 2 == 0 ? 2 : 1);
+            P.stage_bytes = (uint32_t)P.kch * kTileBytes;
+            P.NS = 4 / P.kch > 2 ? 4 / P.kch : 2;
+        } else if (P.nkc % 2 == 0) {
+            P.kch = 2;
+            P.stage_bytes = 4 * kTileBytes;
+            P.NS = 2;
+        } else {
+            P.NS = 3;
+        }
         P.v_bytes = (uint32_t)P.DV * 256u;
         P.NVB = P.DV <= 128 ? 2 : 1;
         P.tmem_cols = 512;
