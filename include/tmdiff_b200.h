@@ -125,10 +125,13 @@ int tmd_denoise(tmd_handle h, const float* x_t_dev, const float* t_input_dev, fl
 
 /* DPM_Solver.sample(x_T, ...) (core/dpm_solver_pytorch.py:1081-1289) as a straight-line program of
  * evaluations and updates prepared by the host (tmdiff_b200/dpm_solver.py).  x_T / out: device fp32
- * [B,bands,H,W].  trace_dev (optional, may be NULL): receives the raw network output of every
- * evaluation, [n_eval, B, bands, H, W] ([n_eval, 2B, ...] when plan->cfg). */
-int tmd_sample(tmd_handle h, const float* x_T_dev, const tmd_plan* plan, float* out_dev, float* trace_dev,
-               void* stream);
+ * [B,bands,H,W]; the four extents are checked against the condition bound by tmd_precompute_condition
+ * (B is half of the bound patches when plan->cfg).  Patches of any size (the per-sample quantile is a
+ * radix select over several CTAs).  trace_dev (optional, may be NULL): receives the raw network output
+ * of every evaluation, [n_eval, B, bands, H, W] ([n_eval, 2B, ...] when plan->cfg); trace_x_dev
+ * (optional): the x each evaluation was given, [n_eval, B, bands, H, W]. */
+int tmd_sample(tmd_handle h, const float* x_T_dev, int32_t B, int32_t bands, int32_t H, int32_t W, const tmd_plan* plan,
+               float* out_dev, float* trace_dev, float* trace_x_dev, void* stream);
 
 /* One ancestral DDPM step after the denoiser call (GeneralDiffusion.p_sample, GeneralModel/diffusion_general.py:134-138,
  * 155-174, 196-201): x0 = c_recip*x - c_recipm1*eps, clamped to [-1,1] when clip; out = coef1*x0 + coef2*x + sigma*z.
@@ -225,7 +228,11 @@ enum { TMD_K_CONV3 = 0,        /* 3x3x3 implicit-GEMM convolutions (tensor-bound
        TMD_K_SOLVER = 3,       /* x0 conversion + dynamic threshold, dpmsolver++ updates          */
        TMD_K_COND = 4,         /* time-embedding MLP + per-layer bias table                       */
        TMD_NUM_KINDS = 5 };
-typedef struct { double ms, flops, bytes; int64_t launches; } tmd_profile_kind;
+typedef struct {
+    double ms, flops, bytes;
+    int64_t launches;
+    double flops_executed;   /* FLOPs the kernels issued: the tcgen05 conv skips the zero-padding band planes that `flops` counts */
+} tmd_profile_kind;
 typedef struct { tmd_profile_kind kind[TMD_NUM_KINDS]; } tmd_profile;
 int tmd_profile_begin(tmd_handle h);
 /* csv_path (optional, may be NULL): also write one line per launch (label, ms, flops, bytes) */

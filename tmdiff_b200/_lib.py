@@ -46,7 +46,8 @@ KIND_NAMES = ("conv3x3x3", "conv1x1x1", "elementwise", "solver", "conditioning")
 
 
 class ProfileKind(C.Structure):
-    _fields_ = [("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double), ("launches", C.c_int64)]
+    _fields_ = [("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double), ("launches", C.c_int64),
+                ("flops_executed", C.c_double)]
 
 
 class Profile(C.Structure):
@@ -67,7 +68,7 @@ SIGNATURES = {
     "tmd_precompute_condition": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32,
                                            C.c_int32, _P]),
     "tmd_denoise": (C.c_int, [_P, _P, _P, _P, _P]),
-    "tmd_sample": (C.c_int, [_P, _P, C.POINTER(Plan), _P, _P, _P]),
+    "tmd_sample": (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(Plan), _P, _P, _P, _P]),
     "tmd_dwt2d": (C.c_int, [_P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
     "tmd_idwt2d": (C.c_int, [_P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
     "tmd_conv3d_mod": (C.c_int, [_P, _P, _P, _P, _P] + [C.c_int32] * 8 + [_P]),

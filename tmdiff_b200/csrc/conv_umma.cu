@@ -964,14 +964,19 @@ bool umma_disabled() {
     return off;
 }
 
+// per device: a process may hold engines on several GPUs (the Python layer rebuilds the engine when the device changes)
+constexpr int kMaxDevices = 64;
 int sm_count() {
-    static const int n = []() {
-        int dev = 0, v = 148;
-        cudaGetDevice(&dev);
+    static int n[kMaxDevices] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= kMaxDevices) dev = 0;
+    if (!n[dev]) {
+        int v = 148;
         cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-        return v;
-    }();
-    return n;
+        n[dev] = v;
+    }
+    return n[dev];
 }
 
 }  // namespace
@@ -1005,6 +1010,15 @@ bool conv_umma_supported(const ConvOp& op) {
     }
     if (op.W < 2 || op.H < 2) return false;
     return true;
+}
+
+bool conv_umma_skips_padding_planes(const ConvOp& op) {
+    if (op.taps != 27) return false;
+    if (op.H >= 16 && op.W >= 8) return true;                       // REUSE: planes outside [0, N) are neither loaded nor issued
+    // SIMPLE: only when a box holds one band plane (the whole-padding boxes are skipped)
+    const int TW = floor_pow2(op.W < 16 ? op.W : 16), TH = floor_pow2(op.H < 128 / TW ? op.H : 128 / TW);
+    const int TN = floor_pow2(op.N < 128 / (TW * TH) ? op.N : 128 / (TW * TH));
+    return TN == 1 || op.B >= 128 / (TW * TH);
 }
 
 UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
@@ -1175,7 +1189,12 @@ KernelFn pick_kernel(const UmmaParams& p) {
 
 cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t stream) {
     (void)op;
-    static bool attr_set = false;
+    // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device setting
+    static bool attr_done[kMaxDevices] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= kMaxDevices) dev = 0;
+    bool& attr_set = attr_done[dev];
     if (!attr_set) {
         KernelFn all[7] = {conv_umma_kernel<1, 8, 2, true>, conv_umma_kernel<1, 4, 2, true>, conv_umma_kernel<1, 2, 2, true>,
                            conv_umma_kernel<1, 2, 2, false>, conv_umma_kernel<1, 1, 2, false>, conv_umma_kernel<0, 1, 4, false>,

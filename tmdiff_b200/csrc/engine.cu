@@ -63,7 +63,7 @@ struct HostTensor {
 struct ProfSpan {
     cudaEvent_t a, b;
     int kind;
-    double flops, bytes;
+    double flops, bytes, flops_exec;
     const char* label;
 };
 using LaunchFn = std::function<cudaError_t(cudaStream_t)>;
@@ -71,6 +71,7 @@ struct Launch {       // one kernel launch of the plan + what it costs algorithm
     LaunchFn fn;
     int kind = TMD_K_ELEMENTWISE;
     double flops = 0.0, bytes = 0.0;
+    double flops_exec = -1.0;   // FLOPs the kernel issues (< flops where zero-padding work is skipped); -1: same as flops
     std::string label;
     cudaError_t operator()(cudaStream_t s) const { return fn(s); }
 };
@@ -90,7 +91,9 @@ struct tmd_engine {
     std::map<std::string, int> time_off, text_off;
     int time_rows = 0, text_rows = 0;
     bool finalized = false, text_dirty = true;
-    std::vector<void*> allocs;
+    std::vector<void*> allocs;      // lives as long as the handle
+    std::vector<void*> w_allocs;    // repacked weights and tables: released by the next tmd_finalize_weights
+    bool weight_scope = false;
 
     // conditioning
     float *d_freqs = nullptr, *d_e_w1 = nullptr, *d_e_b1 = nullptr, *d_e_w2 = nullptr, *d_e_b2 = nullptr;
@@ -119,6 +122,7 @@ struct tmd_engine {
     float* slots[TMD_NUM_SLOTS] = {};
     float* d_out = nullptr;
     float* d_xdup = nullptr;            // [x | x] for classifier-free-guidance plans (x evaluated against both condition halves)
+    void* d_th_ws = nullptr;            // radix-select scratch of the dynamic threshold (solver.cu)
     // tmd_sample: the time tables of every evaluation of a plan are computed by ONE launch up front
     // (t is a host scalar per evaluation and shared by the batch); each evaluation then broadcasts its row.
     float *d_tb_all = nullptr, *d_tin_all = nullptr;
@@ -139,7 +143,7 @@ struct tmd_engine {
 
     template <typename T> int dmalloc(T** p, size_t n) {
         CK(cudaMalloc((void**)p, n * sizeof(T)));
-        allocs.push_back(*p);
+        (weight_scope ? w_allocs : allocs).push_back(*p);
         return 0;
     }
     template <typename T> int upload(T** p, const std::vector<T>& v) {
@@ -256,6 +260,7 @@ extern "C" int tmd_destroy(tmd_handle h) {
     if (!h) return 0;
     for (auto* p : h->plans) conv_umma_plan_destroy(p);
     for (void* p : h->allocs) cudaFree(p);
+    for (void* p : h->w_allocs) cudaFree(p);
     for (auto& sp : h->prof_events) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     if (h->arena) cudaFree(h->arena);
     h->drop_graphs();
@@ -322,6 +327,17 @@ extern "C" int tmd_finalize_weights(tmd_handle h) {
         if (!h->host.count(it.first)) return fail("tmd_finalize_weights: missing weight '%s'", it.first.c_str());
     if (h->freqs_host.empty()) return fail("tmd_finalize_weights: tmd_set_time_frequencies was not called");
     CK(cudaSetDevice(h->device));
+    // a re-finalize (second load_state_dict, checkpoint sweep) replaces every repacked tensor: drop what the previous one
+    // uploaded, and the launch lists / tensor maps that point into it
+    CK(cudaDeviceSynchronize());
+    for (auto* p : h->plans) conv_umma_plan_destroy(p);
+    h->plans.clear();
+    h->pre_ops.clear();
+    h->step_ops.clear();
+    for (void* p : h->w_allocs) cudaFree(p);
+    h->w_allocs.clear();
+    struct Scope { tmd_engine* e; ~Scope() { e->weight_scope = false; } } scope{h};
+    h->weight_scope = true;
     const int E = h->cfg.embed_dim;
     auto H = [&](const std::string& k) -> const std::vector<float>& { return h->host[k].data; };
 
@@ -394,11 +410,13 @@ extern "C" int tmd_finalize_weights(tmd_handle h) {
         if (h->upload(&h->d_p_w[i], H(std::string(pk[i]) + ".weight")) || h->upload(&h->d_p_b[i], H(std::string(pk[i]) + ".bias"))) return 1;
     const int MB = h->cfg.max_batch;
     if (!h->d_text) {
+        h->weight_scope = false;      // sized by the configuration, not by the weights: kept across re-finalizes
         if (h->dmalloc(&h->d_text, (size_t)TMD_NUM_SENSORS * 768) || h->dmalloc(&h->d_p_tmp0, (size_t)TMD_NUM_SENSORS * 4 * E) ||
             h->dmalloc(&h->d_p_tmp1, (size_t)TMD_NUM_SENSORS * 4 * E) || h->dmalloc(&h->d_prompt, (size_t)TMD_NUM_SENSORS * E) ||
             h->dmalloc(&h->d_tin, (size_t)MB) || h->dmalloc(&h->d_embed, (size_t)MB * E) || h->dmalloc(&h->d_sensor, (size_t)MB))
             return 1;
         CK(cudaMemset(h->d_text, 0, (size_t)TMD_NUM_SENSORS * 768 * sizeof(float)));
+        h->weight_scope = true;
     }
     if (h->dmalloc(&h->d_sc_sensor, (size_t)TMD_NUM_SENSORS * h->text_rows) || h->dmalloc(&h->d_tb, (size_t)MB * h->time_rows) ||
         h->dmalloc(&h->d_sc, (size_t)MB * h->text_rows) || h->dmalloc(&h->d_tb_all, (size_t)kMaxPlanEvals * h->time_rows) ||
@@ -514,6 +532,12 @@ struct Planner {
         if (cw2) bytes += nv * cw2->Ci * e->esize + (double)cw2->Ci * cw.Co * e->esize;
         if (out.pool.p) bytes += nv / 4 * cw.Co * e->esize;
         const int kind = cw.taps == 27 ? TMD_K_CONV3 : TMD_K_CONV1;
+        // issued FLOPs: the tcgen05 kernel neither loads nor multiplies the band planes outside [0, N) (zero padding of the
+        // band axis): of the 3N (plane, dz) pairs of a 3x3x3 conv 3N - 2 remain.  The algorithmic count above includes them,
+        // as the reference executes them.
+        double flops_exec = flops;
+        if (e->dtype == TMD_BF16 && cw.taps == 27 && conv_umma_supported(op) && conv_umma_skips_padding_planes(op))
+            flops_exec = 2.0 * nv * cw.Ci * cw.taps * cw.Co * (3.0 * N - 2.0) / (3.0 * N) + (cw2 ? 2.0 * nv * cw2->Ci * cw.Co : 0.0);
         char lb[160];
         snprintf(lb, sizeof(lb), "%s Ci=%d Co=%d L%d %s", wname.c_str(), cw.Ci, cw.Co, lvl,
                  mode == CONV_POOL ? "pool" : (mode == CONV_UPSAMPLE ? "up" : "same"));
@@ -526,6 +550,7 @@ struct Planner {
             if (!plan) { err = "tensor map creation failed"; return; }
             e->plans.push_back(plan);
             push(kind, flops, bytes, [op, plan](cudaStream_t s) { return conv_umma_bf16(op, plan, s); }, label + " umma");
+            ops->back().flops_exec = flops_exec;
         } else {
             push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_bf16(op, s); }, label + " simt");
         }
@@ -616,6 +641,9 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         for (int i = 0; i < TMD_NUM_SLOTS; ++i)
             if (e->dmalloc(&e->slots[i], v0)) return 1;
         if (e->dmalloc(&e->d_out, v0) || e->dmalloc(&e->d_xdup, v0)) return 1;
+        char* ws = nullptr;
+        if (e->dmalloc(&ws, threshold_workspace_bytes(e->cfg.max_batch))) return 1;
+        e->d_th_ws = ws;
     }
     Planner P{e, &e->pre_ops, B, N, H, W};
     {
@@ -795,7 +823,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
 
 // Profiling (tmd_profile_begin/end): every launch is bracketed by a CUDA event pair on the launching
 // stream; the pairs are resolved into per-kind totals at tmd_profile_end.
-int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t s, bool begin, const char* label = "") {
+int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t s, bool begin, const char* label = "", double flops_exec = -1.0) {
     if (!e->profiling) return 0;
     if (begin) {
         if (e->prof_used == e->prof_events.size()) {
@@ -806,6 +834,7 @@ int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t 
         }
         ProfSpan& sp = e->prof_events[e->prof_used];
         sp.kind = kind; sp.flops = flops; sp.bytes = bytes; sp.label = label;
+        sp.flops_exec = flops_exec < 0 ? flops : flops_exec;
         CK(cudaEventRecord(sp.a, s));
     } else {
         CK(cudaEventRecord(e->prof_events[e->prof_used].b, s));
@@ -816,7 +845,7 @@ int prof_mark(tmd_engine* e, int kind, double flops, double bytes, cudaStream_t 
 
 int run_ops(tmd_engine* e, std::vector<Launch>& ops, cudaStream_t s) {
     for (auto& op : ops) {
-        if (prof_mark(e, op.kind, op.flops, op.bytes, s, true, op.label.c_str())) return 1;
+        if (prof_mark(e, op.kind, op.flops, op.bytes, s, true, op.label.c_str(), op.flops_exec)) return 1;
         cudaError_t err = op(s);
         if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
         if (prof_mark(e, op.kind, op.flops, op.bytes, s, false)) return 1;
@@ -883,7 +912,8 @@ extern "C" int tmd_denoise(tmd_handle h, const float* x_t, const float* t_input_
 // The launch sequence of one plan: every evaluation's time table in one launch, then per step either one denoiser
 // evaluation + x0 conversion / dynamic threshold, or one solver update.  Touches engine-owned buffers only (unless a
 // trace is requested), so it can be captured into a CUDA graph.
-static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, int n_evals, bool pre_tb, cudaStream_t s) {
+static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, float* trace_x, int n_evals, bool pre_tb, cudaStream_t s) {
+    static const bool fuse_updates = !getenv("TMD_NO_FUSE_UPDATE");
     const bool cfg = plan->cfg != 0;
     const bool noise_type = plan->model_type == TMD_MODEL_NOISE;
     const int Bx = cfg ? h->B / 2 : h->B;      // patches being sampled
@@ -906,6 +936,7 @@ static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, int n_e
             if (!slot_ok(ev.src) || !slot_ok(ev.dst)) return fail("tmd_sample: bad slot in step %d", i);
             float* net_out = trace ? trace + (size_t)n_eval * n_net : h->d_out;
             const float* net_in = h->slots[ev.src];
+            if (trace_x) CK(cudaMemcpyAsync(trace_x + (size_t)n_eval * n, net_in, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
             if (cfg) {   // x_in = cat([x] * 2)  (:338)
                 CK(cudaMemcpyAsync(h->d_xdup, net_in, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
                 CK(cudaMemcpyAsync(h->d_xdup + n, net_in, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
@@ -913,12 +944,27 @@ static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, int n_e
             }
             h->tb_bcast_src = pre_tb ? h->d_tb_all + (size_t)n_eval * h->time_rows : nullptr;
             if (denoise_impl(h, net_in, nullptr, ev.t_input, net_out, s)) return 1;
-            if (prof_mark(h, TMD_K_SOLVER, 0, (cfg ? 6.0 : 5.0) * n * 4, s, true, "x0_threshold")) return 1;   // x, out in; x0 written, re-read, re-written
+            // the singlestep update that consumes this x0 rides in the threshold's last pass (north_star item 5: the solver
+            // update fused behind the evaluation; the per-sample quantile is why it cannot sit in the conv epilogue itself)
+            FusedUpdate fu{};
+            bool fused = false;
+            if (fuse_updates && i + 1 < plan->n_steps && plan->steps[i + 1].kind == 1 && plan->steps[i + 1].update.form == 0) {
+                const tmd_update& u = plan->steps[i + 1].update;
+                if (slot_ok(u.dst) && slot_ok(u.x) && slot_ok(u.m) && u.m1 < TMD_NUM_SLOTS && u.dst != ev.dst) {
+                    fu.dst = h->slots[u.dst]; fu.x = h->slots[u.x]; fu.m = h->slots[u.m]; fu.m1 = u.m1 >= 0 ? h->slots[u.m1] : nullptr;
+                    fu.c1 = u.c1; fu.c2 = u.c2; fu.c3 = u.c3;
+                    fused = true;
+                }
+            }
+            // x, out in; x0 written, re-read three times (L2), re-written; fused update: its operands and result
+            const double th_bytes = (cfg ? 4.0 : 3.0) * n * 4 + (fused ? (fu.m1 ? 3.0 : 2.0) * n * 4 : 0.0);
+            if (prof_mark(h, TMD_K_SOLVER, 0, th_bytes, s, true, fused ? "x0_threshold+update" : "x0_threshold")) return 1;
             CK(x0_threshold(h->slots[ev.src], net_out, cfg ? net_out + n : nullptr, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, noise_type,
-                            plan->guidance_scale, Bx, (int)n_per, plan->q_lo, plan->q_weight, plan->max_val, s));
+                            plan->guidance_scale, Bx, (int)n_per, plan->q_lo, plan->q_weight, plan->max_val, h->d_th_ws, fused ? &fu : nullptr, s));
             if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
-            ++h->launches;
+            h->launches += 4;
             ++n_eval;
+            if (fused) ++i;
         } else {
             const tmd_update& u = st.update;
             if (!slot_ok(u.dst) || !slot_ok(u.x) || !slot_ok(u.m) || u.m1 >= TMD_NUM_SLOTS) return fail("tmd_sample: bad slot in step %d", i);
@@ -944,7 +990,8 @@ static uint64_t fnv1a(uint64_t hsh, const void* p, size_t n) {
     return hsh;
 }
 
-extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, float* out, float* trace, void* stream) {
+extern "C" int tmd_sample(tmd_handle h, const float* x_T, int32_t B, int32_t bands, int32_t H, int32_t W, const tmd_plan* plan, float* out,
+                          float* trace, float* trace_x, void* stream) {
     if (!h || !x_T || !plan || !out || !plan->steps) return fail("tmd_sample: null argument");
     if (h->B == 0 || h->step_ops.empty()) return fail("tmd_sample: call tmd_precompute_condition first");
     cudaStream_t s = (cudaStream_t)stream;
@@ -954,7 +1001,11 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
     if (plan->model_type != TMD_MODEL_X_START && plan->model_type != TMD_MODEL_NOISE) return fail("tmd_sample: bad model_type %d", plan->model_type);
     const int Bx = cfg ? h->B / 2 : h->B;
     const size_t n_per = (size_t)h->N * h->H * h->W, n = n_per * Bx;
-    if (n_per > 51200) return fail("tmd_sample: %zu values per patch exceeds the in-shared-memory quantile select (51200)", n_per);
+    if (B != Bx || bands != h->N || H != h->H || W != h->W)
+        return fail("tmd_sample: x_T is [%d,%d,%d,%d] but the bound condition holds %d patches of [%d,%d,%d]%s", B, bands, H, W, Bx, h->N, h->H,
+                    h->W, cfg ? " (classifier-free guidance: half of the 2B bound patches)" : "");
+    if (n_per > (size_t)INT32_MAX) return fail("tmd_sample: patch too large");
+    if (plan->q_lo < 0 || (size_t)plan->q_lo >= n_per) return fail("tmd_sample: quantile position %d outside the patch (%zu values)", plan->q_lo, n_per);
     if (plan->result_slot < 0 || plan->result_slot >= TMD_NUM_SLOTS) return fail("tmd_sample: bad result slot");
 
     // every evaluation's t_input -> device (the time tables are then computed by one launch inside sample_body)
@@ -972,7 +1023,7 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
     static const bool graphs_on = !getenv("TMD_NO_GRAPH");
     cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(s, &capturing);
-    if (graphs_on && pre_tb && !trace && !h->profiling && capturing == cudaStreamCaptureStatusNone) {
+    if (graphs_on && pre_tb && !trace && !trace_x && !h->profiling && capturing == cudaStreamCaptureStatusNone) {
         uint64_t key = fnv1a(1469598103934665603ull, plan->steps, (size_t)plan->n_steps * sizeof(tmd_step));
         const int32_t scal[6] = {plan->n_steps, plan->result_slot, plan->q_lo, plan->model_type, plan->cfg, h->B};
         const float fsc[3] = {plan->q_weight, plan->max_val, plan->guidance_scale};
@@ -984,7 +1035,7 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
             if (!h->cap_stream) CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
             const int64_t l0 = h->launches;
             CK(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed));
-            const int rc = sample_body(h, plan, nullptr, n_evals, pre_tb, h->cap_stream);
+            const int rc = sample_body(h, plan, nullptr, nullptr, n_evals, pre_tb, h->cap_stream);
             cudaGraph_t graph = nullptr;
             const cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
             const int64_t counted = h->launches - l0;
@@ -1001,7 +1052,7 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, const tmd_plan* plan, 
         }
         CK(cudaGraphLaunch(g->exec, s));
         h->launches += g->launches;
-    } else if (sample_body(h, plan, trace, n_evals, pre_tb, s)) {
+    } else if (sample_body(h, plan, trace, trace_x, n_evals, pre_tb, s)) {
         return 1;
     }
     CK(cudaMemcpyAsync(out, h->slots[plan->result_slot], n * sizeof(float), cudaMemcpyDeviceToDevice, s));
@@ -1025,14 +1076,14 @@ extern "C" int tmd_profile_end(tmd_handle h, tmd_profile* out, const char* csv_p
     CK(cudaSetDevice(h->device));
     CK(cudaDeviceSynchronize());
     FILE* csv = csv_path ? fopen(csv_path, "w") : nullptr;
-    if (csv) fprintf(csv, "index,kind,label,ms,flops,bytes\n");
+    if (csv) fprintf(csv, "index,kind,label,ms,flops,bytes,flops_executed\n");
     for (size_t i = 0; i < h->prof_used; ++i) {
         const ProfSpan& sp = h->prof_events[i];
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, sp.a, sp.b));
-        if (csv) fprintf(csv, "%zu,%d,%s,%.6f,%.0f,%.0f\n", i, sp.kind, sp.label ? sp.label : "", ms, sp.flops, sp.bytes);
+        if (csv) fprintf(csv, "%zu,%d,%s,%.6f,%.0f,%.0f,%.0f\n", i, sp.kind, sp.label ? sp.label : "", ms, sp.flops, sp.bytes, sp.flops_exec);
         tmd_profile_kind& k = out->kind[sp.kind];
-        k.ms += ms; k.flops += sp.flops; k.bytes += sp.bytes; k.launches += 1;
+        k.ms += ms; k.flops += sp.flops; k.bytes += sp.bytes; k.launches += 1; k.flops_executed += sp.flops_exec;
     }
     if (csv) fclose(csv);
     h->prof_used = 0;
@@ -1065,8 +1116,12 @@ extern "C" int tmd_idwt2d(const float* ll, const float* lh, const float* hl, con
 extern "C" int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream) {
     if (!x0) return fail("tmd_dynamic_threshold: null argument");
     if (B <= 0 || n <= 0 || q_lo < 0 || q_lo >= n) return fail("tmd_dynamic_threshold: bad sizes");
-    if (n > 51200) return fail("tmd_dynamic_threshold: n=%d exceeds the in-shared-memory select limit (51200)", n);
-    CK(dynamic_threshold_inplace(x0, B, n, q_lo, q_weight, max_val, (cudaStream_t)stream));
+    cudaStream_t s = (cudaStream_t)stream;
+    void* ws = nullptr;
+    CK(cudaMallocAsync(&ws, threshold_workspace_bytes(B), s));
+    const cudaError_t err = dynamic_threshold_inplace(x0, B, n, q_lo, q_weight, max_val, ws, s);
+    cudaFreeAsync(ws, s);
+    if (err != cudaSuccess) return fail("tmd_dynamic_threshold: %s", cudaGetErrorString(err));
     return 0;
 }
 

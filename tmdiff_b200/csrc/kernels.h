@@ -13,6 +13,8 @@ cudaError_t conv_simt_f32(const ConvOp& op, cudaStream_t stream);
 cudaError_t conv_simt_bf16(const ConvOp& op, cudaStream_t stream);
 // tcgen05/TMA implicit GEMM; returns cudaErrorNotSupported when the shape is outside its envelope
 bool conv_umma_supported(const ConvOp& op);
+// true when the schedule chosen for `op` skips the band planes that are pure zero padding (instead of multiplying zeros)
+bool conv_umma_skips_padding_planes(const ConvOp& op);
 struct UmmaPlan;  // per-op TMA descriptors + launch geometry, built once
 UmmaPlan* conv_umma_plan_create(const ConvOp& op);
 void conv_umma_plan_destroy(UmmaPlan*);
@@ -56,9 +58,20 @@ cudaError_t broadcast_rows(const float* row, float* out, int B, int width, cudaS
 // ---- solver (solver.cu) ----
 // eps = (x - a*out)/s ; x0 = (x - s*eps)/a ; dynamic threshold (quantile 0.995, max 1) -> dst
 // out_c (optional): conditional half for classifier-free guidance, eps = eps_u + g*(eps_c - eps_u); noise_type: out is eps
+// ws: threshold_workspace_bytes(B) bytes of device scratch (radix-select histograms; any sample size, several CTAs per sample)
+// fu (optional): the dpmsolver++ singlestep update that consumes this x0, evaluated in the same pass as the clamp:
+//   fu->dst = (c1*x - c2*m) [+ c3*(m1 - m)],  m / m1 == dst meaning "the fresh x0"
+struct FusedUpdate {
+    float* dst;
+    const float* x;
+    const float* m;
+    const float* m1;    // null: no third term
+    float c1, c2, c3;
+};
+size_t threshold_workspace_bytes(int B);
 cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
-                         float g, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s);
-cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s);
+                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, const FusedUpdate* fu, cudaStream_t s);
+cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s);
 cudaError_t solver_update(float* dst, const float* x, const float* m, const float* m1, float c1, float c2, float c3, size_t n,
                           cudaStream_t s);
 cudaError_t solver_update_multistep(int form, float* dst, const float* x, const float* m, const float* m1, const float* m2, float c1,

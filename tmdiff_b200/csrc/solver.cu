@@ -9,8 +9,6 @@
 
 namespace tmd {
 
-constexpr int TH_THREADS = 1024;
-
 // noise_pred_fn (:296-306): the network output as eps.  noise_type: the output already is eps.
 __device__ __forceinline__ float eps_of(float x, float out, float alpha, float sigma, bool noise_type) {
     return noise_type ? out : __fdiv_rn(__fsub_rn(x, __fmul_rn(alpha, out)), sigma);
@@ -19,137 +17,282 @@ __device__ __forceinline__ float x0_of_eps(float x, float eps, float alpha, floa
     return __fdiv_rn(__fsub_rn(x, __fmul_rn(sigma, eps)), alpha);              // data_prediction_fn (:447-456)
 }
 
-// In-block bitonic sort, descending, P = power of two.
-__device__ void bitonic_desc(float* v, int P) {
-    for (int k = 2; k <= P; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = threadIdx.x; i < P; i += blockDim.x) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const float a = v[i], b = v[ixj];
-                    const bool desc = (i & k) == 0;
-                    if (desc ? (a < b) : (a > b)) { v[i] = b; v[ixj] = a; }
-                }
-            }
-            __syncthreads();
+// ------------------------------------------------------------------------------------------------
+// dynamic_thresholding_fn (:430-439): s = max(quantile(|x0|, q), max_val), x0 = clamp(x0, -s, s) / s
+//
+// torch.quantile interpolates linearly between the sorted positions q_lo and q_lo + 1, so two exact
+// order statistics per sample are needed.  They are found by a three-level radix select over the
+// bit pattern of |x0| (a non-negative float orders like its bits): 10 + 11 + 10 bits, one histogram
+// pass per level over the (L2-resident) x0, several CTAs per sample so that a batch of 64 patches
+// fills the machine and a patch of any size fits (no shared-memory copy of the sample).
+//
+//   th_first   x0 from (x, out) -> dst, histogram of bits [30:21]                    (level 0)
+//   th_level1  picks the level-0 bins of both ranks, histograms bits [20:10] of the values in them
+//   th_level2  picks the level-1 bins, histograms bits [9:0]
+//   th_apply   picks the level-2 bins = the exact values, interpolates as at::lerp does, clamps and
+//              divides; optionally also evaluates the solver update that consumes this x0
+//              (dpmsolver++ singlestep family, :589-592, :648-658, :744-760) in the same pass.
+//
+// Workspace per sample: TH_WS_INTS ints = hist0 | hist1[2] | hist2[2] | sel[8].  hist0 is zeroed by a
+// memset node in front of th_first, which zeroes hist1 / hist2 itself.
+// ------------------------------------------------------------------------------------------------
+constexpr int TH_THREADS = 256;
+constexpr int TH_BINS = 2048;
+constexpr int TH_WS_INTS = 5 * TH_BINS + 8;
+
+__device__ __forceinline__ uint32_t th_key(float v) { return __float_as_uint(fabsf(v)); }
+
+// Block-wide: the bin holding the k-th largest entry (k >= 1) of a TH_BINS histogram in shared memory, and k's rank inside
+// that bin.  All threads get the result.  scratch: 16 ints of shared memory.
+__device__ void th_select(const int* h, int k, int& bin, int& res, int* scratch) {
+    constexpr int PER = TH_BINS / TH_THREADS;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    int c[PER], sum = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) { c[i] = h[TH_BINS - 1 - (t * PER + i)]; sum += c[i]; }   // thread t: bins in descending order
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    __syncthreads();                       // scratch may still be read from a previous call
+    if (lane == 31) scratch[w] = incl;
+    __syncthreads();
+    int before_w = 0;
+    for (int i = 0; i < w; ++i) before_w += scratch[i];
+    incl += before_w;
+    const int before = incl - sum;
+    if (before < k && k <= incl) {
+        int acc = before;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            if (acc < k && k <= acc + c[i]) { scratch[8] = TH_BINS - 1 - (t * PER + i); scratch[9] = k - acc; }
+            acc += c[i];
         }
     }
+    __syncthreads();
+    bin = scratch[8];
+    res = scratch[9];
 }
 
-// One CTA per sample.  kFromModel: compute x0 from (x, out) first; otherwise threshold dst in place.
-//
-// s = max(quantile(|x0|, q), max_val) with torch.quantile's linear interpolation between sorted
-// positions q_lo and q_lo+1.  The exact order statistics are only needed when at least
-// n-q_lo-1 values exceed max_val; otherwise both neighbours are <= max_val and s == max_val.
-// In the needed case only the values > max_val take part: they are gathered into shared memory
-// and sorted there (worst case all n of them).
-//
-// out_c != nullptr: classifier-free guidance (model_wrapper :336-344) -- `out` is the unconditional
-// half, `out_c` the conditional one, eps = eps_u + g*(eps_c - eps_u).
+__device__ __forceinline__ void th_load_hist(int* dst, const int* src) {
+    for (int i = threadIdx.x; i < TH_BINS; i += TH_THREADS) dst[i] = src[i];
+}
+__device__ __forceinline__ void th_flush_hist(const int* src, int* dst) {
+    for (int i = threadIdx.x; i < TH_BINS; i += TH_THREADS) {
+        const int v = src[i];
+        if (v) atomicAdd(dst + i, v);
+    }
+}
+// this CTA's share [lo, hi) of a sample of n values; multiples of 4 when n is one
+__device__ __forceinline__ void th_range(int n, int& lo, int& hi) {
+    const int S = gridDim.x;
+    int per = (n + S - 1) / S;
+    per = (per + 3) & ~3;
+    lo = min(n, (int)blockIdx.x * per);
+    hi = min(n, lo + per);
+}
+
 template <bool kFromModel>
-__global__ void __launch_bounds__(TH_THREADS) x0_threshold_kernel(const float* x, const float* out, const float* out_c,
-                                                                   float* dst, float alpha, float sigma, bool noise_type,
-                                                                   float g, int n, int q_lo, float q_w, float max_val) {
-    extern __shared__ float big[];
-    __shared__ int s_count;
-    __shared__ float s_red[32];
-    __shared__ float s_scale;
-    const int b = blockIdx.x;
+__global__ void __launch_bounds__(TH_THREADS) th_first_kernel(const float* __restrict__ x, const float* __restrict__ out,
+                                                               const float* __restrict__ out_c, float* __restrict__ dst, float alpha,
+                                                               float sigma, bool noise_type, float g, int n, int* __restrict__ ws) {
+    __shared__ int h[TH_BINS];
+    const int b = blockIdx.y;
     const size_t base = (size_t)b * n;
-    if (threadIdx.x == 0) s_count = 0;
+    int* wsb = ws + (size_t)b * TH_WS_INTS;
+    for (int i = threadIdx.x; i < TH_BINS; i += TH_THREADS) h[i] = 0;
+    {   // zero the deeper histograms of this sample (4 * TH_BINS ints, split over the sample's CTAs)
+        const int tot = 4 * TH_BINS, per = (tot + gridDim.x - 1) / gridDim.x;
+        const int z0 = blockIdx.x * per, z1 = min(tot, z0 + per);
+        for (int i = z0 + threadIdx.x; i < z1; i += TH_THREADS) wsb[TH_BINS + i] = 0;
+    }
     __syncthreads();
-
-    int cnt = 0;
-    float m1 = 0.f;  // largest |x0| that is <= max_val
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        float v;
-        if (kFromModel) {
-            const float xv = x[base + i];
-            float eps = eps_of(xv, out[base + i], alpha, sigma, noise_type);
-            if (out_c) eps = __fadd_rn(eps, __fmul_rn(g, __fsub_rn(eps_of(xv, out_c[base + i], alpha, sigma, noise_type), eps)));
-            v = x0_of_eps(xv, eps, alpha, sigma);
-            dst[base + i] = v;
-        } else {
-            v = dst[base + i];
+    int lo, hi;
+    th_range(n, lo, hi);
+    auto one = [&](float xv, float ov, float ocv) {
+        float eps = eps_of(xv, ov, alpha, sigma, noise_type);
+        if (out_c) eps = __fadd_rn(eps, __fmul_rn(g, __fsub_rn(eps_of(xv, ocv, alpha, sigma, noise_type), eps)));
+        return x0_of_eps(xv, eps, alpha, sigma);
+    };
+    if ((n & 3) == 0) {
+        for (int i = lo + 4 * threadIdx.x; i < hi; i += 4 * TH_THREADS) {
+            float4 v;
+            if (kFromModel) {
+                const float4 X = *reinterpret_cast<const float4*>(x + base + i), O = *reinterpret_cast<const float4*>(out + base + i);
+                float4 Oc = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (out_c) Oc = *reinterpret_cast<const float4*>(out_c + base + i);
+                v = make_float4(one(X.x, O.x, Oc.x), one(X.y, O.y, Oc.y), one(X.z, O.z, Oc.z), one(X.w, O.w, Oc.w));
+                *reinterpret_cast<float4*>(dst + base + i) = v;
+            } else {
+                v = *reinterpret_cast<const float4*>(dst + base + i);
+            }
+            atomicAdd(&h[th_key(v.x) >> 21], 1);
+            atomicAdd(&h[th_key(v.y) >> 21], 1);
+            atomicAdd(&h[th_key(v.z) >> 21], 1);
+            atomicAdd(&h[th_key(v.w) >> 21], 1);
         }
-        const float a = fabsf(v);
-        if (a > max_val) ++cnt; else m1 = fmaxf(m1, a);
-    }
-    // block reductions
-    for (int o = 16; o > 0; o >>= 1) {
-        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
-    }
-    if ((threadIdx.x & 31) == 0) { atomicAdd(&s_count, cnt); s_red[threadIdx.x >> 5] = m1; }
-    __syncthreads();
-    const int total = s_count;
-    if (threadIdx.x < 32) {
-        float m = threadIdx.x < (blockDim.x >> 5) ? s_red[threadIdx.x] : 0.f;
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (threadIdx.x == 0) s_red[0] = m;
-    }
-    __syncthreads();
-    m1 = s_red[0];
-
-    const int hi_pos = min(q_lo + 1, n - 1);
-    const int need_hi = n - hi_pos;   // v[hi_pos] is the need_hi-th largest
-    const int need_lo = n - q_lo;     // v[q_lo]  is the need_lo-th largest
-    if (total < need_hi) {
-        if (threadIdx.x == 0) s_scale = max_val;
     } else {
-        __syncthreads();
-        if (threadIdx.x == 0) s_count = 0;
-        __syncthreads();
-        int P = 1;
-        while (P < total) P <<= 1;
-        for (int i = threadIdx.x; i < n; i += blockDim.x) {
-            const float a = fabsf(dst[base + i]);
-            if (a > max_val) big[atomicAdd(&s_count, 1)] = a;
-        }
-        for (int i = total + threadIdx.x; i < P; i += blockDim.x) big[i] = -FLT_MAX;
-        __syncthreads();
-        bitonic_desc(big, P);
-        if (threadIdx.x == 0) {
-            const float v_hi = big[need_hi - 1];
-            const float v_lo = (total >= need_lo) ? big[need_lo - 1] : m1;
-            // at::lerp: weight < 0.5 ? a + w*(b-a) : b - (b-a)*(1-w)
-            const float diff = __fsub_rn(v_hi, v_lo);
-            const float qv = (fabsf(q_w) < 0.5f) ? __fadd_rn(v_lo, __fmul_rn(q_w, diff))
-                                                 : __fsub_rn(v_hi, __fmul_rn(diff, __fsub_rn(1.f, q_w)));
-            s_scale = fmaxf(qv, max_val);
+        for (int i = lo + threadIdx.x; i < hi; i += TH_THREADS) {
+            float v;
+            if (kFromModel) {
+                v = one(x[base + i], out[base + i], out_c ? out_c[base + i] : 0.f);
+                dst[base + i] = v;
+            } else {
+                v = dst[base + i];
+            }
+            atomicAdd(&h[th_key(v) >> 21], 1);
         }
     }
     __syncthreads();
-    const float s = s_scale;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const float v = dst[base + i];
-        dst[base + i] = __fdiv_rn(fminf(fmaxf(v, -s), s), s);   // clamp(x0, -s, s) / s
-    }
+    th_flush_hist(h, wsb);
 }
+
+// kLevel 1: select in hist0, histogram bits [20:10] of the values whose bits [30:21] match; kLevel 2: select in hist1,
+// histogram bits [9:0] of the values whose bits [30:10] match.  The two ranks (sorted positions q_lo + 1 and q_lo) share
+// a histogram while their prefixes agree.
+template <int kLevel>
+__global__ void __launch_bounds__(TH_THREADS) th_level_kernel(const float* __restrict__ dst, int n, int k_hi, int k_lo, int* __restrict__ ws) {
+    __shared__ int hA[TH_BINS], hB[TH_BINS];
+    __shared__ int scratch[16];
+    const int b = blockIdx.y;
+    const size_t base = (size_t)b * n;
+    int* wsb = ws + (size_t)b * TH_WS_INTS;
+    int* sel = wsb + 5 * TH_BINS;
+    uint32_t pA, pB;       // prefixes the values must match (compared after the shift below)
+    int rA, rB;            // remaining ranks inside those prefixes
+    if (kLevel == 1) {
+        th_load_hist(hA, wsb);
+        __syncthreads();
+        int bA, bB;
+        th_select(hA, k_hi, bA, rA, scratch);
+        th_select(hA, k_lo, bB, rB, scratch);
+        pA = (uint32_t)bA; pB = (uint32_t)bB;
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sel[0] = bA; sel[1] = rA; sel[2] = bB; sel[3] = rB; }
+    } else {
+        const int bA0 = sel[0], rA0 = sel[1], bB0 = sel[2], rB0 = sel[3];
+        th_load_hist(hA, wsb + TH_BINS);
+        if (bB0 != bA0) th_load_hist(hB, wsb + 2 * TH_BINS);
+        __syncthreads();
+        int bA, bB;
+        th_select(hA, rA0, bA, rA, scratch);
+        th_select(bB0 != bA0 ? hB : hA, rB0, bB, rB, scratch);
+        pA = ((uint32_t)bA0 << 11) | (uint32_t)bA;
+        pB = ((uint32_t)bB0 << 11) | (uint32_t)bB;
+        if (blockIdx.x == 0 && threadIdx.x == 0) { sel[4] = (int)pA; sel[5] = rA; sel[6] = (int)pB; sel[7] = rB; }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < TH_BINS; i += TH_THREADS) { hA[i] = 0; hB[i] = 0; }
+    __syncthreads();
+    constexpr int kShift = kLevel == 1 ? 21 : 10;
+    constexpr uint32_t kMask = kLevel == 1 ? 2047u : 1023u;
+    constexpr int kSub = kLevel == 1 ? 10 : 0;
+    const bool two = pA != pB;
+    auto one = [&](float v) {
+        const uint32_t key = th_key(v), top = key >> kShift;
+        if (top == pA) atomicAdd(&hA[(key >> kSub) & kMask], 1);
+        else if (two && top == pB) atomicAdd(&hB[(key >> kSub) & kMask], 1);
+    };
+    int lo, hi;
+    th_range(n, lo, hi);
+    if ((n & 3) == 0) {
+        for (int i = lo + 4 * threadIdx.x; i < hi; i += 4 * TH_THREADS) {
+            const float4 v = *reinterpret_cast<const float4*>(dst + base + i);
+            one(v.x); one(v.y); one(v.z); one(v.w);
+        }
+    } else {
+        for (int i = lo + threadIdx.x; i < hi; i += TH_THREADS) one(dst[base + i]);
+    }
+    __syncthreads();
+    int* g = wsb + (kLevel == 1 ? 1 : 3) * TH_BINS;
+    th_flush_hist(hA, g);
+    if (two) th_flush_hist(hB, g + TH_BINS);
+}
+
+// The dpmsolver++ singlestep update that follows an evaluation, evaluated by th_apply on the x0 it has in registers:
+//   upd.dst = (c1*x - c2*m) [+ c3*(m1 - m)]      (same rounding as solver_update_kernel)
+// m / m1 equal to the threshold's dst mean "the fresh x0".  dst == nullptr: no fused update.
+struct ThUpdate {
+    float* dst;
+    const float* x;
+    const float* m;
+    const float* m1;
+    float c1, c2, c3;
+};
+
+__global__ void __launch_bounds__(TH_THREADS) th_apply_kernel(float* dst, int n, int q_pair, float q_w, float max_val,
+                                                               const int* __restrict__ ws, ThUpdate upd) {
+    __shared__ int hA[TH_BINS], hB[TH_BINS];
+    __shared__ int scratch[16];
+    const int b = blockIdx.y;
+    const size_t base = (size_t)b * n;
+    const int* wsb = ws + (size_t)b * TH_WS_INTS;
+    const int* sel = wsb + 5 * TH_BINS;
+    const uint32_t pA = (uint32_t)sel[4], pB = (uint32_t)sel[6];
+    const int rA = sel[5], rB = sel[7];
+    th_load_hist(hA, wsb + 3 * TH_BINS);
+    if (pB != pA) th_load_hist(hB, wsb + 4 * TH_BINS);
+    __syncthreads();
+    int bA, bB, dummy;
+    th_select(hA, rA, bA, dummy, scratch);
+    th_select(pB != pA ? hB : hA, rB, bB, dummy, scratch);
+    const float v_hi = __uint_as_float((pA << 10) | (uint32_t)bA);     // sorted position q_lo + 1
+    const float v_lo = q_pair ? __uint_as_float((pB << 10) | (uint32_t)bB) : v_hi;
+    // at::lerp: weight < 0.5 ? a + w*(b-a) : b - (b-a)*(1-w)
+    const float diff = __fsub_rn(v_hi, v_lo);
+    const float qv = (fabsf(q_w) < 0.5f) ? __fadd_rn(v_lo, __fmul_rn(q_w, diff)) : __fsub_rn(v_hi, __fmul_rn(diff, __fsub_rn(1.f, q_w)));
+    const float s = fmaxf(qv, max_val);
+    const bool fuse = upd.dst != nullptr;
+    const bool m_fresh = upd.m == dst, m1_fresh = upd.m1 == dst;
+    auto one = [&](float v, size_t gi) -> float {
+        const float r = __fdiv_rn(fminf(fmaxf(v, -s), s), s);   // clamp(x0, -s, s) / s
+        if (fuse) {
+            const float mv = m_fresh ? r : upd.m[gi];
+            float u = __fsub_rn(__fmul_rn(upd.c1, upd.x[gi]), __fmul_rn(upd.c2, mv));
+            if (upd.m1) u = __fadd_rn(u, __fmul_rn(upd.c3, __fsub_rn(m1_fresh ? r : upd.m1[gi], mv)));
+            upd.dst[gi] = u;
+        }
+        return r;
+    };
+    int lo, hi;
+    th_range(n, lo, hi);
+    for (int i = lo + threadIdx.x; i < hi; i += TH_THREADS) dst[base + i] = one(dst[base + i], base + i);
+}
+
+size_t threshold_workspace_bytes(int B) { return (size_t)B * TH_WS_INTS * sizeof(int); }
 
 static cudaError_t launch_threshold(bool from_model, const float* x, const float* out, const float* out_c, float* dst, float alpha,
-                                    float sigma, bool noise_type, float g, int B, int n, int q_lo, float q_w, float max_val,
-                                    cudaStream_t s) {
-    int P = 1;
-    while (P < n) P <<= 1;
-    const size_t smem = (size_t)P * sizeof(float);
-    if (smem > 200 * 1024) return cudaErrorInvalidValue;  // > 51200 values per sample: not supported by the in-smem select
-    if (from_model) {
-        cudaFuncSetAttribute(x0_threshold_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        x0_threshold_kernel<true><<<B, TH_THREADS, smem, s>>>(x, out, out_c, dst, alpha, sigma, noise_type, g, n, q_lo, q_w, max_val);
-    } else {
-        cudaFuncSetAttribute(x0_threshold_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        x0_threshold_kernel<false><<<B, TH_THREADS, smem, s>>>(nullptr, nullptr, nullptr, dst, 1.f, 1.f, false, 0.f, n, q_lo, q_w, max_val);
-    }
+                                    float sigma, bool noise_type, float g, int B, int n, int q_lo, float q_w, float max_val, void* ws,
+                                    const ThUpdate& upd, cudaStream_t s) {
+    if (!ws || B <= 0 || n <= 0) return cudaErrorInvalidValue;
+    int* w = reinterpret_cast<int*>(ws);
+    // CTAs per sample: two waves of the machine over the batch, at least 2048 values each
+    int S = (2 * 148 + B - 1) / B;
+    const int max_s = (n + 2047) / 2048;
+    if (S > max_s) S = max_s;
+    if (S < 1) S = 1;
+    const dim3 grid((unsigned)S, (unsigned)B);
+    cudaError_t e = cudaMemset2DAsync(w, TH_WS_INTS * sizeof(int), 0, TH_BINS * sizeof(int), (size_t)B, s);   // hist0 of every sample
+    if (e != cudaSuccess) return e;
+    if (from_model) th_first_kernel<true><<<grid, TH_THREADS, 0, s>>>(x, out, out_c, dst, alpha, sigma, noise_type, g, n, w);
+    else th_first_kernel<false><<<grid, TH_THREADS, 0, s>>>(nullptr, nullptr, nullptr, dst, 1.f, 1.f, false, 0.f, n, w);
+    const int hi_pos = q_lo + 1 < n - 1 ? q_lo + 1 : n - 1;
+    const int k_hi = n - hi_pos, k_lo = n - q_lo;      // sorted position p is the (n - p)-th largest
+    th_level_kernel<1><<<grid, TH_THREADS, 0, s>>>(dst, n, k_hi, k_lo, w);
+    th_level_kernel<2><<<grid, TH_THREADS, 0, s>>>(dst, n, k_hi, k_lo, w);
+    th_apply_kernel<<<grid, TH_THREADS, 0, s>>>(dst, n, k_hi != k_lo ? 1 : 0, q_w, max_val, w, upd);
     return cudaGetLastError();
 }
 
 cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
-                         float g, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s) {
-    return launch_threshold(true, x, out, out_c, dst, alpha, sigma, noise_type, g, B, n, q_lo, q_w, max_val, s);
+                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, const FusedUpdate* fu, cudaStream_t s) {
+    ThUpdate u{};
+    if (fu) { u.dst = fu->dst; u.x = fu->x; u.m = fu->m; u.m1 = fu->m1; u.c1 = fu->c1; u.c2 = fu->c2; u.c3 = fu->c3; }
+    return launch_threshold(true, x, out, out_c, dst, alpha, sigma, noise_type, g, B, n, q_lo, q_w, max_val, ws, u, s);
 }
-cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, cudaStream_t s) {
-    return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, s);
+cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s) {
+    return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, ws, ThUpdate{}, s);
 }
 
 // dst = (c1*x - c2*m) [+ c3*(m1 - m)], 128-bit vectorised; dst may alias x.

@@ -358,6 +358,8 @@ class DPM_Solver:
         if not x.is_cuda:
             raise RuntimeError("x must be a CUDA tensor (no CPU path)")
         xT = x.contiguous().float()
+        if xT.dim() != 4:
+            raise ValueError("x must be [B, bands, H, W]")
         B = xT.shape[0]
         MS = kw["MS"]
         cfg = bool(getattr(fn, "cfg_active", False))
@@ -372,13 +374,21 @@ class DPM_Solver:
             PAN = fn.condition
             if MS.shape[0] == 2 * B:
                 MS = MS[B:]
+        if tuple(MS.shape) != (MS.shape[0],) + tuple(xT.shape[1:]) or MS.shape[0] != (2 * B if cfg else B):
+            raise ValueError("x %s does not match the condition MS %s%s" % (tuple(xT.shape), tuple(MS.shape),
+                                                                            " (classifier-free guidance: MS holds 2B patches)" if cfg else ""))
         h = model.bind_condition(PAN, MS, kw["prompt"])
         n_per = xT[0].numel()
         cplan = plan.to_c(n_per, self.dynamic_thresholding_ratio, self.thresholding_max_val, fn.model_type, cfg, fn.guidance_scale)
         out = torch.empty_like(xT)
         nB = 2 * B if cfg else B
         trace = torch.empty((plan.n_eval, nB) + tuple(xT.shape[1:]), device=xT.device) if return_trace else None
+        # return_trace == "x": also the x every evaluation was given (eps parity from the trajectory's own x)
+        trace_x = torch.empty((plan.n_eval,) + tuple(xT.shape), device=xT.device) if return_trace == "x" else None
         with torch.cuda.device(xT.device):
-            _lib.check(_lib.load().tmd_sample(h, _lib.ptr(xT), C.byref(cplan), _lib.ptr(out), _lib.ptr(trace), _lib.stream_ptr()))
+            _lib.check(_lib.load().tmd_sample(h, _lib.ptr(xT), B, xT.shape[1], xT.shape[2], xT.shape[3], C.byref(cplan), _lib.ptr(out),
+                                              _lib.ptr(trace), _lib.ptr(trace_x), _lib.stream_ptr()))
         out = out.to(x.dtype)
+        if trace_x is not None:
+            return out, (trace, trace_x)
         return (out, trace) if return_trace else out

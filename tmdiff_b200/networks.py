@@ -169,6 +169,8 @@ class WavBEST(nn.Module):
             self._handle = h
             self._handle_key = (mb, N, H, W, self.compute_dtype, device.index)
             self._weights_key = self._text_key = self._cond_key = None
+        # parameters are held by the module, so (address, version) cannot be recycled under us; writes that bypass the
+        # version counter (`p.data.copy_`, EMA swaps through .data) need refresh_weights()
         wkey = tuple((p.data_ptr(), p._version) for p in self.parameters())
         if wkey != self._weights_key:
             for name in self._names:
@@ -193,6 +195,16 @@ class WavBEST(nn.Module):
             self._text_key = tkey
             self._cond_key = None
         return self._handle
+
+    def refresh_weights(self):
+        """Re-upload the parameters on the next call.  Needed only after writes autograd's version counter does not see
+        (`param.data.copy_(...)`, DLPack / external kernels); `load_state_dict` and in-place tensor ops are noticed."""
+        self._weights_key = None
+        self._cond_key = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        super()._load_from_state_dict(*args, **kwargs)
+        self._weights_key = None
 
     def release(self):
         if getattr(self, "_handle", None) is not None:
@@ -222,7 +234,11 @@ class WavBEST(nn.Module):
             if self.get_embeding(p) is None:
                 raise ValueError("no text embedding for prompt %r" % (p,))   # reference: .repeat on None raises
         h = self._ensure_engine(B, N, H, W, MS.device)
-        key = (PAN.data_ptr(), PAN._version, MS.data_ptr(), MS._version, tuple(prompts), B, N, H, W)
+        # The cache holds the caller's OWN tensor objects (not only converted copies), so their storage cannot be freed
+        # and handed to a new batch at the same address while the entry is alive; identity + autograd version then
+        # identify the contents.  Writes the version counter does not see (`.data.copy_`, external kernels) need
+        # reset_condition_cache().
+        key = (id(PAN), PAN.data_ptr(), PAN._version, id(MS), MS.data_ptr(), MS._version, tuple(prompts), B, N, H, W)
         if key != self._cond_key:
             pan, ms = PAN.contiguous().float(), MS.contiguous().float()
             ids = (C.c_int32 * B)(*[_lib.SENSOR_IDS[p] for p in prompts])
@@ -230,7 +246,7 @@ class WavBEST(nn.Module):
                 _lib.check(self._lib().tmd_precompute_condition(h, _lib.ptr(pan), _lib.ptr(ms), ids, B, N, H, W,
                                                                 _lib.stream_ptr()))
             self._cond_key = key
-            self._cond_keepalive = (pan, ms)
+            self._cond_keepalive = (PAN, MS, pan, ms)
         return h
 
     @torch.no_grad()
@@ -269,7 +285,7 @@ class WavBEST(nn.Module):
         (device time from CUDA events on the launching stream; algorithmic flops / bytes)."""
         prof = _lib.Profile()
         _lib.check(self._lib().tmd_profile_end(self._handle, C.byref(prof), csv_path.encode() if csv_path else None))
-        return {name: {"ms": k.ms, "flops": k.flops, "bytes": k.bytes, "launches": int(k.launches)}
+        return {name: {"ms": k.ms, "flops": k.flops, "bytes": k.bytes, "launches": int(k.launches), "flops_executed": k.flops_executed}
                 for name, k in zip(_lib.KIND_NAMES, prof.kind)}
 
 
