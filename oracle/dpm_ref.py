@@ -46,7 +46,8 @@ class ScheduleVP:
         la = 0.5 * torch.log(1 - betas).cumsum(dim=0)
         self.total_N = la.numel()
         self.T = 1.0
-        self.t_array = torch.linspace(0.0, 1.0, self.total_N + 1)[1:].reshape(1, -1)
+        self.device = betas.device              # CPU for the oracle; a CUDA device for bench.py's eager-GPU baseline arm
+        self.t_array = torch.linspace(0.0, 1.0, self.total_N + 1)[1:].reshape(1, -1).to(betas.device)
         self.log_alpha_array = la.reshape(1, -1)
 
     def log_alpha(self, t):
@@ -63,7 +64,7 @@ class ScheduleVP:
         return la - 0.5 * torch.log(1.0 - torch.exp(2.0 * la))
 
     def inv_lam(self, lamb):
-        la = -0.5 * torch.logaddexp(torch.zeros(1), -2.0 * lamb)
+        la = -0.5 * torch.logaddexp(torch.zeros(1, device=lamb.device), -2.0 * lamb)
         t = piecewise_linear(la.reshape(-1, 1), torch.flip(self.log_alpha_array, [1]), torch.flip(self.t_array, [1]))
         return t.reshape(-1)
 
@@ -120,14 +121,15 @@ class Sampler:
         return x0
 
     def time_steps_logsnr(self, t_T, t_0, N):  # :482-486
-        lT, l0 = self.ns.lam(torch.tensor(t_T)), self.ns.lam(torch.tensor(t_0))
-        return self.ns.inv_lam(torch.linspace(lT.item(), l0.item(), N + 1))
+        dev = self.ns.device
+        lT, l0 = self.ns.lam(torch.tensor(t_T, device=dev)), self.ns.lam(torch.tensor(t_0, device=dev))
+        return self.ns.inv_lam(torch.linspace(lT.item(), l0.item(), N + 1).to(dev))
 
     def time_steps(self, skip_type, t_T, t_0, N):
         if skip_type == "logSNR":
             return self.time_steps_logsnr(t_T, t_0, N)
         if skip_type == "time_uniform":
-            return torch.linspace(t_T, t_0, N + 1)
+            return torch.linspace(t_T, t_0, N + 1).to(self.ns.device)
         raise ValueError(skip_type)
 
     def _update(self, x, s, t, order, r1, r2):
@@ -210,7 +212,7 @@ class Sampler:
             else:
                 m_list = m_list[1:] + [m_list[-1]]
         if denoise_to_zero:
-            x = self.data_prediction(x, torch.ones(1) * t_0)
+            x = self.data_prediction(x, torch.ones(1, device=x.device) * t_0)
         return x
 
     @torch.no_grad()
@@ -232,5 +234,5 @@ class Sampler:
             r2 = None if o <= 2 else (li[2] - li[0]) / h
             x = self._update(x, s, t, o, r1, r2)
         if denoise_to_zero:
-            x = self.data_prediction(x, torch.ones(1) * t_0)
+            x = self.data_prediction(x, torch.ones(1, device=x.device) * t_0)
         return x

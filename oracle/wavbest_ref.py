@@ -137,8 +137,9 @@ def haar_matrices(n, dtype=torch.float32):
 def dwt2d(x):
     """Haar analysis by the reference's six matmuls (DWT_IDWT_Functions.py:52-57)."""
     H, W = x.shape[-2:]
-    l0, h0 = haar_matrices(H)
-    l1, h1 = haar_matrices(W)
+    # built on the host and moved to the input's device on every call, as DWT_2D.get_matrix does (DWT_IDWT_layer.py:310-319)
+    l0, h0 = (m.to(x.device) for m in haar_matrices(H))
+    l1, h1 = (m.to(x.device) for m in haar_matrices(W))
     l1, h1 = l1.t(), h1.t()
     L = torch.matmul(l0, x)
     Hh = torch.matmul(h0, x)
@@ -149,8 +150,8 @@ def idwt2d(LL, LH, HL, HH):
     """Haar synthesis (DWT_IDWT_Functions.py:95-100; synthesis filters are the reversed
     dec_lo/dec_hi = the same [s,s], [s,-s] taps, DWT_IDWT_layer.py:352-356)."""
     h, w = LL.shape[-2:]
-    l0, h0 = haar_matrices(2 * h)
-    l1, h1 = haar_matrices(2 * w)
+    l0, h0 = (m.to(LL.device) for m in haar_matrices(2 * h))
+    l1, h1 = (m.to(LL.device) for m in haar_matrices(2 * w))
     l1, h1 = l1.t(), h1.t()
     L = torch.matmul(LL, l1.t()) + torch.matmul(LH, h1.t())
     Hh = torch.matmul(HL, l1.t()) + torch.matmul(HH, h1.t())

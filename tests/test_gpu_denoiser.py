@@ -267,3 +267,114 @@ def test_mixed_sensor_batch(model_fp32):
         assert rel_l2(joint[i:i + 1], one) < 1e-6, p
     same = G.sample_by_dpmsolver({"PAN": pan, "MS": ms, "Res": x_T}, "QB", steps=6, x_T=x_T)
     assert rel_l2(joint[1:2], same[1:2]) > 1e-4          # the text modulation really differs between sensors
+
+
+# ------------------------------------------------------------------------------------------------
+# the benchmarked workload itself (BASELINE config 2 / the 8-band twin): B = 64, 64x64, 20 steps
+# ------------------------------------------------------------------------------------------------
+def _oracle_trace(p, pan, ms, x_T, sensor, steps):
+    sd, emb = wavbest_ref.seeded_weights(), wavbest_ref.seeded_text_embeddings()[sensor]
+    ns = dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000))
+    tr = []
+    net = lambda x, t: wavbest_ref.wavbest_forward(sd, x, t, pan[p:p + 1], ms[p:p + 1], emb, faithful=False)
+    final = dpm_ref.Sampler(net, ns, trace=tr).sample(x_T[p:p + 1], steps=steps, order=3)
+    return tr, final, ns
+
+
+@pytest.mark.parametrize("bands,sensor", [(4, "QB"), (8, "WV3")])
+def test_benchmarked_shape_parity(lib_built, bands, sensor):
+    """What bench.py times -- 64 patches of 64x64, 20 DPM-Solver++ steps, bf16, CUDA-graph replay -- against the oracle run at
+    B = 1 on patches {0, 31, 63} (batch independence: test_batch_is_independent_patches): raw network output and eps at every
+    evaluation, eps formed from the x the CUDA trajectory itself fed to the network (core/dpm_solver_pytorch.py:296-306,
+    :447-456), final image PSNR; the fp32 mode of the same batch is the second witness at 1e-5."""
+    from tmdiff_b200 import WavBEST
+    B, HW, steps = 64, 64, 20
+    pan, ms, x_T = make_inputs(B, bands, HW, HW)                 # seed 3407: rank 0's batch in bench.py
+    x_in = {"PAN": pan.cuda(), "MS": ms.cuda(), "Res": x_T}
+    results = {}
+    for dtype in ("bf16", "fp32"):
+        m = WavBEST(channels=[32, 64, 128, 256], dtype=dtype, text_embeddings=wavbest_ref.seeded_text_embeddings(), max_batch=B)
+        m.load_state_dict(wavbest_ref.seeded_weights(), strict=True)
+        m = m.cuda()
+        G = _diffusion(m)
+        img_graph = G.sample_by_dpmsolver(x_in, sensor, steps=steps, x_T=x_T.cuda())          # captures the graph
+        m.reset_condition_cache()
+        img_replay = G.sample_by_dpmsolver(x_in, sensor, steps=steps, x_T=x_T.cuda())         # replays it
+        assert torch.equal(img_graph, img_replay)
+        m.reset_condition_cache()
+        img, (trace, trace_x) = G.sample_by_dpmsolver(x_in, sensor, steps=steps, x_T=x_T.cuda(), return_trace="x")
+        assert torch.equal(img, img_graph)                        # the graph replays exactly the eager launch list
+        assert trace.shape == (steps + 1, B, bands, HW, HW) and trace_x.shape == trace.shape
+        results[dtype] = (img.cpu(), trace.cpu(), trace_x.cpu())
+        m.release()
+    for p in (0, 31, 63):
+        tr, final, ns = _oracle_trace(p, pan, ms, x_T, sensor, steps)
+        assert len(tr) == steps + 1
+        for dtype, tol in (("bf16", BF16_TOL), ("fp32", FP32_TOL)):
+            img, trace, trace_x = results[dtype]
+            worst_out = worst_eps = 0.0
+            for i, rec in enumerate(tr):
+                t = torch.tensor([rec["t"]])
+                a, s = ns.alpha(t), ns.sigma(t)
+                eps_cuda = (trace_x[i, p] - a * trace[i, p]) / s          # from the CUDA trajectory's own x
+                worst_out = max(worst_out, rel_l2(trace[i, p], rec["out"][0]))
+                worst_eps = max(worst_eps, rel_l2(eps_cuda, rec["eps"][0]))
+            assert worst_out < tol, (dtype, p, worst_out)
+            assert worst_eps < tol, (dtype, p, worst_eps)
+            assert psnr(img[p], final[0] + ms[p]) >= 45.0, (dtype, p)
+    # every patch of the batch: the bf16 image against the fp32 one
+    for p in range(B):
+        assert psnr(results["bf16"][0][p], results["fp32"][0][p]) >= 45.0, p
+
+
+def test_large_patch_8band_128(lib_built):
+    """The denoiser is fully convolutional (the reference's self-test runs 512x512, Hyper_unet_general.py:664-671) and
+    dynamic_thresholding_fn has no size limit: an 8-band 128x128 patch (131072 values per sample) samples."""
+    pan, ms, x_T = make_inputs(1, 8, 128, 128)
+    m = make_model("fp32")
+    G = _diffusion(m)
+    img, trace = G.sample_by_dpmsolver({"PAN": pan.cuda(), "MS": ms.cuda(), "Res": x_T}, "WV3", steps=4, x_T=x_T.cuda(), return_trace=True)
+    tr, final, _ = _oracle_trace(0, pan, ms, x_T, "WV3", 4)
+    for i, rec in enumerate(tr):
+        assert rel_l2(trace[i], rec["out"]) < FP32_TOL, i
+    assert rel_l2(img.cpu() - ms, final) < FP32_TOL
+    m.release()
+
+
+def test_condition_cache_survives_address_reuse(model_fp32):
+    """Non-contiguous / fp16 PAN and MS are converted copies inside the module; when the caller frees the originals the
+    caching allocator hands the next batch the same addresses with version 0 -- the cache must not hit."""
+    pan, ms, x_T = make_inputs(1, 4, 32, 32)
+    t = torch.tensor([300.0]).cuda()
+    x = x_T.cuda()
+    outs = []
+    for scale in (1.0, 0.5):
+        pan_h, ms_h = (pan * scale).cuda().half(), (ms * scale).cuda().half()
+        outs.append(model_fp32(x, t, PAN=pan_h, MS=ms_h, prompt="QB"))
+        want = model_fp32(x, t, PAN=pan_h.float().clone(), MS=ms_h.float().clone(), prompt="QB")
+        assert torch.equal(outs[-1], want)
+        del pan_h, ms_h, want
+    assert not torch.allclose(outs[0], outs[1])
+    # weights: a second load_state_dict is noticed, and refresh_weights() covers `.data` writes
+    sd = wavbest_ref.seeded_weights()
+    y0 = model_fp32(x, t, PAN=pan.cuda(), MS=ms.cuda(), prompt="QB")
+    p = model_fp32.get_parameter("final.conv24.weight")
+    p.data.mul_(2.0)
+    model_fp32.refresh_weights()
+    y1 = model_fp32(x, t, PAN=pan.cuda(), MS=ms.cuda(), prompt="QB")
+    assert rel_l2(y1, 2.0 * y0) < 1e-6
+    model_fp32.load_state_dict(sd, strict=True)
+    assert torch.equal(model_fp32(x, t, PAN=pan.cuda(), MS=ms.cuda(), prompt="QB"), y0)
+
+
+def test_sample_validates_x_against_condition(model_fp32):
+    """DPM_Solver.sample raises (instead of reading out of bounds) when x does not match the bound condition."""
+    from tmdiff_b200 import DPM_Solver, NoiseScheduleVP, model_wrapper
+    pan, ms, x_T = [t.cuda() for t in make_inputs(2, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    ns = NoiseScheduleVP("discrete", betas=G.betas)
+    fn = model_wrapper(model_fp32, ns, model_type="x_start", model_kwargs={"PAN": pan, "MS": ms, "prompt": "QB"})
+    sol = DPM_Solver(fn, ns, algorithm_type="dpmsolver++", correcting_x0_fn="dynamic_thresholding")
+    for bad in (x_T[:1], x_T[:, :2], torch.cat([x_T, x_T]), x_T[..., :16]):
+        with pytest.raises(ValueError):
+            sol.sample(bad, steps=3, order=3, skip_type="logSNR", method="singlestep")

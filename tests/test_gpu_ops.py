@@ -103,6 +103,71 @@ def test_modulated_conv3d_linearity_full_size(ops):
     assert rel_l2(f(0.5 * x + y), 0.5 * f(x) + f(y)) < 1e-5
 
 
+# the layer shapes of the benchmarked workload (BASELINE config 2: B = 64, 4 bands, 64x64): these run the code paths the
+# headline number runs -- 512..2048 tiles over 148 persistent CTAs, NACC = 4 with pl_off = 1, several waves of accumulator
+# double-buffering, the Co = 256 channel-group split, batch folded into M at the 8x8 level
+BENCH_CONV_CASES = [
+    (64, 32, 32, 4, 64, 64, 3),
+    (64, 64, 64, 4, 64, 64, 3),
+    (64, 96, 32, 4, 64, 64, 3),
+    (64, 128, 128, 4, 32, 32, 3),
+    (64, 256, 256, 4, 16, 16, 3),
+    (64, 768, 128, 4, 8, 8, 3),
+    (64, 256, 256, 4, 8, 8, 3),
+    (64, 32, 32, 8, 64, 64, 3),      # 8 bands: two band tiles of 4 planes
+    (64, 96, 32, 4, 64, 64, 1),
+]
+
+
+@pytest.mark.parametrize("case", BENCH_CONV_CASES)
+def test_modulated_conv3d_benchmark_shapes(ops, case):
+    """tcgen05 kernel at the benchmarked layer shapes against (i) the fp32 CUDA-core kernel on the whole tensor and (ii) the
+    reference formulation (groups=B conv of per-sample modulated weights, Hyper_unet_general.py:51-77) on the CPU for the
+    first, a middle and the last sample of the batch."""
+    B, Ci, Co, N, H, W, k = case
+    g = torch.Generator(device="cuda").manual_seed(23)
+    x = torch.randn(B, Ci, N, H, W, generator=g, device="cuda")
+    w = torch.randn(Co, Ci, k, k, k, generator=g, device="cuda") / (Ci * k ** 3) ** 0.5
+    s = torch.randn(B, Ci, 1, 1, generator=g, device="cuda")
+    got = ops.modulated_conv3d(x, w, s, padding=k // 2, dtype="bf16")
+    ref32 = ops.modulated_conv3d(x, w, s, padding=k // 2, dtype="fp32")
+    assert rel_l2(got, ref32) < 1e-2
+    # per sample too: a tile-scheduling bug would hide in a whole-tensor norm
+    per = ((got - ref32).flatten(1).norm(dim=1) / ref32.flatten(1).norm(dim=1)).max().item()
+    assert per < 1e-2, per
+    for b in (0, B // 2, B - 1):
+        want = wavbest_ref.modulated_conv3d(x[b:b + 1].cpu(), w.cpu(), s[b:b + 1].cpu(), k // 2, faithful=True)
+        assert rel_l2(ref32[b:b + 1], want) < 5e-6, b
+        assert rel_l2(got[b:b + 1], want) < 1e-2, b
+
+
+@pytest.mark.parametrize("shape", [(2, 8 * 128 * 128), (1, 8 * 512 * 512), (3, 51201), (2, 7), (64, 4 * 64 * 64)])
+def test_dynamic_threshold_any_size(ops, shape):
+    """No per-sample size limit (the reference's denoiser is fully convolutional and its self-test runs 512x512,
+    Hyper_unet_general.py:664-671; dynamic_thresholding_fn has no limit, dpm_solver_pytorch.py:430-439); odd sizes take
+    the scalar path."""
+    g = torch.Generator().manual_seed(shape[1] % 1000)
+    x = torch.randn(shape, generator=g) * 2.0
+    x[0] *= 0.2
+    want = dpm_ref.dynamic_threshold(x)
+    got = ops.dynamic_thresholding(x.cuda()).cpu()
+    assert torch.equal(got, want) or float((got - want).abs().max()) <= 1e-6, float((got - want).abs().max())
+
+
+def test_dynamic_threshold_degenerate_values(ops):
+    """All-equal samples (every radix level lands in one bin), exact ties at the two interpolated ranks, zeros and a huge
+    outlier."""
+    n = 4 * 64 * 64
+    x = torch.full((4, n), 2.5)
+    x[1] = 0.0
+    x[2, ::2] = -2.5
+    x[3] = torch.linspace(-3, 3, n)
+    x[3, 7] = 1e30
+    want = dpm_ref.dynamic_threshold(x)
+    got = ops.dynamic_thresholding(x.cuda()).cpu()
+    assert torch.allclose(got, want, rtol=0, atol=1e-6)
+
+
 @pytest.mark.parametrize("scale", [0.3, 1.0, 3.0, 50.0])
 @pytest.mark.parametrize("n", [4 * 32 * 32, 4 * 64 * 64, 8 * 64 * 64, 1000])
 def test_dynamic_threshold(ops, scale, n):
