@@ -55,6 +55,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
     ap.add_argument("--launch-csv", default=None, help="write the per-launch CUDA-event times of the profiled step here")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed batch")
+    ap.add_argument("--no-eager-baseline", action="store_true", help="skip the PyTorch-eager-on-GPU (cuDNN) baseline arm")
+    ap.add_argument("--eager-budget-s", type=float, default=45.0, help="time budget per eager-baseline variant")
     return ap.parse_args()
 
 
@@ -67,13 +70,26 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def kernel_source_hash():
+    """sha256 (16 hex digits) of the conv kernel's sources: an ncu capture describes one build of them."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("conv_umma.cu", "conv_op.h"):
+        h.update(open(os.path.join(ROOT, "tmdiff_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def conv_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per conv launch from the committed ncu capture
-    (profiles/capture.sh -> profiles/traffic_from_ncu.py), or None when no capture is committed."""
+    (profiles/capture.sh -> profiles/traffic_from_ncu.py).  The capture is stamped with the hash of the kernel sources it
+    was taken from; None (null) when no capture is committed or the kernel has changed since."""
     p = os.path.join(ROOT, "profiles", "conv_traffic.json")
     if not os.path.exists(p):
-        return None
-    return json.load(open(p)).get("traffic_bytes_per_launch")
+        return None, "no capture committed"
+    d = json.load(open(p))
+    if d.get("kernel_source_sha16") != kernel_source_hash():
+        return None, "stale: capture %s is of another build of conv_umma.cu" % d.get("tag")
+    return d.get("traffic_bytes_per_launch"), "ncu capture %s of this build (sha %s)" % (d.get("tag"), d.get("kernel_source_sha16"))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -183,6 +199,105 @@ def workload_config(args, per_step_patches):
 
 
 # ------------------------------------------------------------------------------------------------
+# parity of the timed batch (the oracle as checker)
+# ------------------------------------------------------------------------------------------------
+def parity_of_timed_batch(G, model, x_in, xT_d, pan_h, ms_h, xT_h, args, img_timed):
+    """The tensors that were just timed, checked: (i) the CUDA-graph replay equals the eager launch list bit for bit,
+    (ii) patches {0, B/2-1, B-1} against the oracle run at B = 1 on the host -- raw network output and eps (from the CUDA
+    trajectory's own x, dpm_solver_pytorch.py:296-306) at every evaluation, PSNR of the final image."""
+    import torch
+    from oracle import dpm_ref, wavbest_ref
+    B = xT_d.shape[0]
+    model.reset_condition_cache()
+    img, (trace, trace_x) = G.sample_by_dpmsolver(x_in, args.sensor, steps=args.solver_steps, x_T=xT_d, return_trace="x")
+    graph_equal = bool(torch.equal(img, img_timed))
+    img, trace, trace_x = img.cpu(), trace.cpu(), trace_x.cpu()
+    sd, emb = wavbest_ref.seeded_weights(CHANNELS), wavbest_ref.seeded_text_embeddings()[args.sensor]
+    ns = dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000))
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm())
+    worst_out = worst_eps = 0.0
+    psnr_min = float("inf")
+    patches = sorted({0, max(B // 2 - 1, 0), B - 1})
+    for p in patches:
+        tr = []
+        net = lambda x, t: wavbest_ref.wavbest_forward(sd, x, t, pan_h[p:p + 1], ms_h[p:p + 1], emb, faithful=False)
+        final = dpm_ref.Sampler(net, ns, trace=tr).sample(xT_h[p:p + 1], steps=args.solver_steps, order=3) + ms_h[p:p + 1]
+        for i, rec in enumerate(tr):
+            t = torch.tensor([rec["t"]])
+            a, sg = ns.alpha(t), ns.sigma(t)
+            worst_out = max(worst_out, rel(trace[i, p], rec["out"][0]))
+            worst_eps = max(worst_eps, rel((trace_x[i, p] - a * trace[i, p]) / sg, rec["eps"][0]))
+        mse = float(((img[p].double() - final[0].double()) ** 2).mean())
+        psnr_min = min(psnr_min, float("inf") if mse == 0 else 10.0 * torch.log10(torch.tensor(1.0 / mse)).item())
+    tol = 1e-5 if args.dtype == "fp32" else 2e-2
+    return {"rel_l2_out_max": worst_out, "rel_l2_eps_max": worst_eps, "psnr_min": psnr_min, "patches_checked": patches,
+            "nfe_checked": args.solver_steps + 1, "graph_replay_equals_eager": graph_equal, "tolerance": tol,
+            "ok": bool(worst_out < tol and worst_eps < tol and psnr_min >= 45.0 and graph_equal),
+            "against": "oracle (torch fp32 on the host, B=1 per patch, bit-exact restatement of the reference)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# PyTorch-eager-on-GPU baseline (library kernels on the same B200)
+# ------------------------------------------------------------------------------------------------
+def gpu_eager_baseline(args, dev, pan_d, ms_d, xT_d):
+    """The bar SURVEY.md 0.1 sets: the reference algorithm in eager PyTorch on this same GPU -- the oracle's faithful
+    restatement (per-sample modulated weights as a groups=B conv3d, Haar transforms as dense matmuls, nothing cached, every
+    schedule scalar computed on the device) moved to CUDA, i.e. cuDNN / cuBLAS / ATen kernels, `cudnn.benchmark = True` as the
+    reference sets it (general_sharpening_joint_random_batch_finetune.py:31).  fp32 (TF32 convolutions are torch's default)
+    and torch.autocast(bf16); B = the workload's batch and B = 1 (how the reference's loaders run it).  Not our code path:
+    nothing of tmdiff_b200 is called here."""
+    import torch
+    from oracle import dpm_ref, wavbest_ref
+    torch.backends.cudnn.benchmark = True
+    sd = {k: v.to(dev) for k, v in wavbest_ref.seeded_weights(CHANNELS).items()}
+    emb = wavbest_ref.seeded_text_embeddings()[args.sensor].to(dev)
+    ns = dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000).to(dev))
+    out = {}
+
+    def run(B, autocast, steps):
+        pan, ms, xT = pan_d[:B], ms_d[:B], xT_d[:B]
+        net = lambda x, t: wavbest_ref.wavbest_forward(sd, x, t, pan, ms, emb, faithful=True).float()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+            img = dpm_ref.Sampler(net, ns).sample(xT, steps=steps, order=3) + ms
+        e1.record()
+        torch.cuda.synchronize()
+        assert bool(torch.isfinite(img).all())
+        return e0.elapsed_time(e1) * 1e-3
+
+    for B in (args.batch, 1):
+        for name, autocast in (("fp32_tf32conv", False), ("autocast_bf16", True)):
+            key = "B%d_%s" % (B, name)
+            try:
+                run(B, autocast, 2)                               # warm-up: cuDNN autotuning of every layer shape, 3 NFE
+                t_probe = run(B, autocast, 2)
+                est = t_probe / 3 * (args.solver_steps + 1)
+                if est <= args.eager_budget_s:
+                    sec, extrapolated = run(B, autocast, args.solver_steps), False
+                else:                                             # too slow to time whole: 3 evaluations scaled to the trajectory
+                    sec, extrapolated = est, True
+                out[key] = {"value": B / sec, "unit": "patches/s", "seconds_per_batch": sec, "batch": B, "extrapolated_from_3_nfe": extrapolated}
+            except Exception as exc:                              # e.g. out of memory in the per-sample weight copies
+                out[key] = {"error": "%s: %s" % (type(exc).__name__, str(exc)[:200])}
+            torch.cuda.empty_cache()
+    try:                                                          # kernels per evaluation, from the profiler's CUDA activity list
+        from torch.profiler import ProfilerActivity, profile
+        t = torch.full((1,), 500.0, device=dev)
+        with torch.no_grad(), profile(activities=[ProfilerActivity.CUDA]) as prof:
+            wavbest_ref.wavbest_forward(sd, xT_d[:1], t, pan_d[:1], ms_d[:1], emb, faithful=True)
+            torch.cuda.synchronize()
+        out["gpu_kernels_per_evaluation"] = sum(1 for ev in prof.events() if ev.device_type == torch.autograd.DeviceType.CUDA)
+    except Exception:
+        out["gpu_kernels_per_evaluation"] = None
+    out["what"] = ("oracle.wavbest_ref.wavbest_forward(faithful=True) + oracle.dpm_ref.Sampler on cuda: eager PyTorch "
+                   "(cuDNN conv3d, cuBLAS matmul Haar, ATen elementwise), cudnn.benchmark=True")
+    torch.backends.cudnn.benchmark = False
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
@@ -267,8 +382,9 @@ def run_ours(args):
         return float(ms.item())
 
     for _ in range(max(args.warmup, 3)):
-        step_resident()
+        img_timed = step_resident()
     torch.cuda.synchronize()
+    img_timed = img_timed[rank * B:(rank + 1) * B].clone() if world > 1 else img_timed.clone()
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -298,8 +414,13 @@ def run_ours(args):
         e2e = total * args.steps / (e2e_ms * 1e-3)
         c3 = prof["conv3x3x3"]
         ach = c3["flops"] / (c3["ms"] * 1e-3) / 1e12 if c3["ms"] > 0 else 0.0
+        ach_exec = c3["flops_executed"] / (c3["ms"] * 1e-3) / 1e12 if c3["ms"] > 0 else 0.0
         prof_total = sum(k["ms"] for k in prof.values())
         peak = peaks["bf16_tflops_sustained"]
+        traffic, traffic_note = conv_traffic()
+        mem_ms = sum(prof[k]["ms"] for k in ("elementwise", "solver", "conv1x1x1"))
+        mem_bytes = sum(prof[k]["bytes"] for k in ("elementwise", "solver", "conv1x1x1"))
+        mem_gbs = mem_bytes / (mem_ms * 1e-3) / 1e9 if mem_ms > 0 else 0.0
         gflop_patch = N * (GFLOP_INVARIANT_PER_BAND + (args.solver_steps + 1) * GFLOP_VARIANT_PER_BAND)
         line = {
             "metric": METRIC, "value": value, "unit": "patches/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -313,15 +434,30 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"kernel": "conv3d 3x3x3 implicit GEMM (all %d launches of one step)" % c3["launches"],
                          "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                         "traffic": conv_traffic(), "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peaks["source"],
+                         "achieved_executed": ach_exec, "frac_executed": ach_exec / peak,
+                         "executed_note": "achieved counts the zero-padding band planes as the reference executes them (SURVEY.md 8d); "
+                                          "achieved_executed only the MMAs the kernel issues ((3N-2)/(3N) of the 3x3x3 taps)",
+                         "traffic": traffic, "traffic_note": traffic_note, "peak_source": "%s bf16_tflops_sustained (kernel timed inside a long step)" % peaks["source"],
                          "share_of_step": c3["ms"] / prof_total if prof_total else None,
                          "how": "CUDA events around every launch on the launching stream, one extra step after the timed region"},
+            "roofline_hbm": {"kernel": "memory-bound launches of one step (stems, slice activations, 32->1 projection, 1x1x1 convs, "
+                                       "x0 conversion + dynamic threshold + fused solver update)",
+                             "bound": "hbm", "achieved": mem_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": mem_gbs / peaks["hbm_gbs"],
+                             "share_of_step": mem_ms / prof_total if prof_total else None},
+            "launch_gap_ms": t_ms / args.steps - prof_total,
+            "launch_gap_note": "ms_per_step minus the summed CUDA-event time of every launch of one step: prologue / tail / "
+                               "dependency gaps between the launches of the graph",
             "end_to_end_tensor_frac": value / world * gflop_patch * 1e9 / (peak * 1e12),
             "kernel_kinds": {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
                                  "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 2) if v["ms"] > 0 else 0.0,
                                  "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1) if v["ms"] > 0 else 0.0}
                              for k, v in prof.items()},
         }
+        if not args.no_parity:
+            line["parity"] = parity_of_timed_batch(G, model, {"PAN": pan_d, "MS": ms_d, "Res": xT_d}, xT_d, pan_h, ms_h, xT_h, args, img_timed)
+        if not args.no_eager_baseline and world == 1:
+            model.release()                                # the eager arm gets the whole GPU
+            line["gpu_eager_baseline"] = gpu_eager_baseline(args, dev, pan_d, ms_d, xT_d)
         if not args.no_cpu_baseline and world == 1:        # the reported CPU baseline is an N = 1 item (rank 0 of a multi-rank run has peers waiting)
             threads = args.cpu_threads or os.cpu_count()
             sec = cpu_sample_seconds(N, P, args.solver_steps, args.sensor, threads)
