@@ -378,3 +378,57 @@ def test_sample_validates_x_against_condition(model_fp32):
     for bad in (x_T[:1], x_T[:, :2], torch.cat([x_T, x_T]), x_T[..., :16]):
         with pytest.raises(ValueError):
             sol.sample(bad, steps=3, order=3, skip_type="logSNR", method="singlestep")
+
+
+# ------------------------------------------------------------------------------------------------
+# ancestral sampler against the reference's own p_mean_variance / p_sample / p_sample_loop runs
+# (tests/golden/make_golden_ancestral.py; GeneralModel/diffusion_general.py:155-225, 338-339)
+# ------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def golden_ancestral():
+    import numpy as np
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ancestral_vectors.npz"))
+
+
+def test_ancestral_steps_match_reference(golden_ancestral, model_fp32):
+    """p_mean_variance and p_sample(noise = the reference's draw) at t in {999, 500, 1, 0}."""
+    g = golden_ancestral
+    pan, ms, x_T = [t.cuda() for t in make_inputs(2, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    cond = {"PAN": pan, "MS": ms}
+    for t in (999, 500, 1, 0):
+        x = torch.from_numpy(g["step_%d_x" % t]).cuda()
+        mean, log_var = G.p_mean_variance(x=x, t=t, clip_denoised=True, x_in=cond, prompt="QB")
+        assert rel_l2(mean, torch.from_numpy(g["step_%d_mean" % t])) < FP32_TOL, t
+        assert float(log_var) == pytest.approx(float(g["step_%d_log_var" % t]), rel=1e-6)
+        out = G.p_sample(x, t, condition_x=cond, prompt="QB", noise=torch.from_numpy(g["step_%d_z" % t]).cuda())
+        assert rel_l2(out, torch.from_numpy(g["step_%d_out" % t])) < FP32_TOL, t
+
+
+def test_ancestral_loop_matches_reference(golden_ancestral, model_fp32):
+    """The last six steps of the 1000-step loop, and the reference's own p_sample_loop / super_resolution on a 6-step
+    schedule (continous = True / False; super_resolution passes its prompt into `continous`), replaying the recorded draws."""
+    from tmdiff_b200 import GeneralDiffusion
+    g = golden_ancestral
+    pan, ms, x_T = [t.cuda() for t in make_inputs(2, 4, 32, 32)]
+    G = _diffusion(model_fp32)
+    cond = {"PAN": pan, "MS": ms}
+    zs = iter([torch.from_numpy(g["tail_z_%d" % j]) for j in range(5)])
+    out = G.p_sample_loop_steps(cond, torch.from_numpy(g["tail_x5"]).cuda(), [5, 4, 3, 2, 1, 0], prompt="QB", noise_source=lambda s: next(zs))
+    assert rel_l2(out, torch.from_numpy(g["tail_out"])) < FP32_TOL
+    G6 = GeneralDiffusion(model_fp32)
+    G6.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 6}, "cuda")
+    assert torch.equal(G6.betas.cpu(), torch.from_numpy(g["loop6_betas"]))
+    cond1 = {"PAN": pan[:1], "MS": ms[:1], "Res": x_T[:1]}
+    replay = lambda: (lambda it: (lambda s: next(it)))(iter([torch.from_numpy(g["loop6_noise_%d" % j]) for j in range(6)]))
+    cont = G6.p_sample_loop(cond1, continous=True, prompt="QB", noise_source=replay())
+    want = torch.from_numpy(g["loop6_continuous"])
+    assert cont.shape == want.shape
+    assert rel_l2(cont, want) < FP32_TOL
+    last = G6.p_sample_loop(cond1, continous=False, prompt="QB", noise_source=replay())
+    assert last.shape == tuple(g["loop6_last"].shape) and rel_l2(last, torch.from_numpy(g["loop6_last"])) < FP32_TOL
+    # super_resolution(x_in, continous, prompt, guidance) == p_sample_loop(x_in, prompt): the whole series (:338-339)
+    torch.manual_seed(0)
+    sr = G6.super_resolution(cond1, False, "QB", 1.0)
+    assert sr.shape == want.shape

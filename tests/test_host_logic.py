@@ -216,3 +216,15 @@ def test_bucket_by_bands_and_sample_mixed_order():
     out = parallel.sample_mixed(Fake(), patches, steps=3, x_T=noise)
     for o, (pan, ms, _), z in zip(out, patches, noise):
         assert torch.equal(o, ms + pan + z)
+
+
+def test_ancestral_schedule_buffers_match_reference_run():
+    """set_new_noise_schedule's buffers (GeneralModel/diffusion_general.py:86-132) against values the reference itself
+    produced (tests/golden/make_golden_ancestral.py): the 6-step cosine betas and posterior_log_variance_clipped[t]."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ancestral_vectors.npz"))
+    G = diffusion.GeneralDiffusion(None)
+    G.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 6}, "cpu")
+    assert torch.equal(G.betas, torch.from_numpy(g["loop6_betas"]))
+    G.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 1000}, "cpu")
+    for t in (999, 500, 1, 0):
+        assert float(G.posterior_log_variance_clipped[t]) == float(g["step_%d_log_var" % t])

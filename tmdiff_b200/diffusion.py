@@ -96,24 +96,29 @@ class GeneralDiffusion(nn.Module):
                                     float(h["posterior_mean_coef2"][t]), sigma, clip_denoised, 0 if seed is None else int(seed), t)
 
     @torch.no_grad()
-    def p_sample_loop(self, x_in, continous=False, prompt="QB", guidance=1.0, seed=None):
+    def p_sample_loop(self, x_in, continous=False, prompt="QB", guidance=1.0, seed=None, noise_source=None):
         """:203-225.  seed=None: x_T and every step's noise come from torch's generator exactly where the reference draws
-        them; seed=int: the per-step noise is drawn inside the update kernel (nothing but x and eps is read)."""
+        them; seed=int: the per-step noise is drawn inside the update kernel (nothing but x and eps is read).
+        noise_source (optional): callable(shape) -> tensor that replaces those draws, in the reference's order (x_T first,
+        then one per step with t > 0) -- how a recorded reference run is replayed."""
         device = self.betas.device
         sample_inter = 1 | (self.num_timesteps // 10)
-        img = torch.randn(x_in["Res"].shape, device=device)
+        shape = tuple(x_in["Res"].shape)
+        img = torch.randn(shape, device=device) if noise_source is None else noise_source(shape).to(device)
         ret = res2img(img, x_in["MS"])
         for i in reversed(range(self.num_timesteps)):
-            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, guidance=guidance, seed=seed)
+            z = noise_source(shape).to(device) if (noise_source is not None and i > 0) else None
+            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, guidance=guidance, seed=seed, noise=z)
             if i % sample_inter == 0:
                 ret = torch.cat([ret, res2img(img, x_in["MS"])], dim=0)
         return ret if continous else ret[-1]
 
     @torch.no_grad()
-    def p_sample_loop_steps(self, x_in, img, steps, prompt="QB", seed=None):
+    def p_sample_loop_steps(self, x_in, img, steps, prompt="QB", seed=None, noise_source=None):
         """The body of p_sample_loop over an explicit list of timesteps from a given x_t (tests, truncated schedules)."""
         for i in steps:
-            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, seed=seed)
+            z = noise_source(tuple(img.shape)).to(img.device) if (noise_source is not None and i > 0) else None
+            img = self.p_sample(img, i, condition_x=x_in, prompt=prompt, seed=seed, noise=z)
         return img
 
     @torch.no_grad()
