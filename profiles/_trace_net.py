@@ -12,6 +12,6 @@ pan, ms, x = [t.cuda() for t in make_inputs(B, 4, 64, 64)]
 t = torch.full((B,), 500.0).cuda()
 m(x, t, PAN=pan, MS=ms, prompt="QB")
 torch.cuda.synchronize()
-os.environ["TMD_UMMA_TRACE"] = "1"
+os.environ["TMD_UMMA_TRACE"] = os.environ.get("TRACE_LEVEL", "1")
 m(x, t, PAN=pan, MS=ms, prompt="QB")
 torch.cuda.synchronize()

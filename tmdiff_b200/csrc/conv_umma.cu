@@ -255,10 +255,14 @@ __device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, i
 // Swish through the hardware tanh: x*sigmoid(x) = h + h*tanh(h), h = x/2 (one MUFU op; its 2^-11 relative
 // error is below the bf16 rounding of the stored activation).
 __device__ __forceinline__ float swish_tanh(float x) {
+#ifdef TMD_SWISH_EXACT
+    return __fdividef(x, 1.f + __expf(-x));      // diagnostic variant: ex2 + rcp (two MUFU ops)
+#else
     const float h = 0.5f * x;
     float t;
     asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
     return fmaf(h, t, h);
+#endif
 }
 
 // v = accumulator + bias for channels [co, co+16) of one output voxel: residual adds, raw view and the activated
@@ -311,9 +315,13 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
                     if (!(e.dbg & 16)) {
                         float a, b2, ta, tb2;
                         upk2(x, a, b2);
+#ifdef TMD_SWISH_EXACT
+                        x = pk2(swish_tanh(2.f * a), swish_tanh(2.f * b2));
+#else
                         asm("tanh.approx.f32 %0, %1;" : "=f"(ta) : "f"(a));
                         asm("tanh.approx.f32 %0, %1;" : "=f"(tb2) : "f"(b2));
                         x = fma2(x, pk2(ta, tb2), x);
+#endif
                     } else x = add2(x, x);
                     x = mul2(x, ss[i]);
                     upk2(x, u[2 * i], u[2 * i + 1]);
@@ -656,6 +664,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             if (tr) tq = clock64();
             mbar_wait(acc_empty(ab), ((lt >> P.acc_shift) & 1) ^ 1);
             if (tr) tw_acc += clock64() - tq;
+            if (tr && lane == 0 && lt >= 4 && lt < 8) P.trace[200 + 2 * (lt - 4)] = clock64();          // timeline: MMA issue of this tile starts
             tc_fence_after();
             const uint32_t d0 = tmem_base + ab * NACC * Co;
             uint32_t fresh = 0;                                   // 0 for the first MMA into each accumulator of this tile
@@ -790,6 +799,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             }
             if (elect_one()) tc_commit(acc_full(ab));
             __syncwarp();
+            if (tr && lane == 0 && lt >= 4 && lt < 8) P.trace[201 + 2 * (lt - 4)] = clock64();          // timeline: last MMA issued + commit
         }
         if (tr && lane == 0) {
             P.trace[0] = clock64() - t_all0; P.trace[1] = tw_acc; P.trace[2] = tw_a; P.trace[3] = tw_b; P.trace[4] = t_issue;
@@ -801,8 +811,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const int sub = (warp - 4) >> 2;                  // which of the quarter's warps
         const int r = q * 32 + lane;                      // accumulator row = voxel of the tile
         uint32_t lt = 0;
-        long long tw_full = 0, tw_ld = 0, tw_bar = 0, t_all0 = clock64(), tq = 0;
-        const bool tr = P.trace && blockIdx.x == 0 && threadIdx.x == 128;
+        long long tw_full = 0, tw_ld = 0, tw_bar = 0, tw_sync = 0, t_all0 = clock64(), tq = 0;
+        const bool tr = P.trace && blockIdx.x == 0 && lane == 0;      // lane 0 of every epilogue warp of CTA 0
         const size_t plane_vox = (size_t)P.H * P.W, hplane_vox = (size_t)(P.H / 2) * (P.W / 2);
         // REUSE kernels: a tile lies in one sample, so its per-sample epilogue vectors [bias | tb0 | tb1 | sc0 | sc1][Co]
         // are staged in shared memory once per tile (double-buffered, fetched one tile ahead by the 384 epilogue threads)
@@ -844,7 +854,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             y_in = t % P.TH; t /= P.TH;
             n_in = t % P.TN; b_in = t / P.TN;
         }
+        int n_stamp = 0;
+        auto stamp = [&]() { if (tr && warp == 4 && lt >= 4 && lt < 8 && n_stamp < 24) P.trace[96 + 24 * (lt - 4) + n_stamp++] = clock64(); };
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
+            n_stamp = 0;
+            stamp();                                     // 0: loop top
             const TileCoord tc = decode_tile(P, tile);
             const int ab = lt & (uint32_t)(P.acc_stages - 1);
             const int b = tc.b0 + b_in, n_off = n_in, y = y_in + tc.y0, x = x_in + tc.x0;
@@ -869,10 +883,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             // one warp probes the accumulator barrier for all twelve (every probe is a wavefront on the shared-memory data pipe
             // the tensor core reads through: +2.6 %); the named barrier hands the observation on (and publishes the staged
             // vectors), tcgen05.fence::after_thread_sync orders the TMEM loads behind it
+            stamp();                                     // 1: decode + constant loads issued
             if (tr) tq = clock64();
             if (warp == 4) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
             if (tr) tw_full += clock64() - tq;
+            stamp();                                     // 2: accumulator full
+            if (tr) tq = clock64();
             asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
+            if (tr) tw_sync += clock64() - tq;
             tc_fence_after();
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
@@ -880,7 +898,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
 #ifndef TMD_EXP_NOPREF
             if (normal && pl < NACC) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
 #endif
+            stamp();                                     // 3: barrier + first residual prefetch issued
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
+                stamp();                                 // item: start
                 int pl2 = pl, sl2 = sl + kEpiPerQuarter;
                 while (sl2 >= nslab) { sl2 -= nslab; ++pl2; }
 #ifdef TMD_EXP_NOPREF
@@ -894,19 +914,28 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 float acc[16];
                 if (tr) tq = clock64();
                 tc_ld16(t_row + sl * 16, acc);
-                if (tr) tw_ld += clock64() - tq;
+                if (tr) { tw_ld += clock64() - tq; tq = clock64(); }
+                stamp();                                 // item: accumulator slab in registers
                 epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs, cb);
+                if (tr) tw_bar += clock64() - tq;
+                stamp();                                 // item: done
 #ifndef TMD_EXP_NOPREF
                 cur = nxt;
 #endif
                 pl = pl2; sl = sl2;
             }
             if (MODE && tile + (int)gridDim.x < P.num_tiles) store_consts(&cst[(lt + 1) & 1][0]);
+            stamp();                                     // constants of the next tile stored
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty(ab));
+            stamp();                                     // accumulator released
         }
-        if (tr) { P.trace[8] = clock64() - t_all0; P.trace[9] = tw_full; P.trace[10] = tw_ld; P.trace[11] = tw_bar; }
+        if (tr) {
+            if (warp == 4) { P.trace[8] = clock64() - t_all0; P.trace[9] = tw_full; P.trace[10] = tw_ld; P.trace[11] = tw_bar; }
+            long long* w = P.trace + 16 + 4 * (warp - 4);
+            w[0] = clock64() - t_all0; w[1] = tw_sync; w[2] = tw_ld; w[3] = tw_bar;
+        }
     }
 
     tc_fence_before();
@@ -1211,18 +1240,31 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
     KernelFn kern = pick_kernel(plan->p);
     if (env_int("TMD_UMMA_TRACE", 0)) {
         UmmaParams p = plan->p;
-        cudaMalloc((void**)&p.trace, 16 * sizeof(long long));
-        cudaMemset(p.trace, 0, 16 * sizeof(long long));
+        cudaMalloc((void**)&p.trace, 256 * sizeof(long long));
+        cudaMemset(p.trace, 0, 256 * sizeof(long long));
         kern<<<plan->grid, kThreads, plan->smem, stream>>>(p);
         cudaDeviceSynchronize();
-        long long t[16];
+        long long t[256];
         cudaMemcpy(t, p.trace, sizeof(t), cudaMemcpyDeviceToHost);
         cudaFree(p.trace);
         const long long mmas = t[6] * (p.mode ? 27 : p.taps) * p.nkc * p.NACC * (p.KC / 16);
         fprintf(stderr, "[umma trace] Ci=%d Co=%d %dx%dx%d mode=%d NACC=%d tiles=%d grid=%d | mma warp: total %lld cyc, wait acc %lld, wait A %lld, "
-                "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld, tmem ld %lld, bar %lld\n",
+                "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld, tmem ld %lld, compute+store %lld\n",
                 p.Ci, p.Co, p.N, p.H, p.W, p.mode, p.NACC, p.num_tiles, plan->grid, t[0], t[1], t[2], t[3], t[4],
                 mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9], t[10], t[11]);
+        if (env_int("TMD_UMMA_TRACE", 0) > 1) {
+            fprintf(stderr, "    epilogue warps (total / barrier wait / tmem ld / compute+store):");
+            for (int w = 0; w < 4 * kEpiPerQuarter; ++w) fprintf(stderr, " [w%d %lld %lld %lld %lld]", w + 4, t[16 + 4 * w], t[17 + 4 * w], t[18 + 4 * w], t[19 + 4 * w]);
+            fprintf(stderr, "\n");
+            // timeline of local tiles 4..7 (cycles relative to the MMA start of tile 4): the MMA warp's [issue start, commit] and
+            // warp 4's stamps
+            const long long z = t[200];
+            for (int i = 0; i < 4; ++i) {
+                fprintf(stderr, "    tile %d: mma [%lld, %lld] epi", 4 + i, t[200 + 2 * i] - z, t[201 + 2 * i] - z);
+                for (int k = 0; k < 24 && t[96 + 24 * i + k]; ++k) fprintf(stderr, " %lld", t[96 + 24 * i + k] - z);
+                fprintf(stderr, "\n");
+            }
+        }
         return cudaGetLastError();
     }
     // (programmatic dependent launch was measured: no gain -- one CTA per SM leaves nothing for the next kernel to overlap)
