@@ -40,6 +40,10 @@ struct ConvEpilogue {
     void* hf_out[3]; int ld_hf;      // POOL only: LH, HL, HH
     void* pool_out; int ld_pool;     // NORMAL only (tcgen05 kernel): 2x2 average of v at half resolution
     int dbg;                         // diagnostics of the tcgen05 kernel (TMD_UMMA_DEBUG), 0 in production
+    // tcgen05 kernel: raw_out is written / add0 is read as IEEE half instead of bfloat16 (same bytes, 11-bit instead of 8-bit
+    // significand).  For tensors that are only ever added -- the residual stream of the final block, which no MMA reads:
+    // rounding it to bf16 at every block was the largest avoidable term of the bf16 mode's error.
+    int raw_f16, add0_f16;
 };
 
 struct ConvOp {

@@ -25,6 +25,7 @@
 //   warps 4-7     : epilogue: tcgen05.ld -> bias / residual adds / Haar pooling or 2x upsampling /
 //                   time-bias + Swish + text-scale views -> bf16 stores (conv_op.h)
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 #include <cstdio>
 #include <cstdlib>
@@ -148,6 +149,23 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// The same load split into issue and wait, so the next slab's TMEM read overlaps the arithmetic on the current one.  The wait
+// names the registers as in/out operands: nothing that uses them can be scheduled above it.
+__device__ __forceinline__ void tc_ld16_issue(uint32_t taddr, uint32_t r[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tc_ld16_wait(uint32_t r[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]),
+                   "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :
+                 : "memory");
+}
+
 // K-major shared-memory matrix descriptors (tcgen05 "smem descriptor") are assembled in the MMA loop:
 // start address >> 4 in bits [0,14), LBO = 1 at [16,30), SBO (8-row swizzle atom pitch) >> 4 at [32,46),
 // version 1 at [46,48), swizzle mode at [61,64).
@@ -241,6 +259,21 @@ __device__ __forceinline__ void store16_bf16(__nv_bfloat16* p, const float v[16]
     for (int i = 0; i < 8; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
     st_global_v8(p, w);
 }
+// IEEE-half twins for add-only tensors (ConvEpilogue::raw_f16 / add0_f16); values beyond the half range saturate
+__device__ __forceinline__ void store16_f16(void* p, const float v[16]) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w[i]) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+    st_global_v8(p, w);
+}
+__device__ __forceinline__ void add_f16x16(float v[16], const uint32_t w[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        v[2 * i] += f.x;
+        v[2 * i + 1] += f.y;
+    }
+}
 
 // Residual operand of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
 struct Resid { uint32_t a0[8]; };
@@ -271,12 +304,11 @@ template <bool kPre>
 __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, float v[16], const uint32_t* pre0 = nullptr) {
     typedef __nv_bfloat16 T;
     if (e.add0) {
-        if (kPre) add_bf16x16(v, pre0);
-        else {
-            uint32_t w[8];
-            ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, w);
-            add_bf16x16(v, w);
-        }
+        uint32_t w[8];
+        if (!kPre) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, w);
+        const uint32_t* src = kPre ? pre0 : w;
+        if (e.add0_f16) add_f16x16(v, src);
+        else add_bf16x16(v, src);
     }
     if (e.add1) {
         uint32_t w[8];
@@ -292,7 +324,10 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
                                               int cb = 0) {
     typedef __nv_bfloat16 T;
     const int cg = co + cb;          // channel in the tensors (co: channel of this tile's group, the index into cs)
-    if (e.raw_out && !(e.dbg & 64)) store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
+    if (e.raw_out && !(e.dbg & 64)) {
+        if (e.raw_f16) store16_f16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
+        else store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
+    }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         if (!e.act_out[k]) continue;
@@ -445,6 +480,12 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
 // (back-off in the producers' waits -- nanosleep 32 / 200 ns, try_wait suspend hints 0.5-2 us -- was measured: 0 to -6 %)
 #define PRODUCER_WAIT(bar, ph) mbar_wait<TMD_PRODUCER_SLEEP>(bar, ph)
 struct TileCoord { int b0, n0, y0, x0, ch; };
+// REUSE kernels: what the epilogue warps need to know about a tile, prepared one tile ahead by the helper warp
+struct TileInfo {
+    int b0, n0, y0, x0, cb;          // sample, first band plane, tile origin, first channel of the tile's channel group
+    int pad;
+    long long vox_base, hvox_base;   // voxel index of the tile origin at the conv's resolution and at half of it
+};
 // n / d for n < 2^31 with the host's {multiplier, shift} (round-up method): a 32-bit multiply-high, an add and a shift instead of
 // the ~40-instruction runtime division -- the epilogue warps decode two tiles per tile and are short of issue slots.
 __device__ __forceinline__ uint32_t fdiv(uint32_t n, const uint32_t f[2]) { return (__umulhi(n, f[0]) + n) >> f[1]; }
@@ -492,7 +533,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc];
     __shared__ uint32_t tmem_base_slot;
-    __shared__ __align__(16) float cst[MODE ? 2 : 1][MODE ? 5 * kMaxCo : 4];   // REUSE: per-tile epilogue vectors (see the epilogue warps)
+    __shared__ __align__(16) float cst[MODE ? 2 : 1][MODE ? 5 * kMaxCo : 4];   // REUSE: per-tile epilogue vectors (see the helper warp)
+    __shared__ __align__(16) TileInfo tinfo[2];
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // swizzle atoms need 1024-byte alignment
@@ -805,6 +847,43 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             P.trace[0] = clock64() - t_all0; P.trace[1] = tw_acc; P.trace[2] = tw_a; P.trace[3] = tw_b; P.trace[4] = t_issue;
             P.trace[6] = lt;
         }
+    } else if (warp == 3) {
+        if (MODE) {
+            // ================= helper: tile records + per-sample epilogue vectors, one tile ahead =================
+            // Joins the epilogue warps' per-tile named barrier: after barrier lt nobody reads buffer (lt + 1) & 1 any more (it
+            // served tile lt - 1), so the record of tile lt + 1 is written there and published by barrier lt + 1.
+            const ConvEpilogue& e = P.epi;
+            const int n_cst = 5 * P.Co;
+            auto prepare = [&](int tile, int buf) {
+                const TileCoord tc = decode_tile(P, tile);
+                const int cb = tc.ch * P.Co;
+                float* dst = &cst[buf][0];
+#pragma unroll 4
+                for (int idx = lane; idx < n_cst; idx += 32) {
+                    const int v = (int)fdiv((uint32_t)idx, P.fd[4]), c = idx - v * P.Co + cb;
+                    float val;
+                    if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
+                    else if (v < 3) val = e.tb[v - 1] ? 0.5f * __ldg(e.tb[v - 1] + (size_t)tc.b0 * e.ld_tb + c) : 0.f;   // stored halved (store_views16)
+                    else val = e.sc[v - 3] ? __ldg(e.sc[v - 3] + (size_t)tc.b0 * e.ld_sc + c) : 1.f;
+                    dst[idx] = val;
+                }
+                if (lane == 0) {
+                    TileInfo ti;
+                    ti.b0 = tc.b0; ti.n0 = tc.n0; ti.y0 = tc.y0; ti.x0 = tc.x0; ti.cb = cb; ti.pad = 0;
+                    const long long bn0 = (long long)tc.b0 * P.N + tc.n0;
+                    ti.vox_base = (bn0 * P.H + tc.y0) * P.W + tc.x0;
+                    ti.hvox_base = (bn0 * (P.H / 2) + tc.y0 / 2) * (P.W / 2) + tc.x0 / 2;
+                    tinfo[buf] = ti;
+                }
+            };
+            uint32_t lt = 0;
+            prepare(blockIdx.x, 0);
+            for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
+                asm volatile("bar.sync 1, %0;" ::"n"(128 * kEpiPerQuarter + 32) : "memory");
+                const int nt = tile + gridDim.x;
+                if (nt < P.num_tiles) prepare(nt, (lt + 1) & 1);
+            }
+        }
     } else if (warp >= 4) {
         // ================= epilogue =================
         const int q = warp & 3;                           // TMEM lane quarter this warp may read
@@ -814,37 +893,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         long long tw_full = 0, tw_ld = 0, tw_bar = 0, tw_sync = 0, t_all0 = clock64(), tq = 0;
         const bool tr = P.trace && blockIdx.x == 0 && lane == 0;      // lane 0 of every epilogue warp of CTA 0
         const size_t plane_vox = (size_t)P.H * P.W, hplane_vox = (size_t)(P.H / 2) * (P.W / 2);
-        // REUSE kernels: a tile lies in one sample, so its per-sample epilogue vectors [bias | tb0 | tb1 | sc0 | sc1][Co]
-        // are staged in shared memory once per tile (double-buffered, fetched one tile ahead by the 384 epilogue threads)
-        // instead of being re-read from global memory by every lane for every slab.
-        const int e_tid = (int)threadIdx.x - 128, n_cst = 5 * P.Co;
-        float pre_c[kCstPerThread];
-        auto load_consts = [&](int bb, int cb) {
-            const ConvEpilogue& e = P.epi;
-#pragma unroll
-            for (int j = 0; j < kCstPerThread; ++j) {
-                const int idx = e_tid + j * 128 * kEpiPerQuarter;
-                if (idx >= n_cst) continue;
-                const int v = (int)fdiv((uint32_t)idx, P.fd[4]), c = idx - v * P.Co + cb;
-                float val;
-                if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
-                else if (v < 3) val = e.tb[v - 1] ? 0.5f * __ldg(e.tb[v - 1] + (size_t)bb * e.ld_tb + c) : 0.f;   // stored halved (store_views16)
-                else val = e.sc[v - 3] ? __ldg(e.sc[v - 3] + (size_t)bb * e.ld_sc + c) : 1.f;
-                pre_c[j] = val;
-            }
-        };
-        auto store_consts = [&](float* dst) {
-#pragma unroll
-            for (int j = 0; j < kCstPerThread; ++j) {
-                const int idx = e_tid + j * 128 * kEpiPerQuarter;
-                if (idx < n_cst) dst[idx] = pre_c[j];
-            }
-        };
-        if (MODE && (int)blockIdx.x < P.num_tiles) {
-            const TileCoord t0 = decode_tile(P, blockIdx.x);
-            load_consts(t0.b0, t0.ch * P.Co);
-            store_consts(&cst[0][0]);
-        }
+        // REUSE kernels: a tile lies in one sample; its coordinates and per-sample epilogue vectors [bias | tb0 | tb1 | sc0 | sc1][Co]
+        // are prepared in shared memory one tile ahead by the helper warp (warp 3), so the epilogue warps neither decode tiles
+        // nor wait for global loads of those vectors (their per-tile fixed cost was ~4000 of ~9000 cycles at Co = 32,
+        // profiles/umma_timeline_r02c.txt).
         // the row's place in its tile: REUSE (x, y) of the 16 x 8 plane tile; SIMPLE (x, y, band plane, sample) of the box
         int x_in, y_in, n_in = 0, b_in = 0;
         if (MODE) { x_in = r % P.TW; y_in = r / P.TW; }
@@ -854,78 +906,86 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             y_in = t % P.TH; t /= P.TH;
             n_in = t % P.TN; b_in = t / P.TN;
         }
+        const int lane_vox = y_in * P.W + x_in, lane_hvox = (y_in >> 1) * (P.W >> 1) + (x_in >> 1);     // REUSE: offsets from the tile origin
+        constexpr int kBarCount = 128 * kEpiPerQuarter + (MODE ? 32 : 0);
+        const int nslab = P.Co >> 4, nitems = NACC * nslab;
+        const bool normal = P.epi.mode == CONV_NORMAL;
         int n_stamp = 0;
         auto stamp = [&]() { if (tr && warp == 4 && lt >= 4 && lt < 8 && n_stamp < 24) P.trace[96 + 24 * (lt - 4) + n_stamp++] = clock64(); };
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
             n_stamp = 0;
             stamp();                                     // 0: loop top
-            const TileCoord tc = decode_tile(P, tile);
             const int ab = lt & (uint32_t)(P.acc_stages - 1);
-            const int b = tc.b0 + b_in, n_off = n_in, y = y_in + tc.y0, x = x_in + tc.x0;
-            // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin and
-            // fetch the residual operands of their next item before touching the current accumulator slab
-            const int nslab = P.Co >> 4, nitems = NACC * nslab;
-            const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
-            const bool normal = P.epi.mode == CONV_NORMAL;
-            const int cb = tc.ch * P.Co;                    // first channel of this tile's group
-            const size_t bn0 = (size_t)b * P.N + tc.n0 + n_off;
-            const size_t vox0 = (bn0 * P.H + y) * P.W + x, hvox0 = (bn0 * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
-            const float* cs = nullptr;
-            if (MODE) {
-                // this tile's per-sample vectors were staged by the previous iteration; fetch the next tile's
-                cs = &cst[lt & 1][0];
-                const int nt = tile + gridDim.x;
-                if (nt < P.num_tiles) {
-                    const TileCoord tn = decode_tile(P, nt);
-                    load_consts(tn.b0, tn.ch * P.Co);
-                }
-            }
             // one warp probes the accumulator barrier for all twelve (every probe is a wavefront on the shared-memory data pipe
-            // the tensor core reads through: +2.6 %); the named barrier hands the observation on (and publishes the staged
-            // vectors), tcgen05.fence::after_thread_sync orders the TMEM loads behind it
-            stamp();                                     // 1: decode + constant loads issued
+            // the tensor core reads through: +2.6 %); the named barrier hands the observation on (and publishes the helper
+            // warp's tile record), tcgen05.fence::after_thread_sync orders the TMEM loads behind it
             if (tr) tq = clock64();
             if (warp == 4) mbar_wait(acc_full(ab), (lt >> P.acc_shift) & 1);
             if (tr) tw_full += clock64() - tq;
-            stamp();                                     // 2: accumulator full
-            if (tr) tq = clock64();
-            asm volatile("bar.sync 1, %0;" ::"r"(128 * kEpiPerQuarter) : "memory");
-            if (tr) tw_sync += clock64() - tq;
+            stamp();                                     // 1: accumulator full
+            asm volatile("bar.sync 1, %0;" ::"n"(kBarCount) : "memory");
             tc_fence_after();
+            int b, y, x, n0, cb;
+            size_t vox0, hvox0;
+            const float* cs = nullptr;
+            if (MODE) {
+                const TileInfo& ti = tinfo[lt & 1];
+                b = ti.b0; n0 = ti.n0; cb = ti.cb;
+                y = y_in + ti.y0; x = x_in + ti.x0;
+                vox0 = (size_t)ti.vox_base + lane_vox;
+                hvox0 = (size_t)ti.hvox_base + lane_hvox;
+                cs = &cst[lt & 1][0];
+            } else {
+                const TileCoord tc = decode_tile(P, tile);
+                b = tc.b0 + b_in; n0 = tc.n0 + n_in; cb = tc.ch * P.Co;
+                y = y_in + tc.y0; x = x_in + tc.x0;
+                const size_t bn0 = (size_t)b * P.N + n0;
+                vox0 = (bn0 * P.H + y) * P.W + x;
+                hvox0 = (bn0 * (P.H / 2) + y / 2) * (P.W / 2) + x / 2;
+            }
+            // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin, fetch the residual
+            // operands of their next item and start the TMEM read of the next slab before working on the current one
+            const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
+            const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC) * P.Co;
             Resid cur, nxt;
-#ifndef TMD_EXP_NOPREF
-            if (normal && pl < NACC) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
-#endif
-            stamp();                                     // 3: barrier + first residual prefetch issued
+            uint32_t ra[16], rb[16];
+            if (pl < NACC) {
+                if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl) * P.Co + sl * 16, ra);
+                if (normal) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
+            }
+            stamp();                                     // 2: barrier + first TMEM read / residual prefetch issued
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
                 stamp();                                 // item: start
                 int pl2 = pl, sl2 = sl + kEpiPerQuarter;
                 while (sl2 >= nslab) { sl2 -= nslab; ++pl2; }
-#ifdef TMD_EXP_NOPREF
-                if (normal) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && tc.n0 + n_off + pl < P.N, cur);
-#else
-                if (normal && pl2 < NACC)
-                    load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && tc.n0 + n_off + pl2 < P.N, nxt);
-#endif
-                const bool valid = in_tile && tc.n0 + n_off + pl < P.N;
-                const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC + (NACC - 1 - pl)) * P.Co;
-                float acc[16];
                 if (tr) tq = clock64();
-                tc_ld16(t_row + sl * 16, acc);
+                float acc[16];
+                if (MODE) {
+                    tc_ld16_wait(ra);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) acc[i] = __uint_as_float(ra[i]);
+                } else {
+                    tc_ld16(t_lane + (uint32_t)(NACC - 1 - pl) * P.Co + sl * 16, acc);                  // SIMPLE kernels: no read-ahead (registers)
+                }
                 if (tr) { tw_ld += clock64() - tq; tq = clock64(); }
+                if (pl2 < NACC) {
+                    if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl2) * P.Co + sl2 * 16, rb);
+                    if (normal) load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && n0 + pl2 < P.N, nxt);
+                }
+                const bool valid = in_tile && n0 + pl < P.N;
                 stamp();                                 // item: accumulator slab in registers
                 epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs, cb);
                 if (tr) tw_bar += clock64() - tq;
                 stamp();                                 // item: done
-#ifndef TMD_EXP_NOPREF
                 cur = nxt;
-#endif
+                if (MODE) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) ra[i] = rb[i];
+                }
                 pl = pl2; sl = sl2;
             }
-            if (MODE && tile + (int)gridDim.x < P.num_tiles) store_consts(&cst[(lt + 1) & 1][0]);
-            stamp();                                     // constants of the next tile stored
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty(ab));

@@ -38,6 +38,7 @@ namespace {
 struct View {  // channel slice of a channels-last activation tensor
     void* p = nullptr;
     int C = 0, ld = 0;
+    bool f16 = false;   // bf16 mode: an add-only tensor kept as IEEE half (ConvEpilogue::raw_f16 / add0_f16)
 };
 struct ActSpec {
     View dst;
@@ -512,6 +513,8 @@ struct Planner {
         }
         ep.pool_out = out.pool.p; ep.ld_pool = out.pool.ld;
         ep.add0 = add0.p; ep.ld_add0 = add0.ld;
+        ep.raw_f16 = out.raw.f16 ? 1 : 0; ep.add0_f16 = add0.f16 ? 1 : 0;
+
         ep.add1 = add1.p; ep.ld_add1 = add1.ld;
         ep.raw_out = out.raw.p; ep.ld_raw = out.raw.ld;
         for (int i = 0; i < 2; ++i) {
@@ -542,7 +545,7 @@ struct Planner {
         snprintf(lb, sizeof(lb), "%s Ci=%d Co=%d L%d %s", wname.c_str(), cw.Ci, cw.Co, lvl,
                  mode == CONV_POOL ? "pool" : (mode == CONV_UPSAMPLE ? "up" : "same"));
         const std::string label = std::string(lb) + (cw2 ? " +" + w2name.substr(w2name.rfind('.') + 1) : "") + (out.pool.p ? " +pool" : "");
-        if ((cw2 || out.pool.p) && (e->dtype == TMD_F32 || !conv_umma_supported(op))) { err = "fused conv outside the tcgen05 envelope"; return; }
+        if ((cw2 || out.pool.p || ep.raw_f16 || ep.add0_f16) && (e->dtype == TMD_F32 || !conv_umma_supported(op))) { err = "fused conv outside the tcgen05 envelope"; return; }
         if (e->dtype == TMD_F32) {
             push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); }, label);
         } else if (conv_umma_supported(op)) {
@@ -795,6 +798,9 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         }
         {   // final (:265-273)
             View f[2] = {P.buf("f0", 0, c[0]), P.buf("f1", 0, c[0])};
+            // the residual stream of the final block is only ever added (identity skips, :249): IEEE half instead of bf16
+            static const bool f16_res = !getenv("TMD_NO_F16_RESIDUAL");
+            if (P.fuse && f16_res) f[0].f16 = f[1].f16 = true;
             View af[2] = {P.buf("af0", 0, c[0]), P.buf("af1", 0, c[0])};
             View ia = cat_act[0], ir = cat_raw[0];
             for (int i = 0; i < 4; ++i) {
