@@ -9,7 +9,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libtmdiff_b200.so")
-SOURCES = ["engine.cu", "elementwise.cu", "solver.cu", "conv_simt.cu", "conv_umma.cu", "attn_umma.cu", "operators.cu", "operators2.cu"]
+# conv_umma.cu is compiled three times: the host side + generic kernels, and the epilogue-specialised 4- / 8-accumulator kernels
+SOURCES = ["engine.cu", "elementwise.cu", "solver.cu", "conv_simt.cu", "conv_umma.cu", "conv_umma.cu#1", "conv_umma.cu#2", "attn_umma.cu",
+           "operators.cu", "operators2.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 
@@ -38,8 +40,9 @@ def build(force=False, verbose=False):
     nvcc = _nvcc()
 
     def compile_one(src):
-        obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+        src, _, part = src.partition("#")
+        obj = os.path.join(obj_dir, src.replace(".cu", (".p%s.o" % part) if part else ".o"))
+        cmd = [nvcc] + NVCC_FLAGS + (["-DTMD_UMMA_PART=" + part] if part else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -30,9 +30,16 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <initializer_list>
+#include <set>
+#include <utility>
 
 #include "conv_op.h"
 #include "kernels.h"
+
+#ifndef TMD_UMMA_PART
+#define TMD_UMMA_PART 0
+#endif
 
 namespace tmd {
 
@@ -275,14 +282,36 @@ __device__ __forceinline__ void add_f16x16(float v[16], const uint32_t w[8]) {
     }
 }
 
+// Shape of the epilogue as a compile-time word.  The epilogue of a tile is a short, dependent instruction stream run by twelve
+// warps; with the shape in the launch parameters every `if (e.add0)` was a constant-bank load, a compare and a branch the warp
+// had to resolve before going on (~15 per 16-channel slab, ~1000 of the ~1500 cycles a slab took at Co = 32:
+// profiles/dbg_sweep_r02a.txt, umma_timeline_r02*.txt).  EF >= 0: the shape is this template argument (the kernels of the
+// sampling path); EF < 0: the generic kernel reads it from the parameters (operator API, diagnostics).
+enum : int { EF_POOL = 1, EF_UP = 2, EF_RAW = 4, EF_ACT0 = 8, EF_ACT1 = 16, EF_ADD0 = 32, EF_ADD1 = 64, EF_POOLOUT = 128, EF_HF = 256,
+             EF_RAWF16 = 512, EF_ADD0F16 = 1024 };
+template <int EF> struct Epi {
+    static __device__ __forceinline__ int mode(const ConvEpilogue& e) { return EF < 0 ? e.mode : (EF & 3); }
+    static __device__ __forceinline__ bool raw(const ConvEpilogue& e) { return EF < 0 ? e.raw_out != nullptr : (EF & EF_RAW) != 0; }
+    static __device__ __forceinline__ bool act(const ConvEpilogue& e, int k) { return EF < 0 ? e.act_out[k] != nullptr : (EF & (EF_ACT0 << k)) != 0; }
+    static __device__ __forceinline__ bool add0(const ConvEpilogue& e) { return EF < 0 ? e.add0 != nullptr : (EF & EF_ADD0) != 0; }
+    static __device__ __forceinline__ bool add1(const ConvEpilogue& e) { return EF < 0 ? e.add1 != nullptr : (EF & EF_ADD1) != 0; }
+    static __device__ __forceinline__ bool pool_out(const ConvEpilogue& e) { return EF < 0 ? e.pool_out != nullptr : (EF & EF_POOLOUT) != 0; }
+    static __device__ __forceinline__ bool hf(const ConvEpilogue& e) { return EF < 0 ? e.hf_out[0] != nullptr : (EF & EF_HF) != 0; }
+    static __device__ __forceinline__ bool raw_f16(const ConvEpilogue& e) { return EF < 0 ? e.raw_f16 != 0 : (EF & EF_RAWF16) != 0; }
+    static __device__ __forceinline__ bool add0_f16(const ConvEpilogue& e) { return EF < 0 ? e.add0_f16 != 0 : (EF & EF_ADD0F16) != 0; }
+    static __device__ __forceinline__ int dbg(const ConvEpilogue& e, int bit) { return EF < 0 ? (e.dbg & bit) : 0; }   // TMD_UMMA_DEBUG: generic kernel only
+};
+
 // Residual operand of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
 struct Resid { uint32_t a0[8]; };
+template <int EF>
 __device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, int co, bool valid, Resid& r) {
     typedef __nv_bfloat16 T;
+    if (!Epi<EF>::add0(e)) return;
 #pragma unroll
     for (int i = 0; i < 8; ++i) r.a0[i] = 0u;
-    if (!valid || (e.dbg & 32)) return;
-    if (e.add0) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
+    if (!valid || Epi<EF>::dbg(e, 32)) return;
+    ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
 }
 
 // Swish through the hardware tanh: x*sigmoid(x) = h + h*tanh(h), h = x/2 (one MUFU op; its 2^-11 relative
@@ -300,17 +329,17 @@ __device__ __forceinline__ float swish_tanh(float x) {
 
 // v = accumulator + bias for channels [co, co+16) of one output voxel: residual adds, raw view and the activated
 // views (same contract as epilogue_store4 in conv_op.h).
-template <bool kPre>
+template <int EF, bool kPre>
 __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, float v[16], const uint32_t* pre0 = nullptr) {
     typedef __nv_bfloat16 T;
-    if (e.add0) {
+    if (Epi<EF>::add0(e)) {
         uint32_t w[8];
         if (!kPre) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, w);
         const uint32_t* src = kPre ? pre0 : w;
-        if (e.add0_f16) add_f16x16(v, src);
+        if (Epi<EF>::add0_f16(e)) add_f16x16(v, src);
         else add_bf16x16(v, src);
     }
-    if (e.add1) {
+    if (Epi<EF>::add1(e)) {
         uint32_t w[8];
         ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
         add_bf16x16(v, w);
@@ -319,18 +348,18 @@ __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ov
 
 // kS: the per-sample vectors come from the tile's staged copy in shared memory, cs = [bias | tb0 | tb1 | sc0 | sc1][Co]
 // (tb halved; absent tb reads as 0, absent sc as 1), instead of global memory.
-template <bool kS>
+template <int EF, bool kS>
 __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size_t ovox, int co, const float v[16], const float* cs = nullptr, int Co = 0,
                                               int cb = 0) {
     typedef __nv_bfloat16 T;
     const int cg = co + cb;          // channel in the tensors (co: channel of this tile's group, the index into cs)
-    if (e.raw_out && !(e.dbg & 64)) {
-        if (e.raw_f16) store16_f16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
+    if (Epi<EF>::raw(e) && !Epi<EF>::dbg(e, 64)) {
+        if (Epi<EF>::raw_f16(e)) store16_f16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
         else store16_bf16(reinterpret_cast<T*>(e.raw_out) + ovox * e.ld_raw + cg, v);
     }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-        if (!e.act_out[k]) continue;
+        if (!Epi<EF>::act(e, k)) continue;
         uint32_t w[8];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -347,7 +376,7 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     uint64_t x = fma2(pk2(v[8 * h + 2 * i], v[8 * h + 2 * i + 1]), half2, tt[i]);
-                    if (!(e.dbg & 16)) {
+                    if (!Epi<EF>::dbg(e, 16)) {
                         float a, b2, ta, tb2;
                         upk2(x, a, b2);
 #ifdef TMD_SWISH_EXACT
@@ -368,7 +397,7 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
                 for (int i = 0; i < 8; ++i) {
                     float x = v[8 * h + i];
                     if (e.tb[k]) x += t[i];
-                    if (!(e.dbg & 16)) x = swish_tanh(x);
+                    if (!Epi<EF>::dbg(e, 16)) x = swish_tanh(x);
                     if (e.sc[k]) x *= s[i];
                     u[i] = x;
                 }
@@ -376,14 +405,14 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
 #pragma unroll
             for (int i = 0; i < 4; ++i) w[4 * h + i] = pack_bf16x2(u[2 * i], u[2 * i + 1]);
         }
-        if (!(e.dbg & 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + cg, w);
+        if (!Epi<EF>::dbg(e, 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + cg, w);
     }
 }
 
 // One 16-channel slab of one accumulator row.  All 32 lanes of the warp call this together (the
 // POOL mode exchanges rows through shuffles); `valid` guards the stores only.  ovox / hvox are the row's voxel index at
 // the convolution's resolution and at half of it.
-template <bool kS>
+template <int EF, bool kS>
 __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], int co, int b, int y, int x, size_t ovox, size_t hvox, bool valid,
                                            const Resid& pre, const float* cs, int cb) {
     const ConvEpilogue& e = P.epi;
@@ -402,12 +431,12 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
 #pragma unroll
         for (int i = 0; i < 16; ++i) bias[i] = 0.f;
     }
-    if (e.mode == CONV_NORMAL) {
-        const bool pooled = e.pool_out != nullptr;           // warp-uniform
+    if (Epi<EF>::mode(e) == CONV_NORMAL) {
+        const bool pooled = Epi<EF>::pool_out(e);            // warp-uniform
         if (!valid && !pooled) return;
 #pragma unroll
         for (int i = 0; i < 16; i += 2) upk2(add2(pk2(acc[i], acc[i + 1]), pk2(bias[i], bias[i + 1])), acc[i], acc[i + 1]);
-        if (valid) add_residuals16<true>(e, ovox, hvox, cg, acc, pre.a0);
+        if (valid) add_residuals16<EF, true>(e, ovox, hvox, cg, acc, pre.a0);
         if (pooled) {
             // 2x2 average of v for the consumer's fused Conv_2 path; a quad is wholly inside or outside the tensor
             uint32_t w[8];
@@ -424,11 +453,11 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             if (valid && !(x & 1) && !(y & 1))
                 st_global_v8(reinterpret_cast<__nv_bfloat16*>(e.pool_out) + hvox * e.ld_pool + cg, w);
         }
-        if (valid) store_views16<kS>(e, b, ovox, co, acc, cs, P.Co, cb);
-    } else if (e.mode == CONV_POOL) {
+        if (valid) store_views16<EF, kS>(e, b, ovox, co, acc, cs, P.Co, cb);
+    } else if (Epi<EF>::mode(e) == CONV_POOL) {
         // 2x2 Haar analysis across lanes: x-neighbour = lane^1, y-neighbour = lane^TW
         const bool writer = valid && !(x & 1) && !(y & 1);
-        const bool want_hf = e.hf_out[0] != nullptr;
+        const bool want_hf = Epi<EF>::hf(e);
         float ll[16];
         uint32_t lh[8], hl[8], hh[8];
 #pragma unroll
@@ -458,8 +487,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             st_global_v8(reinterpret_cast<T*>(e.hf_out[1]) + hvox * e.ld_hf + cg, hl);
             st_global_v8(reinterpret_cast<T*>(e.hf_out[2]) + hvox * e.ld_hf + cg, hh);
         }
-        add_residuals16<false>(e, hvox, 0, cg, ll);
-        store_views16<kS>(e, b, hvox, co, ll, cs, P.Co, cb);
+        add_residuals16<EF, false>(e, hvox, 0, cg, ll);
+        store_views16<EF, kS>(e, b, hvox, co, ll, cs, P.Co, cb);
     } else {  // CONV_UPSAMPLE: replicate to the 2x2 block of the double-resolution grid, then add0 / views there
         if (!valid) return;
 #pragma unroll
@@ -471,8 +500,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            add_residuals16<false>(e, uvox, 0, cg, v);
-            store_views16<kS>(e, b, uvox, co, v, cs, P.Co, cb);
+            add_residuals16<EF, false>(e, uvox, 0, cg, v);
+            store_views16<EF, kS>(e, b, uvox, co, v, cs, P.Co, cb);
         }
     }
 }
@@ -528,7 +557,7 @@ __device__ __forceinline__ uint32_t elect_one() {
     return pred;
 }
 
-template <int MODE, int NACC, int KMMA, bool MERGE>
+template <int MODE, int NACC, int KMMA, bool MERGE, int EF>
 __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_constant__ UmmaParams P) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxSA + 2 * kMaxSB + 2 * kMaxAcc];
@@ -909,7 +938,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const int lane_vox = y_in * P.W + x_in, lane_hvox = (y_in >> 1) * (P.W >> 1) + (x_in >> 1);     // REUSE: offsets from the tile origin
         constexpr int kBarCount = 128 * kEpiPerQuarter + (MODE ? 32 : 0);
         const int nslab = P.Co >> 4, nitems = NACC * nslab;
-        const bool normal = P.epi.mode == CONV_NORMAL;
+        const bool normal = Epi<EF>::mode(P.epi) == CONV_NORMAL && Epi<EF>::add0(P.epi);    // residual read-ahead
         int n_stamp = 0;
         auto stamp = [&]() { if (tr && warp == 4 && lt >= 4 && lt < 8 && n_stamp < 24) P.trace[96 + 24 * (lt - 4) + n_stamp++] = clock64(); };
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
@@ -945,7 +974,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             }
             // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin, fetch the residual
             // operands of their next item and start the TMEM read of the next slab before working on the current one
-            const bool in_tile = b < P.B && y < P.H && x < P.W && !(P.dbg & 8);
+            const bool in_tile = b < P.B && y < P.H && x < P.W && !Epi<EF>::dbg(P.epi, 8);
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
             const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC) * P.Co;
@@ -953,7 +982,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             uint32_t ra[16], rb[16];
             if (pl < NACC) {
                 if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl) * P.Co + sl * 16, ra);
-                if (normal) load_resid(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
+                if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
             }
             stamp();                                     // 2: barrier + first TMEM read / residual prefetch issued
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
@@ -972,11 +1001,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 if (tr) { tw_ld += clock64() - tq; tq = clock64(); }
                 if (pl2 < NACC) {
                     if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl2) * P.Co + sl2 * 16, rb);
-                    if (normal) load_resid(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && n0 + pl2 < P.N, nxt);
+                    if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && n0 + pl2 < P.N, nxt);
                 }
                 const bool valid = in_tile && n0 + pl < P.N;
                 stamp();                                 // item: accumulator slab in registers
-                epilogue16<MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs, cb);
+                epilogue16<EF, MODE != 0>(P, acc, sl * 16, b, y, x, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, valid, cur, cs, cb);
                 if (tr) tw_bar += clock64() - tq;
                 stamp();                                 // item: done
                 cur = nxt;
@@ -1070,6 +1099,7 @@ int sm_count() {
 
 }  // namespace
 
+#if TMD_UMMA_PART == 0
 bool conv_umma_supported(const ConvOp& op) {
     if (umma_disabled()) return false;
     if (op.taps != 27 && op.taps != 1) return false;
@@ -1260,44 +1290,108 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
 }
 
 void conv_umma_plan_destroy(UmmaPlan* p) { delete p; }
+#endif
 
 namespace {
 typedef void (*KernelFn)(const UmmaParams);
 // the three dz taps that share an activation view are issued as one MMA when N = 3*Co fits an instruction
 bool merged(const UmmaParams& p) { return p.mode && p.NACC > 1 && 3 * p.Co <= 256; }
+
+// Epilogue shapes with a kernel of their own (see Epi<EF>): every shape the sampling path gives the 4- and 8-accumulator REUSE
+// kernels, i.e. the level-0 / level-1 layers with 32 or 64 output channels, whose time is the epilogue's (profiles/
+// umma_trace_r02a.txt).  Everything else -- the 128-channel and 8x8 layers, whose epilogue waits for the MMAs, the operator API,
+// TMD_UMMA_DEBUG runs -- takes the generic kernels.
+constexpr int kSpecEF[] = {
+    EF_ACT0,                                                     // ResBlock conv20
+    EF_RAW,                                                      // convH_0, last condition-branch Conv_1
+    EF_RAW | EF_ACT0,                                            // stems / Conv_1 of the condition branch, up-path conv21 (+res_conv)
+    EF_RAW | EF_ACT0 | EF_ACT1,                                  // conv2.conv21, main-branch Conv_1 (+Conv_2)
+    EF_RAW | EF_ACT0 | EF_POOLOUT,                               // down-path conv21 (+res_conv, +pooled copy)
+    EF_POOL | EF_ACT0,                                           // wavelet-down Conv_0
+    EF_POOL | EF_ACT0 | EF_HF,                                   // ... of the condition branch (high bands kept)
+    EF_UP | EF_ACT0 | EF_ADD0,                                   // wavelet-up Conv_0
+    EF_RAW | EF_ACT0 | EF_ADD0 | EF_ADD1,                        // wavelet-up Conv_1
+    EF_RAW | EF_RAWF16 | EF_ACT0,                                // final.conv20.conv21
+    EF_RAW | EF_RAWF16 | EF_ACT0 | EF_ADD0 | EF_ADD0F16,         // final.conv21/22.conv21
+    EF_ACT0 | EF_ADD0 | EF_ADD0F16,                              // final.conv23.conv21
+    EF_RAW | EF_ACT0 | EF_ADD0,                                  // identity-skip ResBlock without the half-precision stream
+    EF_ACT0 | EF_ADD0,
+};
+constexpr int kNumSpecEF = (int)(sizeof(kSpecEF) / sizeof(kSpecEF[0]));
+
+int epi_flags(const ConvEpilogue& e) {
+    int f = e.mode & 3;
+    if (e.raw_out) f |= EF_RAW;
+    if (e.act_out[0]) f |= EF_ACT0;
+    if (e.act_out[1]) f |= EF_ACT1;
+    if (e.add0) f |= EF_ADD0;
+    if (e.add1) f |= EF_ADD1;
+    if (e.pool_out) f |= EF_POOLOUT;
+    if (e.hf_out[0]) f |= EF_HF;
+    if (e.raw_f16) f |= EF_RAWF16;
+    if (e.add0_f16) f |= EF_ADD0F16;
+    return f;
+}
+
+template <int MODE, int NACC, int KMMA, bool MERGE, int... I>
+KernelFn find_special(int ef, std::integer_sequence<int, I...>) {
+    KernelFn f = nullptr;
+    (void)std::initializer_list<int>{(ef == kSpecEF[I] ? (f = conv_umma_kernel<MODE, NACC, KMMA, MERGE, kSpecEF[I]>, 0) : 0)...};
+    return f;
+}
+}  // namespace
+
+// One translation unit would take minutes to compile ~35 instantiations of the kernel: the library builds this file three
+// times (tmdiff_b200/build.py), TMD_UMMA_PART = 0 host side + generic kernels, 1 / 2 the specialised 4- / 8-accumulator kernels.
+void* conv_umma_special_nacc4(int ef);
+void* conv_umma_special_nacc8(int ef);
+#if TMD_UMMA_PART == 1
+void* conv_umma_special_nacc4(int ef) { return (void*)find_special<1, 4, 2, true>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
+#elif TMD_UMMA_PART == 2
+void* conv_umma_special_nacc8(int ef) { return (void*)find_special<1, 8, 2, true>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
+#endif
+
+#if TMD_UMMA_PART == 0
+namespace {
 KernelFn pick_kernel(const UmmaParams& p) {
-    if (p.mode) {
-        if (p.NACC == 8) return conv_umma_kernel<1, 8, 2, true>;
-        if (p.NACC == 4) return conv_umma_kernel<1, 4, 2, true>;
-        if (p.NACC == 2) return merged(p) ? conv_umma_kernel<1, 2, 2, true> : conv_umma_kernel<1, 2, 2, false>;
-        return conv_umma_kernel<1, 1, 2, false>;
+    // TMD_UMMA_DEBUG / TMD_UMMA_GENERIC=1: the generic kernels (the debug bits live only there)
+    if (p.mode && !p.dbg && !env_int("TMD_UMMA_GENERIC", 0)) {
+        void* f = nullptr;
+        if (p.NACC == 4) f = conv_umma_special_nacc4(epi_flags(p.epi));
+        else if (p.NACC == 8) f = conv_umma_special_nacc8(epi_flags(p.epi));
+        if (f) return (KernelFn)f;
     }
-    return p.KC == 64 ? conv_umma_kernel<0, 1, 4, false> : conv_umma_kernel<0, 1, 2, false>;
+    if (p.mode) {
+        if (p.NACC == 8) return conv_umma_kernel<1, 8, 2, true, -1>;
+        if (p.NACC == 4) return conv_umma_kernel<1, 4, 2, true, -1>;
+        if (p.NACC == 2) return merged(p) ? conv_umma_kernel<1, 2, 2, true, -1> : conv_umma_kernel<1, 2, 2, false, -1>;
+        return conv_umma_kernel<1, 1, 2, false, -1>;
+    }
+    return p.KC == 64 ? conv_umma_kernel<0, 1, 4, false, -1> : conv_umma_kernel<0, 1, 2, false, -1>;
+}
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device, per-function setting: done once per (device, kernel)
+cudaError_t allow_big_smem(KernelFn f) {
+    static std::set<std::pair<int, KernelFn>> done;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (done.count({dev, f})) return cudaSuccess;
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, f);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);   // static + dynamic <= 227 KB
+    if (e != cudaSuccess) return e;
+    done.insert({dev, f});
+    return cudaSuccess;
 }
 }  // namespace
 
 cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t stream) {
     (void)op;
-    // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device setting
-    static bool attr_done[kMaxDevices] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= kMaxDevices) dev = 0;
-    bool& attr_set = attr_done[dev];
-    if (!attr_set) {
-        KernelFn all[7] = {conv_umma_kernel<1, 8, 2, true>, conv_umma_kernel<1, 4, 2, true>, conv_umma_kernel<1, 2, 2, true>,
-                           conv_umma_kernel<1, 2, 2, false>, conv_umma_kernel<1, 1, 2, false>, conv_umma_kernel<0, 1, 4, false>,
-                           conv_umma_kernel<0, 1, 2, false>};
-        for (KernelFn f : all) {
-            cudaFuncAttributes fa;
-            cudaError_t e = cudaFuncGetAttributes(&fa, f);
-            if (e != cudaSuccess) return e;
-            e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - (int)fa.sharedSizeBytes);   // static + dynamic <= 227 KB
-            if (e != cudaSuccess) return e;
-        }
-        attr_set = true;
-    }
     KernelFn kern = pick_kernel(plan->p);
+    {
+        const cudaError_t e = allow_big_smem(kern);
+        if (e != cudaSuccess) return e;
+    }
     if (env_int("TMD_UMMA_TRACE", 0)) {
         UmmaParams p = plan->p;
         cudaMalloc((void**)&p.trace, 256 * sizeof(long long));
@@ -1331,5 +1425,7 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
     kern<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
     return cudaGetLastError();
 }
+
+#endif  // TMD_UMMA_PART == 0
 
 }  // namespace tmd
