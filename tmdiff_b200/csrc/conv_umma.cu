@@ -303,15 +303,20 @@ template <int EF> struct Epi {
 };
 
 // Residual operand of one 16-channel slab, fetched ahead of the accumulator (NORMAL mode).
-struct Resid { uint32_t a0[8]; };
+struct Resid { uint32_t a0[8], a1[8]; };      // add0 at the output resolution, add1 at half of it (both bf16 / half x 16)
 template <int EF>
-__device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, int co, bool valid, Resid& r) {
+__device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, bool valid, Resid& r) {
     typedef __nv_bfloat16 T;
-    if (!Epi<EF>::add0(e)) return;
+    if (Epi<EF>::add0(e)) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r.a0[i] = 0u;
-    if (!valid || Epi<EF>::dbg(e, 32)) return;
-    ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
+        for (int i = 0; i < 8; ++i) r.a0[i] = 0u;
+        if (valid && !Epi<EF>::dbg(e, 32)) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
+    }
+    if (Epi<EF>::add1(e)) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r.a1[i] = 0u;
+        if (valid && !Epi<EF>::dbg(e, 32)) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, r.a1);
+    }
 }
 
 // Swish through the hardware tanh: x*sigmoid(x) = h + h*tanh(h), h = x/2 (one MUFU op; its 2^-11 relative
@@ -330,7 +335,8 @@ __device__ __forceinline__ float swish_tanh(float x) {
 // v = accumulator + bias for channels [co, co+16) of one output voxel: residual adds, raw view and the activated
 // views (same contract as epilogue_store4 in conv_op.h).
 template <int EF, bool kPre>
-__device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, float v[16], const uint32_t* pre0 = nullptr) {
+__device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ovox, size_t hvox, int co, float v[16], const uint32_t* pre0 = nullptr,
+                                                const uint32_t* pre1 = nullptr) {
     typedef __nv_bfloat16 T;
     if (Epi<EF>::add0(e)) {
         uint32_t w[8];
@@ -341,8 +347,8 @@ __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ov
     }
     if (Epi<EF>::add1(e)) {
         uint32_t w[8];
-        ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
-        add_bf16x16(v, w);
+        if (!kPre) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
+        add_bf16x16(v, kPre ? pre1 : w);
     }
 }
 
@@ -436,7 +442,7 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         if (!valid && !pooled) return;
 #pragma unroll
         for (int i = 0; i < 16; i += 2) upk2(add2(pk2(acc[i], acc[i + 1]), pk2(bias[i], bias[i + 1])), acc[i], acc[i + 1]);
-        if (valid) add_residuals16<EF, true>(e, ovox, hvox, cg, acc, pre.a0);
+        if (valid) add_residuals16<EF, true>(e, ovox, hvox, cg, acc, pre.a0, pre.a1);
         if (pooled) {
             // 2x2 average of v for the consumer's fused Conv_2 path; a quad is wholly inside or outside the tensor
             uint32_t w[8];
@@ -494,13 +500,21 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] += bias[i];
         const size_t up0 = 4 * ovox - 2 * (size_t)x;         // voxel (2y, 2x) of the double-resolution plane
+        // the four residual rows are requested before any arithmetic (the loads are volatile asm: left inside the loop below,
+        // each would wait for the previous row's stores to issue and expose its whole latency)
+        uint32_t res[4][8];
+        if (Epi<EF>::add0(e)) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+                ld_global_v8(reinterpret_cast<const __nv_bfloat16*>(e.add0) + (up0 + (size_t)(r >> 1) * (2 * P.W) + (r & 1)) * e.ld_add0 + cg, res[r]);
+        }
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
             const size_t uvox = up0 + (size_t)(r >> 1) * (2 * P.W) + (r & 1);
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            add_residuals16<EF, false>(e, uvox, 0, cg, v);
+            add_residuals16<EF, true>(e, uvox, 0, cg, v, res[r], nullptr);
             store_views16<EF, kS>(e, b, uvox, co, v, cs, P.Co, cb);
         }
     }
@@ -592,6 +606,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
+    // Programmatic dependent launch: everything above (barriers, TMEM) touched no global memory, so under PDL it overlaps the
+    // tail of the previous kernel of the stream; from here on every warp reads or writes tensors of earlier kernels.
+    // launch_dependents right away: the next kernel's CTAs may be placed as soon as this grid's CTAs leave their SMs.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     constexpr int KC = KMMA * 16;
     const int ngroups = MODE ? 1 : P.taps;              // activation boxes per K chunk (REUSE: ONE haloed box serves all 27 taps)
@@ -938,7 +957,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         const int lane_vox = y_in * P.W + x_in, lane_hvox = (y_in >> 1) * (P.W >> 1) + (x_in >> 1);     // REUSE: offsets from the tile origin
         constexpr int kBarCount = 128 * kEpiPerQuarter + (MODE ? 32 : 0);
         const int nslab = P.Co >> 4, nitems = NACC * nslab;
-        const bool normal = Epi<EF>::mode(P.epi) == CONV_NORMAL && Epi<EF>::add0(P.epi);    // residual read-ahead
+        const bool normal = Epi<EF>::mode(P.epi) == CONV_NORMAL && (Epi<EF>::add0(P.epi) || Epi<EF>::add1(P.epi));    // residual read-ahead
         int n_stamp = 0;
         auto stamp = [&]() { if (tr && warp == 4 && lt >= 4 && lt < 8 && n_stamp < 24) P.trace[96 + 24 * (lt - 4) + n_stamp++] = clock64(); };
         for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, ++lt) {
@@ -982,7 +1001,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             uint32_t ra[16], rb[16];
             if (pl < NACC) {
                 if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl) * P.Co + sl * 16, ra);
-                if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl * plane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
+                if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
             }
             stamp();                                     // 2: barrier + first TMEM read / residual prefetch issued
             for (int it = sub; it < nitems; it += kEpiPerQuarter) {
@@ -1001,7 +1020,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 if (tr) { tw_ld += clock64() - tq; tq = clock64(); }
                 if (pl2 < NACC) {
                     if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl2) * P.Co + sl2 * 16, rb);
-                    if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl2 * plane_vox, cb + sl2 * 16, in_tile && n0 + pl2 < P.N, nxt);
+                    if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl2 * plane_vox, hvox0 + (size_t)pl2 * hplane_vox, cb + sl2 * 16, in_tile && n0 + pl2 < P.N, nxt);
                 }
                 const bool valid = in_tile && n0 + pl < P.N;
                 stamp();                                 // item: accumulator slab in registers
@@ -1421,7 +1440,20 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
         }
         return cudaGetLastError();
     }
-    // (programmatic dependent launch was measured: no gain -- one CTA per SM leaves nothing for the next kernel to overlap)
+    static const bool pdl = env_int("TMD_PDL", 1) != 0;
+    if (pdl) {
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)plan->grid);
+        cfg.blockDim = dim3((unsigned)kThreads);
+        cfg.dynamicSmemBytes = plan->smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        return cudaLaunchKernelEx(&cfg, kern, plan->p);
+    }
     kern<<<plan->grid, kThreads, plan->smem, stream>>>(plan->p);
     return cudaGetLastError();
 }
