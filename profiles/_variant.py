@@ -14,13 +14,13 @@ B.build()
 root = os.path.join(B.HERE, "..")
 out_dir = os.path.join(root, "build", "variants"); os.makedirs(out_dir, exist_ok=True)
 from concurrent.futures import ThreadPoolExecutor
-def one(part):          # conv_umma.cu is built in three parts (tmdiff_b200/build.py)
+def one(part):          # conv_umma.cu is built in five parts (tmdiff_b200/build.py)
     obj = os.path.join(out_dir, "%s.p%s.o" % (name, part))
     cmd = [B._nvcc()] + B.NVCC_FLAGS + ["-I", B.CSRC] + flags + ["-DTMD_UMMA_PART=" + part, "-c", src, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode: sys.exit(r.stderr)
     return obj
-with ThreadPoolExecutor(3) as ex: objs = list(ex.map(one, ["0", "1", "2"]))
+with ThreadPoolExecutor(5) as ex: objs = list(ex.map(one, ["0", "1", "2", "3", "4"]))
 objs += [os.path.join(root, "build", "obj", s.replace(".cu", ".o")) for s in B.SOURCES if not s.startswith("conv_umma.cu")]
 r = subprocess.run([B._nvcc(), "-shared", "-o", os.path.join(out_dir, "lib%s.so" % name)] + objs, capture_output=True, text=True)
 if r.returncode: sys.exit(r.stderr)

@@ -312,10 +312,10 @@ __device__ __forceinline__ void load_resid(const ConvEpilogue& e, size_t ovox, s
         for (int i = 0; i < 8; ++i) r.a0[i] = 0u;
         if (valid && !Epi<EF>::dbg(e, 32)) ld_global_v8(reinterpret_cast<const T*>(e.add0) + ovox * e.ld_add0 + co, r.a0);
     }
-    if (Epi<EF>::add1(e)) {
+    if (EF >= 0 && Epi<EF>::add1(e)) {        // generic kernel: add1 is read where it is used (registers)
 #pragma unroll
         for (int i = 0; i < 8; ++i) r.a1[i] = 0u;
-        if (valid && !Epi<EF>::dbg(e, 32)) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, r.a1);
+        if (valid) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, r.a1);
     }
 }
 
@@ -347,8 +347,9 @@ __device__ __forceinline__ void add_residuals16(const ConvEpilogue& e, size_t ov
     }
     if (Epi<EF>::add1(e)) {
         uint32_t w[8];
-        if (!kPre) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
-        add_bf16x16(v, kPre ? pre1 : w);
+        const bool pre = kPre && EF >= 0;
+        if (!pre) ld_global_v8(reinterpret_cast<const T*>(e.add1) + hvox * e.ld_add1 + co, w);
+        add_bf16x16(v, pre ? pre1 : w);
     }
 }
 
@@ -502,11 +503,11 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
         const size_t up0 = 4 * ovox - 2 * (size_t)x;         // voxel (2y, 2x) of the double-resolution plane
         // the four residual rows are requested before any arithmetic (the loads are volatile asm: left inside the loop below,
         // each would wait for the previous row's stores to issue and expose its whole latency)
-        uint32_t res[4][8];
-        if (Epi<EF>::add0(e)) {
+        uint32_t res[EF >= 0 ? 4 : 1][8];
+        if (EF >= 0 && Epi<EF>::add0(e)) {
 #pragma unroll
             for (int r = 0; r < 4; ++r)
-                ld_global_v8(reinterpret_cast<const __nv_bfloat16*>(e.add0) + (up0 + (size_t)(r >> 1) * (2 * P.W) + (r & 1)) * e.ld_add0 + cg, res[r]);
+                ld_global_v8(reinterpret_cast<const __nv_bfloat16*>(e.add0) + (up0 + (size_t)(r >> 1) * (2 * P.W) + (r & 1)) * e.ld_add0 + cg, res[EF >= 0 ? r : 0]);
         }
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
@@ -514,7 +515,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             float v[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) v[i] = acc[i];
-            add_residuals16<EF, true>(e, uvox, 0, cg, v, res[r], nullptr);
+            if (EF >= 0) add_residuals16<EF, true>(e, uvox, 0, cg, v, res[EF >= 0 ? r : 0], nullptr);
+            else add_residuals16<EF, false>(e, uvox, 0, cg, v);
             store_views16<EF, kS>(e, b, uvox, co, v, cs, P.Co, cb);
         }
     }
@@ -1361,23 +1363,31 @@ KernelFn find_special(int ef, std::integer_sequence<int, I...>) {
 }  // namespace
 
 // One translation unit would take minutes to compile ~35 instantiations of the kernel: the library builds this file three
-// times (tmdiff_b200/build.py), TMD_UMMA_PART = 0 host side + generic kernels, 1 / 2 the specialised 4- / 8-accumulator kernels.
+// times (tmdiff_b200/build.py), TMD_UMMA_PART = 0 host side + generic kernels, 1-4 the specialised kernels of one schedule each.
 void* conv_umma_special_nacc4(int ef);
 void* conv_umma_special_nacc8(int ef);
+void* conv_umma_special_nacc2(int ef);      // two accumulators, one MMA per (plane, dz): the 128-channel layers
+void* conv_umma_special_simple64(int ef);   // SIMPLE schedule, 64-channel chunks: the 8x8 level and the 1x1x1 convs
 #if TMD_UMMA_PART == 1
 void* conv_umma_special_nacc4(int ef) { return (void*)find_special<1, 4, 2, true>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
 #elif TMD_UMMA_PART == 2
 void* conv_umma_special_nacc8(int ef) { return (void*)find_special<1, 8, 2, true>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
+#elif TMD_UMMA_PART == 3
+void* conv_umma_special_nacc2(int ef) { return (void*)find_special<1, 2, 2, false>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
+#elif TMD_UMMA_PART == 4
+void* conv_umma_special_simple64(int ef) { return (void*)find_special<0, 1, 4, false>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
 #endif
 
 #if TMD_UMMA_PART == 0
 namespace {
 KernelFn pick_kernel(const UmmaParams& p) {
     // TMD_UMMA_DEBUG / TMD_UMMA_GENERIC=1: the generic kernels (the debug bits live only there)
-    if (p.mode && !p.dbg && !env_int("TMD_UMMA_GENERIC", 0)) {
+    if (!p.dbg && !env_int("TMD_UMMA_GENERIC", 0)) {
         void* f = nullptr;
-        if (p.NACC == 4) f = conv_umma_special_nacc4(epi_flags(p.epi));
-        else if (p.NACC == 8) f = conv_umma_special_nacc8(epi_flags(p.epi));
+        if (p.mode && p.NACC == 4) f = conv_umma_special_nacc4(epi_flags(p.epi));
+        else if (p.mode && p.NACC == 8) f = conv_umma_special_nacc8(epi_flags(p.epi));
+        else if (p.mode && p.NACC == 2 && !merged(p)) f = conv_umma_special_nacc2(epi_flags(p.epi));
+        else if (!p.mode && p.KC == 64) f = conv_umma_special_simple64(epi_flags(p.epi));
         if (f) return (KernelFn)f;
     }
     if (p.mode) {
