@@ -1450,7 +1450,7 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
         }
         return cudaGetLastError();
     }
-    static const bool pdl = env_int("TMD_PDL", 1) != 0;
+    static const bool pdl = env_int("TMD_PDL", 0) != 0;     // measured twice on one box: 855 / 850 patches/s with, 862 / 855 without (profiles/ab_r02e_pdl.txt)
     if (pdl) {
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)plan->grid);
