@@ -44,6 +44,11 @@ struct ConvEpilogue {
     // significand).  For tensors that are only ever added -- the residual stream of the final block, which no MMA reads:
     // rounding it to bf16 at every block was the largest avoidable term of the bf16 mode's error.
     int raw_f16, add0_f16;
+    // tcgen05 kernel: view 0 is not stored but projected onto one band plane, proj_out[voxel] += sum_co proj_w[co] * act0[co]
+    // (fp32, one red.add per 16-channel slab; proj_out zeroed by the caller).  This is final.conv24 -- a 1x1x1 conv to ONE
+    // channel, Hyper_unet_general.py:271-272 -- riding in the epilogue of the conv in front of it.
+    float* proj_out;
+    const float* proj_w;
 };
 
 struct ConvOp {

@@ -288,7 +288,7 @@ __device__ __forceinline__ void add_f16x16(float v[16], const uint32_t w[8]) {
 // profiles/dbg_sweep_r02a.txt, umma_timeline_r02*.txt).  EF >= 0: the shape is this template argument (the kernels of the
 // sampling path); EF < 0: the generic kernel reads it from the parameters (operator API, diagnostics).
 enum : int { EF_POOL = 1, EF_UP = 2, EF_RAW = 4, EF_ACT0 = 8, EF_ACT1 = 16, EF_ADD0 = 32, EF_ADD1 = 64, EF_POOLOUT = 128, EF_HF = 256,
-             EF_RAWF16 = 512, EF_ADD0F16 = 1024 };
+             EF_RAWF16 = 512, EF_ADD0F16 = 1024, EF_PROJ = 2048 };
 template <int EF> struct Epi {
     static __device__ __forceinline__ int mode(const ConvEpilogue& e) { return EF < 0 ? e.mode : (EF & 3); }
     static __device__ __forceinline__ bool raw(const ConvEpilogue& e) { return EF < 0 ? e.raw_out != nullptr : (EF & EF_RAW) != 0; }
@@ -299,6 +299,7 @@ template <int EF> struct Epi {
     static __device__ __forceinline__ bool hf(const ConvEpilogue& e) { return EF < 0 ? e.hf_out[0] != nullptr : (EF & EF_HF) != 0; }
     static __device__ __forceinline__ bool raw_f16(const ConvEpilogue& e) { return EF < 0 ? e.raw_f16 != 0 : (EF & EF_RAWF16) != 0; }
     static __device__ __forceinline__ bool add0_f16(const ConvEpilogue& e) { return EF < 0 ? e.add0_f16 != 0 : (EF & EF_ADD0F16) != 0; }
+    static __device__ __forceinline__ bool proj(const ConvEpilogue& e) { return EF < 0 ? e.proj_out != nullptr : (EF & EF_PROJ) != 0; }
     static __device__ __forceinline__ int dbg(const ConvEpilogue& e, int bit) { return EF < 0 ? (e.dbg & bit) : 0; }   // TMD_UMMA_DEBUG: generic kernel only
 };
 
@@ -368,6 +369,7 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
     for (int k = 0; k < 2; ++k) {
         if (!Epi<EF>::act(e, k)) continue;
         uint32_t w[8];
+        float dot = 0.f;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             float t[8], s[8], u[8];
@@ -409,8 +411,18 @@ __device__ __forceinline__ void store_views16(const ConvEpilogue& e, int b, size
                     u[i] = x;
                 }
             }
+            if (k == 0 && Epi<EF>::proj(e)) {
+                float pw[8];
+                load8_f32(e.proj_w + cg + 8 * h, pw);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) dot = fmaf(pw[i], u[i], dot);
+            }
 #pragma unroll
             for (int i = 0; i < 4; ++i) w[4 * h + i] = pack_bf16x2(u[2 * i], u[2 * i + 1]);
+        }
+        if (k == 0 && Epi<EF>::proj(e)) {
+            atomicAdd(e.proj_out + ovox, dot);       // two slabs of 16 channels per voxel at Co = 32: a + b == b + a, so still deterministic
+            continue;
         }
         if (!Epi<EF>::dbg(e, 128)) st_global_v8(reinterpret_cast<T*>(e.act_out[k]) + ovox * e.ld_act[k] + cg, w);
     }
@@ -1144,6 +1156,7 @@ bool conv_umma_supported(const ConvOp& op) {
         if (reinterpret_cast<uintptr_t>(q) & 15) return false;
     if ((e.mode == CONV_POOL || e.pool_out) && (op.H % 2 || op.W % 2)) return false;
     if (e.pool_out && (e.mode != CONV_NORMAL || e.ld_pool % 16 || (reinterpret_cast<uintptr_t>(e.pool_out) & 31))) return false;
+    if (e.proj_out && (e.mode != CONV_NORMAL || !e.proj_w || (reinterpret_cast<uintptr_t>(e.proj_w) & 15) || e.act_out[0])) return false;
     if (op.src2) {
         const int kc = (op.taps == 27 && op.H >= 16 && op.W >= 8) ? 32 : ((op.Ci % 64 == 0) ? 64 : 32);   // KC of the plan below
         if (op.Ci2 % kc || op.ld_in2 % 8 || (reinterpret_cast<uintptr_t>(op.src2) & 15) || (reinterpret_cast<uintptr_t>(op.w2_bf16) & 15)) return false;
@@ -1335,6 +1348,8 @@ constexpr int kSpecEF[] = {
     EF_RAW | EF_RAWF16 | EF_ACT0,                                // final.conv20.conv21
     EF_RAW | EF_RAWF16 | EF_ACT0 | EF_ADD0 | EF_ADD0F16,         // final.conv21/22.conv21
     EF_ACT0 | EF_ADD0 | EF_ADD0F16,                              // final.conv23.conv21
+    EF_ACT0 | EF_ADD0 | EF_ADD0F16 | EF_PROJ,                    // ... with final.conv24 (32 -> 1) in its epilogue
+    EF_ACT0 | EF_ADD0 | EF_PROJ,
     EF_RAW | EF_ACT0 | EF_ADD0,                                  // identity-skip ResBlock without the half-precision stream
     EF_ACT0 | EF_ADD0,
 };
@@ -1343,7 +1358,8 @@ constexpr int kNumSpecEF = (int)(sizeof(kSpecEF) / sizeof(kSpecEF[0]));
 int epi_flags(const ConvEpilogue& e) {
     int f = e.mode & 3;
     if (e.raw_out) f |= EF_RAW;
-    if (e.act_out[0]) f |= EF_ACT0;
+    if (e.act_out[0] || e.proj_out) f |= EF_ACT0;
+    if (e.proj_out) f |= EF_PROJ;
     if (e.act_out[1]) f |= EF_ACT1;
     if (e.add0) f |= EF_ADD0;
     if (e.add1) f |= EF_ADD1;

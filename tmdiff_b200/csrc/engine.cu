@@ -49,6 +49,7 @@ struct OutSpec {
     View raw;
     ActSpec act[2];
     View pool;   // 2x2 average of the result at the next level (consumed by a fused Conv_2, see ConvOp::src2)
+    float* proj = nullptr;   // act[0] is not stored but projected onto one band plane with the engine's 32 -> 1 weights (ConvEpilogue::proj_out)
 };
 struct ConvW {
     float* w_f32 = nullptr;
@@ -73,6 +74,7 @@ struct Launch {       // one kernel launch of the plan + what it costs algorithm
     int kind = TMD_K_ELEMENTWISE;
     double flops = 0.0, bytes = 0.0;
     double flops_exec = -1.0;   // FLOPs the kernel issues (< flops where zero-padding work is skipped); -1: same as flops
+    bool is_kernel = true;      // false: a memset / copy node (not counted by tmd_launch_count)
     std::string label;
     cudaError_t operator()(cudaStream_t s) const { return fn(s); }
 };
@@ -522,6 +524,7 @@ struct Planner {
             ep.tb[i] = out.act[i].tb; ep.sc[i] = out.act[i].sc;
         }
         ep.ld_tb = e->time_rows; ep.ld_sc = e->text_rows;
+        if (out.proj) { ep.proj_out = out.proj; ep.proj_w = e->d_proj_w; }
         if (hf) { for (int i = 0; i < 3; ++i) ep.hf_out[i] = hf[i].p; ep.ld_hf = hf[0].ld; }
         // algorithmic cost of this launch: 2*MACs; every operand/result tensor touched once
         const double nv = (double)vox(lvl);
@@ -545,7 +548,7 @@ struct Planner {
         snprintf(lb, sizeof(lb), "%s Ci=%d Co=%d L%d %s", wname.c_str(), cw.Ci, cw.Co, lvl,
                  mode == CONV_POOL ? "pool" : (mode == CONV_UPSAMPLE ? "up" : "same"));
         const std::string label = std::string(lb) + (cw2 ? " +" + w2name.substr(w2name.rfind('.') + 1) : "") + (out.pool.p ? " +pool" : "");
-        if ((cw2 || out.pool.p || ep.raw_f16 || ep.add0_f16) && (e->dtype == TMD_F32 || !conv_umma_supported(op))) { err = "fused conv outside the tcgen05 envelope"; return; }
+        if ((cw2 || out.pool.p || ep.raw_f16 || ep.add0_f16 || ep.proj_out) && (e->dtype == TMD_F32 || !conv_umma_supported(op))) { err = "fused conv outside the tcgen05 envelope"; return; }
         if (e->dtype == TMD_F32) {
             push(kind, flops, bytes, [op](cudaStream_t s) { return conv_simt_f32(op, s); }, label);
         } else if (conv_umma_supported(op)) {
@@ -676,7 +679,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         const float* scs = P.sc("conv1.dense2");
         P.push(TMD_K_ELEMENTWISE, 0, (double)P.vox(0) * (4 + c[0] * e->esize), [=](cudaStream_t s) {
             return stem_expand(dt, e->cur_ms, e->cur_pan, e->d_stem_w[0], e->d_stem_b[0], scs, sr, a_stem.p, c[0], B, N, HW, s);
-        });
+        }, "stem_expand (condition)");
         View in_act = P.buf("in_act@0", 0, c[0]);
         OutSpec o;
         o.raw = P.slice(cat_raw[0], c[0], c[0]);
@@ -717,7 +720,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const int hh = H >> (l + 1), ww = W >> (l + 1), C = c[l];
             // IDWT: 3 coefficient planes in, one double-resolution tensor out
             P.push(TMD_K_ELEMENTWISE, 0, (double)planes * hh * ww * C * e->esize * 7.0,
-                   [=](cudaStream_t s) { return idwt_highbands(dt, hq[0].p, hq[1].p, hq[2].p, T.p, C, planes, hh, ww, s); });
+                   [=](cudaStream_t s) { return idwt_highbands(dt, hq[0].p, hq[1].p, hq[2].p, T.p, C, planes, hh, ww, s); }, "idwt_highbands");
         }
     }
 
@@ -729,7 +732,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             if (e->tb_bcast_src) return broadcast_rows(e->tb_bcast_src, e->d_tb, B, tr, s);
             return time_table(e->cur_t_dev, e->cur_t_scalar, e->d_freqs, e->cfg.inter_dim, e->d_e_w1, e->d_e_b1, e->d_e_w2, e->d_e_b2,
                               e->d_Wt, e->d_bt, e->d_embed, e->d_tb, B, E, tr, s);
-        });
+        }, "time_table");
         // activations of the cached condition slices for this step's time embedding
         const char* consumer[4] = {"final.conv20", "up3.conv20", "up2.conv20", "up1.conv20"};
         for (int l = 0; l < 4; ++l) {
@@ -738,13 +741,13 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const int C = c[l];
             const size_t vps = (size_t)N * (H >> l) * (W >> l);
             P.push(TMD_K_ELEMENTWISE, 0, 2.0 * B * vps * C * e->esize,
-                   [=](cudaStream_t s) { return slice_activate(dt, src.p, src.ld, dst.p, dst.ld, t, tr, C, B, vps, s); });
+                   [=](cudaStream_t s) { return slice_activate(dt, src.p, src.ld, dst.p, dst.ld, t, tr, C, B, vps, s); }, "slice_activate L" + L(l));
         }
         View a_stem = P.buf("a_stem", 0, c[0]);
         const float* scs = P.sc("conv2.dense2");
         P.push(TMD_K_ELEMENTWISE, 0, (double)P.vox(0) * (4 + c[0] * e->esize), [=](cudaStream_t s) {
             return stem_expand(dt, e->cur_x, nullptr, e->d_stem_w[1], e->d_stem_b[1], scs, sr, a_stem.p, c[0], B, N, HW, s);
-        });
+        }, "stem_expand");
         View in_act = P.buf("in_act@0", 0, c[0]);
         OutSpec o;
         o.raw = P.slice(cat_raw[0], 2 * c[0], c[0]);
@@ -803,6 +806,8 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             if (P.fuse && f16_res) f[0].f16 = f[1].f16 = true;
             View af[2] = {P.buf("af0", 0, c[0]), P.buf("af1", 0, c[0])};
             View ia = cat_act[0], ir = cat_raw[0];
+            static const bool proj_env = !getenv("TMD_NO_FUSE_PROJ");
+            const bool proj_fused = P.fuse && proj_env;
             for (int i = 0; i < 4; ++i) {
                 OutSpec fo;
                 if (i < 3) {
@@ -810,6 +815,14 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
                     fo.act[0] = ActSpec{af[i & 1], P.tb("final.conv2" + L(i + 1) + ".dense1"), nullptr};
                 } else {
                     fo.act[0] = ActSpec{af[i & 1], nullptr, P.sc("final.dense2")};  // act(h) then conv24's modulation
+                    if (proj_fused) {
+                        // final.conv24 (1x1x1, 32 -> 1, :271-272) rides in this epilogue: the modulated activation never goes to HBM
+                        fo.act[0].dst = View{};
+                        fo.proj = e->d_out;
+                        const size_t bytes = P.vox(0) * sizeof(float);
+                        P.push(TMD_K_ELEMENTWISE, 0, (double)bytes, [=](cudaStream_t s) { return cudaMemsetAsync(e->d_out, 0, bytes, s); }, "zero projection target");
+                        P.ops->back().is_kernel = false;
+                    }
                 }
                 P.resblock("final.conv2" + L(i), ia, ir, c[0], 0, fo);
                 ia = af[i & 1];
@@ -818,8 +831,14 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const size_t nvox = P.vox(0);
             const int C = c[0];
             View last = af[1];
-            P.push(TMD_K_ELEMENTWISE, 2.0 * nvox * C, (double)nvox * (C * e->esize + 4),
-                   [=](cudaStream_t s) { return project_to_band(dt, last.p, last.ld, e->d_proj_w, e->cur_out, C, nvox, s); });
+            if (proj_fused)      // the projection landed in the engine's own buffer: hand it to the caller's tensor where that is another one
+                P.push(TMD_K_ELEMENTWISE, 0, 0.0, [=](cudaStream_t s) {
+                    return e->cur_out == e->d_out ? cudaSuccess : cudaMemcpyAsync(e->cur_out, e->d_out, nvox * sizeof(float), cudaMemcpyDeviceToDevice, s);
+                }, "network output");
+            if (proj_fused) P.ops->back().is_kernel = false;
+            else
+                P.push(TMD_K_ELEMENTWISE, 2.0 * nvox * C, (double)nvox * (C * e->esize + 4),
+                       [=](cudaStream_t s) { return project_to_band(dt, last.p, last.ld, e->d_proj_w, e->cur_out, C, nvox, s); }, "project_to_band");
         }
     }
     if (P.err) return fail("plan: %s", P.err);
@@ -855,7 +874,7 @@ int run_ops(tmd_engine* e, std::vector<Launch>& ops, cudaStream_t s) {
         cudaError_t err = op(s);
         if (err != cudaSuccess) return fail("kernel launch failed: %s", cudaGetErrorString(err));
         if (prof_mark(e, op.kind, op.flops, op.bytes, s, false)) return 1;
-        ++e->launches;
+        if (op.is_kernel) ++e->launches;
     }
     return 0;
 }
