@@ -105,6 +105,62 @@ __global__ void __launch_bounds__(256) slice_activate_bf16_kernel(const __nv_bfl
     *reinterpret_cast<uint4*>(dst + (size_t)vox * ld_dst + c) = pack8_bf16(v);
 }
 
+// The per-step activation of all four cached skip slices in ONE launch (one per level of the U-Net): a thread takes two
+// 16-byte vectors half a segment apart, so two loads are in flight per thread and three launch edges per evaluation go away.
+struct SliceSeg { const __nv_bfloat16* src; __nv_bfloat16* dst; const float* tb; int ld_src, ld_dst, C; unsigned vps, total8, first; };
+struct SliceSegs { SliceSeg s[4]; int n; int ld_tb; };
+__global__ void __launch_bounds__(256) slice_activate_multi_kernel(const SliceSegs S) {
+    const unsigned g = blockIdx.x * 256u + threadIdx.x;       // index over the first halves of all segments
+    int k = 0;
+#pragma unroll
+    for (int j = 1; j < 4; ++j) k += (j < S.n && g >= S.s[j].first) ? 1 : 0;
+    const SliceSeg& sg = S.s[k];
+    const unsigned half = (sg.total8 + 1) >> 1, i0 = g - sg.first;
+    if (i0 >= half) return;
+    const unsigned c8 = (unsigned)sg.C >> 3;
+    unsigned idx[2] = {i0, i0 + half};
+    uint4 raw[2];
+    float t[2][8];
+    bool ok[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        ok[u] = idx[u] < sg.total8;
+        if (!ok[u]) continue;
+        const unsigned vox = idx[u] / c8, c = (idx[u] % c8) * 8u;
+        raw[u] = *reinterpret_cast<const uint4*>(sg.src + (size_t)vox * sg.ld_src + c);
+        ldg8(sg.tb + (size_t)(vox / sg.vps) * S.ld_tb + c, t[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        if (!ok[u]) continue;
+        const unsigned vox = idx[u] / c8, c = (idx[u] % c8) * 8u;
+        float v[8];
+        unpack8_bf16f(raw[u], v);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[q] = swish_tanh_f(v[q] + t[u][q]);
+        *reinterpret_cast<uint4*>(sg.dst + (size_t)vox * sg.ld_dst + c) = pack8_bf16(v);
+    }
+}
+
+cudaError_t slice_activate_multi(int n, const void* const* src, const int* ld_src, void* const* dst, const int* ld_dst, const float* const* tb,
+                                 int ld_tb, const int* C, int B, const size_t* vps, cudaStream_t s) {
+    if (n < 1 || n > 4) return cudaErrorInvalidValue;
+    SliceSegs S{};
+    S.n = n; S.ld_tb = ld_tb;
+    unsigned first = 0;
+    for (int i = 0; i < n; ++i) {
+        const size_t total8 = (size_t)B * vps[i] * (C[i] / 8);
+        if (C[i] % 8 || ld_src[i] % 8 || ld_dst[i] % 8 || ld_tb % 4 || total8 >= 0x7fffffffull || !tb[i] ||
+            ((reinterpret_cast<uintptr_t>(src[i]) | reinterpret_cast<uintptr_t>(dst[i]) | reinterpret_cast<uintptr_t>(tb[i])) & 15))
+            return cudaErrorInvalidValue;
+        S.s[i] = SliceSeg{(const __nv_bfloat16*)src[i], (__nv_bfloat16*)dst[i], tb[i], ld_src[i], ld_dst[i], C[i], (unsigned)vps[i], (unsigned)total8, first};
+        first += (unsigned)((total8 + 1) / 2);
+        first = (first + 255u) & ~255u;          // segments start on a CTA boundary
+    }
+    slice_activate_multi_kernel<<<first / 256u, 256, 0, s>>>(S);
+    return cudaGetLastError();
+}
+
 // C <= 64: (C/8) lanes per voxel, one 16-byte load each, shuffle reduce
 __global__ void __launch_bounds__(256) project_to_band_bf16_kernel(const __nv_bfloat16* __restrict__ a, int ld, const float* __restrict__ w,
                                                                    float* __restrict__ out, int C, unsigned nvox) {

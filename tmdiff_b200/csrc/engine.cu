@@ -650,6 +650,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         char* ws = nullptr;
         if (e->dmalloc(&ws, threshold_workspace_bytes(e->cfg.max_batch))) return 1;
         e->d_th_ws = ws;
+        CK(cudaMemset(ws, 0, threshold_workspace_bytes(e->cfg.max_batch)));   // each threshold call leaves it clean again
     }
     Planner P{e, &e->pre_ops, B, N, H, W};
     {
@@ -735,7 +736,23 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         }, "time_table");
         // activations of the cached condition slices for this step's time embedding
         const char* consumer[4] = {"final.conv20", "up3.conv20", "up2.conv20", "up1.conv20"};
-        for (int l = 0; l < 4; ++l) {
+        static const bool multi_env = !getenv("TMD_NO_SLICE_MULTI");
+        bool multi = e->dtype == TMD_BF16 && multi_env;
+        for (int l = 0; l < 4; ++l) multi = multi && c[l] % 8 == 0;
+        if (multi) {
+            struct Args { const void* src[4]; void* dst[4]; const float* tb[4]; int ld_src[4], ld_dst[4], C[4]; size_t vps[4]; } A{};
+            double bytes = 0;
+            for (int l = 0; l < 4; ++l) {
+                View src = P.slice(cat_raw[l], c[l], c[l]), dst = P.slice(cat_act[l], c[l], c[l]);
+                A.src[l] = src.p; A.dst[l] = dst.p; A.ld_src[l] = src.ld; A.ld_dst[l] = dst.ld; A.C[l] = c[l];
+                A.tb[l] = P.tb(std::string(consumer[l]) + ".dense1", c[l]);
+                A.vps[l] = (size_t)N * (H >> l) * (W >> l);
+                bytes += 2.0 * B * A.vps[l] * c[l] * e->esize;
+            }
+            P.push(TMD_K_ELEMENTWISE, 0, bytes,
+                   [=](cudaStream_t s) { return slice_activate_multi(4, A.src, A.ld_src, A.dst, A.ld_dst, A.tb, tr, A.C, B, A.vps, s); }, "slice_activate L0-L3");
+        }
+        for (int l = 0; l < 4 && !multi; ++l) {
             View src = P.slice(cat_raw[l], c[l], c[l]), dst = P.slice(cat_act[l], c[l], c[l]);
             const float* t = P.tb(std::string(consumer[l]) + ".dense1", c[l]);
             const int C = c[l];
@@ -985,7 +1002,7 @@ static int sample_body(tmd_handle h, const tmd_plan* plan, float* trace, float* 
             const double th_bytes = (cfg ? 4.0 : 3.0) * n * 4 + (fused ? (fu.m1 ? 3.0 : 2.0) * n * 4 : 0.0);
             if (prof_mark(h, TMD_K_SOLVER, 0, th_bytes, s, true, fused ? "x0_threshold+update" : "x0_threshold")) return 1;
             CK(x0_threshold(h->slots[ev.src], net_out, cfg ? net_out + n : nullptr, h->slots[ev.dst], ev.alpha_t, ev.sigma_t, noise_type,
-                            plan->guidance_scale, Bx, (int)n_per, plan->q_lo, plan->q_weight, plan->max_val, h->d_th_ws, fused ? &fu : nullptr, s));
+                            plan->guidance_scale, Bx, (int)n_per, plan->q_lo, plan->q_weight, plan->max_val, h->d_th_ws, true, fused ? &fu : nullptr, s));
             if (prof_mark(h, TMD_K_SOLVER, 0, 0, s, false)) return 1;
             h->launches += 4;
             ++n_eval;

@@ -28,6 +28,9 @@ cudaError_t stem_expand(int dtype, const float* x, const float* pan, const float
 // dst[vox][c] = swish(src[vox][c] + tb[b][c])  for a channel slice (per-step activation of cached tensors)
 cudaError_t slice_activate(int dtype, const void* src, int ld_src, void* dst, int ld_dst, const float* tb, int ld_tb, int C,
                            int B, size_t vox_per_sample, cudaStream_t s);
+// the same for up to four slices in one launch (bf16 only; every slice needs a time bias)
+cudaError_t slice_activate_multi(int n, const void* const* src, const int* ld_src, void* const* dst, const int* ld_dst, const float* const* tb,
+                                 int ld_tb, const int* C, int B, const size_t* vps, cudaStream_t s);
 // out[vox] = sum_c w[c]*a[vox][c]   (final.conv24: 1x1x1, Co = 1, no bias)
 cudaError_t project_to_band(int dtype, const void* a, int ld, const float* w, float* out, int C, size_t nvox, cudaStream_t s);
 // T[hi vox][c] = IDWT(0, LH, HL, HH)  channels-last (WaveletUPorDown up branch, :383-386)
@@ -58,7 +61,8 @@ cudaError_t broadcast_rows(const float* row, float* out, int B, int width, cudaS
 // ---- solver (solver.cu) ----
 // eps = (x - a*out)/s ; x0 = (x - s*eps)/a ; dynamic threshold (quantile 0.995, max 1) -> dst
 // out_c (optional): conditional half for classifier-free guidance, eps = eps_u + g*(eps_c - eps_u); noise_type: out is eps
-// ws: threshold_workspace_bytes(B) bytes of device scratch (radix-select histograms; any sample size, several CTAs per sample)
+// ws: threshold_workspace_bytes(B) bytes of device scratch (radix-select histograms; any sample size, several CTAs per sample);
+// ws_clean: the workspace was zero-filled once and has only been used by these calls since (each call leaves it clean)
 // fu (optional): the dpmsolver++ singlestep update that consumes this x0, evaluated in the same pass as the clamp:
 //   fu->dst = (c1*x - c2*m) [+ c3*(m1 - m)],  m / m1 == dst meaning "the fresh x0"
 struct FusedUpdate {
@@ -70,7 +74,7 @@ struct FusedUpdate {
 };
 size_t threshold_workspace_bytes(int B);
 cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
-                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, const FusedUpdate* fu, cudaStream_t s);
+                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, bool ws_clean, const FusedUpdate* fu, cudaStream_t s);
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s);
 cudaError_t solver_update(float* dst, const float* x, const float* m, const float* m1, float c1, float c2, float c3, size_t n,
                           cudaStream_t s);

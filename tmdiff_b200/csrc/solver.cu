@@ -208,6 +208,11 @@ __global__ void __launch_bounds__(TH_THREADS) th_level_kernel(const float* __res
     int* g = wsb + (kLevel == 1 ? 1 : 3) * TH_BINS;
     th_flush_hist(hA, g);
     if (two) th_flush_hist(hB, g + TH_BINS);
+    if (kLevel == 2) {   // hist0 has been consumed by level 1: leave it zeroed for the next call on this workspace (no memset node)
+        const int per = (TH_BINS + gridDim.x - 1) / gridDim.x;
+        const int z0 = blockIdx.x * per, z1 = min(TH_BINS, z0 + per);
+        for (int i = z0 + threadIdx.x; i < z1; i += TH_THREADS) wsb[i] = 0;
+    }
 }
 
 // The dpmsolver++ singlestep update that follows an evaluation, evaluated by th_apply on the x0 it has in registers:
@@ -257,14 +262,42 @@ __global__ void __launch_bounds__(TH_THREADS) th_apply_kernel(float* dst, int n,
     };
     int lo, hi;
     th_range(n, lo, hi);
-    for (int i = lo + threadIdx.x; i < hi; i += TH_THREADS) dst[base + i] = one(dst[base + i], base + i);
+    if ((n & 3) == 0) {
+        for (int i = lo + 4 * threadIdx.x; i < hi; i += 4 * TH_THREADS) {
+            float4 v = *reinterpret_cast<const float4*>(dst + base + i);
+            const size_t gi = base + i;
+            float r[4] = {0.f, 0.f, 0.f, 0.f}, u[4];
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+            if (fuse) {
+                const float4 X = *reinterpret_cast<const float4*>(upd.x + gi);
+                float4 M = make_float4(0.f, 0.f, 0.f, 0.f), M1 = M;
+                if (!m_fresh) M = *reinterpret_cast<const float4*>(upd.m + gi);
+                if (upd.m1 && !m1_fresh) M1 = *reinterpret_cast<const float4*>(upd.m1 + gi);
+                const float xs[4] = {X.x, X.y, X.z, X.w}, ms[4] = {M.x, M.y, M.z, M.w}, m1s[4] = {M1.x, M1.y, M1.z, M1.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    r[j] = __fdiv_rn(fminf(fmaxf(vv[j], -s), s), s);
+                    const float mv = m_fresh ? r[j] : ms[j];
+                    u[j] = __fsub_rn(__fmul_rn(upd.c1, xs[j]), __fmul_rn(upd.c2, mv));
+                    if (upd.m1) u[j] = __fadd_rn(u[j], __fmul_rn(upd.c3, __fsub_rn(m1_fresh ? r[j] : m1s[j], mv)));
+                }
+                *reinterpret_cast<float4*>(upd.dst + gi) = make_float4(u[0], u[1], u[2], u[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) r[j] = __fdiv_rn(fminf(fmaxf(vv[j], -s), s), s);
+            }
+            *reinterpret_cast<float4*>(dst + gi) = make_float4(r[0], r[1], r[2], r[3]);
+        }
+    } else {
+        for (int i = lo + threadIdx.x; i < hi; i += TH_THREADS) dst[base + i] = one(dst[base + i], base + i);
+    }
 }
 
 size_t threshold_workspace_bytes(int B) { return (size_t)B * TH_WS_INTS * sizeof(int); }
 
 static cudaError_t launch_threshold(bool from_model, const float* x, const float* out, const float* out_c, float* dst, float alpha,
                                     float sigma, bool noise_type, float g, int B, int n, int q_lo, float q_w, float max_val, void* ws,
-                                    const ThUpdate& upd, cudaStream_t s) {
+                                    bool ws_clean, const ThUpdate& upd, cudaStream_t s) {
     if (!ws || B <= 0 || n <= 0) return cudaErrorInvalidValue;
     int* w = reinterpret_cast<int*>(ws);
     // CTAs per sample: two waves of the machine over the batch, at least 2048 values each
@@ -273,8 +306,10 @@ static cudaError_t launch_threshold(bool from_model, const float* x, const float
     if (S > max_s) S = max_s;
     if (S < 1) S = 1;
     const dim3 grid((unsigned)S, (unsigned)B);
-    cudaError_t e = cudaMemset2DAsync(w, TH_WS_INTS * sizeof(int), 0, TH_BINS * sizeof(int), (size_t)B, s);   // hist0 of every sample
-    if (e != cudaSuccess) return e;
+    if (!ws_clean) {     // hist0 of every sample (a workspace that went through a call before is left clean by its level-2 pass)
+        cudaError_t e = cudaMemset2DAsync(w, TH_WS_INTS * sizeof(int), 0, TH_BINS * sizeof(int), (size_t)B, s);
+        if (e != cudaSuccess) return e;
+    }
     if (from_model) th_first_kernel<true><<<grid, TH_THREADS, 0, s>>>(x, out, out_c, dst, alpha, sigma, noise_type, g, n, w);
     else th_first_kernel<false><<<grid, TH_THREADS, 0, s>>>(nullptr, nullptr, nullptr, dst, 1.f, 1.f, false, 0.f, n, w);
     const int hi_pos = q_lo + 1 < n - 1 ? q_lo + 1 : n - 1;
@@ -286,13 +321,13 @@ static cudaError_t launch_threshold(bool from_model, const float* x, const float
 }
 
 cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
-                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, const FusedUpdate* fu, cudaStream_t s) {
+                         float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, bool ws_clean, const FusedUpdate* fu, cudaStream_t s) {
     ThUpdate u{};
     if (fu) { u.dst = fu->dst; u.x = fu->x; u.m = fu->m; u.m1 = fu->m1; u.c1 = fu->c1; u.c2 = fu->c2; u.c3 = fu->c3; }
-    return launch_threshold(true, x, out, out_c, dst, alpha, sigma, noise_type, g, B, n, q_lo, q_w, max_val, ws, u, s);
+    return launch_threshold(true, x, out, out_c, dst, alpha, sigma, noise_type, g, B, n, q_lo, q_w, max_val, ws, ws_clean, u, s);
 }
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s) {
-    return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, ws, ThUpdate{}, s);
+    return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, ws, false, ThUpdate{}, s);
 }
 
 // dst = (c1*x - c2*m) [+ c3*(m1 - m)], 128-bit vectorised; dst may alias x.
