@@ -20,7 +20,7 @@ def one(part):          # conv_umma.cu is built in five parts (tmdiff_b200/build
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode: sys.exit(r.stderr)
     return obj
-with ThreadPoolExecutor(5) as ex: objs = list(ex.map(one, ["0", "1", "2", "3", "4"]))
+with ThreadPoolExecutor(6) as ex: objs = list(ex.map(one, ["0", "1", "2", "3", "4", "5"]))
 objs += [os.path.join(root, "build", "obj", s.replace(".cu", ".o")) for s in B.SOURCES if not s.startswith("conv_umma.cu")]
 r = subprocess.run([B._nvcc(), "-shared", "-o", os.path.join(out_dir, "lib%s.so" % name)] + objs, capture_output=True, text=True)
 if r.returncode: sys.exit(r.stderr)

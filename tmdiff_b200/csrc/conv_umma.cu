@@ -1384,6 +1384,7 @@ void* conv_umma_special_nacc4(int ef);
 void* conv_umma_special_nacc8(int ef);
 void* conv_umma_special_nacc2(int ef);      // two accumulators, one MMA per (plane, dz): the 128-channel layers
 void* conv_umma_special_simple64(int ef);   // SIMPLE schedule, 64-channel chunks: the 8x8 level and the 1x1x1 convs
+void* conv_umma_special_simple32(int ef);   // SIMPLE schedule, 32-channel chunks (Ci = 32 or 96)
 #if TMD_UMMA_PART == 1
 void* conv_umma_special_nacc4(int ef) { return (void*)find_special<1, 4, 2, true>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
 #elif TMD_UMMA_PART == 2
@@ -1392,6 +1393,8 @@ void* conv_umma_special_nacc8(int ef) { return (void*)find_special<1, 8, 2, true
 void* conv_umma_special_nacc2(int ef) { return (void*)find_special<1, 2, 2, false>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
 #elif TMD_UMMA_PART == 4
 void* conv_umma_special_simple64(int ef) { return (void*)find_special<0, 1, 4, false>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
+#elif TMD_UMMA_PART == 5
+void* conv_umma_special_simple32(int ef) { return (void*)find_special<0, 1, 2, false>(ef, std::make_integer_sequence<int, kNumSpecEF>()); }
 #endif
 
 #if TMD_UMMA_PART == 0
@@ -1404,6 +1407,7 @@ KernelFn pick_kernel(const UmmaParams& p) {
         else if (p.mode && p.NACC == 8) f = conv_umma_special_nacc8(epi_flags(p.epi));
         else if (p.mode && p.NACC == 2 && !merged(p)) f = conv_umma_special_nacc2(epi_flags(p.epi));
         else if (!p.mode && p.KC == 64) f = conv_umma_special_simple64(epi_flags(p.epi));
+        else if (!p.mode && p.KC == 32) f = conv_umma_special_simple32(epi_flags(p.epi));
         if (f) return (KernelFn)f;
     }
     if (p.mode) {
