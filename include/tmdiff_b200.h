@@ -213,6 +213,19 @@ int tmd_band_moments(const float* a, const float* b, float* out, int32_t B, int3
 int tmd_psf_downsample(const float* x, float* y, const float* param, float* psf_out, int32_t mode, int32_t B, int32_t C, int32_t H,
                        int32_t W, int32_t k, int32_t scale, void* stream);
 
+/* ---- full-scene front / back end (BASELINE config 4): the steps either side of the sampler, device to device ------------
+ * Front end: tiles [first, first + count) (row-major tile order of unpatch_16, data/LRHR_dataset.py:55-91, any grid) of a PAN
+ * scene [Hs, Ws] and its low-resolution MS cube [C, Hs/ratio, Ws/ratio], both sensor DN, become the sampler's inputs:
+ * pan_tiles [count,1,tile,tile] = DN / img_scale (2047, or 1023 for GF2, :134-139) and ms_tiles [count,C,tile,tile] = the scaled
+ * MS up-sampled by `ratio` as cv2.resize(INTER_LINEAR) does (Upsample, :97-122).  tile must be a multiple of 4. */
+int tmd_scene_to_tiles(const float* pan_dn, const float* lrms_dn, float* pan_tiles, float* ms_tiles, int32_t C, int32_t Hs, int32_t Ws,
+                       int32_t ratio, int32_t tile, int32_t first, int32_t count, float img_scale, void* stream);
+/* Back end: fused tiles [count,C,tile,tile] written to their places in the scene cube [C,Hs,Ws] (patch_16 order), clamped to
+ * [0,1] when `clamp` and multiplied by img_scale (normlization(min_max=(0,1)) * img_scale,
+ * general_sharpening_joint_random_batch_finetune.py:39-42, 136-142). */
+int tmd_tiles_to_scene(const float* tiles, float* scene, int32_t C, int32_t Hs, int32_t Ws, int32_t tile, int32_t first, int32_t count,
+                       float img_scale, int32_t clamp, void* stream);
+
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);
 

@@ -432,3 +432,30 @@ def test_ancestral_loop_matches_reference(golden_ancestral, model_fp32):
     torch.manual_seed(0)
     sr = G6.super_resolution(cond1, False, "QB", 1.0)
     assert sr.shape == want.shape
+
+
+def test_mixed_sensor_two_band_buckets(lib_built):
+    """BASELINE config 3 in miniature: a joint batch of 8-band (WV3) and 4-band (QB, GF2) patches with per-sample prompts through
+    parallel.sample_mixed -- one engine per band count, chunked buckets -- equals the oracle run patch by patch."""
+    from tmdiff_b200 import parallel
+    sd, emb = wavbest_ref.seeded_weights(), wavbest_ref.seeded_text_embeddings()
+    m = make_model("fp32")
+    G = _diffusion(m)
+    p8, m8, x8 = make_inputs(3, 8, 32, 32, seed=11)
+    p4, m4, x4 = make_inputs(4, 4, 32, 32, seed=12)
+    order = [("WV3", 8, 0), ("QB", 4, 0), ("GF2", 4, 1), ("WV3", 8, 1), ("QB", 4, 2), ("WV3", 8, 2), ("GF2", 4, 3)]
+    patches, noises = [], []
+    for sensor, n, i in order:
+        pan, ms, x = (p8, m8, x8) if n == 8 else (p4, m4, x4)
+        patches.append((pan[i].cuda(), ms[i].cuda(), sensor))
+        noises.append(x[i])
+    got = parallel.sample_mixed(G, patches, steps=6, x_T=noises, batch=2)       # chunks of 2: buckets of 3 and 4 split unevenly
+    assert len(m._engines) == 2                                                 # one engine per band count, both alive
+    ns = dpm_ref.ScheduleVP(dpm_ref.cosine_betas(1000))
+    for k, (sensor, n, i) in enumerate(order):
+        pan, ms, x = (p8, m8, x8) if n == 8 else (p4, m4, x4)
+        net = lambda xx, t: wavbest_ref.wavbest_forward(sd, xx, t, pan[i:i + 1], ms[i:i + 1], emb[sensor], faithful=False)
+        want = dpm_ref.Sampler(net, ns).sample(x[i:i + 1], steps=6, order=3)[0] + ms[i]
+        assert got[k].shape == want.shape
+        assert rel_l2(got[k].cpu() - ms[i], want - ms[i]) < FP32_TOL, (k, sensor)
+    m.release()

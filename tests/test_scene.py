@@ -47,6 +47,7 @@ def test_metrics_match_reference(vec):
 
 class _FakeDiffusion:
     """Deterministic stand-in for GeneralDiffusion: 'fuses' a tile as MS + 0.25*PAN + 0.01*noise."""
+    host_tiling_ok = True           # the sharding / stitching logic runs on CPU tensors under gloo
 
     def sample_by_dpmsolver(self, x_in, prompt, steps=20, x_T=None):
         return x_in["MS"] + 0.25 * x_in["PAN"] + 0.01 * x_T
@@ -121,8 +122,41 @@ def test_scene_on_gpu_equals_per_tile_sampling_and_metrics_gate():
         G = GeneralDiffusion(m)
         G.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 1000}, "cuda")
         got = tiling.sample_scene(G, pan.cuda(), lrms.cuda(), "QB", tile=64, steps=10, batch=3, x_T=noise).cpu()
-        assert rel_l2(got - lms, want - lms) < (tol if dtype == "fp32" else 0.1)
+        assert rel_l2(got - lms, want - lms) < tol          # the sampled residual itself: 1e-5 / 2e-2 (north star)
         got_m = [f(to_hwc(hr), to_hwc(got.clamp(0.01, 1.0))) for f in (metrics_ref.sam, metrics_ref.ergas, metrics_ref.uiqc)]
         for name, a, b in zip(("SAM", "ERGAS", "Q"), got_m, ref_m):
             assert abs(a - b) <= 5e-3 * abs(b), (dtype, name, a, b)
         m.release()
+
+
+@pytest.mark.gpu
+def test_scene_front_and_back_end_kernels(vec):
+    """tmd_scene_to_tiles / tmd_tiles_to_scene against the reference's own helpers: Upsample (cv2.resize INTER_LINEAR) on
+    committed vectors, DN scaling (/2047, /1023), the unpatch_16 / patch_16 order on a non-square grid, clamp + scale back."""
+    lr = torch.from_numpy(vec["lrms"])                               # [2, 4, 16, 16] in [0, 1]; vec["lms"] = Upsample(lr, 64)
+    for b in range(2):
+        for scale in (1.0, 2047.0, 1023.0):
+            lr_dn = (lr[b] * scale).cuda()
+            pan_dn = (torch.rand(1, 64, 64, generator=torch.Generator().manual_seed(b)) * scale).cuda()
+            pan_t, ms_t = tiling.scene_to_tiles(pan_dn, lr_dn, 32, 0, 4, img_scale=scale)
+            want_ms = tiling.unpatch(torch.from_numpy(vec["lms"][b]), 32)
+            assert float((ms_t.cpu() - want_ms).abs().max()) < 2e-6, (b, scale)
+            assert torch.equal(pan_t.cpu(), tiling.unpatch(pan_dn.cpu() / scale, 32))
+    # a 3 x 5 grid of 8-pixel tiles, a tile range in the middle, then back
+    g = torch.Generator().manual_seed(3)
+    pan, lr = torch.rand(1, 24, 40, generator=g).cuda(), torch.rand(3, 6, 10, generator=g).cuda()
+    pan_t, ms_t = tiling.scene_to_tiles(pan, lr, 8, 4, 7)
+    assert torch.equal(pan_t.cpu(), tiling.unpatch(pan.cpu(), 8)[4:11])
+    lms = torch.nn.functional.interpolate(lr[None].cpu(), size=(24, 40), mode="bilinear", align_corners=False)[0]
+    assert float((ms_t.cpu() - tiling.unpatch(lms, 8)[4:11]).abs().max()) < 2e-6
+    tiles = torch.randn(15, 3, 8, 8, generator=g) * 0.7 + 0.5
+    scene = torch.zeros(3, 24, 40).cuda()
+    tiling.tiles_to_scene(tiles[:6].cuda(), scene, 0)
+    tiling.tiles_to_scene(tiles[6:].cuda(), scene, 6)
+    assert torch.equal(scene.cpu(), tiling.patch(tiles, 3, 5))
+    tiling.tiles_to_scene(tiles.cuda(), scene, 0, img_scale=2047.0, clamp=True)
+    assert torch.equal(scene.cpu(), tiling.patch(tiles, 3, 5).clamp(0, 1) * 2047.0)
+    with pytest.raises(RuntimeError):
+        tiling.scene_to_tiles(pan, lr, 8, 10, 7)                     # tile range outside the scene
+    with pytest.raises(RuntimeError):
+        tiling.scene_to_tiles(pan.cpu(), lr.cpu(), 8, 0, 1)          # no CPU path

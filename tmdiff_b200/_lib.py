@@ -84,6 +84,8 @@ SIGNATURES = {
     "tmd_geglu": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P]),
     "tmd_band_moments": (C.c_int, [_P, _P, _P] + [C.c_int32] * 6 + [_P]),
     "tmd_psf_downsample": (C.c_int, [_P, _P, _P, _P] + [C.c_int32] * 7 + [_P]),
+    "tmd_scene_to_tiles": (C.c_int, [_P, _P, _P, _P] + [C.c_int32] * 7 + [C.c_float, _P]),
+    "tmd_tiles_to_scene": (C.c_int, [_P, _P] + [C.c_int32] * 6 + [C.c_float, C.c_int32, _P]),
     "tmd_launch_count": (C.c_int64, [_P]),
     "tmd_profile_begin": (C.c_int, [_P]),
     "tmd_profile_end": (C.c_int, [_P, C.POINTER(Profile), C.c_char_p]),

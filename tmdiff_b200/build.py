@@ -11,7 +11,7 @@ LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libtmdiff_b200.so")
 # conv_umma.cu is compiled five times: the host side + generic kernels, and four families of epilogue-specialised kernels
 SOURCES = ["engine.cu", "elementwise.cu", "solver.cu", "conv_simt.cu", "conv_umma.cu", "conv_umma.cu#1", "conv_umma.cu#2", "conv_umma.cu#3", "conv_umma.cu#4", "conv_umma.cu#5",
-           "attn_umma.cu",
+           "attn_umma.cu", "scene.cu",
            "operators.cu", "operators2.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

@@ -1438,6 +1438,33 @@ extern "C" int tmd_psf_downsample(const float* x, float* y, const float* param, 
     return 0;
 }
 
+extern "C" int tmd_scene_to_tiles(const float* pan_dn, const float* lrms_dn, float* pan_tiles, float* ms_tiles, int32_t C, int32_t Hs, int32_t Ws,
+                                  int32_t ratio, int32_t tile, int32_t first, int32_t count, float img_scale, void* stream) {
+    if (!pan_dn || !lrms_dn || !pan_tiles || !ms_tiles) return fail("tmd_scene_to_tiles: null argument");
+    if (C <= 0 || ratio <= 0 || tile <= 0 || tile % 4 || Hs <= 0 || Ws <= 0 || Hs % tile || Ws % tile || Hs % ratio || Ws % ratio)
+        return fail("tmd_scene_to_tiles: scene %dx%d must be a whole number of %d-pixel tiles (tile a multiple of 4) and of the ratio %d", Hs, Ws, tile, ratio);
+    const int n_tiles = (Hs / tile) * (Ws / tile);
+    if (first < 0 || count < 0 || first + count > n_tiles) return fail("tmd_scene_to_tiles: tiles [%d, %d) outside the %d tiles of the scene", first, first + count, n_tiles);
+    if (!(img_scale > 0.f)) return fail("tmd_scene_to_tiles: img_scale must be positive");
+    if ((reinterpret_cast<uintptr_t>(pan_dn) | reinterpret_cast<uintptr_t>(pan_tiles) | reinterpret_cast<uintptr_t>(ms_tiles)) & 15) return fail("tmd_scene_to_tiles: tensors must be 16-byte aligned");
+    const cudaError_t err = scene_to_tiles(pan_dn, lrms_dn, pan_tiles, ms_tiles, C, Hs, Ws, ratio, tile, first, count, img_scale, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_scene_to_tiles: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+extern "C" int tmd_tiles_to_scene(const float* tiles, float* scene, int32_t C, int32_t Hs, int32_t Ws, int32_t tile, int32_t first, int32_t count,
+                                  float img_scale, int32_t clamp, void* stream) {
+    if (!tiles || !scene) return fail("tmd_tiles_to_scene: null argument");
+    if (C <= 0 || tile <= 0 || tile % 4 || Hs <= 0 || Ws <= 0 || Hs % tile || Ws % tile)
+        return fail("tmd_tiles_to_scene: scene %dx%d must be a whole number of %d-pixel tiles (tile a multiple of 4)", Hs, Ws, tile);
+    const int n_tiles = (Hs / tile) * (Ws / tile);
+    if (first < 0 || count < 0 || first + count > n_tiles) return fail("tmd_tiles_to_scene: tiles [%d, %d) outside the %d tiles of the scene", first, first + count, n_tiles);
+    if ((reinterpret_cast<uintptr_t>(tiles) | reinterpret_cast<uintptr_t>(scene)) & 15) return fail("tmd_tiles_to_scene: tensors must be 16-byte aligned");
+    const cudaError_t err = tiles_to_scene(tiles, scene, C, Hs, Ws, tile, first, count, img_scale, clamp != 0, (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_tiles_to_scene: %s", cudaGetErrorString(err));
+    return 0;
+}
+
 extern "C" int tmd_ancestral_update(const float* x, const float* eps, const float* noise, float* out, float c_recip, float c_recipm1,
                                     float coef1, float coef2, float sigma, int32_t clip, uint64_t seed, uint64_t step, int64_t n,
                                     void* stream) {

@@ -109,6 +109,12 @@ cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cu
 cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, int K, size_t n, cudaStream_t s);    // out[b,:] = sum_k alpha[b,k] w[k,:]
 
 
+// ---- scene.cu: full-scene front / back end (sensor DN <-> sampler tiles) ----
+cudaError_t scene_to_tiles(const float* pan, const float* lrms, float* pan_t, float* ms_t, int C, int Hs, int Ws, int ratio, int tile, int first,
+                           int count, float img_scale, cudaStream_t s);
+cudaError_t tiles_to_scene(const float* tiles, float* scene, int C, int Hs, int Ws, int tile, int first, int count, float img_scale, bool clamp,
+                           cudaStream_t s);
+
 // ---- operators2.cu ----
 // nn.LayerNorm(C, eps) over the rows of x [rows, C]; gamma / beta may be null
 cudaError_t layernorm_rows(const float* x, float* y, const float* gamma, const float* beta, int rows, int C, float eps, cudaStream_t s);

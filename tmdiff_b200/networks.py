@@ -124,12 +124,11 @@ class WavBEST(nn.Module):
         if text_embeddings:
             for k, v in text_embeddings.items():
                 self.set_text_embedding(k, v)
-        self._handle = None
-        self._handle_key = None
-        self._weights_key = None
-        self._text_key = None
-        self._cond_key = None
-        self._cond_keepalive = None
+        # one engine (handle + workspace + bound condition) per band count: a mixed-sensor job alternates between its 4- and
+        # 8-band buckets without re-planning either (BASELINE config 3)
+        self._engines = {}
+        self._cur = None
+        self._weights_epoch = 0
 
     # ---- reference surface ---------------------------------------------------------------
     def get_embeding(self, prompt):                            # :587-598
@@ -140,7 +139,7 @@ class WavBEST(nn.Module):
             raise ValueError("unknown sensor prompt %r (expected one of %s)" % (prompt, SENSORS))
         emb = torch.as_tensor(emb, dtype=torch.float32).reshape(1, 768).detach().cpu().clone()
         setattr(self, prompt.lower() + "_embeding", emb)
-        self._text_key = None
+        self._text_epoch = getattr(self, "_text_epoch", 0) + 1
 
     def encode_prompt(self, clip_text_model, get_prompt):      # :566-572
         """Fill the five cached embeddings from a reference `FrozenCLIPEmbedder` and its prompt texts."""
@@ -151,66 +150,88 @@ class WavBEST(nn.Module):
     def _lib(self):
         return _lib.load()
 
+    class _Engine:
+        __slots__ = ("handle", "handle_key", "weights_key", "text_key", "cond_key", "cond_keepalive")
+
+        def __init__(self):
+            self.handle = self.handle_key = self.weights_key = self.text_key = self.cond_key = self.cond_keepalive = None
+
+    # the attributes older callers / tests poke at, mapped onto the engine used last
+    @property
+    def _handle(self):
+        return self._cur.handle if self._cur is not None else None
+
+    @property
+    def _cond_key(self):
+        return self._cur.cond_key if self._cur is not None else None
+
     def _ensure_engine(self, B, N, H, W, device):
         if not torch.cuda.is_available():
             raise RuntimeError("tmdiff_b200.WavBEST needs a CUDA device; there is no CPU or PyTorch fallback")
         lib = self._lib()
-        key = self._handle_key
-        need = (key is None or key[0] < B or key[1] < N or key[2] * key[3] < H * W or key[4] != self.compute_dtype
-                or key[5] != device.index)
+        eng = self._engines.get(N)
+        if eng is None:
+            eng = self._engines[N] = WavBEST._Engine()
+        self._cur = eng
+        key = eng.handle_key
+        need = (key is None or key[0] < B or key[2] * key[3] < H * W or key[4] != self.compute_dtype or key[5] != device.index)
         if need:
-            self.release()
+            self._release_engine(eng)
             mb = max(B, self.max_batch or 0)
             cfg = _lib.Config((C.c_int32 * 4)(*self.channels), self.embed_dim, self.inter_dim, mb, N, H, W,
                               _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16)
             h = C.c_void_p()
             with torch.cuda.device(device):
                 _lib.check(lib.tmd_create(C.byref(cfg), C.byref(h)))
-            self._handle = h
-            self._handle_key = (mb, N, H, W, self.compute_dtype, device.index)
-            self._weights_key = self._text_key = self._cond_key = None
+            eng.handle = h
+            eng.handle_key = (mb, N, H, W, self.compute_dtype, device.index)
+            eng.weights_key = eng.text_key = eng.cond_key = None
         # parameters are held by the module, so (address, version) cannot be recycled under us; writes that bypass the
         # version counter (`p.data.copy_`, EMA swaps through .data) need refresh_weights()
-        wkey = tuple((p.data_ptr(), p._version) for p in self.parameters())
-        if wkey != self._weights_key:
+        wkey = (self._weights_epoch,) + tuple((p.data_ptr(), p._version) for p in self.parameters())
+        if wkey != eng.weights_key:
             for name in self._names:
                 t = self.get_parameter(name).detach().float().cpu().contiguous()
                 shp = (C.c_int64 * t.dim())(*t.shape)
-                _lib.check(lib.tmd_load_weight(self._handle, name.encode(), _lib.ptr(t), shp, t.dim()))
+                _lib.check(lib.tmd_load_weight(eng.handle, name.encode(), _lib.ptr(t), shp, t.dim()))
             half = self.inter_dim // 2
             # exactly the reference's expression so the fp32 frequencies are bit-identical (:90-92)
             freqs = torch.exp(-math.log(10000) * torch.arange(start=0, end=half, dtype=torch.float32) / half).contiguous()
-            _lib.check(lib.tmd_set_time_frequencies(self._handle, _lib.ptr(freqs), half))
+            _lib.check(lib.tmd_set_time_frequencies(eng.handle, _lib.ptr(freqs), half))
             with torch.cuda.device(device):
-                _lib.check(lib.tmd_finalize_weights(self._handle))
-            self._weights_key = wkey
-            self._text_key = self._cond_key = None
-        tkey = tuple(id(getattr(self, s.lower() + "_embeding")) for s in SENSORS)
-        if tkey != self._text_key:
+                _lib.check(lib.tmd_finalize_weights(eng.handle))
+            eng.weights_key = wkey
+            eng.text_key = eng.cond_key = None
+        tkey = (getattr(self, "_text_epoch", 0),) + tuple(id(getattr(self, s.lower() + "_embeding")) for s in SENSORS)
+        if tkey != eng.text_key:
             for s in SENSORS:
                 e = getattr(self, s.lower() + "_embeding")
                 if e is not None:
                     e = e.detach().float().cpu().contiguous()
-                    _lib.check(lib.tmd_set_text_embedding(self._handle, _lib.SENSOR_IDS[s], _lib.ptr(e)))
-            self._text_key = tkey
-            self._cond_key = None
-        return self._handle
+                    _lib.check(lib.tmd_set_text_embedding(eng.handle, _lib.SENSOR_IDS[s], _lib.ptr(e)))
+            eng.text_key = tkey
+            eng.cond_key = None
+        return eng
 
     def refresh_weights(self):
         """Re-upload the parameters on the next call.  Needed only after writes autograd's version counter does not see
         (`param.data.copy_(...)`, DLPack / external kernels); `load_state_dict` and in-place tensor ops are noticed."""
-        self._weights_key = None
-        self._cond_key = None
+        self._weights_epoch += 1
 
     def _load_from_state_dict(self, *args, **kwargs):
         super()._load_from_state_dict(*args, **kwargs)
-        self._weights_key = None
+        self._weights_epoch += 1
+
+    def _release_engine(self, eng):
+        if eng.handle is not None:
+            self._lib().tmd_destroy(eng.handle)
+            eng.handle = eng.handle_key = None
 
     def release(self):
-        if getattr(self, "_handle", None) is not None:
-            self._lib().tmd_destroy(self._handle)
-            self._handle = None
-            self._handle_key = None
+        for eng in list(getattr(self, "_engines", {}).values()):
+            self._release_engine(eng)
+        self._engines = {}
+        self._cur = None
 
     def __del__(self):
         try:
@@ -233,20 +254,21 @@ class WavBEST(nn.Module):
         for p in set(prompts):
             if self.get_embeding(p) is None:
                 raise ValueError("no text embedding for prompt %r" % (p,))   # reference: .repeat on None raises
-        h = self._ensure_engine(B, N, H, W, MS.device)
+        eng = self._ensure_engine(B, N, H, W, MS.device)
+        h = eng.handle
         # The cache holds the caller's OWN tensor objects (not only converted copies), so their storage cannot be freed
         # and handed to a new batch at the same address while the entry is alive; identity + autograd version then
         # identify the contents.  Writes the version counter does not see (`.data.copy_`, external kernels) need
         # reset_condition_cache().
         key = (id(PAN), PAN.data_ptr(), PAN._version, id(MS), MS.data_ptr(), MS._version, tuple(prompts), B, N, H, W)
-        if key != self._cond_key:
+        if key != eng.cond_key:
             pan, ms = PAN.contiguous().float(), MS.contiguous().float()
             ids = (C.c_int32 * B)(*[_lib.SENSOR_IDS[p] for p in prompts])
             with torch.cuda.device(MS.device):
                 _lib.check(self._lib().tmd_precompute_condition(h, _lib.ptr(pan), _lib.ptr(ms), ids, B, N, H, W,
                                                                 _lib.stream_ptr()))
-            self._cond_key = key
-            self._cond_keepalive = (PAN, MS, pan, ms)
+            eng.cond_key = key
+            eng.cond_keepalive = (PAN, MS, pan, ms)
         return h
 
     @torch.no_grad()
@@ -268,11 +290,13 @@ class WavBEST(nn.Module):
         return out.to(x_t.dtype)
 
     def launch_count(self):
-        return int(self._lib().tmd_launch_count(self._handle)) if self._handle is not None else 0
+        """Kernel launches of every engine of this module since its creation."""
+        return sum(int(self._lib().tmd_launch_count(e.handle)) for e in self._engines.values() if e.handle is not None)
 
     def reset_condition_cache(self):
         """Forget the bound (PAN, MS, prompt): the next call re-runs the step-invariant half."""
-        self._cond_key = None
+        for e in self._engines.values():
+            e.cond_key = e.cond_keepalive = None
 
     # ---- measurement -----------------------------------------------------------------------
     def profile_begin(self):

@@ -44,20 +44,23 @@ def bucket_by_bands(patches):
 
 
 @torch.no_grad()
-def sample_mixed(diffusion, patches, steps=20, x_T=None, group=None):
-    """Sample a joint WV3/QB/GF2 batch: bucket by band count, shard every bucket contiguously over the ranks (equal
-    FLOPs per rank: an 8-band patch costs twice a 4-band one), one all-gather per bucket.  Returns the fused images
-    in input order (list of [N_i, H, W])."""
+def sample_mixed(diffusion, patches, steps=20, x_T=None, group=None, batch=64):
+    """Sample a joint WV3/QB/GF2 batch (BASELINE config 3): bucket by band count, shard every bucket contiguously over the ranks
+    (equal FLOPs per rank: an 8-band patch costs twice a 4-band one, and every rank gets the same share of each bucket), run the
+    local shard in chunks of at most `batch` patches with per-sample prompts (the module keeps one engine per band count, so
+    alternating buckets re-plans nothing), one all-gather per bucket.  Returns the fused images in input order (list of
+    [N_i, H, W])."""
     on = dist.is_available() and dist.is_initialized()
     rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
     result = [None] * len(patches)
     for n, (idx, pan, ms, prompts) in bucket_by_bands(patches).items():
         lo, hi = shard_range(len(idx), rank, world)
-        if hi > lo:
-            noise = torch.randn_like(ms[lo:hi]) if x_T is None else torch.stack([x_T[i] for i in idx[lo:hi]]).to(ms.device)
-            local = diffusion.sample_by_dpmsolver({"PAN": pan[lo:hi], "MS": ms[lo:hi], "Res": noise}, prompts[lo:hi], steps=steps, x_T=noise)
-        else:
-            local = ms.new_zeros((0,) + tuple(ms.shape[1:]))
+        outs = []
+        for s in range(lo, hi, batch):
+            e = min(s + batch, hi)
+            noise = torch.randn_like(ms[s:e]) if x_T is None else torch.stack([x_T[i] for i in idx[s:e]]).to(ms.device)
+            outs.append(diffusion.sample_by_dpmsolver({"PAN": pan[s:e], "MS": ms[s:e], "Res": noise}, prompts[s:e], steps=steps, x_T=noise))
+        local = torch.cat(outs) if outs else ms.new_zeros((0,) + tuple(ms.shape[1:]))
         full = gather_tiles(local, len(idx), group) if world > 1 else local
         for j, i in enumerate(idx):
             result[i] = full[j]
