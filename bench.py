@@ -55,6 +55,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
     ap.add_argument("--launch-csv", default=None, help="write the per-launch CUDA-event times of the profiled step here")
+    ap.add_argument("--workload", default="config2", choices=["config2", "mixed512", "scene2048"],
+                    help="config2 (default, what the driver runs): --batch patches per GPU, weak scaling; mixed512: BASELINE config 3, one "
+                         "512-patch WV3+QB+GF2 batch over the GPUs (strong scaling); scene2048: BASELINE config 4, a 2048x2048 PAN / 8-band "
+                         "512x512 MS scene, 1024 tiles over the GPUs (strong scaling)")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed batch")
     ap.add_argument("--no-eager-baseline", action="store_true", help="skip the PyTorch-eager-on-GPU (cuDNN) baseline arm")
     ap.add_argument("--eager-budget-s", type=float, default=45.0, help="time budget per eager-baseline variant")
@@ -474,10 +478,176 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------
+# BASELINE configs 3 and 4: a fixed job split over the GPUs (strong scaling)
+# ------------------------------------------------------------------------------------------------
+def run_job(args):
+    """--workload mixed512 / scene2048.  The job is the same at every N (strong scaling): rank r takes its contiguous share of
+    every band bucket / of the tile list, there is no per-step communication, one all-gather per bucket (or of the tiles) at the
+    end.  `value` with the inputs resident in HBM, `e2e` from pinned host buffers with the result read back.  `result_sha16` is
+    a hash of the bytes of the result on rank 0: equal across N means the sharded job is bit-identical to the single-GPU one."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    from oracle import wavbest_ref
+    from oracle.inputs import make_inputs
+    from tmdiff_b200 import GeneralDiffusion, WavBEST, ops
+    from tmdiff_b200.parallel import sample_buckets
+    from tmdiff_b200.tiling import sample_scene
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; tmdiff_b200 has no CPU path")
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    if world == 1 and args.gpus > 1:
+        raise SystemExit("bench.py --gpus %d must be launched with torchrun --nproc-per-node %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    chunk = args.batch
+    model = WavBEST(channels=list(CHANNELS), dtype=args.dtype, text_embeddings=wavbest_ref.seeded_text_embeddings(), max_batch=chunk)
+    model.load_state_dict(wavbest_ref.seeded_weights(CHANNELS), strict=True)
+    model = model.to(dev)
+    G = GeneralDiffusion(model)
+    G.set_new_noise_schedule({"schedule": "cosine", "n_timestep": 1000}, dev)
+    P = args.patch
+    gen = torch.Generator().manual_seed(3407)
+
+    if args.workload == "mixed512":
+        # 192 WV3 (8 bands) + 160 QB + 160 GF2 (4 bands): the two 4-band sensors share a bucket with per-sample prompts
+        spec = {8: [("WV3", 192)], 4: [("QB", 160), ("GF2", 160)]}
+        host = {}
+        for n, parts in spec.items():
+            b = sum(c for _, c in parts)
+            pan, ms, xT = make_inputs(b, n, P, P, seed=3407 + n)
+            prompts = [s for s, c in parts for _ in range(c)]
+            perm = torch.randperm(b, generator=gen).tolist()            # sensors interleaved inside the bucket
+            host[n] = (pan.pin_memory(), ms.pin_memory(), [prompts[i] for i in perm], xT.pin_memory())
+        resident = {n: (p.to(dev), m.to(dev), pr, x.to(dev)) for n, (p, m, pr, x) in host.items()}
+        n_patches = sum(v[1].shape[0] for v in host.values())
+        gflop = sum(v[1].shape[0] * n * (GFLOP_INVARIANT_PER_BAND + (args.solver_steps + 1) * GFLOP_VARIANT_PER_BAND) for n, v in host.items())
+        out_host = {n: torch.empty_like(v[1]).pin_memory() for n, v in host.items()}
+        h2d = sum((v[0].numel() + v[1].numel() + v[3].numel()) * 4 for v in host.values())
+        d2h = sum(v.numel() * 4 for v in out_host.values())
+
+        def step(buckets, read_back):
+            model.reset_condition_cache()
+            fused = sample_buckets(G, buckets, steps=args.solver_steps, batch=chunk)
+            if read_back:
+                for n, t in fused.items():
+                    out_host[n].copy_(t, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            return fused
+        step_resident = lambda: step(resident, False)
+        step_e2e = lambda: step(host, True)
+        digest = lambda r: hashlib.sha256(b"".join(r[n].cpu().numpy().tobytes() for n in sorted(r))).hexdigest()[:16]
+        what = "BASELINE config 3: one joint batch of 192 WV3 (8-band) + 160 QB + 160 GF2 (4-band) %dx%d patches, per-sample prompts" % (P, P)
+        extra = lambda r: {}
+    else:
+        Hs = Ws = 2048
+        C8, scale = 8, 2047.0
+        pan_h = (torch.rand(1, Hs, Ws, generator=gen) * scale).pin_memory()                     # sensor DN
+        lrms_h = (torch.rand(C8, Hs // 4, Ws // 4, generator=gen) * scale).pin_memory()
+        T = (Hs // P) * (Ws // P)
+        xT_h = torch.randn(T, C8, P, P, generator=gen).pin_memory()
+        pan_d, lrms_d, xT_d = pan_h.to(dev), lrms_h.to(dev), xT_h.to(dev)
+        out_host = torch.empty(C8, Hs, Ws).pin_memory()
+        n_patches = T
+        gflop = T * C8 * (GFLOP_INVARIANT_PER_BAND + (args.solver_steps + 1) * GFLOP_VARIANT_PER_BAND)
+        h2d, d2h = (pan_h.numel() + lrms_h.numel() + xT_h.numel()) * 4, out_host.numel() * 4
+
+        def step(pan, lrms, xT, read_back):
+            model.reset_condition_cache()
+            if read_back:
+                pan, lrms = pan.to(dev, non_blocking=True), lrms.to(dev, non_blocking=True)
+            scene = sample_scene(G, pan, lrms, "WV3", tile=P, steps=args.solver_steps, batch=chunk, x_T=xT, img_scale=scale, clamp=True)
+            if read_back:
+                out_host.copy_(scene, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            return scene
+        step_resident = lambda: step(pan_d, lrms_d, xT_d, False)
+        step_e2e = lambda: step(pan_h, lrms_h, xT_h, True)
+        digest = lambda r: hashlib.sha256(r.cpu().numpy().tobytes()).hexdigest()[:16]
+        what = ("BASELINE config 4: PAN %dx%d / 8-band MS %dx%d scene in sensor DN, %d tiles of %dx%d in unpatch_16 order, DN scaling + "
+                "bilinear x4 + tile cut and stitch + clamp + scale back on the device" % (Hs, Ws, Hs // 4, Ws // 4, T, P, P))
+
+        def extra(r):        # on-device quality of the fused scene against a seeded synthetic HR scene (SAM / ERGAS / Q, core/metrics.py)
+            hr = (r / scale + 0.02 * torch.randn(r.shape, generator=torch.Generator(device=dev).manual_seed(9), device=dev)).clamp(0.01, 1.0)
+            q = ops.quality_metrics(hr[None], (r / scale).clamp(0.01, 1.0)[None])[0].tolist()
+            return {"quality_vs_synthetic_hr": {"SAM_deg": q[0], "ERGAS": q[1], "Q": q[2]}}
+
+    def timed(fn, k):
+        gc.collect()
+        gc.disable()
+        try:
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(k):
+                r = fn()
+            e1.record()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            return float(ms.item()), r
+        finally:
+            gc.enable()
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = model.launch_count()
+    t_ms, result = timed(step_resident, args.steps)
+    launches = model.launch_count() - l0
+    clocks = sampler.finish()
+    step_e2e()
+    e2e_ms, _ = timed(step_e2e, args.steps)
+    if rank == 0:
+        peaks = measured_peaks()
+        peak = peaks["bf16_tflops_sustained"]
+        value = n_patches * args.steps / (t_ms * 1e-3)
+        ach = gflop * 1e9 * args.steps / (t_ms * 1e-3) / 1e12 / world
+        line = {
+            "metric": METRIC, "value": value, "unit": "patches/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
+            "data": "synthetic (seeded PAN/MS/x_T, seeded weights and text embeddings)",
+            "config": {"workload": what, "patches_per_step": n_patches, "chunk": chunk, "solver_steps": args.solver_steps, "channels": list(CHANNELS),
+                       "l2": "no flush: every chunk streams >2 GB of activations per GPU (L2 is 126 MB)",
+                       "parallelism": "each band bucket / the tile list split contiguously over the GPUs, one all-gather per bucket at the end"},
+            "e2e": {"value": n_patches * args.steps / (e2e_ms * 1e-3), "unit": "patches/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": e2e_ms / args.steps,
+                    "api": "tmdiff_b200.parallel.sample_buckets" if args.workload == "mixed512" else "tmdiff_b200.tiling.sample_scene"},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"kernel": "whole step: minimal algorithmic conv FLOPs (SURVEY.md 8d) / step time, per GPU", "bound": "tensor", "achieved": ach,
+                         "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                         "peak_source": "%s bf16_tflops_sustained" % peaks["source"]},
+            "result_sha16": digest(result),
+        }
+        line.update(extra(result))
+        sys.stdout.flush()
+        os.dup2(_real_stdout, 1)
+        print(json.dumps(line))
+        sys.stdout.flush()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload != "config2":
+        run_job(args)
     else:
         run_ours(args)
 

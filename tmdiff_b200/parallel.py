@@ -44,24 +44,43 @@ def bucket_by_bands(patches):
 
 
 @torch.no_grad()
+def sample_buckets(diffusion, buckets, steps=20, group=None, batch=64):
+    """The sharded core of sample_mixed.  buckets: {bands: (PAN [b,1,H,W], MS [b,bands,H,W], prompts (b names), x_T [b,bands,H,W])},
+    every rank holding the same full buckets on the host (pinned: the local shard is copied asynchronously) or on the device.
+    Each bucket is split contiguously over the ranks, the local shard sampled in chunks of at most `batch` patches, the results
+    all-gathered (one collective per bucket).  Returns {bands: fused images [b,bands,H,W]} on the device."""
+    on = dist.is_available() and dist.is_initialized()
+    rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
+    betas = getattr(diffusion, "betas", None)          # the sampler's device; test doubles without a schedule stay where the data is
+    out = {}
+    for n in sorted(buckets):
+        pan, ms, prompts, x_T = buckets[n]
+        dev = betas.device if betas is not None else ms.device
+        lo, hi = shard_range(ms.shape[0], rank, world)
+        outs = []
+        for s in range(lo, hi, batch):
+            e = min(s + batch, hi)
+            p, m = pan[s:e].to(dev, non_blocking=True), ms[s:e].to(dev, non_blocking=True)
+            noise = torch.randn_like(m) if x_T is None else x_T[s:e].to(dev, non_blocking=True)
+            outs.append(diffusion.sample_by_dpmsolver({"PAN": p, "MS": m, "Res": noise}, list(prompts[s:e]), steps=steps, x_T=noise))
+        local = torch.cat(outs) if outs else torch.zeros((0,) + tuple(ms.shape[1:]), device=dev)
+        out[n] = gather_tiles(local, ms.shape[0], group) if world > 1 else local
+    return out
+
+
+@torch.no_grad()
 def sample_mixed(diffusion, patches, steps=20, x_T=None, group=None, batch=64):
     """Sample a joint WV3/QB/GF2 batch (BASELINE config 3): bucket by band count, shard every bucket contiguously over the ranks
     (equal FLOPs per rank: an 8-band patch costs twice a 4-band one, and every rank gets the same share of each bucket), run the
     local shard in chunks of at most `batch` patches with per-sample prompts (the module keeps one engine per band count, so
     alternating buckets re-plans nothing), one all-gather per bucket.  Returns the fused images in input order (list of
     [N_i, H, W])."""
-    on = dist.is_available() and dist.is_initialized()
-    rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
+    by_bands = bucket_by_bands(patches)
+    buckets = {n: (pan, ms, prompts, None if x_T is None else torch.stack([x_T[i] for i in idx]))
+               for n, (idx, pan, ms, prompts) in by_bands.items()}
+    fused = sample_buckets(diffusion, buckets, steps=steps, group=group, batch=batch)
     result = [None] * len(patches)
-    for n, (idx, pan, ms, prompts) in bucket_by_bands(patches).items():
-        lo, hi = shard_range(len(idx), rank, world)
-        outs = []
-        for s in range(lo, hi, batch):
-            e = min(s + batch, hi)
-            noise = torch.randn_like(ms[s:e]) if x_T is None else torch.stack([x_T[i] for i in idx[s:e]]).to(ms.device)
-            outs.append(diffusion.sample_by_dpmsolver({"PAN": pan[s:e], "MS": ms[s:e], "Res": noise}, prompts[s:e], steps=steps, x_T=noise))
-        local = torch.cat(outs) if outs else ms.new_zeros((0,) + tuple(ms.shape[1:]))
-        full = gather_tiles(local, len(idx), group) if world > 1 else local
+    for n, (idx, _, _, _) in by_bands.items():
         for j, i in enumerate(idx):
-            result[i] = full[j]
+            result[i] = fused[n][j]
     return result
