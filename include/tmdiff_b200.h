@@ -226,6 +226,11 @@ int tmd_scene_to_tiles(const float* pan_dn, const float* lrms_dn, float* pan_til
 int tmd_tiles_to_scene(const float* tiles, float* scene, int32_t C, int32_t Hs, int32_t Ws, int32_t tile, int32_t first, int32_t count,
                        float img_scale, int32_t clamp, void* stream);
 
+/* Debug aid (no reference counterpart): with TMD_ARENA_REDZONE=1 in the environment when the condition is bound, every tensor
+ * of the handle's workspace is followed by a 4 KB canary-filled red zone; this call synchronises the device, checks all of them
+ * and fails (naming the first tensor whose red zone was overwritten) if a kernel stored out of bounds. */
+int tmd_debug_check_redzones(tmd_handle h, int32_t* n_checked, int32_t* n_bad);
+
 /* number of kernel launches issued by this handle since creation (bench.py's gpu_launches) */
 int64_t tmd_launch_count(tmd_handle h);
 

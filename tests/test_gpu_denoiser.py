@@ -459,3 +459,20 @@ def test_mixed_sensor_two_band_buckets(lib_built):
         assert got[k].shape == want.shape
         assert rel_l2(got[k].cpu() - ms[i], want - ms[i]) < FP32_TOL, (k, sensor)
     m.release()
+
+
+def test_arena_redzones_intact(lib_built, monkeypatch):
+    """The library's own bounds check of its workspace (compute-sanitizer is closed on this pool, profiles/sanitizer_r02.md):
+    with TMD_ARENA_REDZONE=1 every activation tensor is followed by a canary-filled red zone; none may be touched by a forward
+    pass or a full sampling run -- bf16 and fp32, 4 and 8 bands, a patch that is not a multiple of the 16 x 8 tile."""
+    monkeypatch.setenv("TMD_ARENA_REDZONE", "1")
+    for dtype in ("bf16", "fp32"):
+        for B, N, H, W, sensor in ((3, 4, 32, 32, "QB"), (2, 8, 64, 64, "WV3"), (2, 4, 24, 40, "GF2")):
+            m = make_model(dtype)
+            G = _diffusion(m)
+            g = torch.Generator().manual_seed(B + N)
+            pan, ms, x = torch.rand(B, 1, H, W, generator=g), torch.rand(B, N, H, W, generator=g), torch.randn(B, N, H, W, generator=g)
+            img = G.sample_by_dpmsolver({"PAN": pan.cuda(), "MS": ms.cuda(), "Res": x}, sensor, steps=4, x_T=x.cuda())
+            assert bool(torch.isfinite(img).all())
+            assert m.check_redzones() > 40                      # every named buffer of the plan has one
+            m.release()

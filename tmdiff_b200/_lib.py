@@ -86,6 +86,7 @@ SIGNATURES = {
     "tmd_psf_downsample": (C.c_int, [_P, _P, _P, _P] + [C.c_int32] * 7 + [_P]),
     "tmd_scene_to_tiles": (C.c_int, [_P, _P, _P, _P] + [C.c_int32] * 7 + [C.c_float, _P]),
     "tmd_tiles_to_scene": (C.c_int, [_P, _P] + [C.c_int32] * 6 + [C.c_float, C.c_int32, _P]),
+    "tmd_debug_check_redzones": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "tmd_launch_count": (C.c_int64, [_P]),
     "tmd_profile_begin": (C.c_int, [_P]),
     "tmd_profile_end": (C.c_int, [_P, C.POINTER(Profile), C.c_char_p]),

@@ -81,7 +81,8 @@ struct Launch {       // one kernel launch of the plan + what it costs algorithm
 
 }  // namespace
 
-constexpr int kMaxPlanEvals = 256;   // evaluations per tmd_sample plan whose time tables are precomputed in one launch
+constexpr int kMaxPlanEvals = 256;
+constexpr size_t kRedzoneBytes = 4096;   // evaluations per tmd_sample plan whose time tables are precomputed in one launch
 
 struct tmd_engine {
     tmd_config cfg{};
@@ -114,6 +115,10 @@ struct tmd_engine {
     char* arena = nullptr;
     size_t arena_size = 0, arena_used = 0;
     std::map<std::string, void*> bufs;
+    // TMD_ARENA_REDZONE=1 (debug): a canary-filled red zone behind every arena buffer, checked by tmd_debug_check_redzones
+    // (compute-sanitizer is not available on every pool; this is the library's own bounds check of its workspace)
+    std::vector<std::pair<std::string, char*>> redzones;
+    bool redzone_on = false;
     std::vector<Launch> pre_ops, step_ops;
     std::vector<UmmaPlan*> plans;
     const float* cur_x = nullptr;
@@ -465,9 +470,11 @@ struct Planner {
         auto it = e->bufs.find(name);
         if (it == e->bufs.end()) {
             const size_t bytes = (vox(lvl) * C * e->esize + 255) & ~(size_t)255;
-            if (e->arena_used + bytes > e->arena_size) { err = "workspace arena exhausted"; return View{}; }
+            const size_t rz = e->redzone_on ? kRedzoneBytes : 0;
+            if (e->arena_used + bytes + rz > e->arena_size) { err = "workspace arena exhausted"; return View{}; }
             void* p = e->arena + e->arena_used;
-            e->arena_used += bytes;
+            e->arena_used += bytes + rz;
+            if (rz) e->redzones.push_back({name, (char*)p + bytes});
             it = e->bufs.emplace(name, p).first;
         }
         return View{it->second, C, C};
@@ -632,7 +639,12 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
     e->pre_ops.clear();
     e->step_ops.clear();
     e->bufs.clear();
+    e->redzones.clear();
     e->arena_used = 0;
+    {
+        const char* rz = getenv("TMD_ARENA_REDZONE");
+        e->redzone_on = rz && rz[0] == '1';
+    }
     if (!e->arena) {
         // worst-case footprint at (max_batch, max_bands, H, W): sum over levels of channel-widths of all named buffers
         const size_t v0 = (size_t)e->cfg.max_batch * e->cfg.max_bands * e->cfg.height * e->cfg.width;
@@ -642,7 +654,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             const size_t v = v0 >> (2 * l);
             elems += v * (size_t)(2 * 3 * c[l] + 8 * cm[l] + 8 * c[l]) + v / 4 * (size_t)cm[l];
         }
-        e->arena_size = elems * e->esize + ((size_t)64 << 20);
+        e->arena_size = elems * e->esize + ((size_t)64 << 20) + (e->redzone_on ? 256 * kRedzoneBytes : 0);
         CK(cudaMalloc((void**)&e->arena, e->arena_size));
         for (int i = 0; i < TMD_NUM_SLOTS; ++i)
             if (e->dmalloc(&e->slots[i], v0)) return 1;
@@ -859,6 +871,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         }
     }
     if (P.err) return fail("plan: %s", P.err);
+    for (auto& rz : e->redzones) CK(cudaMemset(rz.second, 0xCB, kRedzoneBytes));
     e->B = B; e->N = N; e->H = H; e->W = W;
     return 0;
 }
@@ -1102,6 +1115,24 @@ extern "C" int tmd_sample(tmd_handle h, const float* x_T, int32_t B, int32_t ban
 }
 
 extern "C" int64_t tmd_launch_count(tmd_handle h) { return h ? h->launches : 0; }
+
+extern "C" int tmd_debug_check_redzones(tmd_handle h, int32_t* n_checked, int32_t* n_bad) {
+    if (!h || !n_checked || !n_bad) return fail("tmd_debug_check_redzones: null argument");
+    *n_checked = *n_bad = 0;
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    std::vector<unsigned char> host(kRedzoneBytes);
+    std::string first;
+    for (auto& rz : h->redzones) {
+        CK(cudaMemcpy(host.data(), rz.second, kRedzoneBytes, cudaMemcpyDeviceToHost));
+        bool ok = true;
+        for (unsigned char c : host) ok = ok && c == 0xCB;
+        ++*n_checked;
+        if (!ok) { ++*n_bad; if (first.empty()) first = rz.first; }
+    }
+    if (*n_bad) return fail("tmd_debug_check_redzones: %d of %d red zones overwritten (first: behind '%s')", *n_bad, *n_checked, first.c_str());
+    return 0;
+}
 
 extern "C" int tmd_profile_begin(tmd_handle h) {
     if (!h) return fail("tmd_profile_begin: null handle");

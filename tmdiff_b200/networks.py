@@ -289,6 +289,17 @@ class WavBEST(nn.Module):
             _lib.check(self._lib().tmd_denoise(h, _lib.ptr(x), _lib.ptr(t), _lib.ptr(out), _lib.stream_ptr()))
         return out.to(x_t.dtype)
 
+    def check_redzones(self):
+        """Debug: verify the workspace red zones of every engine (TMD_ARENA_REDZONE=1); returns the number checked, raises if any
+        was overwritten."""
+        total = 0
+        for e in self._engines.values():
+            if e.handle is not None:
+                n, bad = C.c_int32(0), C.c_int32(0)
+                _lib.check(self._lib().tmd_debug_check_redzones(e.handle, C.byref(n), C.byref(bad)))
+                total += n.value
+        return total
+
     def launch_count(self):
         """Kernel launches of every engine of this module since its creation."""
         return sum(int(self._lib().tmd_launch_count(e.handle)) for e in self._engines.values() if e.handle is not None)
