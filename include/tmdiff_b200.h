@@ -195,6 +195,14 @@ int tmd_quality_metrics(const float* ref, const float* img, float* out, int32_t 
 int tmd_dynamic_conv(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
                      const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
                      int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream);
+/* The same with the caller's scratch block (no allocation inside the call): `workspace` is device memory of at least
+ * tmd_dynamic_conv_workspace_bytes(...) bytes, 256-byte aligned.  All three entries run one groups=B convolution as ONE launch of
+ * the conv kernel with per-sample weight rows: spatial mean, attention head, expert mix, layout in, conv, layout out. */
+int64_t tmd_dynamic_conv_workspace_bytes(int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K, int32_t dtype);
+int tmd_dynamic_conv_ws(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                        const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                        int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* workspace, int64_t workspace_bytes,
+                        void* stream);
 /* torch.nn.LayerNorm(C, eps) over the rows of x [rows, C] (BasicTransformerBlock.norm1-3, core/Attention.py:282-284);
  * gamma / beta [C] or NULL. */
 int tmd_layernorm(const float* x, float* y, const float* gamma, const float* beta, int32_t rows, int32_t C, float eps, void* stream);

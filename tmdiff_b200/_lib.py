@@ -80,6 +80,8 @@ SIGNATURES = {
     "tmd_quality_metrics": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P]),
     "tmd_ancestral_update": (C.c_int, [_P, _P, _P, _P] + [C.c_float] * 5 + [C.c_int32, C.c_uint64, C.c_uint64, C.c_int64, _P]),
     "tmd_dynamic_conv": (C.c_int, [_P] * 7 + [C.c_int32] * 10 + [C.c_float, C.c_int32, _P]),
+    "tmd_dynamic_conv_workspace_bytes": (C.c_int64, [C.c_int32] * 9),
+    "tmd_dynamic_conv_ws": (C.c_int, [_P] * 7 + [C.c_int32] * 10 + [C.c_float, C.c_int32, _P, C.c_int64, _P]),
     "tmd_layernorm": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_float, _P]),
     "tmd_geglu": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P]),
     "tmd_band_moments": (C.c_int, [_P, _P, _P] + [C.c_int32] * 6 + [_P]),

@@ -30,7 +30,8 @@ enum ConvMode { CONV_NORMAL = 0, CONV_POOL = 1, CONV_UPSAMPLE = 2 };
 
 struct ConvEpilogue {
     int mode;
-    const float* bias;          // [Co] or null
+    const float* bias;          // [Co] or null ([B][ld_bias] when ld_bias != 0)
+    int ld_bias;
     const void* add0; int ld_add0;   // at output resolution
     const void* add1; int ld_add1;   // at half the output resolution (NORMAL only), nearest-upsampled
     void* raw_out; int ld_raw;
@@ -65,6 +66,9 @@ struct ConvOp {
     // front of the 1x1x1 conv) ride in the K loop of the block's last 3x3x3 conv instead of being separate launches.
     const void* src2; int Ci2, ld_in2;
     const __nv_bfloat16* w2_bf16;  // [Co][Ci2]
+    // Per-sample weights (Dynamic_conv: a groups=B convolution, core/dynamic_conv.py:244-268): sample b reads w_f32 / w_bf16 at
+    // + b * w_sample_stride elements (0: one weight set for the whole batch) and bias at + b * epi.ld_bias.
+    long long w_sample_stride;
     ConvEpilogue epi;
 };
 

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(ConvOp op, int TH, int T
                 const int cq = idx % (BN / 4), k = (idx / (BN / 4)) % KC, t = idx / (BN / 4) / KC;
                 float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (c0 + k < op.Ci && co_base + cq * 4 < op.Co)
-                    w = *reinterpret_cast<const float4*>(op.w_f32 + ((size_t)(tap0 + t) * op.Ci + c0 + k) * op.Co + co_base + cq * 4);
+                    w = *reinterpret_cast<const float4*>(op.w_f32 + (size_t)b * op.w_sample_stride + ((size_t)(tap0 + t) * op.Ci + c0 + k) * op.Co + co_base + cq * 4);
                 *reinterpret_cast<float4*>(sB + (t * KC + k) * BN + cq * 4) = w;
             }
             __syncthreads();
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(ConvOp op, int TH, int T
     float bias[4] = {0.f, 0.f, 0.f, 0.f};
     if (e.bias) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) bias[i] = e.bias[co + i];
+        for (int i = 0; i < 4; ++i) bias[i] = e.bias[(size_t)b * e.ld_bias + co + i];
     }
     const size_t bn = (size_t)b * op.N + n;
     if (e.mode == CONV_NORMAL) {

@@ -60,6 +60,7 @@ struct UmmaParams {
     int B, N, H, W, Ci, Co, taps;   // Co: output channels of ONE tile (= the layer's Co / co_split)
     uint32_t fd[5][2];          // {multiplier, shift} of the exact divisions by co_split, tiles_x, tiles_y, tiles_n and Co (decode_tile, staging)
     int co_split;               // REUSE: channel groups the layer's Co is split into (a tile = voxels x planes x one group)
+    int w_rows_per_sample;      // per-sample weights (ConvOp::w_sample_stride): rows of the weight map per sample, else 0
     int mode;                   // 0 = SIMPLE, 1 = REUSE
     int KC, nkc;                // channels per chunk, chunks per tap
     int TW, TH, TN, TB;         // output tile (voxels per accumulator = 128)
@@ -444,8 +445,8 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& P, float acc[16], i
             bias[4 * i] = t.x; bias[4 * i + 1] = t.y; bias[4 * i + 2] = t.z; bias[4 * i + 3] = t.w;
         }
     } else if (e.bias) {
-        load8_f32(e.bias + cg, bias);
-        load8_f32(e.bias + cg + 8, bias + 8);
+        load8_f32(e.bias + (size_t)b * e.ld_bias + cg, bias);
+        load8_f32(e.bias + (size_t)b * e.ld_bias + cg + 8, bias + 8);
     } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) bias[i] = 0.f;
@@ -717,10 +718,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                                     for (int t = ts * b_taps; t < (ts + 1) * b_taps; ++t)    // t = dy*3+dx
 #pragma unroll
                                         for (int dz = 0; dz < 3; ++dz, dst += P.b_tile_bytes)   // tap = dz*9+t; rows [dz*Co, (dz+1)*Co) of the tap's block
-                                            tma_load_2d(dst, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, tc.ch * P.Co);
+                                            tma_load_2d(dst, &P.tmB, b_full(s), (dz * 9 + t) * P.Ci + kc * KC, tc.ch * P.Co + tc.b0 * P.w_rows_per_sample);
                                 } else {
                                     mbar_expect_tx(b_full(s), P.b_tile_bytes);
-                                    tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, tc.ch * P.Co);
+                                    tma_load_2d(dst, &P.tmB, b_full(s), g * P.Ci + kc * KC, tc.ch * P.Co + tc.b0 * P.w_rows_per_sample);
                                 }
                             }
                         }
@@ -924,7 +925,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 for (int idx = lane; idx < n_cst; idx += 32) {
                     const int v = (int)fdiv((uint32_t)idx, P.fd[4]), c = idx - v * P.Co + cb;
                     float val;
-                    if (v == 0) val = e.bias ? __ldg(e.bias + c) : 0.f;
+                    if (v == 0) val = e.bias ? __ldg(e.bias + (size_t)tc.b0 * e.ld_bias + c) : 0.f;
                     else if (v < 3) val = e.tb[v - 1] ? 0.5f * __ldg(e.tb[v - 1] + (size_t)tc.b0 * e.ld_tb + c) : 0.f;   // stored halved (store_views16)
                     else val = e.sc[v - 3] ? __ldg(e.sc[v - 3] + (size_t)tc.b0 * e.ld_sc + c) : 1.f;
                     dst[idx] = val;
@@ -1007,7 +1008,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             }
             // work items = (plane, 16-channel slab); the warps of a lane quarter take items round-robin, fetch the residual
             // operands of their next item and start the TMEM read of the next slab before working on the current one
-            const bool in_tile = b < P.B && y < P.H && x < P.W && !Epi<EF>::dbg(P.epi, 8);
+            const bool in_tile = b < P.B && b_in < P.TB && y < P.H && x < P.W && !Epi<EF>::dbg(P.epi, 8);
             int pl = 0, sl = sub;                           // item = (plane pl, slab sl)
             while (sl >= nslab) { sl -= nslab; ++pl; }
             const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC) * P.Co;
@@ -1162,6 +1163,8 @@ bool conv_umma_supported(const ConvOp& op) {
         if (op.Ci2 % kc || op.ld_in2 % 8 || (reinterpret_cast<uintptr_t>(op.src2) & 15) || (reinterpret_cast<uintptr_t>(op.w2_bf16) & 15)) return false;
     }
     if (op.W < 2 || op.H < 2) return false;
+    if (op.w_sample_stride && (op.w_sample_stride != (long long)op.taps * op.Ci * op.Co || op.src2)) return false;
+    if (e.bias && e.ld_bias % 4) return false;
     return true;
 }
 
@@ -1212,6 +1215,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         // zero padding of the band axis are skipped outright
         if (op.taps == 27 && op.B >= 128 / (P.TW * P.TH)) P.TN = 1;
         P.TB = 128 / (P.TW * P.TH * P.TN);
+        if (op.w_sample_stride) P.TB = 1;              // per-sample weights: a tile may not span samples (rows beyond the box are not stored)
         P.NACC = 1;
         boxA[0] = P.KC; boxA[1] = P.TW; boxA[2] = P.TH; boxA[3] = P.TN; boxA[4] = P.TB;
         P.tiles_n = (op.N + P.TN - 1) / P.TN;
@@ -1289,7 +1293,8 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         }
     }
     {   // weights [Co][taps*Ci] bf16
-        cuuint64_t dims[2] = {(cuuint64_t)op.taps * op.Ci, (cuuint64_t)op.Co};
+        P.w_rows_per_sample = op.w_sample_stride ? op.Co : 0;
+        cuuint64_t dims[2] = {(cuuint64_t)op.taps * op.Ci, (cuuint64_t)op.Co * (op.w_sample_stride ? op.B : 1)};
         cuuint64_t strides[1] = {2ull * op.taps * op.Ci};
         cuuint32_t box[2] = {(cuuint32_t)P.KC, (cuuint32_t)P.Co};
         cuuint32_t estr[2] = {1, 1};

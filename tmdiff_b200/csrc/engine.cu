@@ -1317,30 +1317,93 @@ extern "C" int tmd_attention_bf16(const void* q, const void* k, const void* vt, 
     return 0;
 }
 
+
 namespace {
-// experts' k^ndim taps scattered into the centre of the k^3 layout the convolution operators take (zero elsewhere)
-__global__ void embed_taps_kernel(const float* __restrict__ w, float* __restrict__ out, size_t rows, int k, int ndim) {
-    const int st = ndim == 1 ? k : k * k, dt = k * k * k;
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= rows * (size_t)dt) return;
-    const size_t r = i / dt;
-    const int t = (int)(i - r * dt), dz = t / (k * k), dy = (t / k) % k, dx = t % k, c = k / 2;
-    float v = 0.f;
-    if (ndim == 2) { if (dz == c) v = w[r * st + dy * k + dx]; }
-    else if (dz == c && dy == c) v = w[r * st + dx];
-    out[i] = v;
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+// scratch of one Dynamic_conv call: pooled means, expert weights, mixed weights (one layout per mode) and bias, the two layout
+// conversions of the activations
+size_t dynamic_conv_scratch(int B, int Ci, int Co, size_t nhw, int taps, int K, int dtype) {
+    const size_t wn = (size_t)Co * Ci * taps, es = dtype == TMD_F32 ? 4 : 2;
+    return align256((size_t)B * Ci * 4) + align256((size_t)B * K * 4) + align256((size_t)B * wn * es) + align256((size_t)B * Co * 4) +
+           align256((size_t)B * nhw * Ci * es) + align256((size_t)B * nhw * Co * es);
 }
 }  // namespace
 
+extern "C" int64_t tmd_dynamic_conv_workspace_bytes(int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K, int32_t dtype) {
+    if (B <= 0 || Ci <= 0 || Co <= 0 || N <= 0 || H <= 0 || W <= 0 || (k != 1 && k != 3) || K <= 0) return -1;
+    return (int64_t)dynamic_conv_scratch(B, Ci, Co, (size_t)N * H * W, k * k * k, K, dtype);
+}
+
+// One groups=B convolution (core/dynamic_conv.py:244-268) as ONE launch of the conv kernel with per-sample weight rows
+// (ConvOp::w_sample_stride): spatial mean, attention head, expert mix (straight into the conv's weight layout), layout in, conv,
+// layout out -- six launches, no per-sample tensor maps, one scratch block (the caller's, or one stream-ordered allocation).
 static int dynamic_conv_impl(const char* who, const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
                              const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
-                             int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream);
+                             int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* workspace, int64_t workspace_bytes,
+                             void* stream) {
+    if (!x || !weight || !fc1 || !fc2 || !y) return fail("%s: null argument", who);
+    if (k != 1 && k != 3) return fail("%s: kernel size must be 1 or 3", who);
+    if (Ci % 4 || Co % 4) return fail("%s: Ci and Co must be multiples of 4", who);
+    if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("%s: bad dtype", who);
+    if (B <= 0 || K <= 0 || K > 8 || hidden <= 0) return fail("%s: need a non-empty batch, 1..8 experts and a hidden width", who);
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
+    const int taps = k * k * k;
+    const size_t wn = (size_t)Co * Ci * taps;
+    const size_t need = dynamic_conv_scratch(B, Ci, Co, nhw, taps, K, dtype);
+    char* base = (char*)workspace;
+    bool own = false;
+    if (!base) {
+        keep_pool_warm();
+        CK(cudaMallocAsync((void**)&base, need, s));
+        own = true;
+    } else if (workspace_bytes < (int64_t)need || (reinterpret_cast<uintptr_t>(base) & 255)) {
+        return fail("%s: workspace of %lld bytes (256-byte aligned) needed, got %lld", who, (long long)need, (long long)workspace_bytes);
+    }
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char* p = base + off; off += align256(bytes); return p; };
+    float* pooled = (float*)take((size_t)B * Ci * 4);
+    float* alpha = (float*)take((size_t)B * K * 4);
+    void* wmix = take((size_t)B * wn * es);
+    float* ab = (float*)take((size_t)B * Co * 4);
+    void* xin = take((size_t)B * nhw * Ci * es);
+    void* yout = take((size_t)B * nhw * Co * es);
+    int rc = 0;
+    auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && !rc) rc = fail("%s: %s -> %s", who, what, cudaGetErrorString(e)); };
+    ck(spatial_mean(x, pooled, (size_t)B * Ci, nhw, s), "spatial_mean");
+    ck(dynconv_head(pooled, fc1, fc2, fc2_bias, alpha, B, Ci, hidden, K, temperature, s), "attention head");       // attention1d / 2d carry a bias on fc2 (:18, :108)
+    ck(dynconv_mix(alpha, weight, bias, dtype == TMD_F32 ? (float*)wmix : nullptr, dtype == TMD_BF16 ? (__nv_bfloat16*)wmix : nullptr, ab, B, K, Co, Ci,
+                   k, ndim, s), "expert mix");
+    ck(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s), "layout in");
+    ConvOp op{};
+    op.B = B; op.N = N; op.H = H; op.W = W; op.Ci = Ci; op.ld_in = Ci; op.Co = Co; op.taps = taps;
+    op.src = xin;
+    op.w_f32 = (const float*)wmix; op.w_bf16 = (const __nv_bfloat16*)wmix;
+    op.w_sample_stride = (long long)wn;
+    op.epi.mode = CONV_NORMAL;
+    op.epi.bias = bias ? ab : nullptr; op.epi.ld_bias = bias ? Co : 0;
+    op.epi.raw_out = yout; op.epi.ld_raw = Co;
+    if (!rc) {
+        if (dtype == TMD_F32) ck(conv_simt_f32(op, s), "conv (fp32)");
+        else if (conv_umma_supported(op)) {
+            UmmaPlan* plan = conv_umma_plan_create(op);
+            if (!plan) rc = fail("%s: tensor map creation failed", who);
+            else {
+                ck(conv_umma_bf16(op, plan, s), "conv (tcgen05)");
+                conv_umma_plan_destroy(plan);
+            }
+        } else ck(conv_simt_bf16(op, s), "conv (bf16 SIMT)");
+    }
+    if (!rc) ck(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s), "layout out");
+    if (own) cudaFreeAsync(base, s);
+    return rc;
+}
 
 extern "C" int tmd_dynamic_conv3d(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2, float* y,
                                   int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t K,
                                   int32_t hidden, float temperature, int32_t dtype, void* stream) {
     return dynamic_conv_impl("tmd_dynamic_conv3d", x, weight, bias, fc1, fc2, nullptr, y, B, Ci, Co, N, H, W, k, 3, K, hidden, temperature, dtype,
-                             stream);
+                             nullptr, 0, stream);
 }
 
 extern "C" int tmd_dynamic_conv(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
@@ -1349,79 +1412,18 @@ extern "C" int tmd_dynamic_conv(const float* x, const float* weight, const float
     if (ndim < 1 || ndim > 3) return fail("tmd_dynamic_conv: ndim must be 1, 2 or 3");
     if ((ndim < 3 && N != 1) || (ndim < 2 && H != 1)) return fail("tmd_dynamic_conv: unused leading extents must be 1");
     return dynamic_conv_impl("tmd_dynamic_conv", x, weight, bias, fc1, fc2, fc2_bias, y, B, Ci, Co, N, H, W, k, ndim, K, hidden, temperature, dtype,
-                             stream);
+                             nullptr, 0, stream);
 }
 
-static int dynamic_conv_impl(const char* who, const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
-                             const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
-                             int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* stream) {
-    (void)who;
-    if (!x || !weight || !fc1 || !fc2 || !y) return fail("tmd_dynamic_conv3d: null argument");
-    if (k != 1 && k != 3) return fail("tmd_dynamic_conv3d: kernel size must be 1 or 3");
-    if (Ci % 4 || Co % 4) return fail("tmd_dynamic_conv3d: Ci and Co must be multiples of 4");
-    if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_dynamic_conv3d: bad dtype");
-    if (B <= 0 || K <= 0 || hidden <= 0) return fail("tmd_dynamic_conv3d: empty problem");
-    cudaStream_t s = (cudaStream_t)stream;
-    keep_pool_warm();
-    const size_t nhw = (size_t)N * H * W, es = dtype == TMD_F32 ? 4 : 2;
-    const int taps = k * k * k;
-    const size_t wn = (size_t)Co * Ci * taps;
-    float *pooled = nullptr, *hid = nullptr, *alpha = nullptr, *aw = nullptr, *ab = nullptr, *pf = nullptr, *wemb = nullptr;
-    __nv_bfloat16* pb = nullptr;
-    void *xin = nullptr, *yout = nullptr;
-    CK(cudaMallocAsync((void**)&pooled, (size_t)B * Ci * 4, s));
-    CK(cudaMallocAsync((void**)&hid, (size_t)B * hidden * 4, s));
-    CK(cudaMallocAsync((void**)&alpha, (size_t)B * K * 4, s));
-    CK(cudaMallocAsync((void**)&aw, (size_t)B * wn * 4, s));
-    CK(cudaMallocAsync((void**)&ab, (size_t)B * Co * 4, s));
-    CK(cudaMallocAsync((void**)&pf, wn * 4, s));
-    CK(cudaMallocAsync((void**)&pb, wn * 2, s));
-    CK(cudaMallocAsync(&xin, (size_t)B * nhw * Ci * es, s));
-    CK(cudaMallocAsync(&yout, (size_t)B * nhw * Co * es, s));
-    // attention3d (:194-218): avgpool -> fc1 -> relu -> fc2 -> softmax(. / temperature)
-    CK(spatial_mean(x, pooled, (size_t)B * Ci, nhw, s));
-    CK(dense_rows(pooled, fc1, nullptr, hid, B, Ci, hidden, 2, s));
-    CK(dense_rows(hid, fc2, fc2_bias, alpha, B, hidden, K, 0, s));          // attention1d / attention2d carry a bias here (:18, :108)
-    CK(softmax_temperature(alpha, B, K, temperature, s));
-    // aggregate_weight / aggregate_bias (:251-257)
-    if (ndim < 3 && k > 1) {
-        CK(cudaMallocAsync((void**)&wemb, (size_t)K * wn * 4, s));
-        const size_t tot = (size_t)K * wn;
-        embed_taps_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(weight, wemb, (size_t)K * Co * Ci, k, ndim);
-        CK(cudaGetLastError());
-        weight = wemb;
-    }
-    CK(mix_experts(alpha, weight, aw, B, K, wn, s));
-    if (bias) CK(mix_experts(alpha, bias, ab, B, K, (size_t)Co, s));
-    CK(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s));
-    int rc = 0;
-    for (int b = 0; b < B && !rc; ++b) {       // groups = batch conv (:258-263): one shared-geometry conv per sample with its own weights
-        pack_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, s>>>(aw + (size_t)b * wn, pf, pb, Co, Ci, taps);
-        CK(cudaGetLastError());
-        ConvOp op{};
-        op.B = 1; op.N = N; op.H = H; op.W = W; op.Ci = Ci; op.ld_in = Ci; op.Co = Co; op.taps = taps;
-        op.src = (const char*)xin + (size_t)b * nhw * Ci * es;
-        op.w_f32 = pf; op.w_bf16 = pb;
-        op.epi.mode = CONV_NORMAL; op.epi.bias = bias ? ab + (size_t)b * Co : nullptr;
-        op.epi.raw_out = (char*)yout + (size_t)b * nhw * Co * es; op.epi.ld_raw = Co;
-        if (dtype == TMD_F32) {
-            CK(conv_simt_f32(op, s));
-        } else if (conv_umma_supported(op)) {
-            UmmaPlan* plan = conv_umma_plan_create(op);
-            if (!plan) rc = fail("tmd_dynamic_conv3d: tensor map creation failed");
-            else {
-                const cudaError_t err = conv_umma_bf16(op, plan, s);
-                conv_umma_plan_destroy(plan);
-                if (err != cudaSuccess) rc = fail("tmd_dynamic_conv3d: %s", cudaGetErrorString(err));
-            }
-        } else {
-            CK(conv_simt_bf16(op, s));
-        }
-    }
-    if (!rc) CK(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s));
-    for (void* p : {(void*)pooled, (void*)hid, (void*)alpha, (void*)aw, (void*)ab, (void*)pf, (void*)pb, xin, yout}) cudaFreeAsync(p, s);
-    if (wemb) cudaFreeAsync(wemb, s);
-    return rc;
+extern "C" int tmd_dynamic_conv_ws(const float* x, const float* weight, const float* bias, const float* fc1, const float* fc2,
+                                   const float* fc2_bias, float* y, int32_t B, int32_t Ci, int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k,
+                                   int32_t ndim, int32_t K, int32_t hidden, float temperature, int32_t dtype, void* workspace, int64_t workspace_bytes,
+                                   void* stream) {
+    if (ndim < 1 || ndim > 3) return fail("tmd_dynamic_conv_ws: ndim must be 1, 2 or 3");
+    if ((ndim < 3 && N != 1) || (ndim < 2 && H != 1)) return fail("tmd_dynamic_conv_ws: unused leading extents must be 1");
+    if (!workspace) return fail("tmd_dynamic_conv_ws: null workspace (size it with tmd_dynamic_conv_workspace_bytes)");
+    return dynamic_conv_impl("tmd_dynamic_conv_ws", x, weight, bias, fc1, fc2, fc2_bias, y, B, Ci, Co, N, H, W, k, ndim, K, hidden, temperature, dtype,
+                             workspace, workspace_bytes, stream);
 }
 
 extern "C" int tmd_quality_metrics(const float* ref, const float* img, float* out, int32_t B, int32_t C, int32_t H, int32_t W, float ratio,

@@ -107,6 +107,12 @@ cudaError_t quality_metrics(const float* ref, const float* img, float* out, int 
 cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s);                       // out[r] = mean(x[r, :])
 cudaError_t softmax_temperature(float* x, int rows, int K, float temperature, cudaStream_t s);                      // in place over K
 cudaError_t mix_experts(const float* alpha, const float* w, float* out, int B, int K, size_t n, cudaStream_t s);    // out[b,:] = sum_k alpha[b,k] w[k,:]
+// the attention head in one launch (fc1 -> ReLU -> fc2 (+bias) -> softmax(. / temperature)), K <= 8
+cudaError_t dynconv_head(const float* pooled, const float* fc1, const float* fc2, const float* fc2_bias, float* alpha, int B, int Ci, int hidden, int K,
+                         float temperature, cudaStream_t s);
+// per-sample expert mix written in the conv kernels' weight layouts (pf fp32 [B][taps][Ci][Co] and / or pb bf16 [B][Co][taps*Ci]) + mixed bias
+cudaError_t dynconv_mix(const float* alpha, const float* w, const float* bias, float* pf, __nv_bfloat16* pb, float* ab, int B, int K, int Co, int Ci,
+                        int k, int ndim, cudaStream_t s);
 
 
 // ---- scene.cu: full-scene front / back end (sensor DN <-> sampler tiles) ----

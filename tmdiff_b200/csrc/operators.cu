@@ -454,6 +454,83 @@ cudaError_t quality_metrics(const float* ref, const float* img, float* out, int 
     return e;
 }
 
+// Dynamic_conv attention head (core/dynamic_conv.py:6-43, 106-138, 194-218) for one sample per block: pooled[Ci] -> fc1 -> ReLU ->
+// fc2 (+bias) -> softmax(. / temperature) -> alpha[K].  hidden and K are tiny: one warp per hidden unit, one thread per expert.
+__global__ void __launch_bounds__(128) dynconv_head_kernel(const float* __restrict__ pooled, const float* __restrict__ fc1, const float* __restrict__ fc2,
+                                                            const float* __restrict__ fc2_bias, float* __restrict__ alpha, int Ci, int hidden, int K,
+                                                            float temperature) {
+    extern __shared__ float sh[];            // hidden activations, then K logits
+    const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float* p = pooled + (size_t)b * Ci;
+    for (int j = warp; j < hidden; j += 4) {
+        float a = 0.f;
+        for (int c = lane; c < Ci; c += 32) a = fmaf(fc1[(size_t)j * Ci + c], p[c], a);
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) sh[j] = fmaxf(a, 0.f);
+    }
+    __syncthreads();
+    if (threadIdx.x < K) {
+        float a = fc2_bias ? fc2_bias[threadIdx.x] : 0.f;
+        for (int j = 0; j < hidden; ++j) a = fmaf(fc2[(size_t)threadIdx.x * hidden + j], sh[j], a);
+        sh[hidden + threadIdx.x] = a / temperature;
+    }
+    __syncthreads();
+    if (threadIdx.x < K) {
+        float mx = -INFINITY, sum = 0.f;
+        for (int k = 0; k < K; ++k) mx = fmaxf(mx, sh[hidden + k]);
+        for (int k = 0; k < K; ++k) sum += expf(sh[hidden + k] - mx);
+        alpha[(size_t)b * K + threadIdx.x] = expf(sh[hidden + threadIdx.x] - mx) / sum;
+    }
+}
+
+// aggregate_weight / aggregate_bias (:251-257) written straight into the layouts the conv kernels read: per sample
+// pf [taps][Ci][Co] fp32 (CUDA-core kernel) or pb [Co][taps*Ci] bf16 (K-major B operand of the tcgen05 kernel).  The experts come
+// as [K][Co][Ci][kt] with kt = k^ndim taps that sit in the centre of the k^3 stencil (1-D / 2-D layers), zero elsewhere.
+__global__ void __launch_bounds__(256) dynconv_mix_kernel(const float* __restrict__ alpha, const float* __restrict__ w, const float* __restrict__ bias,
+                                                           float* __restrict__ pf, __nv_bfloat16* __restrict__ pb, float* __restrict__ ab, int K,
+                                                           int Co, int Ci, int k, int ndim) {
+    const int taps = k * k * k, kt = ndim == 3 ? taps : (ndim == 2 ? k * k : k);
+    const size_t wn = (size_t)Co * Ci * taps, wsrc = (size_t)Co * Ci * kt;
+    const int b = blockIdx.y;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    float a[8];
+    for (int q = 0; q < K && q < 8; ++q) a[q] = alpha[(size_t)b * K + q];
+    if (i < wn) {
+        const int t = (int)(i % taps);
+        const int ci = (int)((i / taps) % Ci);
+        const int co = (int)(i / ((size_t)taps * Ci));
+        const int dz = t / (k * k), dy = (t / k) % k, dx = t % k, c = k / 2;
+        int ts = -1;                                          // tap index in the expert's own stencil
+        if (ndim == 3) ts = t;
+        else if (ndim == 2) { if (dz == c) ts = dy * k + dx; }
+        else if (dz == c && dy == c) ts = dx;
+        float v = 0.f;
+        if (ts >= 0)
+            for (int q = 0; q < K; ++q) v = fmaf(a[q < 8 ? q : 7], w[(size_t)q * wsrc + ((size_t)co * Ci + ci) * kt + ts], v);
+        if (pf) pf[(size_t)b * wn + ((size_t)t * Ci + ci) * Co + co] = v;
+        if (pb) pb[(size_t)b * wn + (size_t)co * taps * Ci + (size_t)t * Ci + ci] = __float2bfloat16(v);
+    }
+    if (bias && ab && i < (size_t)Co) {
+        float v = 0.f;
+        for (int q = 0; q < K; ++q) v = fmaf(a[q < 8 ? q : 7], bias[(size_t)q * Co + i], v);
+        ab[(size_t)b * Co + i] = v;
+    }
+}
+
+cudaError_t dynconv_head(const float* pooled, const float* fc1, const float* fc2, const float* fc2_bias, float* alpha, int B, int Ci, int hidden, int K,
+                         float temperature, cudaStream_t s) {
+    if (K > 8 || K > 128) return cudaErrorInvalidValue;
+    dynconv_head_kernel<<<B, 128, (hidden + K) * sizeof(float), s>>>(pooled, fc1, fc2, fc2_bias, alpha, Ci, hidden, K, temperature);
+    return cudaGetLastError();
+}
+cudaError_t dynconv_mix(const float* alpha, const float* w, const float* bias, float* pf, __nv_bfloat16* pb, float* ab, int B, int K, int Co, int Ci,
+                        int k, int ndim, cudaStream_t s) {
+    const size_t wn = (size_t)Co * Ci * k * k * k;
+    const dim3 grid((unsigned)((wn + 255) / 256), (unsigned)B);
+    dynconv_mix_kernel<<<grid, 256, 0, s>>>(alpha, w, bias, pf, pb, ab, K, Co, Ci, k, ndim);
+    return cudaGetLastError();
+}
+
 cudaError_t spatial_mean(const float* x, float* out, size_t rows, size_t S, cudaStream_t s) {
     spatial_mean_kernel<<<(unsigned)rows, 256, 0, s>>>(x, out, S);
     return cudaGetLastError();

@@ -198,6 +198,19 @@ class _Attention3d(nn.Module):
         self.temperature = temperature
 
 
+def _dynconv_workspace(module, device, B, Ci, Co, N, H, W, k, K, code):
+    """The layer's scratch block (tmd_dynamic_conv_workspace_bytes), kept on the module and grown on demand: no allocation
+    inside the call."""
+    need = int(_lib.load().tmd_dynamic_conv_workspace_bytes(B, Ci, Co, N, H, W, k, K, code))
+    if need < 0:
+        raise ValueError("Dynamic_conv: unsupported problem")
+    ws = getattr(module, "_workspace", None)
+    if ws is None or ws.numel() < need or ws.device != device:
+        ws = torch.empty(need, dtype=torch.uint8, device=device)
+        object.__setattr__(module, "_workspace", ws)      # scratch, not a buffer of the state dict
+    return ws
+
+
 class Dynamic_conv3d(nn.Module):
     def __init__(self, in_planes, out_planes, kernel_size, ratio=0.25, stride=1, padding=0, dilation=1, groups=1, bias=True, K=4,
                  temperature=34, dtype="fp32"):
@@ -221,11 +234,12 @@ class Dynamic_conv3d(nn.Module):
         b = None if self.bias is None else _cuda_f32(self.bias, "bias")
         f1 = _cuda_f32(self.attention.fc1.weight, "fc1").reshape(hidden, Ci)
         f2 = _cuda_f32(self.attention.fc2.weight, "fc2").reshape(self.K, hidden)
+        code = _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16
+        ws = _dynconv_workspace(self, x.device, B, Ci, self.out_planes, N, H, W, self.kernel_size, self.K, code)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.load().tmd_dynamic_conv3d(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), _lib.ptr(y),
-                                                      B, Ci, self.out_planes, N, H, W, self.kernel_size, self.K, hidden,
-                                                      float(self.attention.temperature), _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16,
-                                                      _lib.stream_ptr()))
+            _lib.check(_lib.load().tmd_dynamic_conv_ws(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), None, _lib.ptr(y),
+                                                       B, Ci, self.out_planes, N, H, W, self.kernel_size, 3, self.K, hidden,
+                                                       float(self.attention.temperature), code, _lib.ptr(ws), ws.numel(), _lib.stream_ptr()))
         return y
 
 
@@ -262,11 +276,12 @@ class _DynamicConvNd(nn.Module):
         f1 = _cuda_f32(self.attention.fc1.weight, "fc1").reshape(hidden, Ci)
         f2 = _cuda_f32(self.attention.fc2.weight, "fc2").reshape(self.K, hidden)
         f2b = _cuda_f32(self.attention.fc2.bias, "fc2.bias")
+        code = _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16
+        ws = _dynconv_workspace(self, x.device, B, Ci, self.out_planes, sp[0], sp[1], sp[2], self.kernel_size, self.K, code)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.load().tmd_dynamic_conv(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), _lib.ptr(f2b), _lib.ptr(y),
-                                                    B, Ci, self.out_planes, sp[0], sp[1], sp[2], self.kernel_size, self.ndim, self.K, hidden,
-                                                    float(self.attention.temperature), _lib.F32 if self.compute_dtype == "fp32" else _lib.BF16,
-                                                    _lib.stream_ptr()))
+            _lib.check(_lib.load().tmd_dynamic_conv_ws(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(f1), _lib.ptr(f2), _lib.ptr(f2b), _lib.ptr(y),
+                                                       B, Ci, self.out_planes, sp[0], sp[1], sp[2], self.kernel_size, self.ndim, self.K, hidden,
+                                                       float(self.attention.temperature), code, _lib.ptr(ws), ws.numel(), _lib.stream_ptr()))
         return y
 
 
