@@ -229,3 +229,39 @@ def test_torch_metrics_match_reference(vec2):
     assert float(M.D_lambda_torch(big, big)) < 1e-6
     q = M.q_index_matrix(big, big)
     assert float((q.diagonal(dim1=1, dim2=2) - 1).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("shape", [(5, 32, 64, 4, 16, 16, 3), (3, 64, 32, 2, 8, 8, 3), (4, 64, 128, 1, 32, 16, 1), (2, 32, 32, 8, 16, 24, 3)])
+def test_dynamic_conv3d_one_launch_tensor_path(lib_built, shape):
+    """Dynamic_conv3d (core/dynamic_conv.py:244-268: per-sample expert mix, groups=B conv) on the tcgen05 kernel with per-sample
+    weight rows -- REUSE and SIMPLE schedules, 1x1x1 and 3x3x3, with the mixed bias -- against the fp32 CUDA-core mode of the same
+    layer and a torch restatement of the reference formulation."""
+    import torch.nn.functional as F
+    from tmdiff_b200 import operators as O
+    B, Ci, Co, N, H, W, k = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    layers = {}
+    for dtype in ("fp32", "bf16"):
+        m = O.Dynamic_conv3d(Ci, Co, k, padding=k // 2, K=4, temperature=34, dtype=dtype)
+        if dtype == "fp32":
+            m.weight.data = torch.randn(m.weight.shape, generator=g) / (Ci * k ** 3) ** 0.5
+            m.bias.data = torch.randn(m.bias.shape, generator=g) * 0.3
+            m.attention.fc1.weight.data = torch.randn(m.attention.fc1.weight.shape, generator=g) * 2.0
+            m.attention.fc2.weight.data = torch.randn(m.attention.fc2.weight.shape, generator=g) * 30.0      # distinct mixes per sample
+        else:
+            m.load_state_dict(layers["fp32"].state_dict())
+        layers[dtype] = m.cuda()
+    x = torch.randn(B, Ci, N, H, W, generator=g)
+    y32, y16 = layers["fp32"](x.cuda()).cpu(), layers["bf16"](x.cuda()).cpu()
+    m = layers["fp32"].cpu()
+    pooled = x.mean(dim=(2, 3, 4))
+    hid = torch.relu(pooled @ m.attention.fc1.weight.reshape(-1, Ci).t())
+    alpha = torch.softmax((hid @ m.attention.fc2.weight.reshape(4, -1).t()) / 34.0, dim=1)
+    assert float((alpha[0] - alpha[1]).abs().max()) > 1e-3                       # the samples really get different weights
+    wmix = (alpha @ m.weight.reshape(4, -1)).reshape(B * Co, Ci, k, k, k)
+    bmix = (alpha @ m.bias).reshape(-1)
+    want = F.conv3d(x.reshape(1, B * Ci, N, H, W), wmix, bmix, padding=k // 2, groups=B).reshape(B, Co, N, H, W)
+    assert rel_l2(y32, want) < 1e-5
+    assert rel_l2(y16, want) < 2e-2
+    per = ((y16 - want).flatten(1).norm(dim=1) / want.flatten(1).norm(dim=1)).max().item()
+    assert per < 2e-2, per                                                       # every sample (a wrong weight row would show here)

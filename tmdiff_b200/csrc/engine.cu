@@ -1324,7 +1324,7 @@ size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 // conversions of the activations
 size_t dynamic_conv_scratch(int B, int Ci, int Co, size_t nhw, int taps, int K, int dtype) {
     const size_t wn = (size_t)Co * Ci * taps, es = dtype == TMD_F32 ? 4 : 2;
-    return align256((size_t)B * Ci * 4) + align256((size_t)B * K * 4) + align256((size_t)B * wn * es) + align256((size_t)B * Co * 4) +
+    return align256((size_t)B * Ci * 4) + align256((size_t)B * K * 4) + align256((size_t)B * wn * 4) + align256((size_t)B * Co * 4) +
            align256((size_t)B * nhw * Ci * es) + align256((size_t)B * nhw * Co * es);
 }
 }  // namespace
@@ -1364,7 +1364,7 @@ static int dynamic_conv_impl(const char* who, const float* x, const float* weigh
     auto take = [&](size_t bytes) { char* p = base + off; off += align256(bytes); return p; };
     float* pooled = (float*)take((size_t)B * Ci * 4);
     float* alpha = (float*)take((size_t)B * K * 4);
-    void* wmix = take((size_t)B * wn * es);
+    void* wmix = take((size_t)B * wn * 4);       // fp32 [taps][Ci][Co] for the CUDA-core kernels, bf16 [Co][taps*Ci] for the tcgen05 one
     float* ab = (float*)take((size_t)B * Co * 4);
     void* xin = take((size_t)B * nhw * Ci * es);
     void* yout = take((size_t)B * nhw * Co * es);
@@ -1372,9 +1372,6 @@ static int dynamic_conv_impl(const char* who, const float* x, const float* weigh
     auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess && !rc) rc = fail("%s: %s -> %s", who, what, cudaGetErrorString(e)); };
     ck(spatial_mean(x, pooled, (size_t)B * Ci, nhw, s), "spatial_mean");
     ck(dynconv_head(pooled, fc1, fc2, fc2_bias, alpha, B, Ci, hidden, K, temperature, s), "attention head");       // attention1d / 2d carry a bias on fc2 (:18, :108)
-    ck(dynconv_mix(alpha, weight, bias, dtype == TMD_F32 ? (float*)wmix : nullptr, dtype == TMD_BF16 ? (__nv_bfloat16*)wmix : nullptr, ab, B, K, Co, Ci,
-                   k, ndim, s), "expert mix");
-    ck(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s), "layout in");
     ConvOp op{};
     op.B = B; op.N = N; op.H = H; op.W = W; op.Ci = Ci; op.ld_in = Ci; op.Co = Co; op.taps = taps;
     op.src = xin;
@@ -1383,9 +1380,12 @@ static int dynamic_conv_impl(const char* who, const float* x, const float* weigh
     op.epi.mode = CONV_NORMAL;
     op.epi.bias = bias ? ab : nullptr; op.epi.ld_bias = bias ? Co : 0;
     op.epi.raw_out = yout; op.epi.ld_raw = Co;
+    const bool tensor = dtype == TMD_BF16 && conv_umma_supported(op);        // else a CUDA-core kernel (fp32 weights)
+    ck(dynconv_mix(alpha, weight, bias, tensor ? nullptr : (float*)wmix, tensor ? (__nv_bfloat16*)wmix : nullptr, ab, B, K, Co, Ci, k, ndim, s), "expert mix");
+    ck(ncdhw_to_cl(dtype, x, nullptr, xin, B, Ci, nhw, s), "layout in");
     if (!rc) {
         if (dtype == TMD_F32) ck(conv_simt_f32(op, s), "conv (fp32)");
-        else if (conv_umma_supported(op)) {
+        else if (tensor) {
             UmmaPlan* plan = conv_umma_plan_create(op);
             if (!plan) rc = fail("%s: tensor map creation failed", who);
             else {
