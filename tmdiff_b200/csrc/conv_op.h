@@ -65,6 +65,8 @@ struct ConvOp {
     // (Hyper_unet_general.py:247-249) and the wavelet block's `Conv_2` path (:372, with the 2x2 average commuted in
     // front of the 1x1x1 conv) ride in the K loop of the block's last 3x3x3 conv instead of being separate launches.
     const void* src2; int Ci2, ld_in2;
+    int src2_gap_at, src2_gap;     // the Ci2 channels of src2 skip `src2_gap` channels from channel `src2_gap_at` on (a slice of a
+                                   // concat buffer left out: its contribution is step-invariant and arrives through add0)
     const __nv_bfloat16* w2_bf16;  // [Co][Ci2]
     // Per-sample weights (Dynamic_conv: a groups=B convolution, core/dynamic_conv.py:244-268): sample b reads w_f32 / w_bf16 at
     // + b * w_sample_stride elements (0: one weight set for the whole batch) and bias at + b * epi.ld_bias.

@@ -45,7 +45,10 @@ namespace tmd {
 
 namespace {
 
-constexpr int kEpiPerQuarter = 3;      // epilogue warps per TMEM lane quarter
+#ifndef TMD_EPI_PER_QUARTER
+#define TMD_EPI_PER_QUARTER 3
+#endif
+constexpr int kEpiPerQuarter = TMD_EPI_PER_QUARTER;      // epilogue warps per TMEM lane quarter
 constexpr int kThreads = 128 + 128 * kEpiPerQuarter;   // 4 role warps + 16 epilogue warps
 constexpr int kMaxSA = 4, kMaxSB = 16, kMaxAcc = 4;
 constexpr int kMaxCo = 256;
@@ -55,6 +58,7 @@ struct UmmaParams {
     CUtensorMap tmA, tmB;
     CUtensorMap tmA2, tmB2;     // fused 1x1x1 second source (ConvOp::src2): nkc2 extra K chunks after the taps
     int nkc2;
+    int c2_gap_at, c2_gap;      // second source: channel coordinate of chunk kc = kc*KC (+ c2_gap from c2_gap_at on)
     uint32_t a2_piece_bytes;    // REUSE: one un-haloed band plane [TH][TW][KC] of the second source
     ConvEpilogue epi;
     int B, N, H, W, Ci, Co, taps;   // Co: output channels of ONE tile (= the layer's Co / co_split)
@@ -678,16 +682,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 for (int pl = 0; pl < NACC; ++pl) planes2 += (tc.n0 + pl) < P.N;
                 for (int kc = 0; kc < P.nkc2; ++kc) {
                     PRODUCER_WAIT(a_empty(s), ph);
+                    const int c2 = kc * KC + (kc * KC >= P.c2_gap_at ? P.c2_gap : 0);
                     if (elect_one()) {
                         uint32_t dst = a_base + s * P.a_stage_stride;
                         if (MODE) {
                             mbar_expect_tx(a_full(s), P.a2_piece_bytes * (uint32_t)planes2);
 #pragma unroll
                             for (int pl = 0; pl < NACC; ++pl, dst += P.a2_piece_bytes)
-                                if (tc.n0 + pl < P.N) tma_load_5d(dst, &P.tmA2, a_full(s), kc * KC, tc.x0, tc.y0, tc.n0 + pl, tc.b0);
+                                if (tc.n0 + pl < P.N) tma_load_5d(dst, &P.tmA2, a_full(s), c2, tc.x0, tc.y0, tc.n0 + pl, tc.b0);
                         } else {
                             mbar_expect_tx(a_full(s), P.a_stage_bytes);
-                            tma_load_5d(dst, &P.tmA2, a_full(s), kc * KC, tc.x0, tc.y0, tc.n0, tc.b0);
+                            tma_load_5d(dst, &P.tmA2, a_full(s), c2, tc.x0, tc.y0, tc.n0, tc.b0);
                         }
                     }
                     __syncwarp();
@@ -1160,6 +1165,7 @@ bool conv_umma_supported(const ConvOp& op) {
     if (e.proj_out && (e.mode != CONV_NORMAL || !e.proj_w || (reinterpret_cast<uintptr_t>(e.proj_w) & 15) || e.act_out[0])) return false;
     if (op.src2) {
         const int kc = (op.taps == 27 && op.H >= 16 && op.W >= 8) ? 32 : ((op.Ci % 64 == 0) ? 64 : 32);   // KC of the plan below
+        if (op.src2_gap && (op.src2_gap_at % kc || op.src2_gap % kc)) return false;
         if (op.Ci2 % kc || op.ld_in2 % 8 || (reinterpret_cast<uintptr_t>(op.src2) & 15) || (reinterpret_cast<uintptr_t>(op.w2_bf16) & 15)) return false;
     }
     if (op.W < 2 || op.H < 2) return false;
@@ -1268,14 +1274,18 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.b_tile_stride = ((P.mode ? 3 * P.b_taps : 1) * P.b_tile_bytes + 1023u) & ~1023u;
         // activation stages first (their TMA round trip is the long one), at least four weight stages behind them
         const int want_sb = P.mode ? (P.b_taps == 1 ? 6 : (P.b_taps == 3 ? 4 : 2)) : 4;
-        P.SA = P.mode ? env_int("TMD_UMMA_SA", 2) : 4;
+        // REUSE with a fused second source: its chunks share the activation ring with the haloed box, and with two stages every
+        // chunk waits a full TMA round trip for its slot (profiles/umma_trace_r02a.txt: the MMA warp of final.conv20.conv21 waited for
+        // loads 60 % of the time) -- three stages where shared memory allows (fewer taps per weight stage make the room)
+        const int want_sa = (P.mode && op.src2) ? 3 : 2;
+        P.SA = P.mode ? env_int("TMD_UMMA_SA", want_sa) : 4;
         while (P.SA > 2 && (size_t)P.SA * P.a_stage_stride + 4 * (size_t)P.b_tile_stride > budget) --P.SA;
         while (P.SA > 1 && (size_t)P.SA * P.a_stage_stride + 2 * (size_t)P.b_tile_stride > budget) --P.SA;
         size_t left = budget - (size_t)P.SA * P.a_stage_stride;
         P.SB = (int)(left / P.b_tile_stride);
         if (P.SB > want_sb) P.SB = want_sb;
         if (P.SB > kMaxSB) P.SB = kMaxSB;
-        if (P.b_taps == 1 || (P.SA >= 2 && P.SB >= (P.b_taps == 3 ? 3 : 2))) break;   // else: fewer taps per stage
+        if (P.b_taps == 1 || (P.SA >= want_sa && P.SB >= (P.b_taps == 3 ? 3 : 2))) break;   // else: fewer taps per stage
     }
     if (P.SB < 2 || P.SA < 1) { delete plan; return nullptr; }
     plan->smem = (size_t)P.SA * P.a_stage_stride + (size_t)P.SB * P.b_tile_stride + 1024;
@@ -1306,10 +1316,12 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
     }
     if (op.src2) {
         P.nkc2 = op.Ci2 / P.KC;
+        P.c2_gap_at = op.src2_gap ? op.src2_gap_at : (1 << 30);
+        P.c2_gap = op.src2_gap;
         cuuint32_t box2[5] = {boxA[0], boxA[1], boxA[2], boxA[3], boxA[4]};
         if (P.mode) { box2[1] = P.TW; box2[2] = P.TH; }   // no halo: the 1x1x1 conv only reads the tile's own voxels
         P.a2_piece_bytes = box2[1] * box2[2] * box2[3] * box2[4] * P.row_bytes;
-        cuuint64_t dims[5] = {(cuuint64_t)op.Ci2, (cuuint64_t)op.W, (cuuint64_t)op.H, (cuuint64_t)op.N, (cuuint64_t)op.B};
+        cuuint64_t dims[5] = {(cuuint64_t)(op.Ci2 + op.src2_gap), (cuuint64_t)op.W, (cuuint64_t)op.H, (cuuint64_t)op.N, (cuuint64_t)op.B};
         const cuuint64_t e = 2ull * op.ld_in2;
         cuuint64_t strides[4] = {e, e * op.W, e * op.W * op.H, e * op.W * op.H * op.N};
         cuuint32_t estr[5] = {1, 1, 1, 1, 1};
@@ -1355,6 +1367,7 @@ constexpr int kSpecEF[] = {
     EF_ACT0 | EF_ADD0 | EF_ADD0F16,                              // final.conv23.conv21
     EF_ACT0 | EF_ADD0 | EF_ADD0F16 | EF_PROJ,                    // ... with final.conv24 (32 -> 1) in its epilogue
     EF_ACT0 | EF_ADD0 | EF_PROJ,
+    EF_RAW | EF_ACT0 | EF_ADD0 | EF_ADD0F16,                     // up-path conv21 (+ the step-variant two thirds of res_conv; the rest arrives as add0)
     EF_RAW | EF_ACT0 | EF_ADD0,                                  // identity-skip ResBlock without the half-precision stream
     EF_ACT0 | EF_ADD0,
 };

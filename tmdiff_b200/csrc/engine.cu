@@ -374,6 +374,20 @@ extern "C" int tmd_finalize_weights(tmd_handle h) {
             if (h->upload(&h->d_proj_w, wv)) return 1;
         } else {
             if (pack_conv(h, name, w, modulated ? nullptr : b, Co, Ci, k, 1.0f)) return 1;
+            // res_conv over a concat [h | condition skip | main skip] (up*.conv20, final.conv20): the middle third of its input is
+            // step-invariant -> "#cond" (with the bias) runs once per batch, "#var" (the outer thirds) rides in conv21's K loop
+            if (k == 1 && ends_with(name, ".res_conv") && Ci % 3 == 0 && (name.rfind("up", 0) == 0 || name.rfind("final", 0) == 0)) {
+                const int c3 = Ci / 3;
+                std::vector<float> wc((size_t)Co * c3), wv((size_t)Co * 2 * c3);
+                for (int co = 0; co < Co; ++co)
+                    for (int ci = 0; ci < Ci; ++ci) {
+                        const float v = w[(size_t)co * Ci + ci];
+                        if (ci >= c3 && ci < 2 * c3) wc[(size_t)co * c3 + ci - c3] = v;
+                        else wv[(size_t)co * 2 * c3 + (ci < c3 ? ci : ci - c3)] = v;
+                    }
+                if (pack_conv(h, name + "#cond", wc.data(), b, Co, c3, 1, 1.0f)) return 1;
+                if (pack_conv(h, name + "#var", wv.data(), nullptr, Co, 2 * c3, 1, 1.0f)) return 1;
+            }
         }
     }
 
@@ -496,7 +510,7 @@ struct Planner {
     bool fuse = false;
 
     void conv(const std::string& wname, View src, int lvl, int mode, const OutSpec& out, View add0 = View{}, View add1 = View{},
-              View* hf = nullptr, const std::string& w2name = "", View src2 = View{}) {
+              View* hf = nullptr, const std::string& w2name = "", View src2 = View{}, int gap_at = 0, int gap = 0) {
         auto it = e->convs.find(wname);
         if (it == e->convs.end()) { err = "missing conv weights"; return; }
         const ConvW& cw = it->second;
@@ -506,7 +520,7 @@ struct Planner {
             auto it2 = e->convs.find(w2name);
             if (it2 == e->convs.end()) { err = "missing conv weights (fused 1x1x1)"; return; }
             cw2 = &it2->second;
-            if (cw2->taps != 1 || cw2->Co != cw.Co || cw2->Ci != src2.C || (cw.bias && cw2->bias)) { err = "fused 1x1x1 conv mismatch"; return; }
+            if (cw2->taps != 1 || cw2->Co != cw.Co || cw2->Ci + gap != src2.C || (cw.bias && cw2->bias)) { err = "fused 1x1x1 conv mismatch"; return; }
         }
         ConvOp op{};
         op.B = B; op.N = N; op.H = H >> lvl; op.W = W >> lvl;
@@ -518,6 +532,7 @@ struct Planner {
         ep.bias = cw.bias;
         if (cw2) {
             op.src2 = src2.p; op.Ci2 = cw2->Ci; op.ld_in2 = src2.ld; op.w2_bf16 = cw2->w_bf16;
+            op.src2_gap_at = gap_at; op.src2_gap = gap;
             if (cw2->bias) ep.bias = cw2->bias;
         }
         ep.pool_out = out.pool.p; ep.ld_pool = out.pool.ld;
@@ -570,13 +585,20 @@ struct Planner {
     }
 
     // ResBlockModulateBEST.forward (:237-249).  in_act = swish(x [+ dense1(embed)]) prepared by the producer.
-    void resblock(const std::string& p, View in_act, View in_raw, int Co, int lvl, const OutSpec& out) {
+    // rc (fused plans, concat inputs [h | condition skip | main skip]): res_conv of the condition slice + bias, computed once per
+    // batch by the step-invariant pass; the K chunks of the fused res_conv then skip that slice and rc arrives through add0.
+    void resblock(const std::string& p, View in_act, View in_raw, int Co, int lvl, const OutSpec& out, View rc = View{}) {
         View a2 = buf("a2@" + std::to_string(lvl), lvl, cmax(lvl));
         a2.C = Co;
         OutSpec o1;
         o1.act[0] = ActSpec{a2, nullptr, sc(p + ".dense2")};
         conv(p + ".conv20", in_act, lvl, CONV_NORMAL, o1);
         View res = in_raw;
+        if (fuse && rc.p && e->convs.count(p + ".res_conv#var")) {
+            const int third = in_raw.C / 3;
+            conv(p + ".conv21", a2, lvl, CONV_NORMAL, out, rc, View{}, nullptr, p + ".res_conv#var", in_raw, third, third);
+            return;
+        }
         if (fuse && e->convs.count(p + ".res_conv")) {
             conv(p + ".conv21", a2, lvl, CONV_NORMAL, out, View{}, View{}, nullptr, p + ".res_conv", in_raw);
             return;
@@ -737,6 +759,23 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
         }
     }
 
+    // res_conv of the condition slices of the four concat inputs (up1/up2/up3.conv20, final.conv20): step-invariant too
+    View Rc[4];
+    {
+        static const bool rc_env = !getenv("TMD_NO_RC_SPLIT");
+        const char* cons[4] = {"final.conv20", "up3.conv20", "up2.conv20", "up1.conv20"};
+        for (int l = 0; l < 4 && P.fuse && rc_env; ++l) {
+            const std::string w = std::string(cons[l]) + ".res_conv#cond";
+            if (!e->convs.count(w)) continue;
+            const int Co = e->convs[w].Co;
+            Rc[l] = P.buf("Rc@" + L(l), l, Co);
+            Rc[l].f16 = true;                       // add-only tensor
+            OutSpec ro;
+            ro.raw = Rc[l];
+            P.conv(w, P.slice(cat_raw[l], c[l], c[l]), l, CONV_NORMAL, ro);
+        }
+    }
+
     // ================================ per-step main branch ===================================
     P.ops = &e->step_ops;
     {
@@ -822,7 +861,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
             OutSpec ro;
             ro.raw = y;
             ro.act[0] = ActSpec{ay, nullptr, nullptr};
-            P.resblock(nm + ".conv20", cat_act[l], cat_raw[l], c[l - 1], l, ro);
+            P.resblock(nm + ".conv20", cat_act[l], cat_raw[l], c[l - 1], l, ro, Rc[l]);
             OutSpec wo;
             wo.raw = P.slice(cat_raw[l - 1], 0, c[l - 1]);
             wo.act[0] = ActSpec{P.slice(cat_act[l - 1], 0, c[l - 1]), P.tb(std::string(consumer[l - 1]) + ".dense1", 0), nullptr};
@@ -853,7 +892,7 @@ int build_plan(tmd_engine* e, int B, int N, int H, int W) {
                         P.ops->back().is_kernel = false;
                     }
                 }
-                P.resblock("final.conv2" + L(i), ia, ir, c[0], 0, fo);
+                P.resblock("final.conv2" + L(i), ia, ir, c[0], 0, fo, i == 0 ? Rc[0] : View{});
                 ia = af[i & 1];
                 ir = f[i & 1];
             }
