@@ -20,7 +20,9 @@ def main(path, tag):
     rd = sum(p.get("dram__bytes_read.sum", 0.0) for p in per.values())
     wr = sum(p.get("dram__bytes_write.sum", 0.0) for p in per.values())
     t = sum(p.get("gpu__time_duration.sum", 0.0) for p in per.values())
-    out = {"tag": tag, "launches": n, "dram_read_bytes_per_launch": rd / n, "dram_write_bytes_per_launch": wr / n,
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench import kernel_source_hash
+    out = {"tag": tag, "kernel_source_sha16": kernel_source_hash(), "launches": n, "dram_read_bytes_per_launch": rd / n, "dram_write_bytes_per_launch": wr / n,
            "traffic_bytes_per_launch": (rd + wr) / n, "mean_duration_us_under_ncu": 1e6 * t / n,
            "what": "all conv_umma launches of one warm denoiser evaluation (B=64, 4 bands, 64x64, bf16), ncu --clock-control none"}
     json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "conv_traffic.json"), "w"), indent=1)
