@@ -17,13 +17,16 @@
 //     bounds a 3x3x3 conv with 32..128 output channels (L2 feeds ~42 B/cycle/SM).
 //   * SIMPLE (1x1x1, small planes): one box of 128 voxels [TB][TN][TH][TW] per (tap, chunk).
 //
-// Warp roles (256 threads, persistent CTAs, one per SM):
-//   warp 0  lane 0: TMA producer for activation boxes     (ring of SA stages)
-//   warp 1  lane 0: TMA producer for weight tiles         (ring of SB tiles)
-//   warp 2  lane 0: tcgen05.mma issuer; accumulators double-buffered in TMEM
-//   warp 3        : TMEM allocation / release
-//   warps 4-7     : epilogue: tcgen05.ld -> bias / residual adds / Haar pooling or 2x upsampling /
-//                   time-bias + Swish + text-scale views -> bf16 stores (conv_op.h)
+// Warp roles (512 threads, persistent CTAs, one per SM):
+//   warp 0  : TMA producer for activation boxes     (ring of SA stages; one elected lane issues)
+//   warp 1  : TMA producer for weight tiles         (ring of SB stages)
+//   warp 2  : tcgen05.mma issuer; two accumulator sets in TMEM
+//   warp 3  : TMEM allocation / release; REUSE kernels: helper -- decodes the next tile and stages its per-sample epilogue
+//             vectors (bias, time biases, modulation scales) in shared memory one tile ahead
+//   warps 4-15 : epilogue, three warps per TMEM lane quarter: tcgen05.ld (next slab read ahead) -> bias / residual adds /
+//             Haar pooling or 2x upsampling / time-bias + Swish + text-scale views / 32->1 projection -> bf16 or half stores
+// The epilogue's shape (which views, residuals, mode) is a template word (Epi<EF>): the kernels of the sampling path carry no
+// run-time branches on it; the generic instantiation (EF = -1) serves the operator API and the TMD_UMMA_DEBUG role sweeps.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -1207,6 +1210,13 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         P.NACC = 1;
         for (int c = 2; c <= cap; c *= 2)
             if (op.N % c == 0) P.NACC = c;
+        // Small batches (BASELINE config 1 is ONE patch): with the widest tile there are fewer tiles than SMs (32 for one 8-band
+        // 64x64 patch at 8 planes per tile), and a persistent grid is only as fast as its busiest CTA: trade planes per tile for
+        // tiles until the machine is covered.
+        if (env_int("TMD_UMMA_SMALLB", 1)) {
+            const long long per_plane_group = (long long)((op.W + 7) / 8) * ((op.H + 15) / 16) * op.B * P.co_split;
+            while (P.NACC > 1 && per_plane_group * ((op.N + P.NACC - 1) / P.NACC) < sm_count()) P.NACC /= 2;
+        }
         P.pl_off = (P.NACC == op.N) ? 1 : 0;
         P.a_planes = P.NACC + 2 - 2 * P.pl_off;
         P.a_ysplit = 1;
