@@ -300,7 +300,9 @@ enum : int { EF_POOL = 1, EF_UP = 2, EF_RAW = 4, EF_ACT0 = 8, EF_ACT1 = 16, EF_A
 template <int EF> struct Epi {
     static __device__ __forceinline__ int mode(const ConvEpilogue& e) { return EF < 0 ? e.mode : (EF & 3); }
     static __device__ __forceinline__ bool raw(const ConvEpilogue& e) { return EF < 0 ? e.raw_out != nullptr : (EF & EF_RAW) != 0; }
-    static __device__ __forceinline__ bool act(const ConvEpilogue& e, int k) { return EF < 0 ? e.act_out[k] != nullptr : (EF & (EF_ACT0 << k)) != 0; }
+    static __device__ __forceinline__ bool act(const ConvEpilogue& e, int k) {      // view 0 is also computed when it is projected instead of stored
+        return EF < 0 ? (e.act_out[k] != nullptr || (k == 0 && e.proj_out != nullptr)) : (EF & (EF_ACT0 << k)) != 0;
+    }
     static __device__ __forceinline__ bool add0(const ConvEpilogue& e) { return EF < 0 ? e.add0 != nullptr : (EF & EF_ADD0) != 0; }
     static __device__ __forceinline__ bool add1(const ConvEpilogue& e) { return EF < 0 ? e.add1 != nullptr : (EF & EF_ADD1) != 0; }
     static __device__ __forceinline__ bool pool_out(const ConvEpilogue& e) { return EF < 0 ? e.pool_out != nullptr : (EF & EF_POOLOUT) != 0; }
@@ -1215,7 +1217,7 @@ UmmaPlan* conv_umma_plan_create(const ConvOp& op) {
         // tiles until the machine is covered.
         if (env_int("TMD_UMMA_SMALLB", 1)) {
             const long long per_plane_group = (long long)((op.W + 7) / 8) * ((op.H + 15) / 16) * op.B * P.co_split;
-            while (P.NACC > 1 && per_plane_group * ((op.N + P.NACC - 1) / P.NACC) < sm_count()) P.NACC /= 2;
+            while (P.NACC > 1 && 2 * per_plane_group * ((op.N + P.NACC - 1) / P.NACC) <= sm_count()) P.NACC /= 2;   // less than half the SMs busy
         }
         P.pl_off = (P.NACC == op.N) ? 1 : 0;
         P.a_planes = P.NACC + 2 - 2 * P.pl_off;
