@@ -231,6 +231,7 @@ def test_torch_metrics_match_reference(vec2):
     assert float((q.diagonal(dim1=1, dim2=2) - 1).abs().max()) < 1e-4
 
 
+@pytest.mark.gpu
 @pytest.mark.parametrize("shape", [(5, 32, 64, 4, 16, 16, 3), (3, 64, 32, 2, 8, 8, 3), (4, 64, 128, 1, 32, 16, 1), (2, 32, 32, 8, 16, 24, 3)])
 def test_dynamic_conv3d_one_launch_tensor_path(lib_built, shape):
     """Dynamic_conv3d (core/dynamic_conv.py:244-268: per-sample expert mix, groups=B conv) on the tcgen05 kernel with per-sample
