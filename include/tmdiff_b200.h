@@ -155,6 +155,16 @@ int tmd_conv3d_mod(const float* x, const float* w, const float* s, const float* 
                    int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t dtype, void* stream);
 /* DPM_Solver.dynamic_thresholding_fn (core/dpm_solver_pytorch.py:430-439) in place on x0 [B, n] */
 int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream);
+/* The same operation for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments and result
+ * as tmd_dynamic_threshold; the radix-select scratch is a file-scope `static __device__` array of the library
+ * (TMD_THRESHOLD_STATIC_MAX_BATCH samples x 10248 ints = 2 623 488 bytes, resident on every GPU that loads the library
+ * until exit), so the call makes no cudaMalloc / cudaFree / pool allocation.  B > TMD_THRESHOLD_STATIC_MAX_BATCH is
+ * rejected (return 1, tmd_last_error() says so); n is not limited.  All calls on a device share that array: calls that
+ * overlap on the GPU (two streams, two host threads) race and give wrong thresholds -- serialise them.  The stream must
+ * belong to the current device. */
+#define TMD_THRESHOLD_STATIC_MAX_BATCH 64
+int tmd_dynamic_threshold_static(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream);
 
 /* ---- operators the north star names that the reference's sampling path never executes;
  * device fp32, reference layouts ---------------------------------------------------------------- */

@@ -241,6 +241,13 @@ bool contains(const std::string& s, const std::string& sub) { return s.find(sub)
 // C ABI: lifecycle + weights
 // ---------------------------------------------------------------------------------------------
 extern "C" const char* tmd_last_error(void) { return g_err; }
+int tmd::set_last_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
 extern "C" int tmd_version(void) { return 1; }
 
 extern "C" int tmd_create(const tmd_config* cfg, tmd_handle* out) {

@@ -73,6 +73,8 @@ struct FusedUpdate {
     float c1, c2, c3;
 };
 size_t threshold_workspace_bytes(int B);
+// writes the calling thread's tmd_last_error() text and returns 1 (for C-ABI entry points defined outside engine.cu)
+int set_last_error(const char* fmt, ...);
 cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, float* dst, float alpha, float sigma, bool noise_type,
                          float g, int B, int n, int q_lo, float q_w, float max_val, void* ws, bool ws_clean, const FusedUpdate* fu, cudaStream_t s);
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s);

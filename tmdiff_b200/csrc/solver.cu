@@ -4,7 +4,11 @@
 // reference's fp32 tensor expression rounds (no FMA contraction), because x0 = (x - s*eps)/a
 // divides by alpha_t ~ 5e-5 on the first steps and amplifies any re-association.
 #include <float.h>
+#include <stdint.h>
 
+#include <mutex>
+
+#include "../../include/tmdiff_b200.h"
 #include "kernels.h"
 
 namespace tmd {
@@ -329,6 +333,73 @@ cudaError_t x0_threshold(const float* x, const float* out, const float* out_c, f
 cudaError_t dynamic_threshold_inplace(float* x0, int B, int n, int q_lo, float q_w, float max_val, void* ws, cudaStream_t s) {
     return launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_w, max_val, ws, false, ThUpdate{}, s);
 }
+
+// ------------------------------------------------------------------------------------------------
+// tmd_dynamic_threshold_static: the same four kernels with the radix-select workspace in a file-scope device array instead
+// of a stream-ordered allocation, for callers that may not allocate (graph capture, tight serving loops).  No counterpart in
+// the reference.
+//
+// The array holds the workspace of TMD_THRESHOLD_STATIC_MAX_BATCH samples (64 * 10248 ints = 2 623 488 bytes) on every GPU
+// that loads the library, until exit.  In host code `g_th_static_ws` is only the host-side stand-in of the symbol; its device
+// address is looked up once per device with cudaGetSymbolAddress (that device current) and that pointer goes to the kernels.
+// Every call shares the array and finds the previous call's contents in it: hist0 of the B samples is cleared by a kernel in
+// front (th_first clears hist1 / hist2 itself, sel is written before it is read).  Two calls that overlap on the GPU -- two
+// streams, or two host threads -- race on it; callers serialise them.
+// ------------------------------------------------------------------------------------------------
+constexpr int kThStaticMaxBatch = TMD_THRESHOLD_STATIC_MAX_BATCH;
+static __device__ __align__(256) int g_th_static_ws[(size_t)kThStaticMaxBatch * TH_WS_INTS];
+
+// device code names the array directly
+__global__ void __launch_bounds__(TH_THREADS) th_static_clear_kernel() {
+    int* h0 = g_th_static_ws + (size_t)blockIdx.x * TH_WS_INTS;
+    for (int i = threadIdx.x; i < TH_BINS; i += TH_THREADS) h0[i] = 0;
+}
+
+// Device address of g_th_static_ws on the current device (looked up once per device).
+static cudaError_t th_static_ws_address(int** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static int* addr[kMaxDevices] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_th_static_ws);
+        if (e != cudaSuccess) return e;
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) return cudaErrorInvalidSymbol;
+        addr[dev] = static_cast<int*>(p);
+    }
+    *out = addr[dev];
+    return cudaSuccess;
+}
+
+}  // namespace tmd
+
+extern "C" int tmd_dynamic_threshold_static(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream) {
+    using namespace tmd;
+    if (!x0) return set_last_error("tmd_dynamic_threshold_static: null argument");
+    if (B <= 0 || n <= 0 || q_lo < 0 || q_lo >= n) return set_last_error("tmd_dynamic_threshold_static: bad sizes");
+    if (B > kThStaticMaxBatch)
+        return set_last_error("tmd_dynamic_threshold_static: B = %d exceeds the static workspace (TMD_THRESHOLD_STATIC_MAX_BATCH = %d samples); "
+                              "split the batch or use tmd_dynamic_threshold",
+                              (int)B, kThStaticMaxBatch);
+    cudaStream_t s = (cudaStream_t)stream;
+    int* ws = nullptr;
+    cudaError_t e = th_static_ws_address(&ws);
+    if (e != cudaSuccess) return set_last_error("tmd_dynamic_threshold_static: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
+    th_static_clear_kernel<<<(unsigned)B, TH_THREADS, 0, s>>>();
+    e = cudaGetLastError();
+    if (e == cudaSuccess)
+        e = launch_threshold(false, nullptr, nullptr, nullptr, x0, 1.f, 1.f, false, 0.f, B, n, q_lo, q_weight, max_val, ws, /*ws_clean=*/true,
+                             ThUpdate{}, s);
+    if (e != cudaSuccess) return set_last_error("tmd_dynamic_threshold_static: %s", cudaGetErrorString(e));
+    return 0;
+}
+
+namespace tmd {
 
 // dst = (c1*x - c2*m) [+ c3*(m1 - m)], 128-bit vectorised; dst may alias x.
 __global__ void solver_update_kernel(float* dst, const float* x, const float* m, const float* m1, float c1, float c2, float c3, size_t n4) {
