@@ -74,6 +74,22 @@ def main():
         e = torch.randn_like(a)
         row("ancestral step (Philox in kernel)", tuple(a.shape), timed(lambda: ops.ancestral_update(a, e, None, 1.1, 0.4, 0.3, 0.7, 0.5, True, 1, 2)),
             3 * a.numel() * 4)
+    # Dynamic_conv3d (core/dynamic_conv.py:244-268): expert attention (pool + 2 FCs + softmax), expert mix, ONE grouped conv launch
+    for (B, Ci, Co, N, HW, dt) in ((64, 32, 32, 4, 64, "bf16"), (64, 64, 64, 4, 32, "bf16"), (64, 128, 128, 4, 16, "bf16"), (16, 32, 32, 4, 64, "bf16"),
+                                   (64, 32, 32, 4, 32, "fp32")):
+        m = operators.Dynamic_conv3d(Ci, Co, 3, padding=1, K=4, dtype=dt).cuda()
+        x = torch.randn(B, Ci, N, HW, HW, device="cuda")
+        row("Dynamic_conv3d k=3 K=4 %s (head + mix + one conv launch)" % dt, tuple(x.shape), timed(lambda: m(x), 3),
+            nbytes=2 * x.numel() * 4, flops=2.0 * 27 * Ci * Co * B * N * HW * HW)
+    # scene front / back end (data/LRHR_dataset.py:55-139): DN scaling + bilinear x4 + tiling, and the way back
+    from tmdiff_b200 import tiling
+    pan, lrms = torch.rand(1, 2048, 2048, device="cuda") * 2047, torch.rand(8, 512, 512, device="cuda") * 2047
+    row("scene_to_tiles 2048^2, 8 bands -> 1024 tiles", (8, 2048, 2048), timed(lambda: tiling.scene_to_tiles(pan, lrms, 64, 0, 1024, 2047.0)),
+        nbytes=(pan.numel() + lrms.numel() + 9 * 2048 * 2048) * 4)
+    tiles = torch.rand(1024, 8, 64, 64, device="cuda")
+    scene = torch.empty(8, 2048, 2048, device="cuda")
+    row("tiles_to_scene 1024 tiles -> 2048^2, 8 bands", (1024, 8, 64, 64), timed(lambda: tiling.tiles_to_scene(tiles, scene, 0, 2047.0, True)),
+        nbytes=2 * tiles.numel() * 4)
     for (BH, Lq, Lk, D) in ((64, 64, 64, 1024), (16, 256, 256, 512), (8, 1024, 1024, 256), (2, 4096, 4096, 128), (128, 1024, 77, 64),
                             (512, 256, 77, 64)):
         q, k, v = (torch.randn(BH, L, D, device="cuda") for L in (Lq, Lk, Lk))
