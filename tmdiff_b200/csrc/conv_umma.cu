@@ -948,6 +948,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     ti.hvox_base = (bn0 * (P.H / 2) + tc.y0 / 2) * (P.W / 2) + tc.x0 / 2;
                     tinfo[buf] = ti;
                 }
+                // (Requesting the tile's residual rows into L2 from here, one tile ahead, was measured: 870 -> 842 patches/s,
+                // profiles/ab_r02l_l2pf.txt -- the rows are L2 hits already; what the epilogue waits for is its own request queue.)
             };
             uint32_t lt = 0;
             prepare(blockIdx.x, 0);
@@ -1024,6 +1026,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
             const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * NACC) * P.Co;
             Resid cur, nxt;
             uint32_t ra[16], rb[16];
+            // (Requesting the residual rows of three work items together instead of one item ahead was measured: the first row
+            // still takes ~3500 cycles to arrive and the tile takes as long as before, profiles/umma_timeline_r02l.txt -- the rows
+            // queue behind the stores of the twelve epilogue warps in the L1 request path, which handles one 128-byte line of a
+            // warp's access per ~2 cycles, profiles/store_patterns_r02.txt.)
             if (pl < NACC) {
                 if (MODE) tc_ld16_issue(t_lane + (uint32_t)(NACC - 1 - pl) * P.Co + sl * 16, ra);
                 if (normal) load_resid<EF>(P.epi, vox0 + (size_t)pl * plane_vox, hvox0 + (size_t)pl * hplane_vox, cb + sl * 16, in_tile && n0 + pl < P.N, cur);
@@ -1481,7 +1487,9 @@ cudaError_t conv_umma_bf16(const ConvOp& op, const UmmaPlan* plan, cudaStream_t 
         cudaMemcpy(t, p.trace, sizeof(t), cudaMemcpyDeviceToHost);
         cudaFree(p.trace);
         const long long mmas = t[6] * (p.mode ? 27 : p.taps) * p.nkc * p.NACC * (p.KC / 16);
-        fprintf(stderr, "[umma trace] Ci=%d Co=%d %dx%dx%d mode=%d NACC=%d tiles=%d grid=%d | mma warp: total %lld cyc, wait acc %lld, wait A %lld, "
+        fprintf(stderr, "[umma trace] epi=%d%s%s%s%s%s ", p.epi.mode, p.epi.raw_out ? "+raw" : "", p.epi.act_out[0] ? "+act0" : "", p.epi.act_out[1] ? "+act1" : "",
+                p.epi.add0 ? "+add0" : "", p.epi.add1 ? "+add1" : "");
+        fprintf(stderr, "Ci=%d Co=%d %dx%dx%d mode=%d NACC=%d tiles=%d grid=%d | mma warp: total %lld cyc, wait acc %lld, wait A %lld, "
                 "wait B %lld, issue %lld (%.1f cyc/mma), tiles %lld | epilogue: total %lld, wait full %lld, tmem ld %lld, compute+store %lld\n",
                 p.Ci, p.Co, p.N, p.H, p.W, p.mode, p.NACC, p.num_tiles, plan->grid, t[0], t[1], t[2], t[3], t[4],
                 mmas ? (double)t[4] / mmas : 0.0, t[6], t[8], t[9], t[10], t[11]);

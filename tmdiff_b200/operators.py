@@ -70,7 +70,9 @@ def attention_bf16(q, k, v, scale, v_channel_major=False):
     pitch = (Lk + 7) // 8 * 8
     if pitch != Lk:
         vt = torch.nn.functional.pad(vt, (0, pitch - Lk))
-    qb, kb, vb = (t.to(torch.bfloat16).contiguous() for t in (q, k, vt))
+    # one pass per operand: a strided (transposed / sliced) fp32 view is cast and laid out by the same copy
+    qb, kb, vb = (t if t.dtype == torch.bfloat16 and t.is_contiguous() else torch.empty(t.shape, dtype=torch.bfloat16, device=t.device).copy_(t)
+                  for t in (q, k, vt))
     out = torch.empty(BH, Lq, D, device=q.device, dtype=torch.float32)
     with torch.cuda.device(q.device):
         _lib.check(_lib.load().tmd_attention_bf16(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), BH, Lq, Lk, D, pitch,
@@ -93,6 +95,18 @@ def _linear_tokens(x, weight, bias, dtype):
     B, L, Cin = x.shape
     y = _conv1x1(x.reshape(1, B * L, Cin).transpose(1, 2).contiguous(), weight, bias, dtype)
     return y.reshape(weight.shape[0], B * L).t().reshape(B, L, weight.shape[0])
+
+
+def _stacked(module, name, weights, biases, transpose=False):
+    """[w0; w1; ...] and [b0; b1; ...] of projections that read the same input, so that they run as one launch; rebuilt when a
+    parameter changes (its `_version` / storage), kept on the module as plain attributes (not part of the state dict)."""
+    key = tuple((w.data_ptr(), w._version) for w in weights) + tuple((b.data_ptr(), b._version) for b in biases)
+    hit = getattr(module, name, None)
+    if hit is None or hit[0] != key:
+        w = torch.cat([(x.t() if transpose else x).detach().float() for x in weights], 0).contiguous()
+        hit = (key, w, torch.cat([x.detach().float() for x in biases], 0).contiguous() if biases else None)
+        object.__setattr__(module, name, hit)
+    return hit[1], hit[2]
 
 
 class AdaptiveGroupNorm(nn.Module):
@@ -134,9 +148,12 @@ class AttnBlockpp(nn.Module):
         B, Cf, N, H, W = x.shape
         x2 = x.reshape(B, Cf * N, H, W)
         h = group_norm(x2, self.GroupNorm_0.num_groups, self.GroupNorm_0.weight, self.GroupNorm_0.bias, eps=1e-6)
-        q, k, v = (_conv1x1(h, n.W.t().contiguous(), n.b, self.compute_dtype) for n in (self.NIN_0, self.NIN_1, self.NIN_2))
-        tok = lambda t: t.reshape(B, Cf * N, H * W).transpose(1, 2).contiguous()
-        o = attention(tok(q), tok(k), v.reshape(B, Cf * N, H * W), int(Cf) ** (-0.5), self.compute_dtype, v_channel_major=True)
+        Cc = Cf * N
+        w, b = _stacked(self, "_qkv", [n.W for n in (self.NIN_0, self.NIN_1, self.NIN_2)], [n.b for n in (self.NIN_0, self.NIN_1, self.NIN_2)],
+                        transpose=True)
+        qkv = _conv1x1(h, w, b, self.compute_dtype).reshape(B, 3, Cc, H * W)          # one projection launch for q, k and v
+        tok = lambda t: t.transpose(1, 2)                                              # token-major view; the bf16 path lays it out while casting
+        o = attention(tok(qkv[:, 0]), tok(qkv[:, 1]), qkv[:, 2], int(Cf) ** (-0.5), self.compute_dtype, v_channel_major=True)
         o = o.transpose(1, 2).reshape(B, Cf * N, H, W)
         o = _conv1x1(o, self.NIN_3.W.t().contiguous(), self.NIN_3.b, self.compute_dtype)
         out = (x2 + o).reshape(B, Cf, N, H, W)
@@ -154,9 +171,10 @@ class SpatialSelfAttention(nn.Module):
     def forward(self, x):
         B, Cc, H, W = x.shape
         h = group_norm(x, 32, self.norm.weight, self.norm.bias, eps=1e-6)
-        q, k, v = (_conv1x1(h, m.weight.reshape(Cc, Cc), m.bias, self.compute_dtype) for m in (self.q, self.k, self.v))
-        tok = lambda t: t.reshape(B, Cc, H * W).transpose(1, 2).contiguous()
-        o = attention(tok(q), tok(k), v.reshape(B, Cc, H * W), int(Cc) ** (-0.5), self.compute_dtype, v_channel_major=True)
+        w, b = _stacked(self, "_qkv", [m.weight.reshape(Cc, Cc) for m in (self.q, self.k, self.v)], [m.bias for m in (self.q, self.k, self.v)])
+        qkv = _conv1x1(h, w, b, self.compute_dtype).reshape(B, 3, Cc, H * W)          # one projection launch for q, k and v
+        tok = lambda t: t.transpose(1, 2)
+        o = attention(tok(qkv[:, 0]), tok(qkv[:, 1]), qkv[:, 2], int(Cc) ** (-0.5), self.compute_dtype, v_channel_major=True)
         o = o.transpose(1, 2).reshape(B, Cc, H, W)
         return x + _conv1x1(o, self.proj_out.weight.reshape(Cc, Cc), self.proj_out.bias, self.compute_dtype)
 
@@ -180,9 +198,16 @@ class CrossAttention(nn.Module):
         B, L, _ = x.shape
         h = self.heads
         q = _linear_tokens(x.float(), self.to_q.weight, None, self.compute_dtype)
-        k = _linear_tokens(context.float(), self.to_k.weight, None, self.compute_dtype)
-        v = _linear_tokens(context.float(), self.to_v.weight, None, self.compute_dtype)
-        split = lambda t: t.reshape(B, t.shape[1], h, -1).permute(0, 2, 1, 3).reshape(B * h, t.shape[1], -1).contiguous()
+        w_kv, _ = _stacked(self, "_kv", [self.to_k.weight, self.to_v.weight], [])
+        kv = _linear_tokens(context.float(), w_kv, None, self.compute_dtype)          # one projection launch for k and v
+        k, v = kv[..., :kv.shape[-1] // 2], kv[..., kv.shape[-1] // 2:]
+        cast = torch.bfloat16 if self.compute_dtype == "bf16" and (q.shape[-1] // h) % 64 == 0 else torch.float32
+
+        def split(t):       # [B, L, h*d] -> [B*h, L, d], laid out (and cast for the tensor-core kernel) by one copy
+            Lt = t.shape[1]
+            o = torch.empty(B, h, Lt, t.shape[-1] // h, dtype=cast, device=t.device)
+            o.copy_(t.reshape(B, Lt, h, -1).permute(0, 2, 1, 3))
+            return o.view(B * h, Lt, -1)
         o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)   # logits always in fp32 (:194-197)
         o = o.reshape(B, h, L, -1).permute(0, 2, 1, 3).reshape(B, L, -1)
         return _linear_tokens(o, self.to_out[0].weight, self.to_out[0].bias, self.compute_dtype)
