@@ -153,6 +153,14 @@ int tmd_idwt2d(const float* ll, const float* lh, const float* hl, const float* h
  * all device fp32 in the reference (channels-first) layout.  dtype selects the SIMT-fp32 or tcgen05-bf16 kernel. */
 int tmd_conv3d_mod(const float* x, const float* w, const float* s, const float* bias, float* y, int32_t B, int32_t Ci,
                    int32_t Co, int32_t N, int32_t H, int32_t W, int32_t k, int32_t dtype, void* stream);
+/* nn.Linear / a 1x1 convolution over TOKEN-MAJOR activations -- the to_q / to_k / to_v / to_out projections of CrossAttention
+ * (core/Attention.py:176-183, 213), the q / k / v / proj_out convolutions of SpatialSelfAttention (:131-134) and the NIN layers
+ * of AttnBlockpp (Hyper_unet_general.py:488-491) once their input is laid out [tokens, channels]:
+ * y[m, :] = W x[m, :] + bias, x [M, Ci], W [Co, Ci] fp32, bias [Co] fp32 or NULL, y [M, Co].  dtype TMD_BF16: tcgen05 kernel,
+ * x / y are bf16 when x_bf16 / y_bf16 are set (no layout or cast pass at all), else fp32 and cast on the way; Co of any width
+ * (channel groups of 256 per launch).  dtype TMD_F32: CUDA-core kernel on fp32 operands. */
+int tmd_linear(const void* x, const float* w, const float* bias, void* y, int64_t M, int32_t Ci, int32_t Co, int32_t x_bf16,
+               int32_t y_bf16, int32_t dtype, void* stream);
 /* DPM_Solver.dynamic_thresholding_fn (core/dpm_solver_pytorch.py:430-439) in place on x0 [B, n] */
 int tmd_dynamic_threshold(float* x0, int32_t B, int32_t n, int32_t q_lo, float q_weight, float max_val, void* stream);
 /* The same operation for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid

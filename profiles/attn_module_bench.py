@@ -94,6 +94,13 @@ def main():
             t_ref = time_ms(lambda: torch_cross_attention(m, x, ctx))
         out.append("| CrossAttention 8x64, 77 keys | B=%d L=%d dim=%d | %.3f | %.3f | %.3f | %.1f | %.2f | %.2f |" % (
             B, L, qd, t_mod, t_core, t_ref, flops / t_mod / 1e9, flops / t_mod / 1e9 / PEAK, t_ref / t_mod))
+    out += ["", "Projection alone (`tmd_linear`, bf16 in / bf16 out, weight pack included):", "",
+            "| tokens | Ci | Co | ms | TFLOP/s | GB/s (x + y) |", "|---:|---:|---:|---:|---:|---:|"]
+    for (M, Ci, Co) in ((262144, 256, 256), (262144, 320, 512), (65536, 512, 512), (16384, 1024, 1024), (262144, 512, 320)):
+        x = torch.randn(M, Ci, device="cuda").bfloat16()
+        w = torch.randn(Co, Ci, device="cuda") / Ci ** 0.5
+        t = time_ms(lambda: operators._linear_tokens(x, w, None, "bf16", out_bf16=True))
+        out.append("| %d | %d | %d | %.3f | %.1f | %.0f |" % (M, Ci, Co, t, 2.0 * M * Ci * Co / t / 1e9, (M * Ci + M * Co) * 2 / t / 1e6))
     text = "\n".join(out) + "\n"
     print(text)
     if len(sys.argv) > 1:

@@ -266,3 +266,25 @@ def test_dynamic_conv3d_one_launch_tensor_path(lib_built, shape):
     assert rel_l2(y16, want) < 2e-2
     per = ((y16 - want).flatten(1).norm(dim=1) / want.flatten(1).norm(dim=1)).max().item()
     assert per < 2e-2, per                                                       # every sample (a wrong weight row would show here)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,Ci,Co", [(4096, 256, 768), (77 * 3, 768, 512), (1000, 320, 320), (8, 64, 16), (262144, 64, 64)])
+@pytest.mark.parametrize("dtype,tol", [("fp32", 1e-5), ("bf16", 1e-2)])
+def test_linear_tokens(lib_built, M, Ci, Co, dtype, tol):
+    """tmd_linear (nn.Linear / 1x1 convolution over token-major activations; the projections of core/Attention.py:131-134,
+    176-183, 213) against F.linear: wide outputs run as channel groups of 256, an odd token count takes the CUDA-core kernel,
+    bf16 operands go in and out without a cast pass."""
+    from tmdiff_b200 import operators as O
+    g = torch.Generator(device="cuda").manual_seed(M + Ci)
+    x = torch.randn(3, M // 3, Ci, generator=g, device="cuda") if M % 3 == 0 else torch.randn(M, Ci, generator=g, device="cuda")
+    w = torch.randn(Co, Ci, generator=g, device="cuda") / Ci ** 0.5
+    b = torch.randn(Co, generator=g, device="cuda")
+    want = torch.nn.functional.linear(x.double(), w.double(), b.double()).float()
+    got = O._linear_tokens(x, w, b, dtype)
+    assert got.shape == want.shape and got.dtype == torch.float32
+    assert rel_l2(got, want) < tol
+    assert rel_l2(O._linear_tokens(x, w, None, dtype), want - b) < tol
+    if dtype == "bf16":
+        got16 = O._linear_tokens(x.bfloat16(), w, b, dtype, out_bf16=True)
+        assert got16.dtype == torch.bfloat16 and rel_l2(got16.float(), want) < tol

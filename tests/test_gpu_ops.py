@@ -73,6 +73,8 @@ CONV_CASES = [
     (1, 32, 32, 8, 16, 24, 3),       # 8 accumulators per tile, merged-dz MMAs (N = 96)
     (2, 64, 48, 2, 32, 16, 3),       # 2 accumulators, merged (N = 144)
     (1, 32, 16, 6, 16, 8, 3),        # band count 6 -> 2 accumulators, three n-tiles
+    (2, 64, 768, 1, 16, 8, 1),       # wider than one launch takes: three channel groups of 256 (stacked q / k / v projection)
+    (1, 128, 320, 2, 8, 8, 3),       # 256 + 64
 ]
 
 

@@ -72,6 +72,7 @@ SIGNATURES = {
     "tmd_dwt2d": (C.c_int, [_P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
     "tmd_idwt2d": (C.c_int, [_P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
     "tmd_conv3d_mod": (C.c_int, [_P, _P, _P, _P, _P] + [C.c_int32] * 8 + [_P]),
+    "tmd_linear": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P]),
     "tmd_dynamic_threshold": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, _P]),
     "tmd_dynamic_threshold_static": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_float, _P]),
     "tmd_groupnorm": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_float, C.c_int32, _P]),

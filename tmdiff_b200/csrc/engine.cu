@@ -1300,19 +1300,132 @@ extern "C" int tmd_conv3d_mod(const float* x, const float* w, const float* sc, c
     int rc = 0;
     if (dtype == TMD_F32) {
         CK(conv_simt_f32(op, s));
-    } else if (conv_umma_supported(op)) {
-        UmmaPlan* plan = conv_umma_plan_create(op);
-        if (!plan) rc = fail("tmd_conv3d_mod: tensor map creation failed");
-        else {
-            cudaError_t err = conv_umma_bf16(op, plan, s);
-            conv_umma_plan_destroy(plan);
-            if (err != cudaSuccess) rc = fail("tmd_conv3d_mod: %s", cudaGetErrorString(err));
-        }
     } else {
-        CK(conv_simt_bf16(op, s));
+        // The tensor-core kernel takes up to 256 output channels per launch (one accumulator row block): wider layers -- the
+        // stacked q / k / v projections of the attention modules, nn.Linear with 512+ outputs -- run as channel groups of 256,
+        // each writing its slice of the channels-last output.
+        const int group = Co > 256 && Co % 16 == 0 ? 256 : Co;
+        ConvOp first = op;
+        first.Co = group;
+        if (conv_umma_supported(first)) {
+            for (int co0 = 0; co0 < Co && !rc; co0 += group) {
+                ConvOp g = op;
+                g.Co = Co - co0 < group ? Co - co0 : group;
+                g.w_bf16 = pb + (size_t)co0 * taps * Ci;
+                g.epi.bias = bias ? bias + co0 : nullptr;
+                g.epi.raw_out = reinterpret_cast<__nv_bfloat16*>(yout) + co0;
+                if (!conv_umma_supported(g)) { rc = fail("tmd_conv3d_mod: channel group %d..%d is not supported by the tensor-core kernel", co0, co0 + g.Co); break; }
+                UmmaPlan* plan = conv_umma_plan_create(g);
+                if (!plan) { rc = fail("tmd_conv3d_mod: tensor map creation failed"); break; }
+                const cudaError_t err = conv_umma_bf16(g, plan, s);
+                conv_umma_plan_destroy(plan);
+                if (err != cudaSuccess) rc = fail("tmd_conv3d_mod: %s", cudaGetErrorString(err));
+            }
+        } else {
+            CK(conv_simt_bf16(op, s));
+        }
     }
     if (!rc) CK(cl_to_ncdhw(dtype, yout, y, B, Co, nhw, s));
     cudaFreeAsync(xin, s); cudaFreeAsync(yout, s); cudaFreeAsync(pf, s); cudaFreeAsync(pb, s);
+    return rc;
+}
+
+namespace {
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, size_t n8) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n8) return;
+    const float4 a = reinterpret_cast<const float4*>(x)[2 * i], b = reinterpret_cast<const float4*>(x)[2 * i + 1];
+    __nv_bfloat162 o[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w), __floats2bfloat162_rn(b.x, b.y),
+                           __floats2bfloat162_rn(b.z, b.w)};
+    reinterpret_cast<uint4*>(y)[i] = *reinterpret_cast<const uint4*>(o);
+}
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, size_t n8) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n8) return;
+    const uint4 r = reinterpret_cast<const uint4*>(x)[i];
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+    const float2 a = __bfloat1622float2(h[0]), b = __bfloat1622float2(h[1]), c = __bfloat1622float2(h[2]), d = __bfloat1622float2(h[3]);
+    reinterpret_cast<float4*>(y)[2 * i] = make_float4(a.x, a.y, b.x, b.y);
+    reinterpret_cast<float4*>(y)[2 * i + 1] = make_float4(c.x, c.y, d.x, d.y);
+}
+}  // namespace
+
+// nn.Linear / a 1x1 convolution over TOKEN-MAJOR activations: y[m, :] = W x[m, :] + bias for x [M, Ci], W [Co, Ci] (fp32),
+// y [M, Co].  The rows are the "voxels" of the channels-last conv kernels, so nothing is re-laid-out: in bf16 mode x and y may
+// be bf16 (x_bf16 / y_bf16) and then the call is the weight pack plus the tensor-core launches (channel groups of 256); fp32
+// operands are cast on the way in / out.  fp32 mode runs the CUDA-core kernel on fp32 operands.
+extern "C" int tmd_linear(const void* x, const float* w, const float* bias, void* y, int64_t M, int32_t Ci, int32_t Co, int32_t x_bf16,
+                          int32_t y_bf16, int32_t dtype, void* stream) {
+    if (!x || !w || !y) return fail("tmd_linear: null argument");
+    if (M <= 0 || Ci <= 0 || Co <= 0 || M > 0x7fffffffLL) return fail("tmd_linear: bad sizes");
+    if (Ci % 4 || Co % 4) return fail("tmd_linear: Ci and Co must be multiples of 4");
+    if (dtype != TMD_F32 && dtype != TMD_BF16) return fail("tmd_linear: bad dtype");
+    if (dtype == TMD_F32 && (x_bf16 || y_bf16)) return fail("tmd_linear: fp32 mode takes and returns fp32");
+    cudaStream_t s = (cudaStream_t)stream;
+    keep_pool_warm();
+    const int Wd = M % 8 == 0 ? 8 : (M % 4 == 0 ? 4 : (M % 2 == 0 ? 2 : 1));
+    float* pf = nullptr;
+    __nv_bfloat16* pb = nullptr;
+    void *xin = nullptr, *yout = nullptr;
+    CK(cudaMallocAsync((void**)&pf, (size_t)Ci * Co * 4, s));
+    CK(cudaMallocAsync((void**)&pb, (size_t)Ci * Co * 2, s));
+    const size_t total = (size_t)Co * Ci;
+    pack_weights_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(w, pf, pb, Co, Ci, 1);
+    CK(cudaGetLastError());
+    ConvOp op{};
+    op.B = 1; op.N = 1; op.H = (int)(M / Wd); op.W = Wd; op.Ci = Ci; op.ld_in = Ci; op.Co = Co; op.taps = 1;
+    op.w_f32 = pf; op.w_bf16 = pb;
+    op.epi.mode = CONV_NORMAL; op.epi.bias = bias; op.epi.ld_raw = Co;
+    int rc = 0;
+    if (dtype == TMD_F32) {
+        op.src = x; op.epi.raw_out = y;
+        const cudaError_t err = conv_simt_f32(op, s);
+        if (err != cudaSuccess) rc = fail("tmd_linear: %s", cudaGetErrorString(err));
+    } else {
+        const size_t nx = (size_t)M * Ci, ny = (size_t)M * Co;
+        if (!x_bf16) {
+            if (nx % 8) rc = fail("tmd_linear: M*Ci must be a multiple of 8");
+            else {
+                CK(cudaMallocAsync(&xin, nx * 2, s));
+                cast_f32_bf16_kernel<<<(unsigned)((nx / 8 + 255) / 256), 256, 0, s>>>((const float*)x, (__nv_bfloat16*)xin, nx / 8);
+            }
+        }
+        if (!rc && !y_bf16) {
+            if (ny % 8) rc = fail("tmd_linear: M*Co must be a multiple of 8");
+            else CK(cudaMallocAsync(&yout, ny * 2, s));
+        }
+        if (!rc) {
+            op.src = x_bf16 ? x : xin;
+            __nv_bfloat16* yb = reinterpret_cast<__nv_bfloat16*>(y_bf16 ? y : yout);
+            op.epi.raw_out = yb;
+            const int group = Co > 256 && Co % 16 == 0 ? 256 : Co;
+            ConvOp first = op;
+            first.Co = group;
+            if (conv_umma_supported(first)) {
+                for (int co0 = 0; co0 < Co && !rc; co0 += group) {
+                    ConvOp g = op;
+                    g.Co = Co - co0 < group ? Co - co0 : group;
+                    g.w_bf16 = pb + (size_t)co0 * Ci;
+                    g.epi.bias = bias ? bias + co0 : nullptr;
+                    g.epi.raw_out = yb + co0;
+                    if (!conv_umma_supported(g)) { rc = fail("tmd_linear: channel group %d..%d is not supported by the tensor-core kernel", co0, co0 + g.Co); break; }
+                    UmmaPlan* plan = conv_umma_plan_create(g);
+                    if (!plan) { rc = fail("tmd_linear: tensor map creation failed"); break; }
+                    const cudaError_t err = conv_umma_bf16(g, plan, s);
+                    conv_umma_plan_destroy(plan);
+                    if (err != cudaSuccess) rc = fail("tmd_linear: %s", cudaGetErrorString(err));
+                }
+            } else {
+                const cudaError_t err = conv_simt_bf16(op, s);
+                if (err != cudaSuccess) rc = fail("tmd_linear: %s", cudaGetErrorString(err));
+            }
+            if (!rc && !y_bf16) cast_bf16_f32_kernel<<<(unsigned)((ny / 8 + 255) / 256), 256, 0, s>>>(yb, (float*)y, ny / 8);
+            if (!rc && cudaGetLastError() != cudaSuccess) rc = fail("tmd_linear: cast launch failed");
+        }
+    }
+    if (xin) cudaFreeAsync(xin, s);
+    if (yout) cudaFreeAsync(yout, s);
+    cudaFreeAsync(pf, s); cudaFreeAsync(pb, s);
     return rc;
 }
 

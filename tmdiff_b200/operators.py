@@ -90,23 +90,46 @@ def _conv1x1(x, weight, bias, dtype):
     return y.reshape(B, weight.shape[0], *sp)
 
 
-def _linear_tokens(x, weight, bias, dtype):
-    """nn.Linear over the last dim of x [B, L, Cin] (tokens are the voxels of a 1x1 conv)."""
-    B, L, Cin = x.shape
-    y = _conv1x1(x.reshape(1, B * L, Cin).transpose(1, 2).contiguous(), weight, bias, dtype)
-    return y.reshape(weight.shape[0], B * L).t().reshape(B, L, weight.shape[0])
+def _linear_tokens(x, weight, bias, dtype, out_bf16=False):
+    """nn.Linear over the last dim of TOKEN-MAJOR x [..., Cin] (tmd_linear: the rows are the voxels of the channels-last conv
+    kernels, nothing is re-laid-out).  x fp32 or bf16; returns [..., Co] fp32, or bf16 when `out_bf16` in bf16 mode."""
+    if not x.is_cuda:
+        raise RuntimeError("x must be a CUDA tensor (tmdiff_b200 has no CPU path)")
+    code = {"fp32": _lib.F32, "bf16": _lib.BF16}[dtype]
+    x_bf16 = code == _lib.BF16 and x.dtype == torch.bfloat16
+    x = x.contiguous() if x_bf16 else x.contiguous().float()
+    Cin, Co = x.shape[-1], weight.shape[0]
+    M = x.numel() // Cin
+    w = _cuda_f32(weight, "weight").reshape(Co, Cin)
+    b = None if bias is None else _cuda_f32(bias, "bias")
+    y_bf16 = bool(out_bf16) and code == _lib.BF16
+    y = torch.empty(*x.shape[:-1], Co, device=x.device, dtype=torch.bfloat16 if y_bf16 else torch.float32)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().tmd_linear(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(y), M, Cin, Co, int(x_bf16), int(y_bf16), code,
+                                          _lib.stream_ptr()))
+    return y
 
 
-def _stacked(module, name, weights, biases, transpose=False):
-    """[w0; w1; ...] and [b0; b1; ...] of projections that read the same input, so that they run as one launch; rebuilt when a
-    parameter changes (its `_version` / storage), kept on the module as plain attributes (not part of the state dict)."""
-    key = tuple((w.data_ptr(), w._version) for w in weights) + tuple((b.data_ptr(), b._version) for b in biases)
-    hit = getattr(module, name, None)
-    if hit is None or hit[0] != key:
-        w = torch.cat([(x.t() if transpose else x).detach().float() for x in weights], 0).contiguous()
-        hit = (key, w, torch.cat([x.detach().float() for x in biases], 0).contiguous() if biases else None)
-        object.__setattr__(module, name, hit)
-    return hit[1], hit[2]
+def _relayout(t, shape, dtype):
+    """`t` (any strides) as a contiguous tensor of `dtype`: layout change and cast in ONE copy."""
+    return torch.empty(shape, dtype=dtype, device=t.device).copy_(t)
+
+
+def _token_self_attention(h, qkv, out_w, out_b, scale, dtype):
+    """Single-head self-attention over the HW tokens of a normalised feature map h [B, C, HW] (core/Attention.py:140-159,
+    Hyper_unet_general.py:494-508): q / k / v / output projections as token-major GEMMs (tmd_linear), the attention core, and the
+    result back as [B, C, HW] (a view).  bf16 mode: the operands stay bf16 between the kernels; what is left in torch is the
+    layout change of h into tokens, of v into the core's channel-major operand and of the result back (three copies)."""
+    B, C, L = h.shape
+    bf = dtype == "bf16" and C % 64 == 0
+    tdt = torch.bfloat16 if bf else torch.float32
+    ht = _relayout(h.transpose(1, 2), (B, L, C), tdt)
+    q, k, v = (_linear_tokens(ht, w, b, dtype, out_bf16=bf) for (w, b) in qkv)
+    if bf:
+        o = attention_bf16(q, k, _relayout(v.transpose(1, 2), (B, C, L), tdt), scale, v_channel_major=True)
+    else:
+        o = attention(q, k, v, scale, "fp32")
+    return _linear_tokens(o, out_w, out_b, dtype).transpose(1, 2)
 
 
 class AdaptiveGroupNorm(nn.Module):
@@ -149,13 +172,9 @@ class AttnBlockpp(nn.Module):
         x2 = x.reshape(B, Cf * N, H, W)
         h = group_norm(x2, self.GroupNorm_0.num_groups, self.GroupNorm_0.weight, self.GroupNorm_0.bias, eps=1e-6)
         Cc = Cf * N
-        w, b = _stacked(self, "_qkv", [n.W for n in (self.NIN_0, self.NIN_1, self.NIN_2)], [n.b for n in (self.NIN_0, self.NIN_1, self.NIN_2)],
-                        transpose=True)
-        qkv = _conv1x1(h, w, b, self.compute_dtype).reshape(B, 3, Cc, H * W)          # one projection launch for q, k and v
-        tok = lambda t: t.transpose(1, 2)                                              # token-major view; the bf16 path lays it out while casting
-        o = attention(tok(qkv[:, 0]), tok(qkv[:, 1]), qkv[:, 2], int(Cf) ** (-0.5), self.compute_dtype, v_channel_major=True)
-        o = o.transpose(1, 2).reshape(B, Cf * N, H, W)
-        o = _conv1x1(o, self.NIN_3.W.t().contiguous(), self.NIN_3.b, self.compute_dtype)
+        nin = lambda n: (n.W.t(), n.b)
+        o = _token_self_attention(h.reshape(B, Cc, H * W), [nin(self.NIN_0), nin(self.NIN_1), nin(self.NIN_2)], self.NIN_3.W.t(), self.NIN_3.b,
+                                  int(Cf) ** (-0.5), self.compute_dtype).reshape(B, Cc, H, W)
         out = (x2 + o).reshape(B, Cf, N, H, W)
         return out / math.sqrt(2.0) if self.skip_rescale else out
 
@@ -171,12 +190,10 @@ class SpatialSelfAttention(nn.Module):
     def forward(self, x):
         B, Cc, H, W = x.shape
         h = group_norm(x, 32, self.norm.weight, self.norm.bias, eps=1e-6)
-        w, b = _stacked(self, "_qkv", [m.weight.reshape(Cc, Cc) for m in (self.q, self.k, self.v)], [m.bias for m in (self.q, self.k, self.v)])
-        qkv = _conv1x1(h, w, b, self.compute_dtype).reshape(B, 3, Cc, H * W)          # one projection launch for q, k and v
-        tok = lambda t: t.transpose(1, 2)
-        o = attention(tok(qkv[:, 0]), tok(qkv[:, 1]), qkv[:, 2], int(Cc) ** (-0.5), self.compute_dtype, v_channel_major=True)
-        o = o.transpose(1, 2).reshape(B, Cc, H, W)
-        return x + _conv1x1(o, self.proj_out.weight.reshape(Cc, Cc), self.proj_out.bias, self.compute_dtype)
+        conv = lambda m: (m.weight.reshape(Cc, Cc), m.bias)
+        o = _token_self_attention(h.reshape(B, Cc, H * W), [conv(self.q), conv(self.k), conv(self.v)], self.proj_out.weight.reshape(Cc, Cc),
+                                  self.proj_out.bias, int(Cc) ** (-0.5), self.compute_dtype)
+        return x + o.reshape(B, Cc, H, W)
 
 
 class CrossAttention(nn.Module):
@@ -197,19 +214,15 @@ class CrossAttention(nn.Module):
         context = x if context is None else context
         B, L, _ = x.shape
         h = self.heads
-        q = _linear_tokens(x.float(), self.to_q.weight, None, self.compute_dtype)
-        w_kv, _ = _stacked(self, "_kv", [self.to_k.weight, self.to_v.weight], [])
-        kv = _linear_tokens(context.float(), w_kv, None, self.compute_dtype)          # one projection launch for k and v
-        k, v = kv[..., :kv.shape[-1] // 2], kv[..., kv.shape[-1] // 2:]
-        cast = torch.bfloat16 if self.compute_dtype == "bf16" and (q.shape[-1] // h) % 64 == 0 else torch.float32
-
-        def split(t):       # [B, L, h*d] -> [B*h, L, d], laid out (and cast for the tensor-core kernel) by one copy
-            Lt = t.shape[1]
-            o = torch.empty(B, h, Lt, t.shape[-1] // h, dtype=cast, device=t.device)
-            o.copy_(t.reshape(B, Lt, h, -1).permute(0, 2, 1, 3))
-            return o.view(B * h, Lt, -1)
-        o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)   # logits always in fp32 (:194-197)
-        o = o.reshape(B, h, L, -1).permute(0, 2, 1, 3).reshape(B, L, -1)
+        d = self.to_q.weight.shape[0] // h
+        bf = self.compute_dtype == "bf16" and d % 64 == 0
+        tdt = torch.bfloat16 if bf else torch.float32
+        q = _linear_tokens(x, self.to_q.weight, None, self.compute_dtype, out_bf16=bf)            # [B, L, h*d], bf16 in bf16 mode
+        k = _linear_tokens(context, self.to_k.weight, None, self.compute_dtype, out_bf16=bf)
+        v = _linear_tokens(context, self.to_v.weight, None, self.compute_dtype, out_bf16=bf)
+        split = lambda t: _relayout(t.reshape(B, t.shape[1], h, d).permute(0, 2, 1, 3), (B, h, t.shape[1], d), tdt).view(B * h, t.shape[1], d)
+        o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)              # logits always in fp32 (:194-197)
+        o = _relayout(o.view(B, h, L, d).permute(0, 2, 1, 3), (B, L, h, d), tdt).view(B, L, h * d)
         return _linear_tokens(o, self.to_out[0].weight, self.to_out[0].bias, self.compute_dtype)
 
 
