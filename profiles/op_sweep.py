@@ -19,29 +19,54 @@ PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PE
 FLUSH = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
 
-def timed(fn, iters=5):
-    fn(); fn()
+def _median_ms(run, iters):
     ts = []
     for _ in range(iters):
         FLUSH.zero_()                       # evict L2 (126 MB) between iterations
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record()
+        a.record(); run(); b.record()
         torch.cuda.synchronize()
         ts.append(a.elapsed_time(b))
     return sorted(ts)[len(ts) // 2]
 
 
-def row(name, shape, ms, nbytes=None, flops=None):
+def timed(fn, iters=5):
+    """(call, device): one call through the Python wrapper (its allocations, ctypes marshalling and launch latency included --
+    about 30 us, which is all a small operator costs) and the same call replayed from a CUDA graph (device time only)."""
+    fn(); fn()
+    call = _median_ms(fn, iters)
+    dev = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        g.replay()
+        dev = _median_ms(g.replay, iters)
+    except Exception:                       # an operator that cannot be captured keeps the call time only
+        torch.cuda.synchronize()
+    return call, dev
+
+
+def row(name, shape, t, nbytes=None, flops=None):
+    call, dev = t if isinstance(t, tuple) else (t, None)
+    ms = dev if dev else call
     gbs = nbytes / ms / 1e6 if nbytes else None
-    print("| %s | %s | %.3f | %s | %s | %s |" % (name, shape, ms, "%.0f" % gbs if gbs else "", "%.0f%%" % (100 * gbs / PEAK) if gbs else "",
-                                                 "%.1f" % (flops / ms / 1e9) if flops else ""))
+    print("| %s | %s | %.3f | %s | %s | %s | %s |" % (name, shape, call, "%.3f" % dev if dev else "", "%.0f" % gbs if gbs else "",
+                                                      "%.0f%%" % (100 * gbs / PEAK) if gbs else "", "%.1f" % (flops / ms / 1e9) if flops else ""))
 
 
 def main():
     print("# per-operator sweep (median of 5, L2 flushed between iterations); HBM peak = %.0f GB/s (measured copy)\n" % PEAK)
-    print("| operator | shape | ms | GB/s (algorithmic) | of HBM peak | TFLOP/s |")
-    print("|---|---|---:|---:|---:|---:|")
+    print("`call ms` = one call through the Python wrapper; `device ms` = the same call replayed from a CUDA graph; GB/s, the fraction and")
+    print("TFLOP/s are of the device time (of the call time where the operator could not be captured).\n")
+    print("| operator | shape | call ms | device ms | GB/s (algorithmic) | of HBM peak | TFLOP/s |")
+    print("|---|---|---:|---:|---:|---:|---:|")
     dwt, idwt = ops.DWT_2D("haar"), ops.IDWT_2D("haar")
     for B in (1, 16, 64, 256, 1024):
         for (CN, HW) in ((128, 64), (256, 32), (512, 16)):         # 4-band level shapes (C*N, H)

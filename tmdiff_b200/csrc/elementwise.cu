@@ -340,6 +340,39 @@ __global__ void dwt2d_kernel(const float* __restrict__ x, float* __restrict__ ll
     }
 }
 
+// W % 8 == 0: 2 rows x 8 columns per thread -- four 16-byte loads in flight and 16-byte stores (the 8-byte stores of the kernel
+// above write half sectors: 55 % of the copy bandwidth at the U-Net's level-0 shape, profiles/op_sweep_r02.md)
+__global__ void __launch_bounds__(256) dwt2d_wide_kernel(const float* __restrict__ x, float* __restrict__ ll, float* __restrict__ lh,
+                                                         float* __restrict__ hl, float* __restrict__ hh, int H, int W, size_t total) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int w8 = W / 8, h2 = H / 2;
+    const int j = (int)(i % w8);
+    const int r = (int)((i / w8) % h2);
+    const size_t bc = i / ((size_t)w8 * h2);
+    const float* p = x + (bc * H + 2 * r) * W + 8 * j;
+    const float4 t0 = __ldg(reinterpret_cast<const float4*>(p)), t1 = __ldg(reinterpret_cast<const float4*>(p + 4));
+    const float4 u0 = __ldg(reinterpret_cast<const float4*>(p + W)), u1 = __ldg(reinterpret_cast<const float4*>(p + W + 4));
+    const float a[4] = {t0.x, t0.z, t1.x, t1.z}, b[4] = {t0.y, t0.w, t1.y, t1.w};
+    const float c[4] = {u0.x, u0.z, u1.x, u1.z}, d[4] = {u0.y, u0.w, u1.y, u1.w};
+    const size_t o = (bc * h2 + r) * (W / 2) + 4 * j;
+    float4 L, LH, HL, HH;
+    float* Lp = &L.x; float* LHp = &LH.x; float* HLp = &HL.x; float* HHp = &HH.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        Lp[k] = ((a[k] + b[k]) + (c[k] + d[k])) * 0.5f;
+        LHp[k] = ((a[k] - b[k]) + (c[k] - d[k])) * 0.5f;
+        HLp[k] = ((a[k] + b[k]) - (c[k] + d[k])) * 0.5f;
+        HHp[k] = ((a[k] - b[k]) - (c[k] - d[k])) * 0.5f;
+    }
+    *reinterpret_cast<float4*>(ll + o) = L;
+    if (lh) {
+        *reinterpret_cast<float4*>(lh + o) = LH;
+        *reinterpret_cast<float4*>(hl + o) = HL;
+        *reinterpret_cast<float4*>(hh + o) = HH;
+    }
+}
+
 __global__ void dwt2d_scalar_kernel(const float* __restrict__ x, float* __restrict__ ll, float* __restrict__ lh, float* __restrict__ hl,
                                     float* __restrict__ hh, int H, int W, size_t total) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -359,7 +392,11 @@ __global__ void dwt2d_scalar_kernel(const float* __restrict__ x, float* __restri
 }
 
 cudaError_t dwt2d_nchw(const float* x, float* ll, float* lh, float* hl, float* hh, int64_t BC, int H, int W, cudaStream_t s) {
-    if (W % 4 == 0) {
+    const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (W % 8 == 0 && al16(x) && al16(ll) && (!lh || (al16(lh) && al16(hl) && al16(hh)))) {
+        const size_t total = (size_t)BC * (H / 2) * (W / 8);
+        dwt2d_wide_kernel<<<cdiv(total, 256), 256, 0, s>>>(x, ll, lh, hl, hh, H, W, total);
+    } else if (W % 4 == 0) {
         const size_t total = (size_t)BC * (H / 2) * (W / 4);
         dwt2d_kernel<<<cdiv(total, 256), 256, 0, s>>>(x, ll, lh, hl, hh, H, W, total);
     } else {
@@ -387,6 +424,34 @@ __global__ void idwt2d_kernel(const float* __restrict__ ll, const float* __restr
                                                         ((A.y + B.y) - (C.y + D.y)) * 0.5f, ((A.y - B.y) - (C.y - D.y)) * 0.5f);
 }
 
+// w % 4 == 0: four coefficients per band and thread (16-byte loads), two output rows of 8 values (four 16-byte stores)
+__global__ void __launch_bounds__(256) idwt2d_wide_kernel(const float* __restrict__ ll, const float* __restrict__ lh, const float* __restrict__ hl,
+                                                          const float* __restrict__ hh, float* __restrict__ out, int h, int w, size_t total) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int w4 = w / 4;
+    const int j = (int)(i % w4);
+    const int r = (int)((i / w4) % h);
+    const size_t bc = i / ((size_t)w4 * h);
+    const size_t o = (bc * h + r) * w + 4 * j;
+    const float4 A4 = __ldg(reinterpret_cast<const float4*>(ll + o)), B4 = __ldg(reinterpret_cast<const float4*>(lh + o));
+    const float4 C4 = __ldg(reinterpret_cast<const float4*>(hl + o)), D4 = __ldg(reinterpret_cast<const float4*>(hh + o));
+    const float A[4] = {A4.x, A4.y, A4.z, A4.w}, B[4] = {B4.x, B4.y, B4.z, B4.w}, C[4] = {C4.x, C4.y, C4.z, C4.w}, D[4] = {D4.x, D4.y, D4.z, D4.w};
+    float top[8], bot[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        top[2 * k] = ((A[k] + B[k]) + (C[k] + D[k])) * 0.5f;
+        top[2 * k + 1] = ((A[k] - B[k]) + (C[k] - D[k])) * 0.5f;
+        bot[2 * k] = ((A[k] + B[k]) - (C[k] + D[k])) * 0.5f;
+        bot[2 * k + 1] = ((A[k] - B[k]) - (C[k] - D[k])) * 0.5f;
+    }
+    float* p = out + (bc * 2 * h + 2 * r) * (2 * w) + 8 * j;
+    *reinterpret_cast<float4*>(p) = make_float4(top[0], top[1], top[2], top[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(top[4], top[5], top[6], top[7]);
+    *reinterpret_cast<float4*>(p + 2 * w) = make_float4(bot[0], bot[1], bot[2], bot[3]);
+    *reinterpret_cast<float4*>(p + 2 * w + 4) = make_float4(bot[4], bot[5], bot[6], bot[7]);
+}
+
 __global__ void idwt2d_scalar_kernel(const float* __restrict__ ll, const float* __restrict__ lh, const float* __restrict__ hl,
                                      const float* __restrict__ hh, float* __restrict__ out, int h, int w, size_t total) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -404,7 +469,11 @@ __global__ void idwt2d_scalar_kernel(const float* __restrict__ ll, const float* 
 
 cudaError_t idwt2d_nchw(const float* ll, const float* lh, const float* hl, const float* hh, float* out, int64_t BC, int h, int w,
                         cudaStream_t s) {
-    if (w % 2 == 0) {
+    const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (w % 4 == 0 && al16(ll) && al16(lh) && al16(hl) && al16(hh) && al16(out)) {
+        const size_t total = (size_t)BC * h * (w / 4);
+        idwt2d_wide_kernel<<<cdiv(total, 256), 256, 0, s>>>(ll, lh, hl, hh, out, h, w, total);
+    } else if (w % 2 == 0) {
         const size_t total = (size_t)BC * h * (w / 2);
         idwt2d_kernel<<<cdiv(total, 256), 256, 0, s>>>(ll, lh, hl, hh, out, h, w, total);
     } else {
