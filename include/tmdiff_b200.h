@@ -194,6 +194,13 @@ int tmd_attention(const float* q, const float* k, const float* v, float* out, in
  * 64 and scale positive; anything else is an error (the fp32 entry above takes every shape). */
 int tmd_attention_bf16(const void* q, const void* k, const void* vt, float* out, int32_t BH, int32_t Lq, int32_t Lk, int32_t D,
                        int32_t lk_pitch, float scale, void* stream);
+/* The same kernel on the projections' own layout, so that the heads need not be split and merged by copies
+ * (`rearrange(t, 'b n (h d) -> (b h) n d')` and back, core/Attention.py:189-191, 211): q [B,Lq,q_pitch] and k [B,Lk,k_pitch] hold
+ * head h in columns [h*D, (h+1)*D) (bf16; pitches >= heads*D, multiples of 8), vt [B*heads,D,lk_pitch] as above, out
+ * [B,Lq,out_pitch] with head h in the same columns, fp32 or bf16 (out_bf16).  heads = 1, pitches = D is tmd_attention_bf16. */
+int tmd_attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int32_t B, int32_t heads, int32_t Lq,
+                               int32_t Lk, int32_t D, int64_t q_pitch, int64_t k_pitch, int32_t lk_pitch, int64_t out_pitch,
+                               int32_t out_bf16, float scale, void* stream);
 /* Dynamic_conv3d.forward (core/dynamic_conv.py:244-268; groups=1, stride 1, 'same' padding, k in {1,3}):
  * x [B,Ci,N,H,W], weight [K,Co,Ci,k,k,k], bias [K,Co] or NULL, fc1 [hidden,Ci], fc2 [K,hidden] (attention3d's 1x1x1 convs,
  * :194-218) -> y [B,Co,N,H,W]. */

@@ -288,3 +288,25 @@ def test_linear_tokens(lib_built, M, Ci, Co, dtype, tol):
     if dtype == "bf16":
         got16 = O._linear_tokens(x.bfloat16(), w, b, dtype, out_bf16=True)
         assert got16.dtype == torch.bfloat16 and rel_l2(got16.float(), want) < tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,h,Lq,Lk,d", [(3, 8, 300, 77, 64), (2, 4, 256, 333, 128), (2, 1, 200, 200, 256), (1, 2, 130, 1024, 512)])
+@pytest.mark.parametrize("out_bf16", [False, True])
+def test_attention_bf16_heads_in_place_layout(lib_built, B, h, Lq, Lk, d, out_bf16):
+    """tmd_attention_bf16_strided: heads side by side in the rows of q / k / out (the projections' own layout,
+    core/Attention.py:189-191, 211) against softmax(q k^T * scale) v per head in fp64 on the same bf16-rounded operands, and
+    against the split-heads entry point."""
+    from tmdiff_b200 import operators as O
+    g = torch.Generator(device="cuda").manual_seed(B * 100 + h)
+    q, k, v = (torch.randn(B, L, h * d, generator=g, device="cuda").bfloat16() for L in (Lq, Lk, Lk))
+    scale = d ** -0.5
+    got = O.attention_bf16_heads(q, k, v, h, scale, out_bf16=out_bf16)
+    assert got.shape == (B, Lq, h * d) and got.dtype == (torch.bfloat16 if out_bf16 else torch.float32)
+    sp = lambda t: t.double().reshape(B, t.shape[1], h, d).permute(0, 2, 1, 3)
+    want = (torch.softmax(sp(q) @ sp(k).transpose(-1, -2) * scale, -1) @ sp(v)).permute(0, 2, 1, 3).reshape(B, Lq, h * d).float()
+    assert rel_l2(got.float(), want) < (8e-3 if out_bf16 else 5e-3)
+    split = lambda t: t.reshape(B, t.shape[1], h, d).permute(0, 2, 1, 3).reshape(B * h, t.shape[1], d).contiguous()
+    old = O.attention_bf16(split(q), split(k), split(v), scale).view(B, h, Lq, d).permute(0, 2, 1, 3).reshape(B, Lq, h * d)
+    if not out_bf16:
+        assert torch.equal(got, old)          # same kernel, same operands: bit-identical

@@ -36,7 +36,9 @@ constexpr uint32_t kTileBytes = 128 * 128;      // [128 rows][64 bf16]: one swiz
 
 struct AttnParams {
     CUtensorMap tmQ, tmK, tmV;
-    float* out;
+    void* out;                    // fp32, or bf16 when out_bf16; row (b, query) at b*Lq*out_pitch + query*out_pitch, head h at column h*D
+    int out_bf16, heads;          // heads: q / k / out hold `heads` heads side by side in a row ([B, L, heads*D]); bh = b*heads + h
+    long long out_pitch;          // elements
     int BH, Lq, Lk, D, DV;
     int nkc, nkb;                 // 64-wide chunks of D; 128-key blocks
     int q_resident, NS, NVB;
@@ -85,6 +87,29 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+// 16 accumulator values * inv -> 64 bytes of fp32 or 32 bytes of bf16 at p
+__device__ __forceinline__ void store_out16(char* p, const float v[16], float inv, bool bf16) {
+    if (bf16) {
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i] * inv, v[2 * i + 1] * inv);
+            w[i] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        reinterpret_cast<uint4*>(p)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<uint4*>(p)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            reinterpret_cast<float4*>(p)[i] = make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
+    }
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -209,6 +234,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
     const uint32_t tmem_o = tmem_base + (SINGLE ? 0u : 256u);
 
     const int q0 = blockIdx.x * 128, dv0 = SINGLE ? 0 : blockIdx.y * P.DV, bh = blockIdx.z;
+    const int hh = bh % P.heads, bb = bh / P.heads;      // head and batch of this (batch, head) index
     const int nkc = P.nkc, nkb = P.nkb;                  // SINGLE: one block, or two for a wide head (Lk <= 256)
     const int nvload = SINGLE ? P.ndv : nkb;             // V tiles this CTA consumes
 
@@ -217,7 +243,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             // ================= K (and Q) chunks =================
             if (P.q_resident) {
                 mbar_expect_tx(q_full, (uint32_t)nkc * kTileBytes);
-                for (int kc = 0; kc < nkc; ++kc) tma_load_3d(q_base + (uint32_t)kc * kTileBytes, &P.tmQ, q_full, kc * 64, q0, bh);
+                for (int kc = 0; kc < nkc; ++kc) tma_load_4d(q_base + (uint32_t)kc * kTileBytes, &P.tmQ, q_full, kc * 64, hh, q0, bb);
             }
             uint32_t s = 0, ph = 1;
             const int kch = P.kch;
@@ -229,8 +255,8 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     mbar_expect_tx(k_full(s), P.stage_bytes);
                     const uint32_t dst = st_base + s * P.stage_bytes;
                     for (int c = 0; c < kch; ++c) {
-                        tma_load_3d(dst + (uint32_t)c * pitch, &P.tmK, k_full(s), (kc + c) * 64, j * 128, bh);
-                        if (!P.q_resident) tma_load_3d(dst + (uint32_t)c * pitch + kTileBytes, &P.tmQ, k_full(s), (kc + c) * 64, q0, bh);
+                        tma_load_4d(dst + (uint32_t)c * pitch, &P.tmK, k_full(s), (kc + c) * 64, hh, j * 128, bb);
+                        if (!P.q_resident) tma_load_4d(dst + (uint32_t)c * pitch + kTileBytes, &P.tmQ, k_full(s), (kc + c) * 64, hh, q0, bb);
                     }
                     if (++s == (uint32_t)P.NS) { s = 0; ph ^= 1; }
                 }
@@ -329,7 +355,9 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
         const uint32_t p_row = p_base + (uint32_t)r * 128u;
         const uint32_t sw = (uint32_t)(r & 7);
         const bool valid = q0 + r < P.Lq;
-        float* orow = P.out + ((size_t)bh * P.Lq + (size_t)(q0 + r)) * P.D + dv0;
+        const uint32_t esz = P.out_bf16 ? 2u : 4u;
+        char* orow = reinterpret_cast<char*>(P.out) +
+                     (((size_t)bb * P.Lq + (size_t)(q0 + r)) * (size_t)P.out_pitch + (size_t)hh * P.D + dv0) * esz;
         if (SINGLE) {
             // the logits of all keys are at hand: exact softmax in two passes over 64-column pieces (few registers: four CTAs per SM)
             mbar_wait(s_full(0), 0);
@@ -388,19 +416,31 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 // P / V tiles, pitch D*4 + 16 bytes: conflict-free 16-byte stores) and leaves as ONE bulk copy per row.
                 mbar_wait(o_full(0), 0);
                 tc_fence_after();
-                const uint32_t srow = q_base + (uint32_t)r * ((uint32_t)P.DV * 4u + 16u);
+                const uint32_t srow = q_base + (uint32_t)r * ((uint32_t)P.DV * esz + 16u);
                 for (int cc = 0; cc < P.DV / 16; ++cc) {
                     float v[16];
                     tc_ld16(tmem_o + lane_addr + cc * 16, v);
+                    if (P.out_bf16) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(srow + (uint32_t)cc * 64u + (uint32_t)i * 16u), "f"(v[4 * i] * inv),
-                                     "f"(v[4 * i + 1] * inv), "f"(v[4 * i + 2] * inv), "f"(v[4 * i + 3] * inv)
-                                     : "memory");
+                        for (int i = 0; i < 2; ++i) {
+                            uint32_t w[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) w[j] = pack_bf16x2(v[8 * i + 2 * j] * inv, v[8 * i + 2 * j + 1] * inv);
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(srow + (uint32_t)cc * 32u + (uint32_t)i * 16u), "r"(w[0]), "r"(w[1]),
+                                         "r"(w[2]), "r"(w[3])
+                                         : "memory");
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(srow + (uint32_t)cc * 64u + (uint32_t)i * 16u), "f"(v[4 * i] * inv),
+                                         "f"(v[4 * i + 1] * inv), "f"(v[4 * i + 2] * inv), "f"(v[4 * i + 3] * inv)
+                                         : "memory");
+                    }
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 if (valid)
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(orow), "r"(srow), "r"((uint32_t)P.DV * 4u) : "memory");
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(orow), "r"(srow), "r"((uint32_t)P.DV * esz) : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             } else
@@ -411,12 +451,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 for (int cc = 0; cc < P.DV / 16; ++cc) {
                     float v[16];
                     tc_ld16(tmem_o + lane_addr + (uint32_t)ob * P.DV + cc * 16, v);
-                    if (valid) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            reinterpret_cast<float4*>(orow + c * P.DV + cc * 16)[i] =
-                                make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
-                    }
+                    if (valid) store_out16(orow + (size_t)(c * P.DV + cc * 16) * esz, v, inv, P.out_bf16 != 0);
                 }
                 tc_fence_before();
                 mbar_arrive(o_empty(ob));
@@ -528,12 +563,7 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
         for (int c = 0; c < hdv / 16; ++c) {
             float v[16];
             tc_ld16(tmem_o + lane_addr + (uint32_t)(wg * hdv + c * 16), v);
-            if (valid) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    reinterpret_cast<float4*>(orow + wg * hdv + c * 16)[i] =
-                        make_float4(v[4 * i] * inv, v[4 * i + 1] * inv, v[4 * i + 2] * inv, v[4 * i + 3] * inv);
-            }
+            if (valid) store_out16(orow + (size_t)(wg * hdv + c * 16) * esz, v, inv, P.out_bf16 != 0);
         }
         }
     }
@@ -569,6 +599,18 @@ bool make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, u
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// bf16 [batch][rows][heads][inner]: `heads` heads of `inner` channels side by side in a row of `pitch` elements; boxes of
+// [128 rows][one head][64] (coordinates: channel, head, row, batch -- strides in ascending order)
+bool make_map4(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t heads, uint64_t batch, uint64_t pitch) {
+    EncodeTiledFn enc = attn_encode_fn();
+    if (!enc) return false;
+    const cuuint64_t dims[4] = {inner, heads, rows, batch};
+    const cuuint64_t strides[3] = {inner * 2, pitch * 2, pitch * rows * 2};
+    const cuuint32_t box[4] = {64, 1, 128, 1}, es[4] = {1, 1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 }  // namespace
 
 bool attention_bf16_supported(int BH, int Lq, int Lk, int D, int lk_pitch) {
@@ -577,7 +619,20 @@ bool attention_bf16_supported(int BH, int Lq, int Lk, int D, int lk_pitch) {
 
 cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* out, int BH, int Lq, int Lk, int D, int lk_pitch,
                            float scale, cudaStream_t stream) {
+    return attention_bf16_strided(q, k, vt, out, BH, 1, Lq, Lk, D, D, D, lk_pitch, D, 0, scale, stream);
+}
+
+// q [B, Lq, q_pitch] and k [B, Lk, k_pitch] with head h in columns [h*D, (h+1)*D); vt [B*heads, D, lk_pitch]; out [B, Lq, out_pitch]
+// (fp32, or bf16 when out_bf16) with head h in the same columns: the projections' own token-major layout on both sides.
+cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int B, int heads, int Lq, int Lk, int D,
+                                   long long q_pitch, long long k_pitch, int lk_pitch, long long out_pitch, int out_bf16, float scale,
+                                   cudaStream_t stream) {
+    if (B <= 0 || heads <= 0 || (long long)B * heads > 65535) return cudaErrorInvalidValue;
+    const int BH = B * heads;
     if (!attention_bf16_supported(BH, Lq, Lk, D, lk_pitch)) return cudaErrorInvalidValue;
+    if (q_pitch < (long long)heads * D || k_pitch < (long long)heads * D || out_pitch < (long long)heads * D || q_pitch % 8 || k_pitch % 8 ||
+        out_pitch % 8)
+        return cudaErrorInvalidValue;
     if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(vt) | reinterpret_cast<uintptr_t>(out)) & 15)
         return cudaErrorMisalignedAddress;
     static int smem_limit[2] = {0, 0};
@@ -596,6 +651,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     AttnParams P;
     memset(&P, 0, sizeof(P));
     P.out = out;
+    P.out_bf16 = out_bf16 ? 1 : 0; P.heads = heads; P.out_pitch = out_pitch;
     P.BH = BH; P.Lq = Lq; P.Lk = Lk; P.D = D;
     P.nkc = D / 64;
     P.nkb = (Lk + 127) / 128;
@@ -650,7 +706,7 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
     P.idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
     P.idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)P.DV >> 3) << 17) | ((128u >> 4) << 24);
     P.scale_log2 = scale * 1.4426950408889634f;
-    if (!make_map(&P.tmQ, q, D, Lq, BH, D, 128) || !make_map(&P.tmK, k, D, Lk, BH, D, 128) ||
+    if (!make_map4(&P.tmQ, q, D, Lq, heads, B, q_pitch) || !make_map4(&P.tmK, k, D, Lk, heads, B, k_pitch) ||
         !make_map(&P.tmV, vt, Lk, D, BH, lk_pitch, (uint32_t)P.DV))
         return cudaErrorInvalidValue;
     if (single) {

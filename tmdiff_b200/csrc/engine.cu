@@ -1476,6 +1476,21 @@ extern "C" int tmd_attention_bf16(const void* q, const void* k, const void* vt, 
     return 0;
 }
 
+extern "C" int tmd_attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int32_t B, int32_t heads, int32_t Lq,
+                                          int32_t Lk, int32_t D, int64_t q_pitch, int64_t k_pitch, int32_t lk_pitch, int64_t out_pitch,
+                                          int32_t out_bf16, float scale, void* stream) {
+    if (!q || !k || !vt || !out) return fail("tmd_attention_bf16_strided: null argument");
+    if (B <= 0 || heads <= 0 || (int64_t)B * heads > 65535 || !attention_bf16_supported(B * heads, Lq, Lk, D, lk_pitch))
+        return fail("tmd_attention_bf16_strided: unsupported problem B=%d heads=%d Lq=%d Lk=%d D=%d lk_pitch=%d (D must be a multiple of 64, "
+                    "lk_pitch a multiple of 8 and >= Lk, B*heads <= 65535)", B, heads, Lq, Lk, D, lk_pitch);
+    if (q_pitch < (int64_t)heads * D || k_pitch < (int64_t)heads * D || out_pitch < (int64_t)heads * D || q_pitch % 8 || k_pitch % 8 || out_pitch % 8)
+        return fail("tmd_attention_bf16_strided: row pitches must be multiples of 8 elements and hold heads*D = %d channels", heads * D);
+    if (!(scale > 0.f)) return fail("tmd_attention_bf16_strided: the logit scale must be positive");
+    const cudaError_t err = attention_bf16_strided(q, k, vt, out, B, heads, Lq, Lk, D, q_pitch, k_pitch, lk_pitch, out_pitch, out_bf16, scale,
+                                                   (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_attention_bf16_strided: %s", cudaGetErrorString(err));
+    return 0;
+}
 
 namespace {
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }

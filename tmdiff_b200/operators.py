@@ -57,9 +57,10 @@ def attention(q, k, v, scale, dtype="fp32", v_channel_major=False):
     return out
 
 
-def attention_bf16(q, k, v, scale, v_channel_major=False):
+def attention_bf16(q, k, v, scale, v_channel_major=False, out_bf16=False):
     """The tensor-core attention core (tmd_attention_bf16).  q [BH, Lq, D], k [BH, Lk, D]; v [BH, Lk, D], or [BH, D, Lk] when
-    v_channel_major (the layout the reference's 1x1 convs produce, which is the one the kernel reads).  Returns fp32."""
+    v_channel_major (the layout the reference's 1x1 convs produce, which is the one the kernel reads).  Returns fp32, or bf16 when
+    `out_bf16` (for a consumer that takes bf16: the output projection)."""
     if not (q.is_cuda and k.is_cuda and v.is_cuda):
         raise RuntimeError("attention_bf16: CUDA tensors required (no CPU fallback)")
     BH, Lq, D = q.shape
@@ -73,10 +74,38 @@ def attention_bf16(q, k, v, scale, v_channel_major=False):
     # one pass per operand: a strided (transposed / sliced) fp32 view is cast and laid out by the same copy
     qb, kb, vb = (t if t.dtype == torch.bfloat16 and t.is_contiguous() else torch.empty(t.shape, dtype=torch.bfloat16, device=t.device).copy_(t)
                   for t in (q, k, vt))
-    out = torch.empty(BH, Lq, D, device=q.device, dtype=torch.float32)
+    out = torch.empty(BH, Lq, D, device=q.device, dtype=torch.bfloat16 if out_bf16 else torch.float32)
     with torch.cuda.device(q.device):
-        _lib.check(_lib.load().tmd_attention_bf16(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), BH, Lq, Lk, D, pitch,
-                                                  float(scale), _lib.stream_ptr()))
+        if out_bf16:
+            _lib.check(_lib.load().tmd_attention_bf16_strided(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), BH, 1, Lq, Lk, D, D, D,
+                                                              pitch, D, 1, float(scale), _lib.stream_ptr()))
+        else:
+            _lib.check(_lib.load().tmd_attention_bf16(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), BH, Lq, Lk, D, pitch,
+                                                      float(scale), _lib.stream_ptr()))
+    return out
+
+
+def attention_bf16_heads(q, k, v, heads, scale, out_bf16=True):
+    """Multi-head attention on the projections' own layout (tmd_attention_bf16_strided): q [B, Lq, heads*d], k and v
+    [B, Lk, heads*d] bf16, head h in columns [h*d, (h+1)*d) -- no `(b h) n d` split of q / k and no merge of the result
+    (core/Attention.py:189-191, 211); only v is re-laid-out (channel-major per head, the kernel's K-major operand).
+    Returns [B, Lq, heads*d], bf16 or fp32."""
+    if not (q.is_cuda and k.is_cuda and v.is_cuda):
+        raise RuntimeError("attention_bf16_heads: CUDA tensors required (no CPU fallback)")
+    B, Lq, inner = q.shape
+    Lk, d = k.shape[1], inner // heads
+    if inner % heads or d % 64 or k.shape != (B, Lk, inner) or v.shape != k.shape:
+        raise ValueError("attention_bf16_heads: q [B,Lq,h*d], k and v [B,Lk,h*d] with d a multiple of 64 expected")
+    qb, kb = (t if t.dtype == torch.bfloat16 and t.is_contiguous() else torch.empty(t.shape, dtype=torch.bfloat16, device=t.device).copy_(t)
+              for t in (q, k))
+    pitch = (Lk + 7) // 8 * 8
+    vt = torch.zeros(B, heads, d, pitch, dtype=torch.bfloat16, device=q.device) if pitch != Lk else \
+        torch.empty(B, heads, d, pitch, dtype=torch.bfloat16, device=q.device)
+    vt[..., :Lk].copy_(v.reshape(B, Lk, heads, d).permute(0, 2, 3, 1))
+    out = torch.empty(B, Lq, inner, device=q.device, dtype=torch.bfloat16 if out_bf16 else torch.float32)
+    with torch.cuda.device(q.device):
+        _lib.check(_lib.load().tmd_attention_bf16_strided(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vt), _lib.ptr(out), B, heads, Lq, Lk, d, inner,
+                                                          inner, pitch, inner, int(bool(out_bf16)), float(scale), _lib.stream_ptr()))
     return out
 
 
@@ -126,7 +155,7 @@ def _token_self_attention(h, qkv, out_w, out_b, scale, dtype):
     ht = _relayout(h.transpose(1, 2), (B, L, C), tdt)
     q, k, v = (_linear_tokens(ht, w, b, dtype, out_bf16=bf) for (w, b) in qkv)
     if bf:
-        o = attention_bf16(q, k, _relayout(v.transpose(1, 2), (B, C, L), tdt), scale, v_channel_major=True)
+        o = attention_bf16(q, k, _relayout(v.transpose(1, 2), (B, C, L), tdt), scale, v_channel_major=True, out_bf16=True)
     else:
         o = attention(q, k, v, scale, "fp32")
     return _linear_tokens(o, out_w, out_b, dtype).transpose(1, 2)
@@ -220,9 +249,12 @@ class CrossAttention(nn.Module):
         q = _linear_tokens(x, self.to_q.weight, None, self.compute_dtype, out_bf16=bf)            # [B, L, h*d], bf16 in bf16 mode
         k = _linear_tokens(context, self.to_k.weight, None, self.compute_dtype, out_bf16=bf)
         v = _linear_tokens(context, self.to_v.weight, None, self.compute_dtype, out_bf16=bf)
-        split = lambda t: _relayout(t.reshape(B, t.shape[1], h, d).permute(0, 2, 1, 3), (B, h, t.shape[1], d), tdt).view(B * h, t.shape[1], d)
-        o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)              # logits always in fp32 (:194-197)
-        o = _relayout(o.view(B, h, L, d).permute(0, 2, 1, 3), (B, L, h, d), tdt).view(B, L, h * d)
+        if bf:          # the heads stay side by side in the rows: no split / merge copies
+            o = attention_bf16_heads(q, k, v, h, self.scale, out_bf16=True)
+        else:
+            split = lambda t: _relayout(t.reshape(B, t.shape[1], h, d).permute(0, 2, 1, 3), (B, h, t.shape[1], d), tdt).view(B * h, t.shape[1], d)
+            o = attention(split(q), split(k), split(v), self.scale, self.compute_dtype)          # logits always in fp32 (:194-197)
+            o = _relayout(o.view(B, h, L, d).permute(0, 2, 1, 3), (B, L, h, d), tdt).view(B, L, h * d)
         return _linear_tokens(o, self.to_out[0].weight, self.to_out[0].bias, self.compute_dtype)
 
 
