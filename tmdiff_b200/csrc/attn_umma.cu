@@ -635,7 +635,15 @@ cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt,
         return cudaErrorInvalidValue;
     if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(vt) | reinterpret_cast<uintptr_t>(out)) & 15)
         return cudaErrorMisalignedAddress;
-    static int smem_limit[2] = {0, 0};
+    // cudaFuncSetAttribute is per device: one record per device of the process
+    static int smem_limit_dev[64][2] = {};
+    int dev = 0;
+    {
+        const cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    }
+    int* smem_limit = smem_limit_dev[dev];
     if (!smem_limit[0]) {
         const void* fns[2] = {(const void*)attn_umma_kernel<false>, (const void*)attn_umma_kernel<true>};
         for (int i = 0; i < 2; ++i) {

@@ -557,10 +557,13 @@ cudaError_t groupnorm_affine(const float* x, float* y, float* partial, const flo
         while (cs < 8 && ((n + cs - 1) / cs > want_slice || (size_t)B * G * cs < 2 * 148)) cs *= 2;
         const size_t slice = (((n + cs - 1) / cs) + 3) & ~(size_t)3;
         if (slice <= max_slice && slice >= 4) {
-            static bool attr = false;
-            if (!attr) {
-                cudaFuncSetAttribute(gn_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(max_slice * sizeof(float)));
-                attr = true;
+            static bool attr[64] = {};          // the attribute is per device
+            int dev = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+            if (!attr[dev]) {
+                const cudaError_t e = cudaFuncSetAttribute(gn_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(max_slice * sizeof(float)));
+                if (e != cudaSuccess) return e;
+                attr[dev] = true;
             }
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3((unsigned)((size_t)B * G * cs));
