@@ -133,6 +133,8 @@ def _linear_tokens(x, weight, bias, dtype, out_bf16=False):
     b = None if bias is None else _cuda_f32(bias, "bias")
     y_bf16 = bool(out_bf16) and code == _lib.BF16
     y = torch.empty(*x.shape[:-1], Co, device=x.device, dtype=torch.bfloat16 if y_bf16 else torch.float32)
+    if M == 0:
+        return y
     with torch.cuda.device(x.device):
         _lib.check(_lib.load().tmd_linear(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(y), M, Cin, Co, int(x_bf16), int(y_bf16), code,
                                           _lib.stream_ptr()))
