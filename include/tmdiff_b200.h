@@ -201,6 +201,11 @@ int tmd_attention_bf16(const void* q, const void* k, const void* vt, float* out,
 int tmd_attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int32_t B, int32_t heads, int32_t Lq,
                                int32_t Lk, int32_t D, int64_t q_pitch, int64_t k_pitch, int32_t lk_pitch, int64_t out_pitch,
                                int32_t out_bf16, float scale, void* stream);
+/* ... and with v token-major as well, [B,Lk,v_pitch] like k (the value projection's own output: the kernel reads it as the
+ * MN-major B operand of P V), so a module lays nothing out between its projections and the core. */
+int tmd_attention_bf16_tokens(const void* q, const void* k, const void* v, void* out, int32_t B, int32_t heads, int32_t Lq,
+                              int32_t Lk, int32_t D, int64_t q_pitch, int64_t k_pitch, int64_t v_pitch, int64_t out_pitch,
+                              int32_t out_bf16, float scale, void* stream);
 /* Dynamic_conv3d.forward (core/dynamic_conv.py:244-268; groups=1, stride 1, 'same' padding, k in {1,3}):
  * x [B,Ci,N,H,W], weight [K,Co,Ci,k,k,k], bias [K,Co] or NULL, fc1 [hidden,Ci], fc2 [K,hidden] (attention3d's 1x1x1 convs,
  * :194-218) -> y [B,Co,N,H,W]. */

@@ -310,3 +310,5 @@ def test_attention_bf16_heads_in_place_layout(lib_built, B, h, Lq, Lk, d, out_bf
     old = O.attention_bf16(split(q), split(k), split(v), scale).view(B, h, Lq, d).permute(0, 2, 1, 3).reshape(B, Lq, h * d)
     if not out_bf16:
         assert torch.equal(got, old)          # same kernel, same operands: bit-identical
+    # v read in place (MN-major operand) or copied into the channel-major layout first: the same products in the same order
+    assert torch.equal(got, O.attention_bf16_heads(q, k, v, h, scale, out_bf16=out_bf16, v_in_place=False))

@@ -80,6 +80,8 @@ SIGNATURES = {
     "tmd_attention_bf16": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P]),
     "tmd_attention_bf16_strided": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64,
                                              C.c_int32, C.c_int64, C.c_int32, C.c_float, _P]),
+    "tmd_attention_bf16_tokens": (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64,
+                                            C.c_int64, C.c_int64, C.c_int32, C.c_float, _P]),
     "tmd_dynamic_conv3d": (C.c_int, [_P] * 6 + [C.c_int32] * 9 + [C.c_float, C.c_int32, _P]),
     "tmd_quality_metrics": (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P]),
     "tmd_ancestral_update": (C.c_int, [_P, _P, _P, _P] + [C.c_float] * 5 + [C.c_int32, C.c_uint64, C.c_uint64, C.c_int64, _P]),

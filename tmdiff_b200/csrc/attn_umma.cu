@@ -37,6 +37,7 @@ constexpr uint32_t kTileBytes = 128 * 128;      // [128 rows][64 bf16]: one swiz
 struct AttnParams {
     CUtensorMap tmQ, tmK, tmV;
     void* out;                    // fp32, or bf16 when out_bf16; row (b, query) at b*Lq*out_pitch + query*out_pitch, head h at column h*D
+    int v_tok;                    // v is token-major [B, Lk, heads*D] (tmV is a 4-D map like tmQ / tmK): MN-major B operand of P V
     int out_bf16, heads;          // heads: q / k / out hold `heads` heads side by side in a row ([B, L, heads*D]); bh = b*heads + h
     long long out_pitch;          // elements
     int BH, Lq, Lk, D, DV;
@@ -270,6 +271,18 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                 const int vb = it % P.NVB, use = it / P.NVB;
                 const int key0 = SINGLE ? 0 : it * 128, dv = SINGLE ? it * P.DV : dv0;
                 mbar_wait(v_empty(vb), (use & 1) ^ 1);
+                if (P.v_tok) {
+                    // token-major v: [128 keys][64 channels] boxes (rows = keys, 128 bytes each), DV / 64 of them per key block; keys
+                    // past the end are zero-filled by TMA and multiplied by P = 0
+                    mbar_expect_tx(v_full(vb), P.v_bytes);
+                    const uint32_t dstv = v_base + (uint32_t)vb * P.v_bytes;
+                    const int nblk = SINGLE ? nkb : 1;
+                    for (int kb = 0; kb < nblk; ++kb)
+                        for (int t = 0; t < P.DV / 64; ++t)
+                            tma_load_4d(dstv + (uint32_t)kb * ((uint32_t)P.DV * 256u) + (uint32_t)t * kTileBytes, &P.tmV, v_full(vb), dv + 64 * t, hh,
+                                        key0 + 128 * kb, bb);
+                    continue;
+                }
                 // 64-key columns of this tile that hold keys: one past the end is neither loaded nor multiplied
                 int ncol = (P.Lk - key0 + 63) >> 6;
                 const int maxcol = SINGLE ? 2 * nkb : 2;
@@ -285,6 +298,12 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             // ================= MMA issue =================
             const uint32_t q_lo0 = sdesc_lo(q_base), st_lo0 = sdesc_lo(st_base), p_lo0 = sdesc_lo(p_base), v_lo0 = sdesc_lo(v_base);
             const uint32_t tile16 = kTileBytes >> 4, stage16 = P.stage_bytes >> 4, half16 = ((uint32_t)P.DV * 128u) >> 4;
+            // token-major v (MN-major operand): LBO = distance of the 64-channel boxes (16 KB), a 16-key step is 16 rows = 2 KB
+            const uint32_t v_lo0_mn = ((v_base & 0x3FFFFu) >> 4) | ((kTileBytes >> 4) << 16), blk16 = ((uint32_t)P.DV * 256u) >> 4;
+            auto v_desc = [&](uint32_t vb, uint32_t k) -> uint64_t {
+                if (P.v_tok) return sdesc(v_lo0_mn + vb * (P.v_bytes >> 4) + (k >> 3) * blk16 + (k & 7) * 128u);
+                return sdesc(v_lo0 + vb * (P.v_bytes >> 4) + (k >> 2) * half16 + (k & 3) * 2u);
+            };
             uint32_t ks = 0, kph = 0;
             if (P.q_resident) mbar_wait(q_full, 0);
             auto issue_qk = [&](int j) {
@@ -315,10 +334,9 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     mbar_wait(v_full(vb), use & 1);
                     if (c >= 2) mbar_wait(o_empty(ob), ((c >> 1) - 1) & 1);
                     tc_fence_after();
-                    const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
                     for (int k = 0; k < ksteps; ++k) {
                         const uint32_t blk = k >> 2, kk = k & 3;
-                        tc_mma_bf16(tmem_o + (uint32_t)ob * P.DV, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv,
+                        tc_mma_bf16(tmem_o + (uint32_t)ob * P.DV, sdesc(p_lo0 + blk * tile16 + kk * 2), v_desc((uint32_t)vb, (uint32_t)k), P.idesc_pv,
                                     (uint32_t)k);
                     }
                     tc_commit(v_empty(vb));
@@ -335,10 +353,9 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
                     tc_fence_after();
                     const int keys = P.Lk - j * 128;
                     const int ksteps = keys >= 128 ? 8 : (keys + 15) >> 4;
-                    const uint32_t v_lo = v_lo0 + (uint32_t)vb * (P.v_bytes >> 4);
                     for (int k = 0; k < ksteps; ++k) {
                         const uint32_t blk = k >> 2, kk = k & 3;
-                        tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), sdesc(v_lo + blk * half16 + kk * 2), P.idesc_pv, (uint32_t)(j | k));
+                        tc_mma_bf16(tmem_o, sdesc(p_lo0 + blk * tile16 + kk * 2), v_desc((uint32_t)vb, (uint32_t)k), P.idesc_pv, (uint32_t)(j | k));
                     }
                     tc_commit(v_empty(vb));
                     tc_commit(pv_done);
@@ -627,8 +644,20 @@ cudaError_t attention_bf16(const void* q, const void* k, const void* vt, float* 
 cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int B, int heads, int Lq, int Lk, int D,
                                    long long q_pitch, long long k_pitch, int lk_pitch, long long out_pitch, int out_bf16, float scale,
                                    cudaStream_t stream) {
+    return attention_bf16_general(q, k, vt, out, B, heads, Lq, Lk, D, q_pitch, k_pitch, 0, lk_pitch, out_pitch, out_bf16, scale, stream);
+}
+
+// v_tok_pitch > 0: v is token-major [B, Lk, v_tok_pitch] like k (head h in columns [h*D, (h+1)*D)) and lk_pitch is ignored;
+// v_tok_pitch == 0: v is channel-major [B*heads, D, lk_pitch].
+cudaError_t attention_bf16_general(const void* q, const void* k, const void* vt, void* out, int B, int heads, int Lq, int Lk, int D,
+                                   long long q_pitch, long long k_pitch, long long v_tok_pitch, int lk_pitch, long long out_pitch, int out_bf16,
+                                   float scale, cudaStream_t stream) {
     if (B <= 0 || heads <= 0 || (long long)B * heads > 65535) return cudaErrorInvalidValue;
     const int BH = B * heads;
+    if (v_tok_pitch) {
+        if (v_tok_pitch < (long long)heads * D || v_tok_pitch % 8) return cudaErrorInvalidValue;
+        lk_pitch = (Lk + 7) / 8 * 8;          // only for the shape check below
+    }
     if (!attention_bf16_supported(BH, Lq, Lk, D, lk_pitch)) return cudaErrorInvalidValue;
     if (q_pitch < (long long)heads * D || k_pitch < (long long)heads * D || out_pitch < (long long)heads * D || q_pitch % 8 || k_pitch % 8 ||
         out_pitch % 8)
@@ -660,6 +689,7 @@ cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt,
     memset(&P, 0, sizeof(P));
     P.out = out;
     P.out_bf16 = out_bf16 ? 1 : 0; P.heads = heads; P.out_pitch = out_pitch;
+    P.v_tok = v_tok_pitch ? 1 : 0;
     P.BH = BH; P.Lq = Lq; P.Lk = Lk; P.D = D;
     P.nkc = D / 64;
     P.nkb = (Lk + 127) / 128;
@@ -713,9 +743,10 @@ cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt,
     // D = f32, A = B = bf16, both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
     P.idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
     P.idesc_pv = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)P.DV >> 3) << 17) | ((128u >> 4) << 24);
+    if (P.v_tok) P.idesc_pv |= 1u << 16;          // B operand MN-major (channels contiguous)
     P.scale_log2 = scale * 1.4426950408889634f;
     if (!make_map4(&P.tmQ, q, D, Lq, heads, B, q_pitch) || !make_map4(&P.tmK, k, D, Lk, heads, B, k_pitch) ||
-        !make_map(&P.tmV, vt, Lk, D, BH, lk_pitch, (uint32_t)P.DV))
+        !(P.v_tok ? make_map4(&P.tmV, vt, D, Lk, heads, B, v_tok_pitch) : make_map(&P.tmV, vt, Lk, D, BH, lk_pitch, (uint32_t)P.DV)))
         return cudaErrorInvalidValue;
     if (single) {
         const dim3 grid((Lq + 127) / 128, 1, BH);

@@ -1492,6 +1492,23 @@ extern "C" int tmd_attention_bf16_strided(const void* q, const void* k, const vo
     return 0;
 }
 
+extern "C" int tmd_attention_bf16_tokens(const void* q, const void* k, const void* v, void* out, int32_t B, int32_t heads, int32_t Lq,
+                                         int32_t Lk, int32_t D, int64_t q_pitch, int64_t k_pitch, int64_t v_pitch, int64_t out_pitch,
+                                         int32_t out_bf16, float scale, void* stream) {
+    if (!q || !k || !v || !out) return fail("tmd_attention_bf16_tokens: null argument");
+    if (B <= 0 || heads <= 0 || (int64_t)B * heads > 65535 || !attention_bf16_supported(B * heads, Lq, Lk, D, (Lk + 7) / 8 * 8))
+        return fail("tmd_attention_bf16_tokens: unsupported problem B=%d heads=%d Lq=%d Lk=%d D=%d (D must be a multiple of 64, B*heads <= 65535)",
+                    B, heads, Lq, Lk, D);
+    const int64_t need = (int64_t)heads * D;
+    if (q_pitch < need || k_pitch < need || v_pitch < need || out_pitch < need || q_pitch % 8 || k_pitch % 8 || v_pitch % 8 || out_pitch % 8)
+        return fail("tmd_attention_bf16_tokens: row pitches must be multiples of 8 elements and hold heads*D = %d channels", heads * D);
+    if (!(scale > 0.f)) return fail("tmd_attention_bf16_tokens: the logit scale must be positive");
+    const cudaError_t err = attention_bf16_general(q, k, v, out, B, heads, Lq, Lk, D, q_pitch, k_pitch, v_pitch, 0, out_pitch, out_bf16, scale,
+                                                   (cudaStream_t)stream);
+    if (err != cudaSuccess) return fail("tmd_attention_bf16_tokens: %s", cudaGetErrorString(err));
+    return 0;
+}
+
 namespace {
 size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 // scratch of one Dynamic_conv call: pooled means, expert weights, mixed weights (one layout per mode) and bias, the two layout

@@ -100,6 +100,9 @@ cudaError_t attention_f32(const float* q, const float* k, const float* v, float*
 // bf16 tensor-core variant (attn_umma.cu): q [BH,Lq,D], k [BH,Lk,D] token-major, vt [BH,D,lk_pitch] channel-major (lk_pitch >= Lk,
 // multiple of 8), out [BH,Lq,D] fp32; D a multiple of 64
 bool attention_bf16_supported(int BH, int Lq, int Lk, int D, int lk_pitch);
+cudaError_t attention_bf16_general(const void* q, const void* k, const void* vt, void* out, int B, int heads, int Lq, int Lk, int D,
+                                   long long q_pitch, long long k_pitch, long long v_tok_pitch, int lk_pitch, long long out_pitch, int out_bf16,
+                                   float scale, cudaStream_t stream);
 cudaError_t attention_bf16_strided(const void* q, const void* k, const void* vt, void* out, int B, int heads, int Lq, int Lk, int D,
                                    long long q_pitch, long long k_pitch, int lk_pitch, long long out_pitch, int out_bf16, float scale,
                                    cudaStream_t stream);

@@ -85,11 +85,11 @@ def attention_bf16(q, k, v, scale, v_channel_major=False, out_bf16=False):
     return out
 
 
-def attention_bf16_heads(q, k, v, heads, scale, out_bf16=True):
-    """Multi-head attention on the projections' own layout (tmd_attention_bf16_strided): q [B, Lq, heads*d], k and v
-    [B, Lk, heads*d] bf16, head h in columns [h*d, (h+1)*d) -- no `(b h) n d` split of q / k and no merge of the result
-    (core/Attention.py:189-191, 211); only v is re-laid-out (channel-major per head, the kernel's K-major operand).
-    Returns [B, Lq, heads*d], bf16 or fp32."""
+def attention_bf16_heads(q, k, v, heads, scale, out_bf16=True, v_in_place=True):
+    """Multi-head attention on the projections' own layout: q [B, Lq, heads*d], k and v [B, Lk, heads*d] bf16, head h in columns
+    [h*d, (h+1)*d) -- no `(b h) n d` split and no merge of the result (core/Attention.py:189-191, 211).  v_in_place: v is read
+    as it is too (tmd_attention_bf16_tokens: the MN-major B operand of P V); otherwise it is copied into the channel-major
+    per-head layout first (tmd_attention_bf16_strided).  Returns [B, Lq, heads*d], bf16 or fp32."""
     if not (q.is_cuda and k.is_cuda and v.is_cuda):
         raise RuntimeError("attention_bf16_heads: CUDA tensors required (no CPU fallback)")
     B, Lq, inner = q.shape
@@ -98,6 +98,13 @@ def attention_bf16_heads(q, k, v, heads, scale, out_bf16=True):
         raise ValueError("attention_bf16_heads: q [B,Lq,h*d], k and v [B,Lk,h*d] with d a multiple of 64 expected")
     qb, kb = (t if t.dtype == torch.bfloat16 and t.is_contiguous() else torch.empty(t.shape, dtype=torch.bfloat16, device=t.device).copy_(t)
               for t in (q, k))
+    if v_in_place:
+        vb = v if v.dtype == torch.bfloat16 and v.is_contiguous() else torch.empty(v.shape, dtype=torch.bfloat16, device=v.device).copy_(v)
+        out = torch.empty(B, Lq, inner, device=q.device, dtype=torch.bfloat16 if out_bf16 else torch.float32)
+        with torch.cuda.device(q.device):
+            _lib.check(_lib.load().tmd_attention_bf16_tokens(_lib.ptr(qb), _lib.ptr(kb), _lib.ptr(vb), _lib.ptr(out), B, heads, Lq, Lk, d, inner,
+                                                             inner, inner, inner, int(bool(out_bf16)), float(scale), _lib.stream_ptr()))
+        return out
     pitch = (Lk + 7) // 8 * 8
     vt = torch.zeros(B, heads, d, pitch, dtype=torch.bfloat16, device=q.device) if pitch != Lk else \
         torch.empty(B, heads, d, pitch, dtype=torch.bfloat16, device=q.device)
@@ -156,8 +163,8 @@ def _token_self_attention(h, qkv, out_w, out_b, scale, dtype):
     tdt = torch.bfloat16 if bf else torch.float32
     ht = _relayout(h.transpose(1, 2), (B, L, C), tdt)
     q, k, v = (_linear_tokens(ht, w, b, dtype, out_bf16=bf) for (w, b) in qkv)
-    if bf:
-        o = attention_bf16(q, k, _relayout(v.transpose(1, 2), (B, C, L), tdt), scale, v_channel_major=True, out_bf16=True)
+    if bf:          # q, k, v as the projections wrote them; the result bf16 for the output projection
+        o = attention_bf16_heads(q, k, v, 1, scale, out_bf16=True)
     else:
         o = attention(q, k, v, scale, "fp32")
     return _linear_tokens(o, out_w, out_b, dtype).transpose(1, 2)
