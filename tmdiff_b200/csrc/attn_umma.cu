@@ -300,9 +300,11 @@ __global__ void __launch_bounds__(SINGLE ? 192 : 384, SINGLE ? 4 : 1) attn_umma_
             const uint32_t tile16 = kTileBytes >> 4, stage16 = P.stage_bytes >> 4, half16 = ((uint32_t)P.DV * 128u) >> 4;
             // token-major v (MN-major operand): LBO = distance of the 64-channel boxes (16 KB), a 16-key step is 16 rows = 2 KB
             const uint32_t v_lo0_mn = ((v_base & 0x3FFFFu) >> 4) | ((kTileBytes >> 4) << 16), blk16 = ((uint32_t)P.DV * 256u) >> 4;
+            // (one formula for both layouts, its constants chosen once: this thread's instruction stream is the critical path)
+            const uint32_t vd_base = P.v_tok ? v_lo0_mn : v_lo0, vd_shift = P.v_tok ? 3u : 2u, vd_mask = P.v_tok ? 7u : 3u;
+            const uint32_t vd_blk = P.v_tok ? blk16 : half16, vd_step = P.v_tok ? 128u : 2u, vd_buf = P.v_bytes >> 4;
             auto v_desc = [&](uint32_t vb, uint32_t k) -> uint64_t {
-                if (P.v_tok) return sdesc(v_lo0_mn + vb * (P.v_bytes >> 4) + (k >> 3) * blk16 + (k & 7) * 128u);
-                return sdesc(v_lo0 + vb * (P.v_bytes >> 4) + (k >> 2) * half16 + (k & 3) * 2u);
+                return sdesc(vd_base + vb * vd_buf + (k >> vd_shift) * vd_blk + (k & vd_mask) * vd_step);
             };
             uint32_t ks = 0, kph = 0;
             if (P.q_resident) mbar_wait(q_full, 0);
